@@ -1,0 +1,192 @@
+"""ctypes bindings of the two native libraries (include/gk_b200.h).
+
+``libgk_cuda.so`` (csrc/gk_cuda.cu, sm_100a) and ``libgk_cpu.so`` (csrc/gk_cpu.cpp) are built
+IN-TREE next to this file so that they travel with the repository snapshot to the GPU box.
+The structures below mirror the C header field by field.
+
+The reference has no native code; every kernel here replaces an implicit
+ATen/Horovod kernel listed in SURVEY.md §2.5.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(os.path.dirname(_HERE))
+CSRC = os.path.join(_ROOT, "csrc")
+INCLUDE = os.path.join(_ROOT, "include")
+CUDA_SO = os.path.join(_HERE, "libgk_cuda.so")
+CPU_SO = os.path.join(_HERE, "libgk_cpu.so")
+
+GK_NC = 16
+GK_MAXP = 16
+GK_HIST_BINS = 2048
+GK_THREADS = 256
+GK_SLOT_HDR = 2
+
+MODE_GAUSSIAN, MODE_TOPK, MODE_REDSYNC, MODE_REDSYNCTRIM, MODE_THRESHOLD, MODE_MINK = range(6)
+
+
+class GkBlk(C.Structure):
+    _fields_ = [("start", C.c_int32), ("len", C.c_int32), ("seg", C.c_int32), ("soff", C.c_int32)]
+
+
+class GkSeg(C.Structure):
+    _fields_ = [("n", C.c_int32), ("k", C.c_int32), ("blk_begin", C.c_int32), ("blk_end", C.c_int32),
+                ("zabs", C.c_double), ("param", C.c_float), ("aux", C.c_int32)]
+
+
+class GkSegStat(C.Structure):
+    _fields_ = [("mean", C.c_float), ("std", C.c_float), ("meanabs", C.c_float), ("maxabs", C.c_float),
+                ("cand", C.c_float * GK_NC), ("thr", C.c_float), ("tbits", C.c_uint32), ("ties", C.c_uint32),
+                ("chosen", C.c_int32), ("count", C.c_uint32), ("out_base", C.c_uint32),
+                ("prefix", C.c_uint32), ("krem", C.c_uint32)]
+
+
+class GkCtrl(C.Structure):
+    _fields_ = [("done", C.c_uint32 * 8), ("total", C.c_uint32), ("sent", C.c_uint32), ("seq", C.c_uint32),
+                ("err", C.c_uint32), ("overflow", C.c_uint32), ("rsv", C.c_uint32 * 3),
+                ("sent_total", C.c_uint64)]
+
+
+class GkChain(C.Structure):
+    _fields_ = [("grad", C.c_void_p), ("resid", C.c_void_p), ("blk", C.c_void_p), ("seg", C.c_void_p),
+                ("part", C.c_void_p), ("stat", C.c_void_p), ("bcnt", C.c_void_p), ("boff", C.c_void_p),
+                ("hist", C.c_void_p), ("ctrl", C.c_void_p),
+                ("nblk", C.c_int32), ("nseg", C.c_int32), ("mode", C.c_int32), ("nloops", C.c_int32),
+                ("use_residual", C.c_int32), ("zero_grad", C.c_int32), ("cap", C.c_uint32), ("rsv", C.c_int32)]
+
+
+class GkDst(C.Structure):
+    _fields_ = [("slot", C.c_void_p * GK_MAXP), ("ndst", C.c_int32), ("rsv", C.c_int32),
+                ("parity_stride", C.c_uint64)]
+
+
+class GkSrc(C.Structure):
+    _fields_ = [("arena", C.c_void_p), ("slot_stride", C.c_uint64), ("parity_stride", C.c_uint64),
+                ("nsrc", C.c_int32), ("wait", C.c_int32), ("timeout_ns", C.c_uint64)]
+
+
+class GkHyper(C.Structure):
+    _fields_ = [("lr", C.c_float), ("momentum", C.c_float), ("dampening", C.c_float),
+                ("weight_decay", C.c_float), ("nesterov", C.c_int32), ("first_step", C.c_int32),
+                ("lars_eeta", C.c_float), ("lars_eps", C.c_float)]
+
+
+assert C.sizeof(GkBlk) == 16 and C.sizeof(GkSeg) == 32 and C.sizeof(GkSegStat) == 112
+assert C.sizeof(GkCtrl) == 72 and C.sizeof(GkHyper) == 32
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+              "-shared", "-Xcompiler", "-fPIC"]
+GXX_FLAGS = ["-O2", "-ffp-contract=off", "-std=c++17", "-shared", "-fPIC"]
+
+
+def _stale(so: str, srcs) -> bool:
+    if not os.path.exists(so):
+        return True
+    t = os.path.getmtime(so)
+    return any(os.path.exists(s) and os.path.getmtime(s) > t for s in srcs)
+
+
+def _nvcc() -> str:
+    for cand in (os.environ.get("NVCC"), "/usr/local/cuda/bin/nvcc", "nvcc"):
+        if cand and (os.path.isabs(cand) and os.path.exists(cand) or not os.path.isabs(cand)):
+            return cand
+    return "nvcc"
+
+
+def build_cuda(force: bool = False, verbose: bool = False) -> str:
+    """Cross-compile csrc/gk_cuda.cu for sm_100a (works without a GPU)."""
+    src = os.path.join(CSRC, "gk_cuda.cu")
+    hdr = os.path.join(INCLUDE, "gk_b200.h")
+    if force or _stale(CUDA_SO, [src, hdr]):
+        cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", CUDA_SO + ".tmp", src]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
+        os.replace(CUDA_SO + ".tmp", CUDA_SO)
+        if verbose:
+            print(r.stderr)
+    return CUDA_SO
+
+
+def build_cpu(force: bool = False) -> str:
+    src = os.path.join(CSRC, "gk_cpu.cpp")
+    hdr = os.path.join(INCLUDE, "gk_b200.h")
+    if force or _stale(CPU_SO, [src, hdr]):
+        cmd = ["g++"] + GXX_FLAGS + ["-o", CPU_SO + ".tmp", src]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("g++ failed:\n" + r.stdout + r.stderr)
+        os.replace(CPU_SO + ".tmp", CPU_SO)
+    return CPU_SO
+
+
+_lock = threading.Lock()
+_libs = {}
+
+_P = C.c_void_p
+
+
+def _proto(lib, name, argtypes, restype=C.c_int):
+    f = getattr(lib, name)
+    f.argtypes = argtypes
+    f.restype = restype
+    return f
+
+
+def cuda_lib():
+    """Load (building if needed) the sm_100a library.  Fails loudly: on a GPU box the native path
+    is the only path."""
+    with _lock:
+        if "cuda" not in _libs:
+            if _stale(CUDA_SO, [os.path.join(CSRC, "gk_cuda.cu"), os.path.join(INCLUDE, "gk_b200.h")]):
+                build_cuda()
+            lib = C.CDLL(CUDA_SO)
+            ch, ds, sr = C.POINTER(GkChain), C.POINTER(GkDst), C.POINTER(GkSrc)
+            _proto(lib, "gk_version", [], C.c_char_p)
+            for n in ("gk_accumulate", "gk_count_pick", "gk_topk_select"):
+                _proto(lib, n, [ch, _P])
+            _proto(lib, "gk_compact_send", [ch, ds, _P])
+            _proto(lib, "gk_compress", [ch, ds, _P])
+            _proto(lib, "gk_scatter", [sr, _P, _P, C.c_float, C.c_int32, _P])
+            _proto(lib, "gk_unscatter", [sr, _P, _P, C.c_int32, _P])
+            _proto(lib, "gk_sgd", [_P, _P, _P, _P, C.c_int32, _P, _P, _P])
+            _proto(lib, "gk_lars", [_P, _P, _P, _P, C.c_int32, _P, C.c_int32, _P, _P, _P, _P, _P])
+            _proto(lib, "gk_grad_norm", [_P, _P, C.c_int32, _P, C.c_float, _P, _P, _P])
+            _proto(lib, "gk_scale", [_P, _P, C.c_int32, _P, _P])
+            _proto(lib, "gk_randomk_send", [ch, ds, C.c_uint64, _P])
+            _proto(lib, "gk_bucket_means", [ch, _P, _P])
+            _proto(lib, "gk_bucket_reconstruct", [ch, _P, _P, _P])
+            _proto(lib, "gk_copy", [_P, _P, C.c_int64, _P])
+            _proto(lib, "gk_histogram", [_P, C.c_int64, C.c_float, C.c_float, C.c_int32, _P, _P])
+            _libs["cuda"] = lib
+        return _libs["cuda"]
+
+
+def cpu_lib():
+    with _lock:
+        if "cpu" not in _libs:
+            build_cpu()
+            lib = C.CDLL(CPU_SO)
+            ch, ds, sr = C.POINTER(GkChain), C.POINTER(GkDst), C.POINTER(GkSrc)
+            _proto(lib, "gkcpu_version", [], C.c_char_p)
+            _proto(lib, "gkcpu_compress", [ch, ds])
+            _proto(lib, "gkcpu_scatter", [sr, _P, _P, C.c_float, C.c_int32])
+            _proto(lib, "gkcpu_unscatter", [sr, _P, _P, C.c_int32])
+            _proto(lib, "gkcpu_sgd", [_P, _P, _P, _P, C.c_int32, _P, _P])
+            _proto(lib, "gkcpu_lars", [_P, _P, _P, _P, C.c_int32, _P, C.c_int32, _P, _P, _P])
+            _proto(lib, "gkcpu_grad_norm", [_P, _P, C.c_int32, C.c_float, _P])
+            _proto(lib, "gkcpu_randomk_send", [ch, ds, C.c_uint64])
+            _proto(lib, "gkcpu_bucket_means", [ch, _P])
+            _proto(lib, "gkcpu_bucket_reconstruct", [ch, _P, _P])
+            _libs["cpu"] = lib
+        return _libs["cpu"]
+
+
+def check(err: int, what: str = "gk") -> None:
+    if err != 0:
+        raise RuntimeError(f"{what}: native call failed with code {err}")

@@ -1,0 +1,228 @@
+/*
+ * gk_b200.h — C ABI of the B200-native sparsified-gradient kernel chain.
+ *
+ * Two shared libraries implement this interface:
+ *   libgk_cuda.so  (csrc/gk_cuda.cu, sm_100a)  — entry points prefixed gk_
+ *   libgk_cpu.so   (csrc/gk_cpu.cpp, host)     — entry points prefixed gkcpu_
+ * Both are plain C ABI (no torch / pybind dependency) and allocate nothing unless stated:
+ * every buffer, scratch included, is passed in by the caller (the Python layer hands in
+ * torch tensors).  All device entry points enqueue on the given stream and return
+ * immediately; the return value is a cudaError_t cast to int (0 = success).
+ *
+ * The chain replaces the per-op torch pipeline of the reference
+ * (compression.py:358-389 gaussian-k, :45-49 exact top-k, distributed_optimizer.py:416-430
+ * send side, :449-485 receive side, dl_trainer.py:848-872 SGD math, lars.py:67-134).
+ */
+#ifndef GK_B200_H
+#define GK_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GK_NC 16          /* max candidate thresholds evaluated in one counting pass      */
+#define GK_MAXP 16        /* max ranks whose receive slots one send kernel can store into */
+#define GK_HIST_BINS 2048 /* radix-select digit width (11 bits)                           */
+#define GK_THREADS 256    /* threads per block of every chain kernel                      */
+#define GK_SLOT_HDR 2     /* u64 words in front of every slot: [count | seq<<32, reserved]*/
+
+/* selection modes (GkChain.mode) */
+enum {
+  GK_MODE_GAUSSIAN = 0,    /* compression.py:358-389 (nloops=3) and :405-435 (nloops=5) */
+  GK_MODE_TOPK = 1,        /* compression.py:45-49 exact k largest |x|, ties -> lowest index */
+  GK_MODE_REDSYNC = 2,     /* compression.py:644-677 */
+  GK_MODE_REDSYNCTRIM = 3, /* compression.py:707-738 */
+  GK_MODE_THRESHOLD = 4,   /* fixed threshold supplied in GkSeg.param (select |x| > param) */
+  GK_MODE_MINK = 5         /* compression.py:52-56 k smallest |x| */
+};
+
+/* One block of work: a contiguous extent of the arena that belongs to one segment. */
+typedef struct GkBlk {
+  int32_t start; /* arena index of the first element (multiple of 4)      */
+  int32_t len;   /* number of elements (<= chunk)                          */
+  int32_t seg;   /* selection segment (compress tables) / param group or tensor (optimizer tables) */
+  int32_t soff;  /* segment-local index of the block's first element (dense numbering of the segment) */
+} GkBlk;
+
+/* One selection segment = one tensor (threshold=0) or one merged group. */
+typedef struct GkSeg {
+  int32_t n;         /* real element count (sum of its blocks' len)           */
+  int32_t k;         /* max(int(n*density),1), host-computed (compression.py:363) */
+  int32_t blk_begin; /* its blocks are [blk_begin, blk_end) of the table       */
+  int32_t blk_end;
+  double zabs;       /* |Phi^-1(density/2)| (utils.py:136-138); gaussian only  */
+  float param;       /* GK_MODE_THRESHOLD: the threshold                       */
+  int32_t aux;       /* compress tables: prefix sum of k over earlier segments (random-k output base);
+                        LARS tensor tables: index of the tensor's param group in the GkHyper array */
+} GkSeg;
+
+/* Per-segment device-side state written by the kernels. */
+typedef struct GkSegStat {
+  float mean, std, meanabs, maxabs; /* moments of acc = grad + residual            */
+  float cand[GK_NC];                /* candidate thresholds of the counting pass   */
+  float thr;                        /* chosen threshold (strict |x| > thr)         */
+  uint32_t tbits;                   /* top-k: bit pattern of the k-th magnitude    */
+  uint32_t ties;                    /* top-k: how many |x|==T elements to take     */
+  int32_t chosen;                   /* index of the chosen candidate               */
+  uint32_t count;                   /* elements selected in this segment (pre-cap) */
+  uint32_t out_base;                /* first output position of this segment       */
+  uint32_t prefix;                  /* radix-select: matched high bits so far      */
+  uint32_t krem;                    /* radix-select: rank still to find            */
+} GkSegStat;
+
+/* Chain-wide control block (device memory, zero-initialised once by the caller). */
+typedef struct GkCtrl {
+  uint32_t done[8];  /* last-block-done tickets, self-resetting                 */
+  uint32_t total;    /* pairs selected by the last compress (pre-cap)           */
+  uint32_t sent;     /* pairs actually emitted (min(total, cap))                */
+  uint32_t seq;      /* sequence number of the last completed send              */
+  uint32_t err;      /* !=0: receive timed out / protocol error (sticky)        */
+  uint32_t overflow; /* cumulative pairs withheld because of the cap            */
+  uint32_t rsv[3];
+  uint64_t sent_total; /* cumulative pairs emitted (for logging)                */
+} GkCtrl;
+
+/* Everything one compress chain needs.  Passed by pointer from the host; the library
+ * copies it by value into the kernel parameters, so it may live on the caller's stack. */
+typedef struct GkChain {
+  float* grad;        /* gradient arena (read; zeroed behind the read if zero_grad)  */
+  float* resid;       /* residual arena (read, overwritten with acc, selected zeroed) */
+  const GkBlk* blk;   /* [nblk] device                                               */
+  GkSeg* seg;         /* [nseg] device (host rewrites k / zabs when density changes) */
+  double* part;       /* [nblk*4] scratch: per-block sum, sumsq, sumabs, maxabs      */
+  GkSegStat* stat;    /* [nseg] scratch                                              */
+  uint32_t* bcnt;     /* [nblk*GK_NC] scratch: per-block counts per candidate        */
+  uint32_t* boff;     /* [nblk*2] scratch: per-block (gt, eq) exclusive prefixes     */
+  uint32_t* hist;     /* [nseg*GK_HIST_BINS] scratch (top-k only; zero-initialised)  */
+  GkCtrl* ctrl;       /* [1] device                                                  */
+  int32_t nblk, nseg;
+  int32_t mode;         /* GK_MODE_*                                                 */
+  int32_t nloops;       /* gaussian: 3 (gaussian) or 5 (gaussian2)                   */
+  int32_t use_residual; /* 1: acc = grad + resid (error feedback); 0: acc = grad     */
+  int32_t zero_grad;    /* 1: write 0 into grad after it is consumed                 */
+  uint32_t cap;         /* max pairs emitted per send (receive-slot capacity)        */
+  int32_t rsv;
+} GkChain;
+
+/* Where the compaction kernel stores this rank's pairs: one slot per destination.
+ * A slot is GK_SLOT_HDR u64 header words followed by cap u64 pairs
+ * (low 32 bits = int32 arena index, high 32 bits = fp32 value bits).
+ * slot[d] is the parity-0 copy; parity p lives parity_stride u64 words further. */
+typedef struct GkDst {
+  uint64_t* slot[GK_MAXP];
+  int32_t ndst;
+  int32_t rsv;
+  uint64_t parity_stride; /* 0 = single-buffered (all_gather transports) */
+} GkDst;
+
+/* Receive arena of one rank: nsrc slots of slot_stride u64 words each, per parity. */
+typedef struct GkSrc {
+  const uint64_t* arena; /* parity-0 slot 0                                   */
+  uint64_t slot_stride;  /* = GK_SLOT_HDR + cap                                */
+  uint64_t parity_stride;
+  int32_t nsrc;
+  int32_t wait;          /* 1: spin (bounded) until every slot's seq matches   */
+  uint64_t timeout_ns;   /* bound of that spin; on expiry ctrl->err is set     */
+} GkSrc;
+
+/* Optimizer hyper-parameters of one param group (device array, rewritten by the host
+ * whenever lr changes; dl_trainer.py:197-228 defines the values). */
+typedef struct GkHyper {
+  float lr, momentum, dampening, weight_decay;
+  int32_t nesterov;
+  int32_t first_step; /* 1 on the first step: momentum buffer := grad (torch.optim.SGD) */
+  float lars_eeta, lars_eps;
+} GkHyper;
+
+/* ------------------------------------------------------------------ CUDA entry points */
+
+/* K1  ef_accumulate_moments (+ first radix histogram when mode is top-k / min-k).
+ * acc = grad (+ resid) -> resid; per-segment mean/std(unbiased)/mean|x|/max|x|; candidate
+ * thresholds.  Replaces compression.py:365-370 and distributed_optimizer.py:375. */
+int gk_accumulate(const GkChain* c, void* stream);
+
+/* K2  count |acc| > cand[j] for every candidate in one pass, replay the reference's
+ * refinement loop on the device, pick the threshold, prefix-sum the per-block counts.
+ * Replaces compression.py:372-381 (and :653-672, :719-732).  No host sync. */
+int gk_count_pick(const GkChain* c, void* stream);
+
+/* K4  exact top-k radix select (3 digit passes; the first is fused into gk_accumulate)
+ * followed by the (gt, eq) counting pass.  Replaces compression.py:45-49. */
+int gk_topk_select(const GkChain* c, void* stream);
+
+/* K3  select + ordered compaction + residual update + send: stores the (index,value)
+ * pairs into dst->slot[d] of every destination (peer-mapped memory for NVLink P2P),
+ * then publishes {count, seq} with a system-scope release store.
+ * Replaces compression.py:373-388 and distributed_optimizer.py:426-427. */
+int gk_compact_send(const GkChain* c, const GkDst* dst, void* stream);
+
+/* Convenience: the whole send-side chain for c->mode. */
+int gk_compress(const GkChain* c, const GkDst* dst, void* stream);
+
+/* K5  receive: (optionally wait for all slots,) scatter-add value*scale into the dense
+ * gradient arena.  Replaces distributed_optimizer.py:461-482. */
+int gk_scatter(const GkSrc* src, GkCtrl* ctrl, float* grad, float scale, int32_t nelem_arena,
+               void* stream);
+
+/* zero_grad for a sparse gradient: clear exactly the coordinates the last receive wrote. */
+int gk_unscatter(const GkSrc* src, GkCtrl* ctrl, float* grad, int32_t nelem_arena, void* stream);
+
+/* K6  fused momentum-SGD over the parameter / gradient / momentum arenas
+ * (torch.optim.SGD arithmetic, dl_trainer.py:848-872).  grad_scale may be NULL. */
+int gk_sgd(float* param, const float* grad, float* mom, const GkBlk* blk, int32_t nblk,
+           const GkHyper* hyper, const float* grad_scale, void* stream);
+
+/* K7  LARS (lars.py:67-134): segmented ||w||, ||g|| then the trust-ratio update. */
+int gk_lars(float* param, const float* grad, float* mom, const GkBlk* blk, int32_t nblk,
+            const GkSeg* tens, int32_t ntens, const GkHyper* hyper, double* part, float* ratio,
+            GkCtrl* ctrl, void* stream);
+
+/* K8  global L2 norm of the gradient arena and the clip coefficient
+ * min(1, max_norm/(norm+1e-6)) written to out[0..1] = {norm, coef}
+ * (dist_trainer.py:80-85).  The coefficient is consumed by gk_sgd via grad_scale. */
+int gk_grad_norm(const float* grad, const GkBlk* blk, int32_t nblk, double* part, float max_norm,
+                 float* out, GkCtrl* ctrl, void* stream);
+
+/* y[i] *= *scale over the blocks (materialised clipping). */
+int gk_scale(float* grad, const GkBlk* blk, int32_t nblk, const float* scale, void* stream);
+
+/* K9  random-k: k distinct pseudo-random indices per segment from a keyed bijection of
+ * [0,n) (compression.py:461-475); gathers values, zeroes the residual there, sends. */
+int gk_randomk_send(const GkChain* c, const GkDst* dst, uint64_t seed, void* stream);
+
+/* K10 bucket compressor (compression.py:243-265, 305-312): per-segment mean of the
+ * non-negative and of the negative entries -> means[2*nseg]; then reconstruct. */
+int gk_bucket_means(const GkChain* c, float* means, void* stream);
+int gk_bucket_reconstruct(const GkChain* c, const float* local_means, const float* global_means,
+                          void* stream);
+
+/* K13 flat broadcast helper / generic: dst[i] = src[i] over n floats (peer pointers ok). */
+int gk_copy(float* dst, const float* src, int64_t n, void* stream);
+
+/* K14 on-device histogram of acc for the gradient-distribution study
+ * (distributed_optimizer.py:422-424 dumped the whole tensor to disk instead). */
+int gk_histogram(const float* x, int64_t n, float lo, float hi, int32_t nbins, uint32_t* out,
+                 void* stream);
+
+const char* gk_version(void);
+
+/* ------------------------------------------------------------------- CPU twins (host) */
+int gkcpu_compress(const GkChain* c, const GkDst* dst);
+int gkcpu_scatter(const GkSrc* src, GkCtrl* ctrl, float* grad, float scale, int32_t nelem_arena);
+int gkcpu_unscatter(const GkSrc* src, GkCtrl* ctrl, float* grad, int32_t nelem_arena);
+int gkcpu_sgd(float* param, const float* grad, float* mom, const GkBlk* blk, int32_t nblk,
+              const GkHyper* hyper, const float* grad_scale);
+int gkcpu_lars(float* param, const float* grad, float* mom, const GkBlk* blk, int32_t nblk,
+               const GkSeg* tens, int32_t ntens, const GkHyper* hyper, double* part, float* ratio);
+int gkcpu_grad_norm(const float* grad, const GkBlk* blk, int32_t nblk, float max_norm, float* out);
+int gkcpu_randomk_send(const GkChain* c, const GkDst* dst, uint64_t seed);
+int gkcpu_bucket_means(const GkChain* c, float* means);
+int gkcpu_bucket_reconstruct(const GkChain* c, const float* local_means, const float* global_means);
+const char* gkcpu_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GK_B200_H */
