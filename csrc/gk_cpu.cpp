@@ -52,6 +52,7 @@ void publish(const GkChain* c, const GkDst* d, uint64_t poff, uint32_t seqn, uin
   ct->sent = sent;
   ct->overflow += total - sent;
   ct->sent_total += sent;
+  ct->ring[seqn & 63u] = total;
   ct->seq = seqn;
 }
 

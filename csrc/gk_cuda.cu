@@ -20,6 +20,7 @@
 //     The receive kernel acquires those headers (bounded spin) and scatter-adds from local HBM.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <string.h>
 
 #include "../include/gk_b200.h"
 
@@ -642,6 +643,7 @@ __global__ void __launch_bounds__(GK_THREADS) k_compact_send(GkChain c, GkDst d)
       c.ctrl->sent = sent;
       c.ctrl->overflow += total - sent;
       c.ctrl->sent_total += sent;
+      c.ctrl->ring[seqn & 63u] = total;
       c.ctrl->seq = seqn;
     }
   }
@@ -904,6 +906,7 @@ __global__ void __launch_bounds__(GK_THREADS) k_randomk(GkChain c, GkDst d, uint
       for (int q = 0; q < d.ndst; ++q) st_release_sys_u64(d.slot[q] + poff, hdr);
       c.ctrl->total = total; c.ctrl->sent = sent;
       c.ctrl->overflow += total - sent; c.ctrl->sent_total += sent;
+      c.ctrl->ring[seqn & 63u] = total;
       c.ctrl->seq = seqn;
     }
   }
@@ -1125,5 +1128,30 @@ int gk_histogram(const float* x, int64_t n, float lo, float hi, int32_t nbins, u
   k_histogram<<<(int)blocks, T, nbins * sizeof(uint32_t), S(stream)>>>(x, n, lo, (float)nbins / (hi - lo), nbins, out);
   GK_RET();
 }
+
+// ---- peer-memory plumbing for the P2P transport (set-up time only; these are the only
+// entry points of the library that allocate).  The arena they hand out is written by peers'
+// k_compact_send kernels over NVLink and read by the local k_scatter kernel.
+int gk_ipc_alloc(uint64_t bytes, void** ptr, unsigned char* handle64) {
+  cudaError_t e = cudaMalloc(ptr, bytes);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaMemset(*ptr, 0, bytes);
+  if (e != cudaSuccess) return (int)e;
+  cudaIpcMemHandle_t h;
+  e = cudaIpcGetMemHandle(&h, *ptr);
+  if (e != cudaSuccess) return (int)e;
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(handle64, &h, 64);
+  return (int)cudaDeviceSynchronize();
+}
+
+int gk_ipc_open(const unsigned char* handle64, void** ptr) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  return (int)cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess);
+}
+
+int gk_ipc_close(void* ptr) { return (int)cudaIpcCloseMemHandle(ptr); }
+int gk_ipc_free(void* ptr) { return (int)cudaFree(ptr); }
 
 }  // extern "C"

@@ -1,0 +1,545 @@
+"""Distributed optimizer: sparsified synchronous data-parallel SGD on flat arenas.
+
+Public surface of the reference module, used ``as hvd`` by the training loop:
+``init() rank() size() local_rank() local_size() broadcast(t, root_rank) DistributedOptimizer(...)
+broadcast_parameters(state_dict, root_rank) broadcast_optimizer_state(opt, root_rank)`` and the
+optimizer methods ``step() synchronize() zero_grad() increase_one_epoch() get_current_density()``
+plus the ``local`` flag (distributed_optimizer.py:38-585, 588-736).
+
+What happens underneath is different by design:
+
+* parameters, gradients, residuals and momentum live in four flat fp32 arenas
+  (:mod:`parallel.arena`); ``p.grad`` are arena views, so autograd accumulates in place and the
+  reference's per-tensor staging copy (`_push_to_buffer`, :364-383) does not exist;
+* a group's send side is one kernel chain (:class:`ops.chain.CompressChain`) without host syncs; its
+  compaction kernel stores the (index,value) pairs into every peer's receive slot over NVLink
+  (:mod:`parallel.transport`) — the two ``hvd.allgather_async`` calls of :426-427 are gone;
+* ``synchronize()`` launches the receive kernel (bounded spin on the peers' headers, scatter-add of
+  value/P into the zeroed gradient arena: the *exact* mean of the workers' sparse vectors, also when
+  the per-rank counts differ — the reference's equal-chunk split at :471 mis-partitions them);
+* ``step()`` is one fused momentum-SGD (or LARS) kernel over the arenas with torch.optim.SGD
+  arithmetic instead of 3-4 launches per tensor.
+"""
+from __future__ import annotations
+
+import os
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import settings
+from .ops import chain as ch
+from .parallel import comm, grouping
+from .parallel.arena import ParamArena
+from .parallel.comm import (allreduce_, barrier, broadcast, init, local_rank, local_size, rank,  # noqa: F401
+                            shutdown, size)
+from .parallel.transport import Transport, make_transport
+from .settings import logger
+
+DEFAULT_DYNAMIC_DENSITIES = [0.015625, 0.004, 0.001]  # distributed_optimizer.py:60
+_SPARSE_KERNEL_COMPRESSORS = {"gaussian", "gaussiank", "gaussian2", "topk", "topk2", "mink", "redsync",
+                              "redsynctrim", "dgcsampling", "randomk", "randomkec", "randomksame",
+                              "randomksameec"}
+
+
+def synchronize(handle=None):
+    """Module-level ``hvd.synchronize``: wait for an async collective handle (None = no-op)."""
+    if handle is not None and hasattr(handle, "wait"):
+        handle.wait()
+    return handle
+
+
+def _compressor_name(compression) -> str:
+    if compression is None:
+        return "none"
+    if isinstance(compression, str):
+        return compression
+    return getattr(compression, "key", None) or getattr(compression, "name", "none")
+
+
+class _Group:
+    """One communication group: tensors that are compressed and exchanged together."""
+
+    def __init__(self, names: List[str], idx: int):
+        self.names = names
+        self.idx = idx
+        self.chain: Optional[ch.CompressChain] = None
+        self.transport: Optional[Transport] = None
+        self.pending = 0          # gradients still missing in this backward pass
+        self.launched = False
+        self.extents = []
+        self.lo = self.hi = 0     # arena span (dense path)
+        self.work = None
+        self.means = None
+        self.gmeans = None
+        self.ready_event = None
+
+
+class _DistributedOptimizer(torch.optim.Optimizer):
+    def __init__(self, params, named_parameters, compression, is_sparse=False, density=0.001,
+                 seq_layernames=None, layerwise_times=None, norm_clip=None, threshold=0, writer=None,
+                 gradient_path=None, fused=True, transport=None, dynamic_densities="default",
+                 force_compress=False, chunk=ch.DEFAULT_CHUNK, overlap=None):
+        super(self.__class__, self).__init__(params)
+        self._compression = compression
+        self._compressor = _compressor_name(compression)
+        self._density = float(density)
+        self._sparse = bool(is_sparse) and self._compressor not in ("none", "bucket")
+        self._seq_layernames = seq_layernames
+        self._layerwise_times = layerwise_times
+        self._norm_clip = norm_clip
+        self._threshold = threshold
+        self._writer = writer
+        self._gradient_path = gradient_path
+        self._profiling = settings.PROFILE_PHASES
+        self._timers = {"compress": [], "comm": [], "update": []}
+        self.train_epoch = 0
+        self.train_iter = 0
+        if dynamic_densities == "default":
+            dynamic_densities = settings.DYNAMIC_DENSITIES
+        self._dynamic_densities = list(dynamic_densities) if dynamic_densities else None
+        logger.info('_dynamic_densities: %s', self._dynamic_densities)
+        self._selected_num_gradients: List[int] = []
+        self.local = False
+        self._force_compress = force_compress or settings.COMPRESS_SINGLE
+        self._chunk = chunk
+        self._transport_kind = transport
+        self._random_seed = 0
+
+        named_parameters = list(named_parameters) if named_parameters is not None else []
+        if any(not isinstance(p, tuple) for p in named_parameters):
+            raise ValueError('named_parameters should be a sequence of tuples (name, parameter), '
+                             'usually produced by model.named_parameters().')
+        if not named_parameters:
+            named_parameters = [('allreduce.noname.%d.%d' % (gi, i), v)
+                                for gi, g in enumerate(self.param_groups) for i, v in enumerate(g['params'])]
+        in_groups = {id(p) for g in self.param_groups for p in g['params']}
+        named_parameters = [(n, p) for n, p in named_parameters if p.requires_grad and id(p) in in_groups]
+        self._named_parameters: Dict[str, torch.nn.Parameter] = dict(named_parameters)
+        self._parameter_names = {p: n for n, p in named_parameters}
+        self._sequential_keys = list(seq_layernames) if seq_layernames is not None else [n for n, _ in named_parameters]
+
+        # ---- arenas ------------------------------------------------------------------------
+        self._arena = ParamArena(named_parameters)
+        self.device = self._arena.device
+        self._resid = self._arena.new_arena() if self._sparse or self._compressor == "bucket" else None
+        self._active = size() > 1 or self._force_compress   # distributed_optimizer.py:97: 1 worker => plain optimizer
+        group_of_tensor = self._param_group_index()
+        self._tables = ch.FlatTables(self._arena.extents(), group_of_tensor, self.device, chunk)
+        self._fused_kind = self._detect_fused(fused)
+        self._mom = None
+        self._hyper_host = None
+        self._hyper_dev = None
+        self._hyper_key = None
+        self._steps_done = 0
+        if self._fused_kind is not None:
+            self._init_fused_state()
+        self._clip_coef = None     # device scalar consumed by the next fused step
+
+        # ---- groups / chains ----------------------------------------------------------------
+        self._generate_merged_parameters()
+        self._grad_state = "zero"
+        self._hooks = []
+        self._overlap = (len(self._groups) > 1) if overlap is None else overlap
+        self._comm_stream = None
+        if self._active:
+            self._register_hooks()
+
+    # ------------------------------------------------------------------ set-up helpers
+    def _param_group_index(self) -> List[int]:
+        gid = {}
+        for gi, g in enumerate(self.param_groups):
+            for p in g['params']:
+                gid[id(p)] = gi
+        return [gid[id(p)] for p in self._arena.params]
+
+    def _detect_fused(self, fused):
+        if not fused:
+            return None
+        base = type(self).__mro__[1]
+        if base.__name__ == "LARS":
+            return "lars"
+        if base is torch.optim.SGD or base.__name__ == "SGD":
+            g0 = self.param_groups[0]
+            if g0.get("maximize", False):
+                return None
+            return "sgd"
+        return None
+
+    def _init_fused_state(self):
+        """Momentum (or LARS acceleration) arena with views installed as the optimizer state, so
+        ``state_dict()`` keeps torch's format (checkpointed, unlike the reference)."""
+        if self._fused_kind == "lars":
+            self._mom = self._arena.new_arena(1.0)      # lars.py:116-119: acceleration starts at ones
+            key = "acceleration"
+        else:
+            self._mom = self._arena.new_arena(0.0)
+            key = "momentum_buffer"
+        need = self._fused_kind == "lars" or any(g.get("momentum", 0) != 0 for g in self.param_groups)
+        if need:
+            for i, p in enumerate(self._arena.params):
+                self.state[p][key] = self._arena.view(self._mom, i)
+        else:
+            self._mom = None
+
+    def _generate_merged_parameters(self):
+        sizes = {k: self._named_parameters[k].numel() for k in self._sequential_keys}
+        self._sizes = [sizes[k] for k in self._sequential_keys][::-1]
+        P = size()
+        info = {}
+        if settings.ADAPTIVE_MERGE and self._layerwise_times is not None and self._seq_layernames is not None:
+            if self._density < 1:
+                groups, gof, info = grouping.groups_mgs(self._seq_layernames, sizes, self._layerwise_times,
+                                                        max(P, 2), self._density)
+            else:
+                groups, gof, info = grouping.groups_mgwfbp(self._seq_layernames, sizes, self._layerwise_times,
+                                                           max(P, 2))
+        else:
+            groups, gof = grouping.groups_by_threshold(self._sequential_keys, sizes, self._threshold)
+        logger.info('# of parameters: %d', int(np.sum(self._sizes)))
+        logger.info('Total number of tensors: %s', len(self._sizes))
+        logger.info('Merged Number of groups: %s', len(groups))
+        if info:
+            logger.info('Merge planner: %s', info)
+        self._key_groupidx_maps = gof
+        self._per_tensor = len(groups) == len(self._sequential_keys) and len(groups) > 1
+        arena = self._arena
+        if self._per_tensor:
+            # threshold=0: every tensor is its own selection segment, but all of them go through ONE
+            # segmented launch instead of 161 chains.
+            g = _Group([n for grp in groups for n in grp], 0)
+            g.segments = [[arena.extent(arena.index[n])] for n in g.names]
+            self._groups = [g]
+        else:
+            self._groups = []
+            for gi, names in enumerate(groups):
+                g = _Group(list(names), gi)
+                g.segments = [[arena.extent(arena.index[n]) for n in names]]
+                self._groups.append(g)
+        self._group_of_param = {}
+        for g in self._groups:
+            for n in g.names:
+                self._group_of_param[self._named_parameters[n]] = g
+            g.extents = [arena.extent(arena.index[n]) for n in g.names]
+            g.lo = min(o for o, _ in g.extents)
+            g.hi = max(o + m for o, m in g.extents)
+        self._layerwise_compressors = {':'.join(g.names): self._density for g in self._groups}
+        if not self._active:
+            return
+        dmax = max([self._density] + (self._dynamic_densities or []))
+        for g in self._groups:
+            if self._sparse:
+                comp = self._compressor
+                use_res = comp not in ("topk2", "gaussian2", "randomk", "randomksame")
+                kcomp = comp if comp in ch.MODES else "topk"
+                g.chain = ch.CompressChain(arena.grad, self._resid, g.segments, compressor=kcomp,
+                                           density=min(self.get_current_density(), 0.999), use_residual=use_res,
+                                           zero_grad=True, chunk=self._chunk, max_density=min(dmax, 0.999))
+                g.transport = make_transport(g.chain.cap, self.device, self._transport_kind)
+                if rank() == 0:
+                    logger.info('group %d: %d tensors, %d elements, cap %d pairs, transport %s', g.idx,
+                                len(g.names), g.chain.n_total, g.chain.cap, g.transport.name)
+            elif self._compressor == "bucket":
+                g.chain = ch.CompressChain(arena.grad, self._resid, g.segments, compressor="topk",
+                                           density=0.5, use_residual=False, zero_grad=False, chunk=self._chunk)
+                g.means = torch.zeros(2 * g.chain.nseg, dtype=torch.float32, device=self.device)
+                g.gmeans = torch.zeros_like(g.means)
+
+    def _register_hooks(self):
+        for p in self._arena.params:
+            self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(p)))
+        for g in self._groups:
+            g.pending = len(g.names)
+
+    def _make_hook(self, p):
+        group = self._group_of_param[p]
+
+        def hook(_param):
+            self._grad_state = "dense"
+            if self.local:
+                return
+            group.pending -= 1
+            if group.pending == 0 and self._overlap and not group.launched:
+                self._launch_group(group, from_hook=True)
+        return hook
+
+    # ------------------------------------------------------------------ density schedule
+    def increase_one_epoch(self):
+        """distributed_optimizer.py:136-144: advance the density schedule and log the selection stats."""
+        self.train_epoch += 1
+        if rank() == 0 and self._sparse and self._active:
+            density = self.get_current_density()
+            total = int(np.sum(self._sizes))
+            k = max(int(total * density), 1)
+            sel = self.selected_num_gradients()
+            if sel:
+                logger.info('Average number of selected gradients: %f, exact k: %d', float(np.mean(sel)), k)
+                logger.info('The number of selected gradients: %s', sel)
+        self._selected_num_gradients = []
+        self._apply_density()
+
+    def get_current_density(self, name=None):
+        """Effective density = max(user density, schedule[epoch]) (distributed_optimizer.py:146-160)."""
+        density = self._density
+        if self._dynamic_densities:
+            sched = self._dynamic_densities[min(self.train_epoch, len(self._dynamic_densities) - 1)]
+            density = max(self._density, sched)
+        return density
+
+    def _apply_density(self):
+        if not (self._active and self._sparse):
+            return
+        d = min(self.get_current_density(), 0.999)
+        for g in self._groups:
+            if g.chain is not None:
+                g.chain.set_density(d)
+
+    def selected_num_gradients(self) -> List[int]:
+        """Pairs selected by the most recent sends (<= 64, oldest first), read from the device-side ring
+        (the reference appends ``ctx.numel()`` on the host every iteration, :420)."""
+        out: List[int] = []
+        for g in self._groups:
+            if g.chain is None or not self._sparse:
+                continue
+            c = g.chain.read_ctrl()
+            seq = c["seq"]
+            n = min(seq, 64)
+            out.extend(int(c["ring"][(seq - n + 1 + i) & 63]) for i in range(n))
+        return out
+
+    # ------------------------------------------------------------------ send side
+    def _launch_group(self, g: _Group, from_hook: bool = False):
+        if g.launched:
+            return
+        g.launched = True
+        stream_ctx = None
+        if self._overlap and self.device.type == "cuda":
+            if self._comm_stream is None:
+                self._comm_stream = torch.cuda.Stream(self.device)
+            self._comm_stream.wait_stream(torch.cuda.current_stream(self.device))
+            stream_ctx = torch.cuda.stream(self._comm_stream)
+            stream_ctx.__enter__()
+        try:
+            if self._sparse:
+                comp = self._compressor
+                if comp.startswith("randomk"):
+                    seed = self._random_seed if comp.startswith("randomksame") else self._random_seed * 1000003 + rank() + 1
+                    g.chain.randomk_send(g.transport.dst(), seed)
+                else:
+                    g.chain.compress(g.transport.dst())
+                g.transport.exchange()
+            elif self._compressor == "bucket":
+                g.chain.bucket_means(g.means)
+                g.gmeans.copy_(g.means)
+                allreduce_(g.gmeans, average=True)
+            else:
+                buf = self._arena.grad[g.lo:g.hi]
+                g.work = allreduce_(buf, average=True, async_op=True)
+        finally:
+            if stream_ctx is not None:
+                stream_ctx.__exit__(None, None, None)
+
+    # ------------------------------------------------------------------ receive side
+    def synchronize(self):
+        """Finish the exchange: afterwards every ``p.grad`` holds the averaged (sparse) gradient
+        (distributed_optimizer.py:449-519)."""
+        if not self._active:
+            return
+        P = size()
+        any_launched = False
+        for g in self._groups:
+            if not g.launched and self._grad_state == "dense":
+                self._launch_group(g)
+            if not g.launched:
+                continue
+            any_launched = True
+            if self._overlap and self._comm_stream is not None:
+                torch.cuda.current_stream(self.device).wait_stream(self._comm_stream)
+            if self._sparse:
+                ch.scatter(g.transport.src(), g.chain.ctrl, self._arena.grad, 1.0 / P)
+            elif self._compressor == "bucket":
+                g.chain.bucket_reconstruct(g.means, g.gmeans)
+            else:
+                if g.work is not None:
+                    g.work.wait()
+                    g.work = None
+            g.launched = False
+            g.pending = len(g.names)
+        if any_launched:
+            self._random_seed += 1
+            self.train_iter += 1
+            self._grad_state = "sparse" if self._sparse else "dense"
+            if self._norm_clip is not None:
+                # honour norm_clip (the reference's factory discards it); same scaling
+                # as its dense path (:498-505)
+                self.clip_grad_norm(float(np.sqrt(1.0 / P) * self._norm_clip))
+
+    def clip_grad_norm(self, max_norm: float) -> torch.Tensor:
+        """Fused global-norm clipping of the arena (dist_trainer.py:80-85 does it with
+        ``clip_grad_norm_`` after ``synchronize()``).  The coefficient stays on the device and is folded
+        into the next fused step; with a non-fused optimizer the gradient is scaled in place."""
+        out = ch.grad_norm(self._arena.grad, self._tables, max_norm)
+        if self._fused_kind == "sgd":
+            self._clip_coef = out[1:2]
+        else:
+            ch.scale_(self._arena.grad, self._tables, out[1:2])
+        return out
+
+    def check_errors(self) -> None:
+        """Host-side check of the device error flags (receive timeouts).  Synchronises."""
+        for g in self._groups:
+            if g.chain is not None and self._sparse:
+                c = g.chain.read_ctrl()
+                if c["err"]:
+                    raise RuntimeError(f"sparse exchange of group {g.idx} timed out on rank {rank()} (seq {c['seq']})")
+
+    # ------------------------------------------------------------------ update
+    def _refresh_hyper(self):
+        first = self._steps_done == 0
+        key = tuple((g['lr'], g.get('momentum', 0.0), g.get('dampening', 0.0), g.get('weight_decay', 0.0),
+                     bool(g.get('nesterov', False)), g.get('eeta', 0.0), g.get('epsilon', 0.0))
+                    for g in self.param_groups) + (first,)
+        if key == self._hyper_key:
+            return
+        self._hyper_key = key
+        host = ch.make_hyper(self.param_groups, "cpu", first)
+        if self.device.type == "cuda":
+            if self._hyper_host is None:
+                self._hyper_host = torch.empty_like(host).pin_memory()
+                self._hyper_dev = torch.empty_like(host, device=self.device)
+            self._hyper_host.copy_(host)
+            self._hyper_dev.copy_(self._hyper_host, non_blocking=True)
+        else:
+            self._hyper_dev = host
+
+    def fused_update(self):
+        """The fused optimizer kernel alone (graph-capturable: reads lr & co from device memory)."""
+        a = self._arena
+        if self._fused_kind == "sgd":
+            ch.sgd_step(a.param, a.grad, self._mom, self._tables, self._hyper_dev, self._clip_coef)
+        else:
+            ch.lars_step(a.param, a.grad, self._mom, self._tables, self._hyper_dev)
+        self._clip_coef = None
+
+    def step(self, closure=None):
+        """Synchronise the exchange, then update (distributed_optimizer.py:543-546)."""
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        if not self.local:
+            self.synchronize()
+        if self._fused_kind is not None:
+            self._refresh_hyper()
+            self.fused_update()
+            self._steps_done += 1
+            return loss
+        return super(self.__class__, self).step()
+
+    def zero_grad(self, set_to_none: bool = False):
+        """Keep the arena views alive (torch's default ``set_to_none=True`` would drop them) and clear
+        only what was written: after a sparse step just the received coordinates."""
+        a = self._arena
+        if self._grad_state == "sparse" and self._active and self._sparse and settings.SPARSE_ZERO:
+            for g in self._groups:
+                ch.unscatter(g.transport.src(), g.chain.ctrl, a.grad)
+        elif self._grad_state != "zero" or not self._active:
+            a.grad.zero_()
+        self._grad_state = "zero"
+        a.rebind_grads()
+
+    # ------------------------------------------------------------------ state
+    def residual_state(self) -> Optional[torch.Tensor]:
+        return self._resid
+
+    def extra_state_dict(self) -> dict:
+        """Compressor residuals + schedule position (not saved by the reference)."""
+        return {"residual": None if self._resid is None else self._resid.detach().cpu().clone(),
+                "train_epoch": self.train_epoch, "train_iter": self.train_iter,
+                "steps_done": self._steps_done, "random_seed": self._random_seed}
+
+    def load_extra_state_dict(self, sd: dict) -> None:
+        if sd.get("residual") is not None and self._resid is not None and sd["residual"].numel() == self._resid.numel():
+            self._resid.copy_(sd["residual"])
+        self.train_epoch = int(sd.get("train_epoch", 0))
+        self.train_iter = int(sd.get("train_iter", 0))
+        self._steps_done = int(sd.get("steps_done", 0))
+        self._random_seed = int(sd.get("random_seed", 0))
+        self._hyper_key = None
+        self._apply_density()
+
+    def close(self):
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []
+        for g in self._groups:
+            if g.transport is not None:
+                g.transport.close()
+
+
+def DistributedOptimizer(optimizer, named_parameters=None, compression=None, is_sparse=False, density=0.001,
+                         seq_layernames=None, layerwise_times=None, norm_clip=None, threshold=0, writer=None,
+                         gradient_path=None, **kwargs):
+    """Wrap ``optimizer`` (factory of distributed_optimizer.py:550-585).  Like the reference, the result
+    is an instance of a dynamically created subclass of the wrapped optimizer's class, so it *is* an
+    ``SGD`` / ``LARS`` whose ``step()`` first finishes the gradient exchange.
+
+    Extra keyword arguments (all optional): ``fused`` (default True: arena kernel instead of the per-tensor
+    torch update), ``transport`` (auto|p2p|allgather), ``dynamic_densities`` (list or None; default the
+    reference's warm-up schedule [0.015625, 0.004, 0.001]), ``force_compress`` (run the chain even with
+    one worker), ``chunk``, ``overlap``.  ``norm_clip`` is honoured (the reference drops it, Q4)."""
+    cls = type(optimizer.__class__.__name__, (optimizer.__class__,), dict(_DistributedOptimizer.__dict__))
+    return cls(optimizer.param_groups, named_parameters, compression, is_sparse, density,
+               seq_layernames=seq_layernames, layerwise_times=layerwise_times, norm_clip=norm_clip,
+               threshold=threshold, writer=writer, gradient_path=gradient_path, **kwargs)
+
+
+def broadcast_parameters(params, root_rank=0):
+    """Make every rank start from ``root_rank``'s values (distributed_optimizer.py:588-617).  The
+    reference broadcasts tensor by tensor; here tensors are packed per dtype into one flat buffer."""
+    if isinstance(params, dict):
+        items = sorted(params.items())
+    elif isinstance(params, list):
+        items = [p if isinstance(p, tuple) else (None, p) for p in params]
+    else:
+        raise ValueError('invalid params of type: %s' % type(params))
+    if not comm.is_distributed():
+        return
+    by_dtype: Dict[torch.dtype, List[torch.Tensor]] = {}
+    for _, t in items:
+        if torch.is_tensor(t):
+            by_dtype.setdefault(t.dtype, []).append(t)
+    for dtype, tensors in by_dtype.items():
+        flat = torch.cat([t.detach().reshape(-1) for t in tensors]) if len(tensors) > 1 else tensors[0].detach().reshape(-1).clone()
+        comm.broadcast_(flat, root_rank)
+        off = 0
+        with torch.no_grad():
+            for t in tensors:
+                n = t.numel()
+                t.copy_(flat[off:off + n].view(t.shape))
+                off += n
+
+
+def broadcast_optimizer_state(optimizer, root_rank=0):
+    """Broadcast the optimizer state and hyper-parameters (distributed_optimizer.py:620-736)."""
+    if not comm.is_distributed():
+        return
+    sd = optimizer.state_dict() if rank() == root_rank else None
+    meta = comm.bcast_object({"param_groups": sd["param_groups"]} if sd is not None else None, root_rank)
+    for g, m in zip(optimizer.param_groups, meta["param_groups"]):
+        for k, v in m.items():
+            if k != "params":
+                g[k] = v
+    tensors = []
+    for g in optimizer.param_groups:
+        for p in g["params"]:
+            for k, v in sorted(optimizer.state.get(p, {}).items()):
+                if torch.is_tensor(v):
+                    tensors.append(v)
+    if tensors:
+        broadcast_parameters([(None, t) for t in tensors], root_rank)
+    extra = getattr(optimizer, "residual_state", None)
+    if callable(extra) and extra() is not None:
+        comm.broadcast_(extra(), root_rank)

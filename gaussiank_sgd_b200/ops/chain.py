@@ -26,10 +26,11 @@ STAT_DTYPE = np.dtype([("mean", "<f4"), ("std", "<f4"), ("meanabs", "<f4"), ("ma
                        ("chosen", "<i4"), ("count", "<u4"), ("out_base", "<u4"), ("prefix", "<u4"),
                        ("krem", "<u4")])
 CTRL_DTYPE = np.dtype([("done", "<u4", (8,)), ("total", "<u4"), ("sent", "<u4"), ("seq", "<u4"),
-                       ("err", "<u4"), ("overflow", "<u4"), ("rsv", "<u4", (3,)), ("sent_total", "<u8")])
+                       ("err", "<u4"), ("overflow", "<u4"), ("rsv", "<u4", (3,)), ("sent_total", "<u8"),
+                       ("ring", "<u4", (64,))])
 HYPER_DTYPE = np.dtype([("lr", "<f4"), ("momentum", "<f4"), ("dampening", "<f4"), ("weight_decay", "<f4"),
                         ("nesterov", "<i4"), ("first_step", "<i4"), ("lars_eeta", "<f4"), ("lars_eps", "<f4")])
-assert SEG_DTYPE.itemsize == 32 and STAT_DTYPE.itemsize == 112 and CTRL_DTYPE.itemsize == 72
+assert SEG_DTYPE.itemsize == 32 and STAT_DTYPE.itemsize == 112 and CTRL_DTYPE.itemsize == 328
 assert HYPER_DTYPE.itemsize == 32
 
 DEFAULT_CHUNK = 8192
@@ -389,7 +390,7 @@ def scale_(grad: torch.Tensor, tables: FlatTables, scale: torch.Tensor) -> None:
         N.check(N.cuda_lib().gk_scale(grad.data_ptr(), tables.group_blk_t.data_ptr(), tables.nblk,
                                       scale.data_ptr(), _stream_ptr(grad.device)), "gk_scale")
     else:
-        s = float(scale.reshape(-1)[-1] if scale.numel() > 1 else scale)
+        s = float(scale.reshape(-1)[0])
         if s != 1.0:
             grad.mul_(s)
 

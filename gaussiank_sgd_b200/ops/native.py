@@ -49,7 +49,7 @@ class GkSegStat(C.Structure):
 class GkCtrl(C.Structure):
     _fields_ = [("done", C.c_uint32 * 8), ("total", C.c_uint32), ("sent", C.c_uint32), ("seq", C.c_uint32),
                 ("err", C.c_uint32), ("overflow", C.c_uint32), ("rsv", C.c_uint32 * 3),
-                ("sent_total", C.c_uint64)]
+                ("sent_total", C.c_uint64), ("ring", C.c_uint32 * 64)]
 
 
 class GkChain(C.Structure):
@@ -77,7 +77,7 @@ class GkHyper(C.Structure):
 
 
 assert C.sizeof(GkBlk) == 16 and C.sizeof(GkSeg) == 32 and C.sizeof(GkSegStat) == 112
-assert C.sizeof(GkCtrl) == 72 and C.sizeof(GkHyper) == 32
+assert C.sizeof(GkCtrl) == 328 and C.sizeof(GkHyper) == 32
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC"]
@@ -163,6 +163,10 @@ def cuda_lib():
             _proto(lib, "gk_bucket_reconstruct", [ch, _P, _P, _P])
             _proto(lib, "gk_copy", [_P, _P, C.c_int64, _P])
             _proto(lib, "gk_histogram", [_P, C.c_int64, C.c_float, C.c_float, C.c_int32, _P, _P])
+            _proto(lib, "gk_ipc_alloc", [C.c_uint64, C.POINTER(C.c_void_p), C.c_char_p])
+            _proto(lib, "gk_ipc_open", [C.c_char_p, C.POINTER(C.c_void_p)])
+            _proto(lib, "gk_ipc_close", [_P])
+            _proto(lib, "gk_ipc_free", [_P])
             _libs["cuda"] = lib
         return _libs["cuda"]
 

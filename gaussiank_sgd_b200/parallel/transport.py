@@ -1,0 +1,207 @@
+"""Sparse-allgather transports: where the compaction kernel stores its pairs and where the
+receive kernel finds everybody's.
+
+The reference issues two Horovod ``allgather_async`` calls per group (values and int32 indexes,
+distributed_optimizer.py:426-427) and blocks on them in ``synchronize`` (:461-463).  Here the
+"collective" is part of the kernels:
+
+* :class:`P2PTransport` — every rank owns a double-buffered receive arena in peer-mapped device
+  memory (``torch.distributed._symmetric_memory`` or, failing that, CUDA IPC handles of a raw
+  allocation).  Rank r's compaction kernel stores its pairs straight into slot r of every peer's
+  arena over NVLink and publishes {count, seq}; the receive kernel spins (bounded) on the headers.
+  No NCCL call on the sparse path.
+* :class:`AllGatherTransport` — one fixed-size ``all_gather_into_tensor`` of (header + pairs); the
+  NCCL baseline on GPUs and the gloo path on CPUs (BASELINE.json config 1).
+* :class:`LocalTransport` — world of one.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops import native as N
+from ..ops.chain import SlotBuffer, make_dst
+from . import comm
+
+
+class Transport:
+    name = "base"
+    wait = False
+
+    def dst(self) -> N.GkDst:
+        raise NotImplementedError
+
+    def src(self) -> N.GkSrc:
+        raise NotImplementedError
+
+    def exchange(self) -> None:
+        """Host-issued part of the exchange, enqueued after the send kernel (no-op for P2P)."""
+
+    def close(self) -> None:
+        pass
+
+
+class LocalTransport(Transport):
+    name = "local"
+
+    def __init__(self, cap: int, device):
+        self.buf = SlotBuffer(1, cap, device)
+        self._dst = make_dst([self.buf.slot_ptr(0)], 0)
+        self._src = self.buf.src(wait=False)
+
+    def dst(self):
+        return self._dst
+
+    def src(self):
+        return self._src
+
+
+class AllGatherTransport(Transport):
+    name = "allgather"
+
+    def __init__(self, cap: int, device, group=None):
+        self.P = comm.size()
+        self.group = group
+        self.send = SlotBuffer(1, cap, device)
+        self.recv = SlotBuffer(self.P, cap, device)
+        self._dst = make_dst([self.send.slot_ptr(0)], 0)
+        self._src = self.recv.src(wait=False)
+        self._stage = None
+        if device.type == "cuda" and dist.is_initialized() and dist.get_backend() == "gloo":
+            self._stage = (torch.empty_like(self.send.t, device="cpu"), torch.empty_like(self.recv.t, device="cpu"))
+
+    def dst(self):
+        return self._dst
+
+    def src(self):
+        return self._src
+
+    def exchange(self):
+        if self.P == 1:
+            self.recv.t.copy_(self.send.t)
+        elif self._stage is not None:
+            s, r = self._stage
+            s.copy_(self.send.t)
+            dist.all_gather_into_tensor(r, s, group=self.group)
+            self.recv.t.copy_(r)
+        else:
+            dist.all_gather_into_tensor(self.recv.t, self.send.t, group=self.group)
+
+
+class P2PTransport(Transport):
+    """Peer-mapped, double-buffered receive arenas; the kernels do the communication."""
+    name = "p2p"
+    wait = True
+
+    def __init__(self, cap: int, device, timeout_s: float = 20.0, backend: str = "auto"):
+        assert device.type == "cuda"
+        self.P, self.rank = comm.size(), comm.rank()
+        self.cap = int(cap)
+        self.device = device
+        self.timeout_s = timeout_s
+        slot_stride = N.GK_SLOT_HDR + self.cap
+        words = 2 * self.P * slot_stride
+        self._ipc_ptrs: List[int] = []
+        self._own_raw = None
+        self._symm_t = None
+        self.backend = None
+        errs = []
+        if backend in ("auto", "symm"):
+            try:
+                self._init_symm(words)
+                self.backend = "symm"
+            except Exception as e:  # noqa: BLE001 - any failure falls through to CUDA IPC
+                errs.append(f"symmetric memory: {type(e).__name__}: {e}")
+                if backend == "symm":
+                    raise
+        if self.backend is None:
+            self._init_ipc(words)
+            self.backend = "ipc"
+        self.errors = errs
+        self.slot_stride = slot_stride
+        parity_stride = self.P * slot_stride
+        my_slots = [base + 8 * self.rank * slot_stride for base in self.peer_ptrs]
+        self._dst = make_dst(my_slots, parity_stride)
+        self._src = N.GkSrc(self.peer_ptrs[self.rank], slot_stride, parity_stride, self.P, 1,
+                            int(timeout_s * 1e9))
+        comm.barrier()
+
+    def _init_symm(self, words: int) -> None:
+        import torch.distributed._symmetric_memory as symm
+        group = dist.group.WORLD
+        try:
+            symm.enable_symm_mem_for_group(group.group_name)
+        except Exception:  # noqa: BLE001 - newer torch enables groups implicitly
+            pass
+        t = symm.empty(words, dtype=torch.int64, device=self.device)
+        t.zero_()
+        hdl = symm.rendezvous(t, group=group)
+        self.peer_ptrs = [int(p) for p in hdl.buffer_ptrs]
+        assert len(self.peer_ptrs) == self.P
+        self._symm_t, self._symm_h = t, hdl
+        self.multicast_ptr = int(getattr(hdl, "multicast_ptr", 0) or 0)
+        torch.cuda.synchronize(self.device)
+        hdl.barrier()
+
+    def _init_ipc(self, words: int) -> None:
+        lib = N.cuda_lib()
+        ptr = C.c_void_p()
+        handle = C.create_string_buffer(64)
+        N.check(lib.gk_ipc_alloc(words * 8, C.byref(ptr), handle), "gk_ipc_alloc")
+        self._own_raw = ptr.value
+        handles: List[Optional[bytes]] = [None] * self.P
+        dist.all_gather_object(handles, handle.raw)
+        ptrs = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                ptrs.append(self._own_raw)
+            else:
+                p = C.c_void_p()
+                N.check(lib.gk_ipc_open(h, C.byref(p)), f"gk_ipc_open(rank {r})")
+                ptrs.append(p.value)
+                self._ipc_ptrs.append(p.value)
+        self.peer_ptrs = ptrs
+        self.multicast_ptr = 0
+
+    def dst(self):
+        return self._dst
+
+    def src(self):
+        return self._src
+
+    def close(self):
+        if self.backend == "ipc":
+            lib = N.cuda_lib()
+            torch.cuda.synchronize(self.device)
+            comm.barrier()
+            for p in self._ipc_ptrs:
+                lib.gk_ipc_close(p)
+            self._ipc_ptrs = []
+            if self._own_raw:
+                lib.gk_ipc_free(self._own_raw)
+                self._own_raw = None
+
+
+def make_transport(cap: int, device, kind: Optional[str] = None) -> Transport:
+    """Pick the transport: ``GK_TRANSPORT`` = auto | p2p | symm | ipc | allgather."""
+    kind = (kind or os.environ.get("GK_TRANSPORT", "auto")).lower()
+    P = comm.size()
+    if P == 1 and kind in ("auto", "local"):
+        return LocalTransport(cap, device)
+    if device.type != "cuda" or kind == "allgather":
+        return AllGatherTransport(cap, device)
+    if kind in ("auto", "p2p", "symm", "ipc"):
+        try:
+            return P2PTransport(cap, device, backend={"p2p": "auto"}.get(kind, kind),
+                                timeout_s=float(os.environ.get("GK_P2P_TIMEOUT_S", "20")))
+        except Exception as e:  # noqa: BLE001
+            if kind != "auto":
+                raise
+            import warnings
+            warnings.warn(f"P2P transport unavailable ({type(e).__name__}: {e}); falling back to NCCL all_gather")
+            return AllGatherTransport(cap, device)
+    raise ValueError(f"unknown transport {kind!r}")

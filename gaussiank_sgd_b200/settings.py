@@ -1,0 +1,81 @@
+"""Global switches and the shared logger.
+
+The reference keeps these as module constants that are edited by hand (settings.py:1-44).  The
+names and defaults are preserved, but every switch can be set from the environment (``GK_<NAME>``),
+and ``LOGGING_GRADIENTS`` is off by default: the reference copies the whole gradient to the host
+and ``np.save``s it on rank 0 every iteration (distributed_optimizer.py:422-424).
+"""
+from __future__ import annotations
+
+import logging
+import os
+import socket
+
+
+def _flag(name: str, default: bool) -> bool:
+    v = os.environ.get("GK_" + name)
+    if v is None:
+        return default
+    return v.strip().lower() not in ("0", "false", "no", "off", "")
+
+
+def _floats(name: str, default):
+    v = os.environ.get("GK_" + name)
+    if v is None:
+        return default
+    v = v.strip()
+    if v.lower() in ("", "none", "off"):
+        return None
+    return [float(x) for x in v.split(",")]
+
+
+DEBUG = _flag("DEBUG", False)
+
+SERVER_PORT = 5911  # vestiges of the reference's parent project, unused there as well
+PORT = 5922
+
+WARMUP = _flag("WARMUP", True)
+
+PREFIX = ''
+if WARMUP:
+    PREFIX = PREFIX + 'gwarmup'
+
+LOGGING_ASSUMPTION = _flag("LOGGING_ASSUMPTION", False)
+LOGGING_GRADIENTS = _flag("LOGGING_GRADIENTS", False)
+GRADIENT_DUMP_EVERY = int(os.environ.get("GK_GRADIENT_DUMP_EVERY", "1"))
+
+EXP = os.environ.get("GK_EXP", '-convergence')
+PREFIX = PREFIX + EXP
+ADAPTIVE_MERGE = _flag("ADAPTIVE_MERGE", False)
+ADAPTIVE_SPARSE = _flag("ADAPTIVE_SPARSE", False)
+if ADAPTIVE_MERGE:
+    PREFIX = PREFIX + '-ada'
+
+TENSORBOARD = _flag("TENSORBOARD", False)
+USE_FP16 = _flag("USE_FP16", False)
+
+MAX_EPOCHS = int(os.environ.get("GK_MAX_EPOCHS", "10"))
+
+# ---- switches that exist only here -------------------------------------------------------------
+DYNAMIC_DENSITIES = _floats("DYNAMIC_DENSITIES", [0.015625, 0.004, 0.001])  # distributed_optimizer.py:60
+COMPRESS_SINGLE = _flag("COMPRESS_SINGLE", False)   # run the chain with one worker too
+SPARSE_ZERO = _flag("SPARSE_ZERO", True)            # zero_grad clears only the received coordinates
+PROFILE_PHASES = _flag("PROFILE_PHASES", False)     # CUDA-event timers for compress / comm / update
+CUDA_GRAPH = _flag("CUDA_GRAPH", True)              # capture the training step in a CUDA graph on GPUs
+CHANNELS_LAST = _flag("CHANNELS_LAST", True)        # NHWC convolutions on GPUs
+CUDNN_BENCHMARK = _flag("CUDNN_BENCHMARK", True)    # the reference pins benchmark=False, deterministic=True
+
+hostname = socket.gethostname()
+logger = logging.getLogger(hostname)
+
+if DEBUG:
+    logger.setLevel(logging.DEBUG)
+else:
+    logger.setLevel(logging.INFO)
+
+formatter = logging.Formatter('%(asctime)s [%(filename)s:%(lineno)d] %(levelname)s %(message)s')
+if not logger.handlers:
+    strhdlr = logging.StreamHandler()
+    strhdlr.setFormatter(formatter)
+    logger.addHandler(strhdlr)
+logger.propagate = False

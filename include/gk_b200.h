@@ -82,6 +82,8 @@ typedef struct GkCtrl {
   uint32_t overflow; /* cumulative pairs withheld because of the cap            */
   uint32_t rsv[3];
   uint64_t sent_total; /* cumulative pairs emitted (for logging)                */
+  uint32_t ring[64];   /* ring[seq & 63] = pairs selected by send number seq (the reference keeps
+                          this list on the host, distributed_optimizer.py:420)   */
 } GkCtrl;
 
 /* Everything one compress chain needs.  Passed by pointer from the host; the library
@@ -205,6 +207,15 @@ int gk_copy(float* dst, const float* src, int64_t n, void* stream);
  * (distributed_optimizer.py:422-424 dumped the whole tensor to disk instead). */
 int gk_histogram(const float* x, int64_t n, float lo, float hi, int32_t nbins, uint32_t* out,
                  void* stream);
+
+/* Peer-memory plumbing of the P2P transport (set-up time only; the only allocating entry
+ * points).  gk_ipc_alloc: cudaMalloc + zero + IPC handle (64 bytes) for the local receive arena;
+ * gk_ipc_open maps a peer's arena into this process.  Replaces Horovod's allgather buffers
+ * (distributed_optimizer.py:426-427). */
+int gk_ipc_alloc(uint64_t bytes, void** ptr, unsigned char* handle64);
+int gk_ipc_open(const unsigned char* handle64, void** ptr);
+int gk_ipc_close(void* ptr);
+int gk_ipc_free(void* ptr);
 
 const char* gk_version(void);
 
