@@ -363,7 +363,8 @@ int gkcpu_randomk_send(const GkChain* c, const GkDst* dst, uint64_t seed) {
   for (int s = 0; s < c->nseg; ++s) {
     const GkSeg& sg = c->seg[s];
     for (uint32_t j = 0; j < (uint32_t)sg.k; ++j) {
-      const uint32_t li = feistel_perm(j, (uint32_t)sg.n, seed + 0x632be59bd9b4e019ull * (uint64_t)(s + 1));
+      const uint32_t li = feistel_perm(j, (uint32_t)sg.n, seed + 0x632be59bd9b4e019ull * (uint64_t)(s + 1) +
+                                                              0x9e3779b97f4a7c15ull * (uint64_t)seqn);
       int lo = sg.blk_begin, hi = sg.blk_end - 1;
       while (lo < hi) {
         const int mid = (lo + hi + 1) >> 1;

@@ -876,7 +876,8 @@ __global__ void __launch_bounds__(GK_THREADS) k_randomk(GkChain c, GkDst d, uint
   for (int s = 0; s < c.nseg; ++s) {
     const GkSeg sg = c.seg[s];
     for (uint32_t j = blockIdx.x * T + threadIdx.x; j < (uint32_t)sg.k; j += gridDim.x * T) {
-      const uint32_t li = feistel_perm(j, (uint32_t)sg.n, seed + 0x632be59bd9b4e019ull * (uint64_t)(s + 1));
+      const uint32_t li = feistel_perm(j, (uint32_t)sg.n, seed + 0x632be59bd9b4e019ull * (uint64_t)(s + 1) +
+                                                              0x9e3779b97f4a7c15ull * (uint64_t)seqn);
       // segment-local index -> arena index: last block whose GkBlk.soff <= li
       int lo = sg.blk_begin, hi = sg.blk_end - 1;
       while (lo < hi) {

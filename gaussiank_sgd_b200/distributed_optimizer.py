@@ -184,6 +184,20 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         else:
             self._mom = None
 
+    def _init_fused_state_from_loaded(self):
+        """After ``load_state_dict``: move the loaded momentum tensors back into the arena views."""
+        if self._mom is None:
+            return
+        key = "acceleration" if self._fused_kind == "lars" else "momentum_buffer"
+        with torch.no_grad():
+            for i, p in enumerate(self._arena.params):
+                view = self._arena.view(self._mom, i)
+                buf = self.state[p].get(key)
+                if buf is not None and buf.data_ptr() != view.data_ptr():
+                    view.copy_(buf.to(view.device))
+                self.state[p][key] = view
+        self._hyper_key = None
+
     def _generate_merged_parameters(self):
         sizes = {k: self._named_parameters[k].numel() for k in self._sequential_keys}
         self._sizes = [sizes[k] for k in self._sequential_keys][::-1]

@@ -35,6 +35,10 @@ assert HYPER_DTYPE.itemsize == 32
 
 DEFAULT_CHUNK = 8192
 
+# kernels of THIS library launched so far (Python-side count; a replayed CUDA graph re-launches the
+# kernels counted while it was captured)
+LAUNCHES = {"n": 0}
+
 MODES = {
     "gaussian": (N.MODE_GAUSSIAN, 3), "gaussiank": (N.MODE_GAUSSIAN, 3), "gaussian2": (N.MODE_GAUSSIAN, 5),
     "topk": (N.MODE_TOPK, 0), "topk2": (N.MODE_TOPK, 0), "mink": (N.MODE_MINK, 0),
@@ -223,6 +227,7 @@ class CompressChain:
     # ------------------------------------------------------------------------ launches
     def compress(self, dst: N.GkDst) -> None:
         """Enqueue the whole send-side chain on the current stream (no host sync)."""
+        LAUNCHES["n"] += 5 if self.mode in (N.MODE_TOPK, N.MODE_MINK) else 3
         if self.is_cuda:
             N.check(self._lib.gk_compress(C.byref(self._desc), C.byref(dst), _stream_ptr(self.device)),
                     "gk_compress")
@@ -249,6 +254,7 @@ class CompressChain:
     def randomk_send(self, dst: N.GkDst, seed: int) -> None:
         """acc -> resid, then k distinct pseudo-random coordinates per segment
         (compression.py:461-475 / :497-509)."""
+        LAUNCHES["n"] += 2
         if self.is_cuda:
             st = _stream_ptr(self.device)
             N.check(self._lib.gk_accumulate(C.byref(self._desc), st), "gk_accumulate")
@@ -271,12 +277,14 @@ class CompressChain:
                 g.zero_()
 
     def bucket_means(self, means: torch.Tensor) -> None:
+        LAUNCHES["n"] += 1
         if self.is_cuda:
             N.check(self._lib.gk_bucket_means(C.byref(self._desc), means.data_ptr(), _stream_ptr(self.device)))
         else:
             N.check(self._lib.gkcpu_bucket_means(C.byref(self._desc), means.data_ptr()))
 
     def bucket_reconstruct(self, local_means: torch.Tensor, global_means: torch.Tensor) -> None:
+        LAUNCHES["n"] += 1
         if self.is_cuda:
             N.check(self._lib.gk_bucket_reconstruct(C.byref(self._desc), local_means.data_ptr(),
                                                     global_means.data_ptr(), _stream_ptr(self.device)))
@@ -296,6 +304,7 @@ class CompressChain:
 # ------------------------------------------------------------------- receive side / optimizer
 def scatter(src: N.GkSrc, ctrl: torch.Tensor, grad: torch.Tensor, scale: float) -> None:
     """grad[idx] += val*scale over every slot (distributed_optimizer.py:468-482)."""
+    LAUNCHES["n"] += 1
     if grad.device.type == "cuda":
         N.check(N.cuda_lib().gk_scatter(C.byref(src), ctrl.data_ptr(), grad.data_ptr(), C.c_float(scale),
                                         grad.numel(), _stream_ptr(grad.device)), "gk_scatter")
@@ -305,6 +314,7 @@ def scatter(src: N.GkSrc, ctrl: torch.Tensor, grad: torch.Tensor, scale: float) 
 
 
 def unscatter(src: N.GkSrc, ctrl: torch.Tensor, grad: torch.Tensor) -> None:
+    LAUNCHES["n"] += 1
     if grad.device.type == "cuda":
         N.check(N.cuda_lib().gk_unscatter(C.byref(src), ctrl.data_ptr(), grad.data_ptr(), grad.numel(),
                                           _stream_ptr(grad.device)), "gk_unscatter")
@@ -347,6 +357,7 @@ class FlatTables:
 def sgd_step(param: torch.Tensor, grad: torch.Tensor, mom: Optional[torch.Tensor], tables: FlatTables,
              hyper: torch.Tensor, grad_scale: Optional[torch.Tensor] = None) -> None:
     """One fused momentum-SGD pass over the arenas (torch.optim.SGD math, dl_trainer.py:848-872)."""
+    LAUNCHES["n"] += 1
     if param.device.type == "cuda":
         N.check(N.cuda_lib().gk_sgd(param.data_ptr(), grad.data_ptr(), _ptr(mom), tables.group_blk_t.data_ptr(),
                                     tables.nblk, hyper.data_ptr(), _ptr(grad_scale),
@@ -359,6 +370,7 @@ def sgd_step(param: torch.Tensor, grad: torch.Tensor, mom: Optional[torch.Tensor
 def lars_step(param: torch.Tensor, grad: torch.Tensor, acc: torch.Tensor, tables: FlatTables,
               hyper: torch.Tensor) -> None:
     """LARS (lars.py:67-134): segmented norms, trust ratio, clamped update."""
+    LAUNCHES["n"] += 2
     if param.device.type == "cuda":
         N.check(N.cuda_lib().gk_lars(param.data_ptr(), grad.data_ptr(), acc.data_ptr(),
                                      tables.tensor_blk_t.data_ptr(), tables.nblk, tables.tens_t.data_ptr(),
@@ -374,6 +386,7 @@ def lars_step(param: torch.Tensor, grad: torch.Tensor, acc: torch.Tensor, tables
 
 def grad_norm(grad: torch.Tensor, tables: FlatTables, max_norm: float) -> torch.Tensor:
     """Global L2 norm and clip coefficient on the device: out = [norm, coef] (dist_trainer.py:80-85)."""
+    LAUNCHES["n"] += 1
     if grad.device.type == "cuda":
         N.check(N.cuda_lib().gk_grad_norm(grad.data_ptr(), tables.group_blk_t.data_ptr(), tables.nblk,
                                           tables.part.data_ptr(), C.c_float(max_norm),
@@ -386,6 +399,7 @@ def grad_norm(grad: torch.Tensor, tables: FlatTables, max_norm: float) -> torch.
 
 
 def scale_(grad: torch.Tensor, tables: FlatTables, scale: torch.Tensor) -> None:
+    LAUNCHES["n"] += 1
     if grad.device.type == "cuda":
         N.check(N.cuda_lib().gk_scale(grad.data_ptr(), tables.group_blk_t.data_ptr(), tables.nblk,
                                       scale.data_ptr(), _stream_ptr(grad.device)), "gk_scale")

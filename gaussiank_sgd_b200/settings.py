@@ -63,6 +63,7 @@ SPARSE_ZERO = _flag("SPARSE_ZERO", True)            # zero_grad clears only the 
 PROFILE_PHASES = _flag("PROFILE_PHASES", False)     # CUDA-event timers for compress / comm / update
 CUDA_GRAPH = _flag("CUDA_GRAPH", True)              # capture the training step in a CUDA graph on GPUs
 CHANNELS_LAST = _flag("CHANNELS_LAST", True)        # NHWC convolutions on GPUs
+SYNTHETIC_POOL = _flag("SYNTHETIC_POOL", True)      # pre-collated pinned batches for synthetic image data
 CUDNN_BENCHMARK = _flag("CUDNN_BENCHMARK", True)    # the reference pins benchmark=False, deterministic=True
 
 hostname = socket.gethostname()

@@ -1,0 +1,200 @@
+"""GPU tests of the optimizer, the CUDA-graph step and (with >= 2 GPUs) the P2P transport."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+import torch.nn as nn
+
+import gaussiank_sgd_b200.distributed_optimizer as hvd
+from gaussiank_sgd_b200 import settings
+from gaussiank_sgd_b200.compression import compressors
+from gaussiank_sgd_b200.dl_trainer import DLTrainer
+from gaussiank_sgd_b200.ops import oracle
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _mlp(seed=0):
+    torch.manual_seed(seed)
+    return nn.Sequential(nn.Linear(64, 256), nn.ReLU(), nn.Linear(256, 256), nn.ReLU(), nn.Linear(256, 10)).to(DEV)
+
+
+@pytest.mark.parametrize("comp", ["gaussian", "topk"])
+def test_optimizer_single_gpu_matches_oracle(comp):
+    density = 0.02
+    m1, m2 = _mlp(), _mlp()
+    o1 = torch.optim.SGD(m1.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    o2 = torch.optim.SGD(m2.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    opt = hvd.DistributedOptimizer(o1, named_parameters=m1.named_parameters(), compression=compressors[comp],
+                                   is_sparse=True, density=density, threshold=524288000, dynamic_densities=None,
+                                   force_compress=True)
+    n = sum(p.numel() for p in m2.parameters())
+    resid = torch.zeros(n, device=DEV)
+    x, y = torch.randn(32, 64, device=DEV), torch.randint(0, 10, (32,), device=DEV)
+    for step in range(4):
+        opt.zero_grad()
+        nn.functional.cross_entropy(m1(x), y).backward()
+        opt.step()
+        o2.zero_grad()
+        nn.functional.cross_entropy(m2(x), y).backward()
+        params = [p for p in m2.parameters()][::-1]
+        g = torch.cat([p.grad.reshape(-1) for p in params])
+        acc = g + resid
+        if comp == "gaussian":
+            st = opt._groups[0].chain.read_stats()[0]
+            idx, _ = oracle.gaussian_select(acc, density, 3, mean=float(st["mean"]), std=float(st["std"]))
+        else:
+            idx = oracle.select(comp, acc, density)
+        dense = torch.zeros_like(acc)
+        dense[idx] = acc[idx]
+        resid = acc.clone()
+        resid[idx] = 0
+        off = 0
+        for p in params:
+            p.grad = dense[off:off + p.numel()].view_as(p).clone()
+            off += p.numel()
+        o2.step()
+        for p1, p2 in zip(m1.parameters(), m2.parameters()):
+            assert torch.allclose(p1, p2, rtol=0, atol=1e-6), step
+    opt.check_errors()
+    opt.close()
+
+
+def _make_trainer(graph, seed=0, dnn="resnet20", comp="gaussian"):
+    settings.CUDA_GRAPH = graph
+    torch.manual_seed(seed)
+    t = DLTrainer(0, 1, dist=False, batch_size=16, ngpus=1, data_dir="synthetic", dataset="cifar10", dnn=dnn,
+                  lr=0.05, nworkers=1, synthetic_samples=512)
+    opt = hvd.DistributedOptimizer(t.optimizer, named_parameters=t.net.named_parameters(),
+                                   compression=compressors[comp], is_sparse=True, density=0.01,
+                                   threshold=524288000, dynamic_densities=None, force_compress=True)
+    t.update_optimizer(opt)
+    return t, opt
+
+
+def test_cuda_graph_step_equals_eager_step():
+    torch.backends.cudnn.benchmark = False
+    torch.backends.cudnn.deterministic = True
+    settings.CUDNN_BENCHMARK = False
+    try:
+        res = {}
+        for graph in (False, True):
+            t, opt = _make_trainer(graph, seed=123)
+            for _ in range(8):
+                t.train_and_update()
+            t.flush_metrics()
+            torch.cuda.synchronize()
+            opt.check_errors()
+            res[graph] = (torch.cat([p.detach().reshape(-1) for p in t.net.parameters()]).cpu(), t.loss,
+                          opt.selected_num_gradients())
+            if graph:
+                assert t._graph is not None and t._graph.graph is not None   # the graph path really ran
+            opt.close()
+        w0, l0, s0 = res[False]
+        w1, l1, s1 = res[True]
+        assert s0 == s1
+        assert torch.allclose(w0, w1, rtol=1e-4, atol=1e-5)
+        assert abs(l0 - l1) < 1e-3 * max(1.0, abs(l0))
+    finally:
+        settings.CUDA_GRAPH = True
+        settings.CUDNN_BENCHMARK = True
+        torch.backends.cudnn.deterministic = False
+
+
+def test_reference_style_loop_and_training_reduces_loss():
+    t, opt = _make_trainer(False, seed=7)
+    losses = []
+    for i in range(30):
+        opt.zero_grad()
+        t.train(1)
+        t.update_model()
+        if i % 10 == 9:
+            t.flush_metrics()
+            losses.append(t.loss)
+    assert losses[-1] < losses[0]
+    opt.check_errors()
+    opt.close()
+
+
+def test_checkpoint_roundtrip(tmp_path):
+    t, opt = _make_trainer(False, seed=3)
+    for _ in range(3):
+        t.train_and_update()
+    fn = t.save_checkpoint(filename=str(tmp_path / "ck.pth"))
+    ref = torch.load(fn, weights_only=False)
+    assert {"iter", "epoch", "state"} <= set(ref)          # the reference's keys (dl_trainer.py:651)
+    assert "gk_extra" in ref and ref["gk_extra"]["residual"].abs().sum() > 0
+    t2, opt2 = _make_trainer(False, seed=99)
+    t2.load_model_from_file(fn)
+    t2.restore_optimizer_state()
+    for (_, a), (_, b) in zip(t.net.state_dict().items(), t2.net.state_dict().items()):
+        assert torch.equal(a, b)
+    assert torch.equal(opt._resid, opt2._resid)
+    opt.close(); opt2.close()
+
+
+# --------------------------------------------------------------------------- multi GPU
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, transport, comp, q):
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    hvd.init()
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(rank)
+    model = nn.Sequential(nn.Linear(64, 512), nn.ReLU(), nn.Linear(512, 512), nn.ReLU(), nn.Linear(512, 10)).to(dev)
+    base = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9)
+    opt = hvd.DistributedOptimizer(base, named_parameters=model.named_parameters(), compression=compressors[comp],
+                                   is_sparse=True, density=0.01, threshold=524288000, dynamic_densities=None,
+                                   transport=transport)
+    hvd.broadcast_parameters(model.state_dict(), root_rank=0)
+    g = torch.Generator().manual_seed(1000 + rank)
+    x, y = torch.randn(32, 64, generator=g).to(dev), torch.randint(0, 10, (32,), generator=g).to(dev)
+    for _ in range(6):
+        opt.zero_grad()
+        nn.functional.cross_entropy(model(x), y).backward()
+        opt.step()
+    torch.cuda.synchronize()
+    opt.check_errors()
+    flat = torch.cat([p.detach().reshape(-1) for p in model.parameters()]).cpu().numpy().copy()
+    q.put((rank, flat, opt._groups[0].transport.name, getattr(opt._groups[0].transport, "backend", "")))
+    hvd.barrier()
+    opt.close()
+    hvd.shutdown()
+
+
+def _run_world(world, transport, comp):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, transport, comp, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=300) for _ in procs], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    return res
+
+
+@pytest.mark.multigpu
+@pytest.mark.parametrize("comp", ["gaussian", "topk"])
+def test_p2p_transport_equals_nccl_allgather(comp):
+    world = min(torch.cuda.device_count(), 8)
+    p2p = _run_world(world, "p2p", comp)
+    ag = _run_world(world, "allgather", comp)
+    assert p2p[0][2] == "p2p" and ag[0][2] == "allgather"
+    import numpy as np
+    for r in range(world):
+        assert np.array_equal(p2p[r][1], p2p[0][1])          # replicas identical
+    # same selection, same mean; only the float add order of >= 3 colliding contributions may differ
+    assert np.allclose(p2p[0][1], ag[0][1], rtol=1e-5, atol=1e-6)
