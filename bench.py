@@ -177,19 +177,31 @@ def run_ours(args):
 
     # ---- sparse path alone (compress + exchange + receive + zero), eager, CUDA events
     g0 = opt._groups[0]
-    opt._arena.grad.normal_(0, 1e-3)
+    sel = opt.selected_num_gradients()
+    grad_saved = torch.randn_like(opt._arena.grad) * 1e-3
+    resid_saved = opt._resid.clone()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(20)]
 
     def sparse_only():
-        for _ in range(20):
+        for e0, e1 in ev:
+            opt._arena.grad.copy_(grad_saved)      # a fresh gradient for every measured exchange
+            opt._resid.copy_(resid_saved)
+            e0.record()
             g0.chain.compress(transport.dst())
             transport.exchange()
             ch.scatter(transport.src(), g0.chain.ctrl, opt._arena.grad, 1.0 / world)
+            ch.unscatter(transport.src(), g0.chain.ctrl, opt._arena.grad)
+            e1.record()
     sparse_only()
-    ms_sparse = _event_time_ms(sparse_only, device) / 20.0
+    _event_time_ms(sparse_only, device)
+    ms_sparse = statistics.median(a.elapsed_time(b) for a, b in ev)
+    if world > 1:
+        t = torch.tensor([ms_sparse], dtype=torch.float64, device=device)
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        ms_sparse = float(t.item())
     n_elem = g0.chain.n_total
     peaks = measured_peaks()
     chain_bytes = 24.0 * n_elem            # K1 16 B/elem (grad+resid read, acc+zero write), K2 4, K3 4
-    sel = opt.selected_num_gradients()
     result = None
     if rank == 0:
         imgs = BATCH_PER_GPU * world * args.steps

@@ -20,12 +20,14 @@
 //     The receive kernel acquires those headers (bounded spin) and scatter-adds from local HBM.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../include/gk_b200.h"
 
 #define T GK_THREADS
 #define NWARP (GK_THREADS / 32)
+#define GK_SUB (NWARP * 1024)  /* elements per sub-tile: every warp owns a contiguous 1024-element slice */
 
 // ----------------------------------------------------------------------------- helpers
 __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
@@ -46,11 +48,7 @@ __device__ __forceinline__ float warp_max(float v) {
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
 }
-__device__ __forceinline__ uint32_t warp_sum_u(uint32_t v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
+__device__ __forceinline__ uint32_t warp_sum_u(uint32_t v) { return __reduce_add_sync(0xffffffffu, v); }
 __device__ __forceinline__ uint32_t warp_incl_scan_u(uint32_t v, int lane) {
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -62,11 +60,13 @@ __device__ __forceinline__ uint32_t warp_incl_scan_u(uint32_t v, int lane) {
 
 // Ticket taken by every block when its global writes are done; true in the last block.
 // The ticket word resets itself so the same control block serves every launch.
-__device__ __forceinline__ bool last_block_done(uint32_t* ticket) {
+__device__ __forceinline__ bool last_block_done(uint32_t* ticket, bool system_scope = false) {
   __shared__ int s_last;
-  __threadfence();
+  // bar.sync makes the block's writes visible to thread 0; its (cumulative) fence then orders them
+  // before the ticket for every observer — one fence per block instead of one per thread.
   __syncthreads();
   if (threadIdx.x == 0) {
+    if (system_scope) __threadfence_system(); else __threadfence();
     uint32_t t = atomicAdd(ticket, 1u);
     s_last = (t == gridDim.x - 1);
     if (s_last) *ticket = 0;
@@ -90,6 +90,14 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
   return t;
 }
 
+// 0xffffffff if a > b else 0 (one FSET; masks are then subtracted / and-ed, which is cheaper than the
+// compare + select + add sequence the compiler emits for `cnt += (a > b)`)
+__device__ __forceinline__ uint32_t gt_mask(float a, float b) {
+  uint32_t m;
+  asm("set.gt.u32.f32 %0, %1, %2;" : "=r"(m) : "f"(a), "f"(b));
+  return m;
+}
+
 // Magnitude key used by the radix select: larger key = selected first.
 template <bool MINK>
 __device__ __forceinline__ uint32_t sel_key(float x) {
@@ -104,61 +112,106 @@ __device__ __forceinline__ int tri_idx(int a, int b) { return (a + b) * (a + b +
 // Epilogue of K1, run by the last block: per-segment moments (fixed-order warp reduction of
 // the per-block partials => deterministic), then the candidate thresholds of the counting
 // pass, or the first radix digit for top-k.
+// Leader work of the K1 epilogue for one segment: moments -> stat, candidate thresholds.
+__device__ void k1_finish_segment(const GkChain& c, int s, const GkSeg& sg, double sum, double sq, double sa, float mx) {
+  GkSegStat* st = c.stat + s;
+  for (int j = 0; j < GK_NC; ++j) st->tot[j] = 0;
+  const double n = (double)sg.n;
+  const double mean = sum / n;
+  double var = (sg.n > 1) ? (sq - sum * mean) / (n - 1.0) : 0.0;  // unbiased, like torch.std
+  if (var < 0) var = 0;
+  // the reference converts the fp32 tensors mean/std to python floats (compression.py:367-369)
+  const float meanf = (float)mean, stdf = (float)sqrt(var);
+  const float meanabs = (float)(sa / n);
+  st->mean = meanf; st->std = stdf; st->meanabs = meanabs; st->maxabs = mx;
+  if (c.mode == GK_MODE_GAUSSIAN) {
+    // right_thres = mu + |z| sigma in double (utils.py:136-138); the loop multiplies by
+    // 0.5 (exact) or 1.5 in double, the comparison rounds the threshold to fp32.
+    const double t0 = (double)meanf + sg.zabs * (double)stdf;
+    const int L = c.nloops;
+    double t15 = t0;
+    for (int b = 0; b < L; ++b) {
+      double t = t15;
+      for (int a = 0; a + b < L; ++a) {
+        st->cand[tri_idx(a, b)] = (float)t;
+        t *= 0.5;
+      }
+      t15 *= 1.5;
+    }
+  } else if (c.mode == GK_MODE_REDSYNC) {
+    // thres = mean|x| + ratio*(max|x| - mean|x|) in fp32 (compression.py:653-662); the
+    // bisection of [0,1] visits a 3-level binary tree of ratios (heap order).
+    const float d = __fsub_rn(mx, meanabs);
+    const float ratios[7] = {0.5f, 0.25f, 0.75f, 0.125f, 0.375f, 0.625f, 0.875f};
+    for (int j = 0; j < 7; ++j) st->cand[j] = __fadd_rn(meanabs, __fmul_rn(ratios[j], d));
+  } else if (c.mode == GK_MODE_REDSYNCTRIM) {
+    const float d = __fsub_rn(mx, meanabs);
+    double r = 1.0 - 0.2;  // compression.py:711-712
+    for (int j = 0; j < GK_NC; ++j) {
+      st->cand[j] = __fadd_rn(meanabs, __fmul_rn((float)r, d));
+      r = r - 0.2;
+    }
+  } else if (c.mode == GK_MODE_THRESHOLD) {
+    st->cand[0] = sg.param;
+  }
+  if (c.mode == GK_MODE_TOPK || c.mode == GK_MODE_MINK) {
+    c.stat[s].prefix = 0; c.stat[s].krem = (uint32_t)sg.k;
+  } else {
+    // Sorted candidate order for the counting pass.  Candidates far in the tail ("high") are only
+    // evaluated in rows where the row maximum exceeds the smallest of them; the split is a speed
+    // heuristic (about 1 % expected exceedance), the counts are exact either way.
+    const int nc = (c.mode == GK_MODE_GAUSSIAN) ? c.nloops * (c.nloops + 1) / 2
+                 : (c.mode == GK_MODE_REDSYNC) ? 7 : (c.mode == GK_MODE_REDSYNCTRIM) ? GK_NC : 1;
+    uint8_t ord[GK_NC];
+    for (int j = 0; j < GK_NC; ++j) ord[j] = (uint8_t)j;
+    for (int j = 1; j < nc; ++j) {          // insertion sort, <= 16 items
+      const uint8_t key = ord[j];
+      const float kv = st->cand[key];
+      int i = j - 1;
+      while (i >= 0 && st->cand[ord[i]] > kv) { ord[i + 1] = ord[i]; --i; }
+      ord[i + 1] = key;
+    }
+    const float gate = (c.mode == GK_MODE_GAUSSIAN) ? fabsf(meanf) + 2.5f * stdf : 3.2f * meanabs;
+    int nlow = 0;
+    while (nlow < nc && !(st->cand[ord[nlow]] > gate)) ++nlow;
+    if (c.mode == GK_MODE_THRESHOLD) nlow = 1;
+    for (int j = 0; j < GK_NC; ++j) st->order[j] = ord[j];
+    st->nlow = nlow;
+  }
+}
+
+// Segments with at least this many table entries are reduced by the whole block, smaller ones by one warp.
+#define GK_BIG_SEG 256
+
 __device__ void k1_epilogue(const GkChain& c) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int s = warp; s < c.nseg; s += NWARP) {
+  __shared__ double s_red[3][NWARP];
+  __shared__ float s_mx[NWARP];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int s = 0; s < c.nseg; ++s) {
     const GkSeg sg = c.seg[s];
+    const bool big = (sg.blk_end - sg.blk_begin) >= GK_BIG_SEG;   // uniform over the block
+    if (!big && (s % NWARP) != warp) continue;
+    const int first = big ? tid : lane, step = big ? T : 32;
     double sum = 0, sq = 0, sa = 0;
     float mx = 0.f;
-    for (int b = sg.blk_begin + lane; b < sg.blk_end; b += 32) {
+#pragma unroll 4
+    for (int b = sg.blk_begin + first; b < sg.blk_end; b += step) {
       const double2 p0 = __ldcg(reinterpret_cast<const double2*>(c.part + 4 * (size_t)b));
       const double2 p1 = __ldcg(reinterpret_cast<const double2*>(c.part + 4 * (size_t)b + 2));
       sum += p0.x; sq += p0.y; sa += p1.x; mx = fmaxf(mx, (float)p1.y);
     }
     sum = warp_sum(sum); sq = warp_sum(sq); sa = warp_sum(sa); mx = warp_max(mx);
-    if (lane == 0) {
-      GkSegStat* st = c.stat + s;
-      const double n = (double)sg.n;
-      const double mean = sum / n;
-      double var = (sg.n > 1) ? (sq - sum * mean) / (n - 1.0) : 0.0;  // unbiased, like torch.std
-      if (var < 0) var = 0;
-      // the reference converts the fp32 tensors mean/std to python floats (compression.py:367-369)
-      const float meanf = (float)mean, stdf = (float)sqrt(var);
-      const float meanabs = (float)(sa / n);
-      st->mean = meanf; st->std = stdf; st->meanabs = meanabs; st->maxabs = mx;
-      if (c.mode == GK_MODE_GAUSSIAN) {
-        // right_thres = mu + |z| sigma in double (utils.py:136-138); the loop multiplies by
-        // 0.5 (exact) or 1.5 in double, the comparison rounds the threshold to fp32.
-        const double t0 = (double)meanf + sg.zabs * (double)stdf;
-        const int L = c.nloops;
-        double t15 = t0;
-        for (int b = 0; b < L; ++b) {
-          double t = t15;
-          for (int a = 0; a + b < L; ++a) {
-            st->cand[tri_idx(a, b)] = (float)t;
-            t *= 0.5;
-          }
-          t15 *= 1.5;
-        }
-      } else if (c.mode == GK_MODE_REDSYNC) {
-        // thres = mean|x| + ratio*(max|x| - mean|x|) in fp32 (compression.py:653-662); the
-        // bisection of [0,1] visits a 3-level binary tree of ratios (heap order).
-        const float d = __fsub_rn(mx, meanabs);
-        const float ratios[7] = {0.5f, 0.25f, 0.75f, 0.125f, 0.375f, 0.625f, 0.875f};
-        for (int j = 0; j < 7; ++j) st->cand[j] = __fadd_rn(meanabs, __fmul_rn(ratios[j], d));
-      } else if (c.mode == GK_MODE_REDSYNCTRIM) {
-        const float d = __fsub_rn(mx, meanabs);
-        double r = 1.0 - 0.2;  // compression.py:711-712
-        for (int j = 0; j < GK_NC; ++j) {
-          st->cand[j] = __fadd_rn(meanabs, __fmul_rn((float)r, d));
-          r = r - 0.2;
-        }
-      } else if (c.mode == GK_MODE_THRESHOLD) {
-        st->cand[0] = sg.param;
+    if (big) {
+      if (lane == 0) { s_red[0][warp] = sum; s_red[1][warp] = sq; s_red[2][warp] = sa; s_mx[warp] = mx; }
+      __syncthreads();
+      if (tid == 0) {
+        sum = sq = sa = 0; mx = 0.f;
+        for (int w = 0; w < NWARP; ++w) { sum += s_red[0][w]; sq += s_red[1][w]; sa += s_red[2][w]; mx = fmaxf(mx, s_mx[w]); }
+        k1_finish_segment(c, s, sg, sum, sq, sa, mx);
       }
-    }
-    if (c.mode == GK_MODE_TOPK || c.mode == GK_MODE_MINK) {
-      if (lane == 0) { c.stat[s].prefix = 0; c.stat[s].krem = (uint32_t)sg.k; }
+      __syncthreads();
+    } else if (lane == 0) {
+      k1_finish_segment(c, s, sg, sum, sq, sa, mx);
     }
   }
 }
@@ -201,67 +254,85 @@ __device__ void radix_pick_warp(const GkChain& c, int s, int shift, int nbins, i
   for (int j = lane; j < nbins; j += 32) h[j] = 0;
 }
 
+// Persistent: a CUDA block walks the table entries blockIdx.x, blockIdx.x + gridDim.x, ... and keeps
+// its partial moments in registers for as long as consecutive entries belong to the same segment (a
+// "run"); only the last entry of a run pays for the block reduction, the others record zeros.  In the
+// merged-buffer mode (one segment) that is one reduction and one ticket per block.
 template <bool HIST, bool MINK>
 __global__ void __launch_bounds__(GK_THREADS) k_accumulate(GkChain c) {
   __shared__ uint32_t shist[HIST ? GK_HIST_BINS : 1];
   __shared__ double sred[3][NWARP];
   __shared__ float smax[NWARP];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const GkBlk B = c.blk[blockIdx.x];
   if (HIST) {
     for (int i = tid; i < GK_HIST_BINS; i += T) shist[i] = 0;
     __syncthreads();
   }
-  const float* __restrict__ g = c.grad + B.start;
-  float* __restrict__ r = c.resid + B.start;
   const bool user = c.use_residual != 0, zg = c.zero_grad != 0;
-  double s = 0, q = 0, sa = 0;
-  float mx = 0.f;
-  const int n4 = B.len >> 2;
   const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 4
-  for (int i = tid; i < n4; i += T) {
-    float4 x = ld4_stream(g + 4 * i);
-    if (user) {
-      const float4 rv = ld4_stream(r + 4 * i);
-      x.x += rv.x; x.y += rv.y; x.z += rv.z; x.w += rv.w;
+  double ds = 0, dq = 0, da = 0;   // this thread's share of the current run
+  float mx = 0.f;
+  for (int eidx = blockIdx.x; eidx < c.nblk; eidx += gridDim.x) {
+    const GkBlk B = c.blk[eidx];
+    const int enext = eidx + gridDim.x;
+    const bool last_of_run = (enext >= c.nblk) || (c.blk[enext].seg != B.seg);   // block-uniform
+    const float* __restrict__ g = c.grad + B.start;
+    float* __restrict__ r = c.resid + B.start;
+    // fp32 partials over one entry (<= chunk/256 elements per thread), fp64 across entries
+    float s = 0.f, q = 0.f, sa = 0.f;
+    const int n4 = B.len >> 2;
+    if (tid < GK_NC) c.bcnt[(size_t)eidx * GK_NC + tid] = 0;   // the counting pass accumulates with atomics
+#pragma unroll 2
+    for (int i = tid; i < n4; i += T) {
+      float4 x = ld4_stream(g + 4 * i);
+      if (user) {
+        const float4 rv = ld4_stream(r + 4 * i);
+        x.x += rv.x; x.y += rv.y; x.z += rv.z; x.w += rv.w;
+      }
+      st4(r + 4 * i, x);  // acc: default policy so that it can stay in L2 for the following passes
+      if (zg) st4_stream(const_cast<float*>(g) + 4 * i, z4);
+      s += (x.x + x.y) + (x.z + x.w);
+      q = fmaf(x.x, x.x, q); q = fmaf(x.y, x.y, q); q = fmaf(x.z, x.z, q); q = fmaf(x.w, x.w, q);
+      const float ax = fabsf(x.x), ay = fabsf(x.y), az = fabsf(x.z), aw = fabsf(x.w);
+      sa += (ax + ay) + (az + aw);
+      mx = fmaxf(fmaxf(mx, fmaxf(ax, ay)), fmaxf(az, aw));
+      if (HIST) {
+        atomicAdd(&shist[sel_key<MINK>(x.x) >> 20], 1u); atomicAdd(&shist[sel_key<MINK>(x.y) >> 20], 1u);
+        atomicAdd(&shist[sel_key<MINK>(x.z) >> 20], 1u); atomicAdd(&shist[sel_key<MINK>(x.w) >> 20], 1u);
+      }
     }
-    st4(r + 4 * i, x);  // acc stays in L2 for the following passes
-    if (zg) st4_stream(const_cast<float*>(g) + 4 * i, z4);
-    const float e[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const double xd = (double)e[j];
-      s += xd; q = fma(xd, xd, q); sa += fabs(xd);
-      mx = fmaxf(mx, fabsf(e[j]));
-      if (HIST) atomicAdd(&shist[sel_key<MINK>(e[j]) >> 20], 1u);
+    for (int i = 4 * n4 + tid; i < B.len; i += T) {  // tail of a tensor whose size % 4 != 0
+      float x = g[i];
+      if (user) x += r[i];
+      r[i] = x;
+      if (zg) const_cast<float*>(g)[i] = 0.f;
+      s += x; q = fmaf(x, x, q); sa += fabsf(x);
+      mx = fmaxf(mx, fabsf(x));
+      if (HIST) atomicAdd(&shist[sel_key<MINK>(x) >> 20], 1u);
     }
-  }
-  for (int i = 4 * n4 + tid; i < B.len; i += T) {  // tail of a tensor whose size % 4 != 0
-    float x = g[i];
-    if (user) x += r[i];
-    r[i] = x;
-    if (zg) const_cast<float*>(g)[i] = 0.f;
-    const double xd = (double)x;
-    s += xd; q = fma(xd, xd, q); sa += fabs(xd);
-    mx = fmaxf(mx, fabsf(x));
-    if (HIST) atomicAdd(&shist[sel_key<MINK>(x) >> 20], 1u);
-  }
-  s = warp_sum(s); q = warp_sum(q); sa = warp_sum(sa); mx = warp_max(mx);
-  if (lane == 0) { sred[0][warp] = s; sred[1][warp] = q; sred[2][warp] = sa; smax[warp] = mx; }
-  __syncthreads();
-  if (tid == 0) {
-    double a = 0, b = 0, d = 0; float m = 0.f;
-    for (int w = 0; w < NWARP; ++w) { a += sred[0][w]; b += sred[1][w]; d += sred[2][w]; m = fmaxf(m, smax[w]); }
-    double* p = c.part + 4 * (size_t)blockIdx.x;
-    p[0] = a; p[1] = b; p[2] = d; p[3] = (double)m;
-  }
-  if (HIST) {
-    uint32_t* h = c.hist + (size_t)B.seg * GK_HIST_BINS;
-    for (int i = tid; i < GK_HIST_BINS; i += T) {
-      const uint32_t v = shist[i];
-      if (v) atomicAdd(h + i, v);
+    ds += (double)s; dq += (double)q; da += (double)sa;
+    double* p = c.part + 4 * (size_t)eidx;
+    if (!last_of_run) {
+      if (tid == 0) { p[0] = 0; p[1] = 0; p[2] = 0; p[3] = 0; }
+      continue;
     }
+    ds = warp_sum(ds); dq = warp_sum(dq); da = warp_sum(da); mx = warp_max(mx);
+    if (lane == 0) { sred[0][warp] = ds; sred[1][warp] = dq; sred[2][warp] = da; smax[warp] = mx; }
+    __syncthreads();
+    if (tid == 0) {
+      double a = 0, b = 0, d = 0; float m = 0.f;
+      for (int w = 0; w < NWARP; ++w) { a += sred[0][w]; b += sred[1][w]; d += sred[2][w]; m = fmaxf(m, smax[w]); }
+      p[0] = a; p[1] = b; p[2] = d; p[3] = (double)m;
+    }
+    if (HIST) {
+      uint32_t* h = c.hist + (size_t)B.seg * GK_HIST_BINS;
+      for (int i = tid; i < GK_HIST_BINS; i += T) {
+        const uint32_t v = shist[i];
+        if (v) { atomicAdd(h + i, v); shist[i] = 0; }
+      }
+    }
+    ds = dq = da = 0; mx = 0.f;
+    __syncthreads();   // sred / shist are reused by the next run
   }
   if (last_block_done(&c.ctrl->done[0])) {
     k1_epilogue(c);
@@ -283,7 +354,7 @@ __global__ void __launch_bounds__(GK_THREADS) k_radix_pass(GkChain c) {
   __shared__ uint32_t shist[NB];
   __shared__ int s_any;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const GkBlk B = c.blk[blockIdx.x];
+  const GkBlk B = c.blk[(PASS == 2) ? (c.nblk - 1 - (int)blockIdx.x) : (int)blockIdx.x];  // zig-zag
   for (int i = tid; i < NB; i += T) shist[i] = 0;
   if (tid == 0) s_any = 0;
   __syncthreads();
@@ -333,88 +404,81 @@ __global__ void __launch_bounds__(GK_THREADS) k_radix_pass(GkChain c) {
 // ----------------------------------------------------------------- K2 counting + decisions
 // Epilogue shared by the threshold-count pass and the (gt,eq) pass: per-segment totals, the
 // reference's refinement loop replayed on the device, then the prefix sums K3 needs.
+// Leader work of the K2 epilogue for one segment: replay the reference's refinement loop on the
+// per-candidate totals and record the decision.
+__device__ void k2_decide_segment(const GkChain& c, int s, const GkSeg& sg, const uint32_t* tot, bool topk) {
+  GkSegStat* st = c.stat + s;
+  const double k = (double)sg.k;
+  int chosen = 0;
+  uint32_t count = 0;
+  if (topk) {
+    const uint32_t ties = st->ties;
+    count = tot[0] + (tot[1] < ties ? tot[1] : ties);
+  } else {
+    if (c.mode == GK_MODE_GAUSSIAN) {
+      // compression.py:372-381: at most nloops evaluations; the indexes returned are those of the
+      // LAST EVALUATED threshold.
+      int a = 0, b = 0;
+      for (int loop = 0; loop < c.nloops; ++loop) {
+        chosen = tri_idx(a, b);
+        const double cnt = (double)tot[chosen];
+        if (cnt < 2.0 * k / 3.0) ++a;
+        else if (cnt > 4.0 * k / 3.0) ++b;
+        else break;
+      }
+    } else if (c.mode == GK_MODE_REDSYNC) {
+      // compression.py:653-672
+      double l = 0.0, r = 1.0;
+      int node = 0;
+      while (r - l > 0.2) {
+        const double mid = l + (r - l) / 2;
+        chosen = node;
+        const double nnz = (double)tot[node];
+        if (nnz > k && 2.0 * k > nnz) break;
+        else if (nnz < k / 2.0) { r = mid; node = 2 * node + 1; }
+        else { l = mid; node = 2 * node + 2; }
+        if (node >= 7) break;
+      }
+    } else if (c.mode == GK_MODE_REDSYNCTRIM) {
+      // compression.py:719-732: lower the ratio until at least k survive
+      chosen = GK_NC - 1;
+      for (int j = 0; j < GK_NC; ++j)
+        if ((double)tot[j] >= k) { chosen = j; break; }
+    }
+    count = tot[chosen];
+    st->thr = st->cand[chosen];
+    st->ties = 0;
+  }
+  st->chosen = chosen;
+  st->count = count;
+}
+
+// Epilogue shared by the threshold-count pass and the (gt,eq) pass: per-segment totals, the
+// reference's refinement loop replayed on the device, then the prefix sums K3 needs.
 __device__ void k2_epilogue(const GkChain& c, bool topk) {
   __shared__ uint32_t sscan[2][T];
-  __shared__ uint32_t stot[NWARP][GK_NC];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  // phase 1: warp per segment
-  for (int s = warp; s < c.nseg; s += NWARP) {
+  const bool dbg = (c.rsv & 4) != 0;
+  if (dbg && tid == 0) c.ctrl->ring[40] = (uint32_t)globaltimer_ns();
+  // phase 1: the counting pass already accumulated the per-candidate totals of every segment with
+  // atomics (stat.tot); one thread per segment replays the refinement loop.  Thread t owns segments
+  // [t*per, (t+1)*per) in phases 1 and 2, so nothing is read back from global memory in between.
+  __shared__ int s_chosen0;
+  const int sper = (c.nseg + T - 1) / T;
+  const int s0 = tid * sper, s1 = min(c.nseg, s0 + sper);
+  uint32_t loc = 0;
+  for (int s = s0; s < s1; ++s) {
     const GkSeg sg = c.seg[s];
-    GkSegStat* st = c.stat + s;
     uint32_t tot[GK_NC];
 #pragma unroll
-    for (int j = 0; j < GK_NC; ++j) tot[j] = 0;
-    for (int b = sg.blk_begin + lane; b < sg.blk_end; b += 32) {
-      const uint4* p = reinterpret_cast<const uint4*>(c.bcnt + (size_t)b * GK_NC);
-#pragma unroll
-      for (int v = 0; v < GK_NC / 4; ++v) {
-        const uint4 u = __ldcg(p + v);
-        tot[4 * v] += u.x; tot[4 * v + 1] += u.y; tot[4 * v + 2] += u.z; tot[4 * v + 3] += u.w;
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < GK_NC; ++j) {
-      const uint32_t w = warp_sum_u(tot[j]);
-      if (lane == 0) stot[warp][j] = w;
-    }
-    __syncwarp();
-    if (lane == 0) {
-      const uint32_t* tot = stot[warp];
-      const double k = (double)sg.k;
-      int chosen = 0;
-      uint32_t count = 0;
-      if (topk) {
-        const uint32_t ties = st->ties;
-        count = tot[0] + (tot[1] < ties ? tot[1] : ties);
-      } else {
-        if (c.mode == GK_MODE_GAUSSIAN) {
-          // compression.py:372-381: at most nloops evaluations; the indexes returned are
-          // those of the LAST EVALUATED threshold.
-          int a = 0, b = 0;
-          for (int loop = 0; loop < c.nloops; ++loop) {
-            chosen = tri_idx(a, b);
-            const double cnt = (double)tot[chosen];
-            if (cnt < 2.0 * k / 3.0) ++a;
-            else if (cnt > 4.0 * k / 3.0) ++b;
-            else break;
-          }
-        } else if (c.mode == GK_MODE_REDSYNC) {
-          // compression.py:653-672
-          double l = 0.0, r = 1.0;
-          int node = 0;
-          while (r - l > 0.2) {
-            const double mid = l + (r - l) / 2;
-            chosen = node;
-            const double nnz = (double)tot[node];
-            if (nnz > k && 2.0 * k > nnz) break;
-            else if (nnz < k / 2.0) { r = mid; node = 2 * node + 1; }
-            else { l = mid; node = 2 * node + 2; }
-            if (node >= 7) break;
-          }
-        } else if (c.mode == GK_MODE_REDSYNCTRIM) {
-          // compression.py:719-732: lower the ratio until at least k survive
-          chosen = GK_NC - 1;
-          for (int j = 0; j < GK_NC; ++j)
-            if ((double)tot[j] >= k) { chosen = j; break; }
-        } else {
-          chosen = 0;
-        }
-        count = tot[chosen];
-        st->thr = st->cand[chosen];
-        st->ties = 0;
-      }
-      st->chosen = chosen;
-      st->count = count;
-    }
+    for (int j = 0; j < GK_NC; ++j) tot[j] = __ldcg(&c.stat[s].tot[j]);   // 4-byte aligned only
+    k2_decide_segment(c, s, sg, tot, topk);
+    loc += c.stat[s].count;
+    if (s == 0) s_chosen0 = c.stat[s].chosen;
   }
-  __syncthreads();
-  __threadfence_block();
+  if (dbg && tid == 0) c.ctrl->ring[41] = (uint32_t)globaltimer_ns();
   // phase 2: exclusive scan of the per-segment counts -> out_base; total
   {
-    const int per = (c.nseg + T - 1) / T;
-    const int s0 = tid * per, s1 = min(c.nseg, s0 + per);
-    uint32_t loc = 0;
-    for (int s = s0; s < s1; ++s) loc += c.stat[s].count;
     sscan[0][tid] = loc;
     __syncthreads();
     if (warp == 0) {
@@ -436,16 +500,50 @@ __device__ void k2_epilogue(const GkChain& c, bool topk) {
     }
   }
   __syncthreads();
-  // phase 3: global exclusive scans over the blocks of (gt, eq); K3 subtracts the value at the
-  // first block of its segment to make them segment-relative.
+  if (dbg && tid == 0) c.ctrl->ring[42] = (uint32_t)globaltimer_ns();
+  // phase 3: global exclusive scans over the table entries of (gt, eq); K3 subtracts the value at the
+  // first entry of its segment to make them segment-relative.  Each thread owns a contiguous run of
+  // entries whose counts stay in registers between the two sweeps when the run is short.
   {
     const int per = (c.nblk + T - 1) / T;
     const int b0 = tid * per, b1 = min(c.nblk, b0 + per);
+    const bool one_seg = c.nseg == 1;
+    const int ch0 = topk ? 0 : s_chosen0;
+    constexpr int KEEP = 16;
+    uint32_t vg[KEEP], ve[KEEP];
     uint32_t lg = 0, le = 0;
-    for (int b = b0; b < b1; ++b) {
-      const int ch = topk ? 0 : c.stat[c.blk[b].seg].chosen;
-      lg += __ldcg(c.bcnt + (size_t)b * GK_NC + ch);
-      if (topk) le += __ldcg(c.bcnt + (size_t)b * GK_NC + 1);
+    if (per <= KEEP) {
+      // all loads are issued unconditionally on clamped indices (one round trip instead of `per`
+      // serialised ones: a bounds check in front of each load would stop the compiler from batching them)
+      int chs[KEEP];
+#pragma unroll
+      for (int i = 0; i < KEEP; ++i) {
+        const int b = min(b0 + i, c.nblk - 1);
+        chs[i] = (topk || one_seg) ? ch0 : c.blk[b].seg;
+      }
+      if (!(topk || one_seg)) {
+#pragma unroll
+        for (int i = 0; i < KEEP; ++i) chs[i] = c.stat[chs[i]].chosen;
+      }
+#pragma unroll
+      for (int i = 0; i < KEEP; ++i) {
+        const int b = min(b0 + i, c.nblk - 1);
+        vg[i] = __ldcg(c.bcnt + (size_t)b * GK_NC + chs[i]);
+        ve[i] = topk ? __ldcg(c.bcnt + (size_t)b * GK_NC + 1) : 0u;
+      }
+#pragma unroll
+      for (int i = 0; i < KEEP; ++i) {
+        const bool in = (i < per) && (b0 + i < b1);
+        vg[i] = in ? vg[i] : 0u;
+        ve[i] = in ? ve[i] : 0u;
+        lg += vg[i]; le += ve[i];
+      }
+    } else {
+      for (int b = b0; b < b1; ++b) {
+        const int ch = topk ? 0 : (one_seg ? ch0 : c.stat[c.blk[b].seg].chosen);
+        lg += __ldcg(c.bcnt + (size_t)b * GK_NC + ch);
+        if (topk) le += __ldcg(c.bcnt + (size_t)b * GK_NC + 1);
+      }
     }
     sscan[0][tid] = lg; sscan[1][tid] = le;
     __syncthreads();
@@ -460,179 +558,312 @@ __device__ void k2_epilogue(const GkChain& c, bool topk) {
     }
     __syncthreads();
     uint32_t rg = sscan[0][tid], re = sscan[1][tid];
-    for (int b = b0; b < b1; ++b) {
-      const int ch = topk ? 0 : c.stat[c.blk[b].seg].chosen;
-      c.boff[2 * (size_t)b] = rg;
-      c.boff[2 * (size_t)b + 1] = re;
-      rg += __ldcg(c.bcnt + (size_t)b * GK_NC + ch);
-      if (topk) re += __ldcg(c.bcnt + (size_t)b * GK_NC + 1);
+    if (per <= KEEP) {
+#pragma unroll
+      for (int i = 0; i < KEEP; ++i) {
+        const int b = b0 + i;
+        if (i < per && b < b1) {
+          *reinterpret_cast<uint2*>(c.boff + 2 * (size_t)b) = make_uint2(rg, re);
+          rg += vg[i]; re += ve[i];
+        }
+      }
+    } else {
+      for (int b = b0; b < b1; ++b) {
+        const int ch = topk ? 0 : (one_seg ? ch0 : c.stat[c.blk[b].seg].chosen);
+        c.boff[2 * (size_t)b] = rg;
+        c.boff[2 * (size_t)b + 1] = re;
+        rg += __ldcg(c.bcnt + (size_t)b * GK_NC + ch);
+        if (topk) re += __ldcg(c.bcnt + (size_t)b * GK_NC + 1);
+      }
     }
   }
+  __syncthreads();
+  if (dbg && tid == 0) c.ctrl->ring[43] = (uint32_t)globaltimer_ns();
 }
 
-// Count |acc| > cand[j] for all candidates of the block's segment in one read of acc.
+// Persistent and barrier-free: a block walks the table entries (backwards, see below); inside an entry
+// every warp owns a contiguous 1024-element slice per 8192-element sub-tile, counts its slice in
+// registers and adds its (non-zero) per-candidate counts to the entry's row of bcnt with integer atomics
+// (K1 zeroed the rows).  Integer adds commute, so the result is deterministic.
 template <int NCAND>
 __global__ void __launch_bounds__(GK_THREADS) k_count(GkChain c) {
-  __shared__ float scand[GK_NC];
-  __shared__ uint32_t swc[NWARP][GK_NC];
+  constexpr bool SKIP_ROWS = NCAND > 6;   // gaussian (<= 6 candidates): the smallest is exceeded in every row
+  constexpr int NLOW = (NCAND + 1) / 2;    // candidates evaluated unconditionally
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const GkBlk B = c.blk[blockIdx.x];
-  if (tid < GK_NC) scand[tid] = c.stat[B.seg].cand[tid];
+  int cur_seg = -1;
+  float cs[NCAND];        // candidates of the current segment in ascending order
+  uint32_t ord[NCAND];    // their original indices
+#pragma unroll
+  for (int j = 0; j < NCAND; ++j) { cs[j] = 0.f; ord[j] = j; }
+  __shared__ uint32_t s_tot[GK_NC];
+  if (tid < GK_NC) s_tot[tid] = 0;
+  if ((c.rsv & 4) && blockIdx.x == 0 && tid == 0) c.ctrl->ring[44] = (uint32_t)globaltimer_ns();
   __syncthreads();
-  float cand[NCAND];
-  uint32_t cnt[NCAND];
+  uint32_t run[NCAND];     // this lane's counts since the last flush (current segment)
 #pragma unroll
-  for (int j = 0; j < NCAND; ++j) { cand[j] = scand[j]; cnt[j] = 0; }
-  const float* __restrict__ a = c.resid + B.start;
-  const int n4 = B.len >> 2;
-#pragma unroll 4
-  for (int i = tid; i < n4; i += T) {
-    const float4 x = ld4(a + 4 * i);
-    const float e[4] = {fabsf(x.x), fabsf(x.y), fabsf(x.z), fabsf(x.w)};
+  for (int j = 0; j < NCAND; ++j) run[j] = 0;
+  for (int it = blockIdx.x; it < c.nblk; it += gridDim.x) {
+    // zig-zag: K1 walked the arena forwards, so its tail is what is still in L2 -> walk backwards here
+    const int eidx = c.nblk - 1 - it;
+    const GkBlk B = c.blk[eidx];
+    if (B.seg != cur_seg) {   // block-uniform
+      if (cur_seg >= 0) {     // segment change inside a block (multi-segment tables): flush straight to global
 #pragma unroll
-    for (int j = 0; j < NCAND; ++j)
-      cnt[j] += (uint32_t)(e[0] > cand[j]) + (uint32_t)(e[1] > cand[j]) + (uint32_t)(e[2] > cand[j]) +
-                (uint32_t)(e[3] > cand[j]);
+        for (int j = 0; j < NCAND; ++j) {
+          const uint32_t w = warp_sum_u(run[j]);
+          if (lane == 0 && w) atomicAdd(&c.stat[cur_seg].tot[ord[j]], w);
+          run[j] = 0;
+        }
+      }
+      cur_seg = B.seg;
+      const GkSegStat* st = c.stat + B.seg;
+#pragma unroll
+      for (int j = 0; j < NCAND; ++j) { ord[j] = st->order[j]; cs[j] = st->cand[ord[j]]; }
+    }
+    uint32_t cnt[NCAND];
+#pragma unroll
+    for (int j = 0; j < NCAND; ++j) cnt[j] = 0;
+    const float* __restrict__ a = c.resid + B.start;
+    for (int t0 = 0; t0 < B.len; t0 += GK_SUB) {
+      const int wbeg = t0 + warp * 1024;
+      if (wbeg >= B.len) break;          // warp-uniform
+      if (wbeg + 1024 <= B.len) {        // warp-uniform fast path: a full 1024-element slice
+        const float* __restrict__ aw = a + wbeg + lane * 4;
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          float4 v[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) v[i] = ld4(aw + (half * 4 + i) * 128);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float e0 = fabsf(v[i].x), e1 = fabsf(v[i].y), e2 = fabsf(v[i].z), e3 = fabsf(v[i].w);
+            // Candidates are sorted ascending.  The lower half is evaluated for every element; the upper
+            // half (far-tail thresholds) only in rows where some lane exceeds the smallest of them — one
+            // row maximum + vote instead of 4 compares per candidate.  Exact either way.
+            const float m = fmaxf(fmaxf(e0, e1), fmaxf(e2, e3));
+            if (SKIP_ROWS && !__any_sync(0xffffffffu, m > cs[0])) continue;
+#pragma unroll
+            for (int j = 0; j < NLOW; ++j)
+              cnt[j] -= (gt_mask(e0, cs[j]) + gt_mask(e1, cs[j])) + (gt_mask(e2, cs[j]) + gt_mask(e3, cs[j]));
+            if (NLOW < NCAND && __any_sync(0xffffffffu, m > cs[NLOW < NCAND ? NLOW : 0])) {
+#pragma unroll
+              for (int j = NLOW; j < NCAND; ++j)
+                cnt[j] -= (gt_mask(e0, cs[j]) + gt_mask(e1, cs[j])) + (gt_mask(e2, cs[j]) + gt_mask(e3, cs[j]));
+            }
+          }
+        }
+      } else {                            // ragged end of a tensor: plain scalar loop
+        const int wend = min(wbeg + 1024, B.len);
+        for (int i = wbeg + lane; i < wend; i += 32) {
+          const float x = fabsf(a[i]);
+#pragma unroll
+          for (int j = 0; j < NCAND; ++j) cnt[j] += (uint32_t)(x > cs[j]);
+        }
+      }
+    }
+    uint32_t* row = c.bcnt + (size_t)eidx * GK_NC;
+#pragma unroll
+    for (int j = 0; j < NCAND; ++j) {
+      run[j] += cnt[j];
+      const uint32_t w = warp_sum_u(cnt[j]);
+      if (lane == 0 && w) atomicAdd(row + ord[j], w);
+    }
   }
-  for (int i = 4 * n4 + tid; i < B.len; i += T) {
-    const float v = fabsf(a[i]);
+  // segment totals: lanes -> warp (REDUX) -> block (smem atomics) -> one global atomic per candidate and block
+  if (cur_seg >= 0) {
 #pragma unroll
-    for (int j = 0; j < NCAND; ++j) cnt[j] += (uint32_t)(v > cand[j]);
-  }
-#pragma unroll
-  for (int j = 0; j < NCAND; ++j) {
-    const uint32_t w = warp_sum_u(cnt[j]);
-    if (lane == 0) swc[warp][j] = w;
+    for (int j = 0; j < NCAND; ++j) {
+      const uint32_t w = warp_sum_u(run[j]);
+      if (lane == 0 && w) atomicAdd(&s_tot[ord[j]], w);
+    }
   }
   __syncthreads();
-  if (tid < GK_NC) {
-    uint32_t tot = 0;
-    if (tid < NCAND)
-      for (int w = 0; w < NWARP; ++w) tot += swc[w][tid];
-    c.bcnt[(size_t)blockIdx.x * GK_NC + tid] = tot;
-  }
+  if (tid < GK_NC && cur_seg >= 0 && s_tot[tid]) atomicAdd(&c.stat[cur_seg].tot[tid], s_tot[tid]);
+  if (c.rsv & 1) return;   // experiment switch (tools/bench_chain.py): skip the epilogue
+  if ((c.rsv & 4) && tid == 0) atomicMax(&c.ctrl->ring[45], (uint32_t)globaltimer_ns());
   if (last_block_done(&c.ctrl->done[2])) k2_epilogue(c, false);
 }
 
 // top-k: per-block counts of key > T (column 0) and key == T (column 1)
 template <bool MINK>
 __global__ void __launch_bounds__(GK_THREADS) k_count_topk(GkChain c) {
-  __shared__ uint32_t swc[NWARP][2];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const GkBlk B = c.blk[blockIdx.x];
-  const uint32_t tb = c.stat[B.seg].tbits;
-  uint32_t gt = 0, eq = 0;
-  const float* __restrict__ a = c.resid + B.start;
-  const int n4 = B.len >> 2;
-#pragma unroll 4
-  for (int i = tid; i < n4; i += T) {
-    const float4 x = ld4(a + 4 * i);
-    const float e[4] = {x.x, x.y, x.z, x.w};
+  for (int it = blockIdx.x; it < c.nblk; it += gridDim.x) {
+    const int eidx = c.nblk - 1 - it;  // zig-zag (see k_count)
+    const GkBlk B = c.blk[eidx];
+    const uint32_t tb = c.stat[B.seg].tbits;
+    uint32_t gt = 0, eq = 0;
+    const float* __restrict__ a = c.resid + B.start;
+    for (int t0 = 0; t0 < B.len; t0 += GK_SUB) {
+      const int wbeg = t0 + warp * 1024;
+      if (wbeg >= B.len) break;
+      if (wbeg + 1024 <= B.len) {
+        float4 v[8];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const uint32_t key = sel_key<MINK>(e[j]);
-      gt += (uint32_t)(key > tb);
-      eq += (uint32_t)(key == tb);
+        for (int i = 0; i < 8; ++i) v[i] = ld4(a + wbeg + (i * 32 + lane) * 4);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float e[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t key = sel_key<MINK>(e[j]);
+            gt += (uint32_t)(key > tb);
+            eq += (uint32_t)(key == tb);
+          }
+        }
+      } else {
+        for (int i = wbeg + lane; i < min(wbeg + 1024, B.len); i += 32) {
+          const uint32_t key = sel_key<MINK>(a[i]);
+          gt += (uint32_t)(key > tb);
+          eq += (uint32_t)(key == tb);
+        }
+      }
     }
-  }
-  for (int i = 4 * n4 + tid; i < B.len; i += T) {
-    const uint32_t key = sel_key<MINK>(a[i]);
-    gt += (uint32_t)(key > tb);
-    eq += (uint32_t)(key == tb);
-  }
-  gt = warp_sum_u(gt); eq = warp_sum_u(eq);
-  if (lane == 0) { swc[warp][0] = gt; swc[warp][1] = eq; }
-  __syncthreads();
-  if (tid < GK_NC) {
-    uint32_t tot = 0;
-    if (tid < 2)
-      for (int w = 0; w < NWARP; ++w) tot += swc[w][tid];
-    c.bcnt[(size_t)blockIdx.x * GK_NC + tid] = tot;
+    gt = warp_sum_u(gt); eq = warp_sum_u(eq);
+    uint32_t* row = c.bcnt + (size_t)eidx * GK_NC;
+    if (lane == 0) {
+      if (gt) { atomicAdd(row, gt); atomicAdd(&c.stat[B.seg].tot[0], gt); }
+      if (eq) { atomicAdd(row + 1, eq); atomicAdd(&c.stat[B.seg].tot[1], eq); }
+    }
   }
   if (last_block_done(&c.ctrl->done[2])) k2_epilogue(c, true);
 }
 
 // ------------------------------------------------------- K3 select + compact + residual + send
+// Every warp owns a contiguous 1024-element slice of the block's 8192-element sub-tile and keeps it
+// in registers (8 float4 per lane).  One block-level exchange of the per-warp counts gives every warp
+// its output base; inside a warp the order is recovered with ballots, and only for the (rare) float4
+// rows that contain a selected element.  One __syncthreads per sub-tile, no per-row scans.
+
 template <bool TOPK, bool MINK>
 __global__ void __launch_bounds__(GK_THREADS) k_compact_send(GkChain c, GkDst d) {
-  __shared__ uint32_t swarp[NWARP];
-  __shared__ uint32_t s_tile_total;
+  __shared__ uint32_t s_wcnt[2][NWARP];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int b = blockIdx.x;
+  const uint32_t seqn = c.ctrl->seq + 1u;  // every block reads it before the last block bumps it
+  const uint64_t poff = (uint64_t)(seqn & 1u) * d.parity_stride;
+  const uint32_t cap = c.cap;
+  const uint32_t lt = (1u << lane) - 1u;
+  int par = 0;
+  for (int b = blockIdx.x; b < c.nblk; b += gridDim.x) {   // persistent over the table entries
   const GkBlk B = c.blk[b];
   const GkSegStat* st = c.stat + B.seg;
   const float thr = st->thr;
   const uint32_t tb = st->tbits, ties = st->ties;
   const uint32_t seg_first = (uint32_t)c.seg[B.seg].blk_begin;
-  const uint32_t base_gt = st->out_base + (c.boff[2 * (size_t)b] - c.boff[2 * (size_t)seg_first]);
-  const uint32_t base_eq = TOPK ? (c.boff[2 * (size_t)b + 1] - c.boff[2 * (size_t)seg_first + 1]) : 0u;
-  const uint32_t seqn = c.ctrl->seq + 1u;  // every block reads it before the last block bumps it
-  const uint64_t poff = (uint64_t)(seqn & 1u) * d.parity_stride;
-  const uint32_t cap = c.cap;
+  const uint2 off_b = *reinterpret_cast<const uint2*>(c.boff + 2 * (size_t)b);
+  const uint2 off_s = *reinterpret_cast<const uint2*>(c.boff + 2 * (size_t)seg_first);
+  const uint32_t base_gt = st->out_base + (off_b.x - off_s.x);
+  const uint32_t base_eq = TOPK ? (off_b.y - off_s.y) : 0u;
   float* __restrict__ a = c.resid + B.start;
-  uint32_t run_gt = 0, run_eq = 0;  // selected before the current tile, inside this block
-  bool wrote = false;
-  const int ntile = (B.len + 4 * T - 1) / (4 * T);
-  for (int t = 0; t < ntile; ++t) {
-    const int i0 = t * 4 * T + tid * 4;
-    float e[4];
-    if (i0 + 3 < B.len) {
-      const float4 x = ld4(a + i0);
-      e[0] = x.x; e[1] = x.y; e[2] = x.z; e[3] = x.w;
+  uint32_t run_gt = 0, run_eq = 0;  // selected before the current sub-tile, inside this entry
+  for (int t0 = 0; t0 < B.len; t0 += GK_SUB, par ^= 1) {
+    const int wbeg = t0 + warp * 1024;
+    float4 v[8];
+    uint32_t fg = 0, fe = 0;  // bit 4*i+j: element j of row i is gt / eq
+    if (wbeg + 1024 <= B.len) {  // warp-uniform fast path: the whole slice is in range
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = ld4(a + wbeg + (i * 32 + lane) * 4);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float e[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (TOPK) {
+            const uint32_t key = sel_key<MINK>(e[j]);
+            if (key > tb) fg |= 1u << (4 * i + j);
+            if (key == tb) fe |= 1u << (4 * i + j);
+          } else {
+            fg |= gt_mask(fabsf(e[j]), thr) & (1u << (4 * i + j));
+          }
+        }
+      }
     } else {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) e[j] = (i0 + j < B.len) ? a[i0 + j] : 0.f;
-    }
-    uint32_t fg = 0, fe = 0;  // bit j set: element j is gt / eq
+      for (int i = 0; i < 8; ++i) {
+        const int i0 = wbeg + (i * 32 + lane) * 4;
+        if (i0 + 3 < B.len) {
+          v[i] = ld4(a + i0);
+        } else {
+          v[i].x = (i0 < B.len) ? a[i0] : 0.f;
+          v[i].y = (i0 + 1 < B.len) ? a[i0 + 1] : 0.f;
+          v[i].z = (i0 + 2 < B.len) ? a[i0 + 2] : 0.f;
+          v[i].w = 0.f;
+        }
+        const float e[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const bool valid = (i0 + j) < B.len;
-      if (TOPK) {
-        const uint32_t key = sel_key<MINK>(e[j]);
-        if (valid && key > tb) fg |= 1u << j;
-        if (valid && key == tb) fe |= 1u << j;
-      } else {
-        if (valid && fabsf(e[j]) > thr) fg |= 1u << j;
+        for (int j = 0; j < 4; ++j) {
+          const bool valid = (i0 + j) < B.len;
+          if (TOPK) {
+            const uint32_t key = sel_key<MINK>(e[j]);
+            if (valid && key > tb) fg |= 1u << (4 * i + j);
+            if (valid && key == tb) fe |= 1u << (4 * i + j);
+          } else {
+            if (valid && fabsf(e[j]) > thr) fg |= 1u << (4 * i + j);
+          }
+        }
       }
     }
-    const uint32_t mine = (uint32_t)__popc(fg) | ((uint32_t)__popc(fe) << 16);
-    const uint32_t inc = warp_incl_scan_u(mine, lane);
-    if (lane == 31) swarp[warp] = inc;
+    const uint32_t wsum = warp_sum_u((uint32_t)__popc(fg) | ((uint32_t)__popc(fe) << 16));
+    if (lane == 0) s_wcnt[par][warp] = wsum;
     __syncthreads();
     uint32_t wbase = 0, total = 0;
 #pragma unroll
     for (int w = 0; w < NWARP; ++w) {
-      const uint32_t v = swarp[w];
-      if (w < warp) wbase += v;
-      total += v;
+      const uint32_t x = s_wcnt[par][w];
+      if (w < warp) wbase += x;
+      total += x;
     }
-    if (mine) {
-      const uint32_t excl = wbase + inc - mine;
-      uint32_t gbefore = run_gt + (excl & 0xffffu);
-      uint32_t ebefore = base_eq + run_eq + (excl >> 16);
+    if (wsum != 0) {  // warp-uniform
+      uint32_t gb = run_gt + (wbase & 0xffffu);            // gt elements before the current row
+      uint32_t eb = base_eq + run_eq + (wbase >> 16);      // eq elements before the current row (segment-wide)
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const bool isg = (fg >> j) & 1u, ise = (fe >> j) & 1u;
-        if (isg || (ise && ebefore < ties)) {
-          const uint32_t pos = base_gt + gbefore + (ebefore < ties ? ebefore : ties);
-          if (pos < cap) {
-            const uint32_t idx = (uint32_t)(B.start + i0 + j);
-            const uint64_t pair = (uint64_t)idx | ((uint64_t)__float_as_uint(e[j]) << 32);
-            for (int q = 0; q < d.ndst; ++q) d.slot[q][poff + GK_SLOT_HDR + pos] = pair;
-            a[i0 + j] = 0.f;  // sent => leaves the residual
-            wrote = true;
+      for (int i = 0; i < 8; ++i) {
+        const uint32_t fgi = (fg >> (4 * i)) & 15u, fei = (fe >> (4 * i)) & 15u;
+        if (__ballot_sync(0xffffffffu, (fgi | fei) != 0u) == 0u) continue;  // warp-uniform
+        uint32_t gbefore = gb, ebefore = eb, tg = 0, te = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          // lanes hold 4 consecutive elements each: everything in lower lanes precedes this lane
+          const uint32_t bg = __ballot_sync(0xffffffffu, (fgi >> j) & 1u);
+          gbefore += __popc(bg & lt);
+          tg += __popc(bg);
+          if (TOPK) {
+            const uint32_t be = __ballot_sync(0xffffffffu, (fei >> j) & 1u);
+            ebefore += __popc(be & lt);
+            te += __popc(be);
           }
         }
-        gbefore += isg ? 1u : 0u;
-        ebefore += ise ? 1u : 0u;
+        if (fgi | fei) {
+          const int i0 = wbeg + (i * 32 + lane) * 4;
+          const float e[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const bool isg = (fgi >> j) & 1u, ise = (fei >> j) & 1u;
+            if (isg || (ise && ebefore < ties)) {
+              const uint32_t pos = base_gt + gbefore + (ebefore < ties ? ebefore : ties);
+              if (pos < cap) {
+                const uint32_t idx = (uint32_t)(B.start + i0 + j);
+                const uint64_t pair = (uint64_t)idx | ((uint64_t)__float_as_uint(e[j]) << 32);
+                for (int q = 0; q < d.ndst; ++q) d.slot[q][poff + GK_SLOT_HDR + pos] = pair;
+                a[i0 + j] = 0.f;  // sent => leaves the residual
+              }
+            }
+            gbefore += isg ? 1u : 0u;
+            ebefore += ise ? 1u : 0u;
+          }
+        }
+        gb += tg;
+        eb += te;
       }
     }
     run_gt += total & 0xffffu;
     run_eq += total >> 16;
-    __syncthreads();
   }
-  (void)s_tile_total;
-  if (wrote) __threadfence_system();  // pairs visible to the peers before the ticket
+  }  // entries
+  // Every block: bar.sync + one gpu-scope fence by thread 0 + ticket.  The last block then issues ONE
+  // system-scope fence before the release store of the header: fences are cumulative, so the pairs the
+  // other blocks stored to peer memory (ordered before their tickets at gpu scope) are ordered before
+  // the header at system scope (same pattern as NCCL's barrier + single-thread fence before a post).
   if (last_block_done(&c.ctrl->done[3])) {
     if (tid == 0) {
       const uint32_t total = c.ctrl->total;
@@ -872,7 +1103,6 @@ __global__ void __launch_bounds__(GK_THREADS) k_randomk(GkChain c, GkDst d, uint
   // grid-stride over all (segment, j) outputs; GkSeg.aux holds the prefix sum of k (out base)
   const uint32_t seqn = c.ctrl->seq + 1u;
   const uint64_t poff = (uint64_t)(seqn & 1u) * d.parity_stride;
-  bool wrote = false;
   for (int s = 0; s < c.nseg; ++s) {
     const GkSeg sg = c.seg[s];
     for (uint32_t j = blockIdx.x * T + threadIdx.x; j < (uint32_t)sg.k; j += gridDim.x * T) {
@@ -892,11 +1122,9 @@ __global__ void __launch_bounds__(GK_THREADS) k_randomk(GkChain c, GkDst d, uint
         const uint64_t pair = (uint64_t)idx | ((uint64_t)__float_as_uint(v) << 32);
         for (int q = 0; q < d.ndst; ++q) d.slot[q][poff + GK_SLOT_HDR + pos] = pair;
         c.resid[idx] = 0.f;
-        wrote = true;
       }
     }
   }
-  if (wrote) __threadfence_system();
   if (last_block_done(&c.ctrl->done[3])) {
     if (threadIdx.x == 0) {
       uint32_t total = 0;
@@ -988,6 +1216,31 @@ __global__ void __launch_bounds__(GK_THREADS) k_histogram(const float* __restric
 
 // =========================================================================== host entry points
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// Exactly one resident wave for a persistent kernel: SM count x the occupancy the runtime reports for
+// that kernel (148 SMs on a B200).  Queried once per kernel and process; no allocation involved.
+template <typename K>
+static int gk_persistent_grid(K kernel, int* cache, int nblk) {
+  if (*cache == 0) {
+    int dev = 0, sms = 148, per = 4;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, kernel, T, 0) != cudaSuccess || per < 1) per = 4;
+    const char* env = getenv("GK_BLOCKS_PER_SM");
+    if (env && atoi(env) > 0 && atoi(env) < per) per = atoi(env);
+    *cache = sms * per;
+  }
+  if (nblk <= *cache) return nblk;
+  // every block gets the same number of table entries (+-1 at the very end): with ~4 entries per block a
+  // plain "one resident wave" grid leaves some blocks with 25 % more work than others
+  const int per_block = (nblk + *cache - 1) / *cache;
+  return (nblk + per_block - 1) / per_block;
+}
+#define GK_LAUNCH_PERSISTENT(kernel, nblk, stream, ...)                         \
+  do {                                                                          \
+    static int cache_ = 0;                                                      \
+    const int grid_ = gk_persistent_grid(kernel, &cache_, nblk);                \
+    kernel<<<grid_, T, 0, S(stream)>>>(__VA_ARGS__);                            \
+  } while (0)
 #define GK_RET() return (int)cudaGetLastError()
 
 extern "C" {
@@ -996,9 +1249,9 @@ const char* gk_version(void) { return "gk_b200 cuda sm_100a 0.1"; }
 
 int gk_accumulate(const GkChain* c, void* stream) {
   if (c->nblk <= 0) return 0;
-  if (c->mode == GK_MODE_TOPK) k_accumulate<true, false><<<c->nblk, T, 0, S(stream)>>>(*c);
-  else if (c->mode == GK_MODE_MINK) k_accumulate<true, true><<<c->nblk, T, 0, S(stream)>>>(*c);
-  else k_accumulate<false, false><<<c->nblk, T, 0, S(stream)>>>(*c);
+  if (c->mode == GK_MODE_TOPK) GK_LAUNCH_PERSISTENT((k_accumulate<true, false>), c->nblk, stream, *c);
+  else if (c->mode == GK_MODE_MINK) GK_LAUNCH_PERSISTENT((k_accumulate<true, true>), c->nblk, stream, *c);
+  else GK_LAUNCH_PERSISTENT((k_accumulate<false, false>), c->nblk, stream, *c);
   GK_RET();
 }
 
@@ -1008,10 +1261,10 @@ int gk_count_pick(const GkChain* c, void* stream) {
   if (c->mode == GK_MODE_GAUSSIAN) nc = c->nloops * (c->nloops + 1) / 2;
   else if (c->mode == GK_MODE_REDSYNC) nc = 7;
   else if (c->mode == GK_MODE_REDSYNCTRIM) nc = GK_NC;
-  if (nc <= 1) k_count<1><<<c->nblk, T, 0, S(stream)>>>(*c);
-  else if (nc <= 6) k_count<6><<<c->nblk, T, 0, S(stream)>>>(*c);
-  else if (nc <= 7) k_count<7><<<c->nblk, T, 0, S(stream)>>>(*c);
-  else k_count<GK_NC><<<c->nblk, T, 0, S(stream)>>>(*c);
+  if (nc <= 1) GK_LAUNCH_PERSISTENT(k_count<1>, c->nblk, stream, *c);
+  else if (nc <= 6) GK_LAUNCH_PERSISTENT(k_count<6>, c->nblk, stream, *c);
+  else if (nc <= 7) GK_LAUNCH_PERSISTENT(k_count<7>, c->nblk, stream, *c);
+  else GK_LAUNCH_PERSISTENT(k_count<GK_NC>, c->nblk, stream, *c);
   GK_RET();
 }
 
@@ -1020,11 +1273,11 @@ int gk_topk_select(const GkChain* c, void* stream) {
   if (c->mode == GK_MODE_MINK) {
     k_radix_pass<2, true><<<c->nblk, T, 0, S(stream)>>>(*c);
     k_radix_pass<3, true><<<c->nblk, T, 0, S(stream)>>>(*c);
-    k_count_topk<true><<<c->nblk, T, 0, S(stream)>>>(*c);
+    GK_LAUNCH_PERSISTENT(k_count_topk<true>, c->nblk, stream, *c);
   } else {
     k_radix_pass<2, false><<<c->nblk, T, 0, S(stream)>>>(*c);
     k_radix_pass<3, false><<<c->nblk, T, 0, S(stream)>>>(*c);
-    k_count_topk<false><<<c->nblk, T, 0, S(stream)>>>(*c);
+    GK_LAUNCH_PERSISTENT(k_count_topk<false>, c->nblk, stream, *c);
   }
   GK_RET();
 }
@@ -1032,9 +1285,9 @@ int gk_topk_select(const GkChain* c, void* stream) {
 int gk_compact_send(const GkChain* c, const GkDst* dst, void* stream) {
   if (c->nblk <= 0) return 0;
   if (dst->ndst < 1 || dst->ndst > GK_MAXP) return (int)cudaErrorInvalidValue;
-  if (c->mode == GK_MODE_TOPK) k_compact_send<true, false><<<c->nblk, T, 0, S(stream)>>>(*c, *dst);
-  else if (c->mode == GK_MODE_MINK) k_compact_send<true, true><<<c->nblk, T, 0, S(stream)>>>(*c, *dst);
-  else k_compact_send<false, false><<<c->nblk, T, 0, S(stream)>>>(*c, *dst);
+  if (c->mode == GK_MODE_TOPK) GK_LAUNCH_PERSISTENT((k_compact_send<true, false>), c->nblk, stream, *c, *dst);
+  else if (c->mode == GK_MODE_MINK) GK_LAUNCH_PERSISTENT((k_compact_send<true, true>), c->nblk, stream, *c, *dst);
+  else GK_LAUNCH_PERSISTENT((k_compact_send<false, false>), c->nblk, stream, *c, *dst);
   GK_RET();
 }
 

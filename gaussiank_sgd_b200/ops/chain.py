@@ -24,13 +24,14 @@ SEG_DTYPE = np.dtype([("n", "<i4"), ("k", "<i4"), ("blk_begin", "<i4"), ("blk_en
 STAT_DTYPE = np.dtype([("mean", "<f4"), ("std", "<f4"), ("meanabs", "<f4"), ("maxabs", "<f4"),
                        ("cand", "<f4", (N.GK_NC,)), ("thr", "<f4"), ("tbits", "<u4"), ("ties", "<u4"),
                        ("chosen", "<i4"), ("count", "<u4"), ("out_base", "<u4"), ("prefix", "<u4"),
-                       ("krem", "<u4")])
+                       ("krem", "<u4"), ("order", "u1", (N.GK_NC,)), ("nlow", "<i4"),
+                       ("tot", "<u4", (N.GK_NC,))])
 CTRL_DTYPE = np.dtype([("done", "<u4", (8,)), ("total", "<u4"), ("sent", "<u4"), ("seq", "<u4"),
                        ("err", "<u4"), ("overflow", "<u4"), ("rsv", "<u4", (3,)), ("sent_total", "<u8"),
                        ("ring", "<u4", (64,))])
 HYPER_DTYPE = np.dtype([("lr", "<f4"), ("momentum", "<f4"), ("dampening", "<f4"), ("weight_decay", "<f4"),
                         ("nesterov", "<i4"), ("first_step", "<i4"), ("lars_eeta", "<f4"), ("lars_eps", "<f4")])
-assert SEG_DTYPE.itemsize == 32 and STAT_DTYPE.itemsize == 112 and CTRL_DTYPE.itemsize == 328
+assert SEG_DTYPE.itemsize == 32 and STAT_DTYPE.itemsize == 196 and CTRL_DTYPE.itemsize == 328
 assert HYPER_DTYPE.itemsize == 32
 
 DEFAULT_CHUNK = 8192
@@ -180,10 +181,11 @@ class CompressChain:
         self.density = None
         dmax = max(density, max_density or density)
         if cap is None:
-            # receive-slot capacity: 4x the largest k this run can ask for;
-            # pairs beyond it stay in the residual (error feedback keeps them)
+            # receive-slot capacity: 8x the largest k this run can ask for (the
+            # gaussian estimate selects up to ~10x k on skewed residuals); pairs beyond it stay in
+            # the residual (error feedback keeps them)
             kmax = sum(compute_k(int(n), dmax) for n in segs["n"])
-            cap = max(4 * kmax, 1024)
+            cap = max(8 * kmax, 1024)
             cap = min(cap, max(self.n_total, 1024))
         self.cap = int(cap)
         self.set_density(density)

@@ -43,7 +43,8 @@ class GkSegStat(C.Structure):
     _fields_ = [("mean", C.c_float), ("std", C.c_float), ("meanabs", C.c_float), ("maxabs", C.c_float),
                 ("cand", C.c_float * GK_NC), ("thr", C.c_float), ("tbits", C.c_uint32), ("ties", C.c_uint32),
                 ("chosen", C.c_int32), ("count", C.c_uint32), ("out_base", C.c_uint32),
-                ("prefix", C.c_uint32), ("krem", C.c_uint32)]
+                ("prefix", C.c_uint32), ("krem", C.c_uint32), ("order", C.c_uint8 * GK_NC), ("nlow", C.c_int32),
+                ("tot", C.c_uint32 * GK_NC)]
 
 
 class GkCtrl(C.Structure):
@@ -76,7 +77,7 @@ class GkHyper(C.Structure):
                 ("lars_eeta", C.c_float), ("lars_eps", C.c_float)]
 
 
-assert C.sizeof(GkBlk) == 16 and C.sizeof(GkSeg) == 32 and C.sizeof(GkSegStat) == 112
+assert C.sizeof(GkBlk) == 16 and C.sizeof(GkSeg) == 32 and C.sizeof(GkSegStat) == 196
 assert C.sizeof(GkCtrl) == 328 and C.sizeof(GkHyper) == 32
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

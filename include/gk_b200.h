@@ -70,6 +70,9 @@ typedef struct GkSegStat {
   uint32_t out_base;                /* first output position of this segment       */
   uint32_t prefix;                  /* radix-select: matched high bits so far      */
   uint32_t krem;                    /* radix-select: rank still to find            */
+  uint8_t order[GK_NC];             /* candidate indices sorted by ascending threshold */
+  int32_t nlow;                     /* number of sorted candidates below the "far tail" gate (diagnostic) */
+  uint32_t tot[GK_NC];              /* per-candidate totals of the counting pass (zeroed by K1's epilogue) */
 } GkSegStat;
 
 /* Chain-wide control block (device memory, zero-initialised once by the caller). */

@@ -25,7 +25,7 @@ def _data(n, seed, kind="normal"):
     if kind == "ties":
         return torch.randint(-3, 4, (n,), generator=g).float() * 0.25
     if kind == "laplace":
-        u = torch.rand(n, generator=g) - 0.5
+        u = (torch.rand(n, generator=g) - 0.5) * 0.9999
         return -0.01 * torch.sign(u) * torch.log1p(-2 * u.abs())
     raise KeyError(kind)
 
@@ -98,7 +98,7 @@ def test_repeated_calls_and_sequence_numbers():
     c = None
     G = torch.zeros(n, device=DEV)
     R = torch.zeros(n, device=DEV)
-    c = ch.CompressChain(G, R, [[(0, n)]], compressor="gaussian", density=0.001)
+    c = ch.CompressChain(G, R, [[(0, n)]], compressor="gaussian", density=0.001, cap=n)
     sb = ch.SlotBuffer(1, c.cap, DEV, parities=2)
     dst = ch.make_dst([sb.slot_ptr(0)], sb.parity_stride)
     r_ref = torch.zeros(n)

@@ -15,7 +15,7 @@ def _data(n, seed, kind="normal"):
     if kind == "normal":
         return torch.randn(n, generator=g) * 0.01
     if kind == "laplace":
-        u = torch.rand(n, generator=g) - 0.5
+        u = (torch.rand(n, generator=g) - 0.5) * 0.9999
         return -0.01 * torch.sign(u) * torch.log1p(-2 * u.abs())
     if kind == "shifted":
         return torch.randn(n, generator=g) * 0.01 + 0.005

@@ -1,0 +1,127 @@
+#!/usr/bin/env python
+"""Per-kernel timing of the sparsification chain and the fused optimizer on one GPU (CUDA events, L2
+flushed between iterations).  Prints achieved GB/s against MEASURED_PEAKS.json.
+
+    python tools/bench_chain.py [--n 25557032] [--comp gaussian] [--density 0.001] [--chunk 8192]
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from gaussiank_sgd_b200.ops import chain as ch  # noqa: E402
+from gaussiank_sgd_b200.utils.perf_model import measured_peaks  # noqa: E402
+
+
+def timed(fn, flush, iters=10, prep=None):
+    ts = []
+    for _ in range(iters):
+        if prep is not None:
+            prep()
+        if flush is not None:
+            flush.add_(1.0)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ts.sort()
+    return ts[len(ts) // 2], ts[0]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--n", type=int, default=25557032)
+    ap.add_argument("--comp", default="gaussian")
+    ap.add_argument("--density", type=float, default=0.001)
+    ap.add_argument("--chunk", type=int, default=ch.DEFAULT_CHUNK)
+    ap.add_argument("--segments", type=int, default=1)
+    ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--json", default=None)
+    a = ap.parse_args()
+    dev = "cuda"
+    n = a.n
+    total = (n + 63) // 64 * 64
+    G = torch.randn(total, device=dev) * 0.01
+    R = torch.randn(total, device=dev) * 0.003
+    P = torch.randn(total, device=dev)
+    M = torch.zeros(total, device=dev)
+    if a.segments == 1:
+        segs = [[(0, n)]]
+    else:
+        per = (n // a.segments) // 64 * 64
+        segs = [[(i * per, per)] for i in range(a.segments)]
+    c = ch.CompressChain(G, R, segs, compressor=a.comp, density=a.density, chunk=a.chunk)
+    sb = ch.SlotBuffer(1, c.cap, dev, parities=2)
+    dst = ch.make_dst([sb.slot_ptr(0)], sb.parity_stride)
+    tables = ch.FlatTables([(0, n)], [0], dev, chunk=a.chunk)
+    hyper = ch.make_hyper([{"lr": 0.01, "momentum": 0.875, "weight_decay": 6.1e-5}], dev, False).to(dev)
+    flush = None if a.no_flush else torch.zeros(64 * 1024 * 1024, device=dev)   # 256 MB > 126 MB L2
+    peaks = measured_peaks()
+    hbm = peaks["hbm_gbs"]
+    rows = []
+
+    G0, R0 = G.clone(), R.clone()
+
+    def restore():          # every timed call sees the same fresh gradient + residual
+        G.copy_(G0)
+        R.copy_(R0)
+
+    def report(name, fn, bytes_per_elem, prep=None):
+        if prep:
+            prep()
+        fn(); torch.cuda.synchronize()
+        med, best = timed(fn, flush, prep=prep)
+        gbs = bytes_per_elem * n / (med * 1e-3) / 1e9
+        rows.append({"kernel": name, "ms_median": round(med, 4), "ms_best": round(best, 4), "bytes_per_elem": bytes_per_elem,
+                     "gbs": round(gbs, 1), "frac_of_%s_hbm" % peaks["source"]: round(gbs / hbm, 3)})
+        print("%-28s %8.4f ms (best %8.4f)  %5.1f B/elem  %7.1f GB/s  %.3f of %s HBM" % (
+            name, med, best, bytes_per_elem, gbs, gbs / hbm, peaks["source"]))
+
+    topk = a.comp in ("topk", "mink")
+    def prep_k2():
+        restore(); c.accumulate()
+
+    def prep_k3():
+        restore(); c.accumulate()
+        c.topk_select() if topk else c.count_pick()
+
+    report("K1 accumulate+moments", c.accumulate, 16.0, prep=restore)
+    if topk:
+        report("K4 radix x2 + count(gt,eq)", c.topk_select, 12.0, prep=prep_k2)
+    else:
+        report("K2 count+pick", c.count_pick, 4.0, prep=prep_k2)
+    if os.environ.get("GK_EXPERIMENT"):
+        for flag, name in ((1, "K2 without epilogue"),):
+            c._desc.rsv = flag
+            report(name, c.count_pick, 4.0, prep=prep_k2)
+        c._desc.rsv = 4
+        prep_k2(); c.ctrl.view(torch.int32)[18 + 45] = 0; torch.cuda.synchronize()
+        c.count_pick(); torch.cuda.synchronize()
+        ring = c.read_ctrl()["ring"]
+        t = [ring[i] for i in range(40, 46)]
+        print("K2 timeline (ns, rel. to block 0 start): last block end %d, epilogue start %d, after phase1 %d, after phase2 %d, after phase3 %d" % (
+            (t[5] - t[4]) & 0xffffffff, (t[0] - t[4]) & 0xffffffff, (t[1] - t[4]) & 0xffffffff, (t[2] - t[4]) & 0xffffffff, (t[3] - t[4]) & 0xffffffff))
+        c._desc.rsv = 0
+    report("K3 compact+send", lambda: c.compact_send(dst), 4.0, prep=prep_k3)
+    report("chain (K1..K3)", lambda: c.compress(dst), 32.0 if topk else 24.0, prep=restore)
+    dense = torch.zeros(total, device=dev)
+    report("K5 scatter (recv)", lambda: ch.scatter(sb.src(), c.ctrl, dense, 1.0), 0.0)
+    report("unscatter (zero_grad)", lambda: ch.unscatter(sb.src(), c.ctrl, dense), 0.0)
+    report("K6 fused SGD", lambda: ch.sgd_step(P, G, M, tables, hyper), 20.0)
+    report("K8 grad norm", lambda: ch.grad_norm(G, tables, 1.0), 4.0)
+    report("memset (torch zero_)", lambda: G.zero_(), 4.0)
+    report("copy (torch, ref)", lambda: M.copy_(P), 8.0)
+    print("ctrl:", {k: v for k, v in c.read_ctrl().items() if k in ("total", "sent", "seq", "err")}, "k =", c.k_total)
+    if a.json:
+        with open(a.json, "w") as f:
+            json.dump({"n": n, "comp": a.comp, "density": a.density, "chunk": a.chunk, "segments": a.segments,
+                       "l2_flush": not a.no_flush, "peaks": peaks, "rows": rows}, f, indent=1)
+
+
+if __name__ == "__main__":
+    main()
