@@ -20,8 +20,11 @@
 //     The receive kernel acquires those headers (bounded spin) and scatter-adds from local HBM.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+
+#include <mutex>
 
 #include "../include/gk_b200.h"
 
@@ -1214,6 +1217,51 @@ __global__ void __launch_bounds__(GK_THREADS) k_histogram(const float* __restric
     if (sh[i]) atomicAdd(out + i, sh[i]);
 }
 
+// ---- gradient norm without caller-provided scratch -------------------------------------------
+// Some callers cannot hand in scratch and must not allocate it either: a host application that
+// carved up all device memory at start-up and links this library through the C ABI (it has no
+// allocator left to ask), a monitoring or abort path that has to work while the device is out of
+// memory, or code that runs while other streams are busy and therefore must avoid cudaMalloc /
+// cudaFree, which synchronise the whole device.  For them the per-block partial sums and the
+// last-block ticket of the norm kernel live in this fixed array instead.
+//   * capacity: GK_NOALLOC_MAX_BLOCKS table entries (16384 -> 134 M elements at the default 8192-element
+//     chunk); larger tables are rejected with GK_ERR_NOALLOC_TOO_LARGE and a message on stderr;
+//   * cost: sizeof(GkNoAllocScratch) = 128 KiB + one GkCtrl of device memory on EVERY GPU that loads
+//     the library, held until the process exits;
+//   * the array is shared by all calls and keeps the previous call's contents.  The partial sums are
+//     fully rewritten by each call; the ticket word must start at zero and is cleared on the stream
+//     before every launch.  Two calls that overlap on the GPU (different streams, or different host
+//     threads) race on it: callers must order them.
+#define GK_NOALLOC_MAX_DEVICES 64   /* GK_NOALLOC_MAX_BLOCKS, GK_ERR_NOALLOC_TOO_LARGE: include/gk_b200.h */
+
+struct GkNoAllocScratch {
+  double part[GK_NOALLOC_MAX_BLOCKS];
+  GkCtrl ctrl;
+};
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(GkNoAllocScratch)];
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not a device address; the address
+// each device uses is looked up once per device (with that device current) and cached here.
+static void* g_noalloc_addr[GK_NOALLOC_MAX_DEVICES];
+static std::mutex g_noalloc_mutex;
+
+static int gk_noalloc_scratch_ptr(GkNoAllocScratch** out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= GK_NOALLOC_MAX_DEVICES) return (int)cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (g_noalloc_addr[dev] == nullptr) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_noalloc_scratch);   // address of the array on the CURRENT device
+    if (e != cudaSuccess) return (int)e;
+    g_noalloc_addr[dev] = p;
+  }
+  *out = reinterpret_cast<GkNoAllocScratch*>(g_noalloc_addr[dev]);
+  return 0;
+}
+
 // =========================================================================== host entry points
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
@@ -1339,6 +1387,24 @@ int gk_grad_norm(const float* grad, const GkBlk* blk, int32_t nblk, double* part
                  GkCtrl* ctrl, void* stream) {
   if (nblk <= 0) return 0;
   k_grad_norm<<<nblk, T, 0, S(stream)>>>(grad, blk, nblk, part, max_norm, out, ctrl);
+  GK_RET();
+}
+
+int gk_grad_norm_static(const float* grad, const GkBlk* blk, int32_t nblk, float max_norm, float* out,
+                        void* stream) {
+  if (nblk <= 0) return 0;
+  if (nblk > GK_NOALLOC_MAX_BLOCKS) {
+    fprintf(stderr, "gk_grad_norm_static: table has %d entries, the built-in scratch holds %d "
+                    "(use gk_grad_norm with caller-provided scratch)\n", nblk, GK_NOALLOC_MAX_BLOCKS);
+    return GK_ERR_NOALLOC_TOO_LARGE;
+  }
+  GkNoAllocScratch* sc = nullptr;
+  const int err = gk_noalloc_scratch_ptr(&sc);   // first call on a device: symbol look-up
+  if (err) return err;
+  // the array still holds whatever the previous call left; only the ticket has to start at zero
+  cudaError_t e = cudaMemsetAsync(&sc->ctrl, 0, sizeof(GkCtrl), S(stream));
+  if (e != cudaSuccess) return (int)e;
+  k_grad_norm<<<nblk, T, 0, S(stream)>>>(grad, blk, nblk, sc->part, max_norm, out, &sc->ctrl);
   GK_RET();
 }
 

@@ -158,6 +158,7 @@ def cuda_lib():
             _proto(lib, "gk_sgd", [_P, _P, _P, _P, C.c_int32, _P, _P, _P])
             _proto(lib, "gk_lars", [_P, _P, _P, _P, C.c_int32, _P, C.c_int32, _P, _P, _P, _P, _P])
             _proto(lib, "gk_grad_norm", [_P, _P, C.c_int32, _P, C.c_float, _P, _P, _P])
+            _proto(lib, "gk_grad_norm_static", [_P, _P, C.c_int32, C.c_float, _P, _P])
             _proto(lib, "gk_scale", [_P, _P, C.c_int32, _P, _P])
             _proto(lib, "gk_randomk_send", [ch, ds, C.c_uint64, _P])
             _proto(lib, "gk_bucket_means", [ch, _P, _P])

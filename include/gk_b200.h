@@ -190,6 +190,28 @@ int gk_lars(float* param, const float* grad, float* mom, const GkBlk* blk, int32
 int gk_grad_norm(const float* grad, const GkBlk* blk, int32_t nblk, double* part, float max_norm,
                  float* out, GkCtrl* ctrl, void* stream);
 
+/* gk_grad_norm without caller-provided scratch.  (No counterpart in the reference: it exists for users
+ * of this C ABI, not for parity.)
+ * Same result as gk_grad_norm, but the per-block partial sums and the ticket live in a fixed
+ * `static __device__` array inside the library, so neither the caller nor the library allocates
+ * anything.  Meant for callers that cannot obtain scratch at call time: hosts that pre-carve all device
+ * memory and talk to this library through the C ABI only, monitoring / abort paths that must work when
+ * the device is out of memory, and code that must not call cudaMalloc/cudaFree because those
+ * synchronise the whole device while other streams are running.
+ *   - limit: at most GK_NOALLOC_MAX_BLOCKS = 16384 table entries (134 M elements at the default
+ *     8192-element chunk); a larger table returns GK_ERR_NOALLOC_TOO_LARGE (-2), prints a message to
+ *     stderr and launches nothing;
+ *   - cost: 128 KiB + sizeof(GkCtrl) of device memory on every GPU that loads the library, until exit;
+ *   - the first call on a device looks up the array's address (cudaGetSymbolAddress with that device
+ *     current) and caches it; make that first call before starting any stream capture;
+ *   - the array is shared by all calls and keeps the last call's contents; the ticket is cleared on
+ *     `stream` before each launch, the partials are fully rewritten.  Calls that overlap on the GPU
+ *     (other streams / threads) race on it — order them. */
+#define GK_NOALLOC_MAX_BLOCKS 16384
+#define GK_ERR_NOALLOC_TOO_LARGE (-2)
+int gk_grad_norm_static(const float* grad, const GkBlk* blk, int32_t nblk, float max_norm, float* out,
+                        void* stream);
+
 /* y[i] *= *scale over the blocks (materialised clipping). */
 int gk_scale(float* grad, const GkBlk* blk, int32_t nblk, const float* scale, void* stream);
 
