@@ -884,9 +884,13 @@ __global__ void __launch_bounds__(GK_THREADS) k_compact_send(GkChain c, GkDst d)
 }
 
 // ------------------------------------------------------------------------ K5 receive side
-template <bool UNSCATTER>
+// Slots [r_begin, r_end) are applied by one launch.  With ORDERED (one launch per source rank, issued in
+// rank order) every coordinate receives its contributions in the same order on every GPU, so all replicas
+// compute bit-identical averaged gradients no matter how the atomics of a single launch would have been
+// scheduled; inside one rank's list the indices are unique, so plain read-modify-writes suffice.
+template <bool UNSCATTER, bool ORDERED>
 __global__ void __launch_bounds__(GK_THREADS) k_scatter(GkSrc s, GkCtrl* ctrl, float* __restrict__ grad,
-                                                         float scale, int nelem) {
+                                                         float scale, int nelem, int r_begin, int r_end) {
   __shared__ uint32_t scnt[GK_MAXP];
   __shared__ int s_bad;
   const int tid = threadIdx.x;
@@ -895,7 +899,7 @@ __global__ void __launch_bounds__(GK_THREADS) k_scatter(GkSrc s, GkCtrl* ctrl, f
   const uint32_t cap = (uint32_t)(s.slot_stride - GK_SLOT_HDR);
   if (tid == 0) s_bad = 0;
   __syncthreads();
-  if (tid < s.nsrc) {
+  if (tid >= r_begin && tid < r_end) {
     const uint64_t* hp = base + (uint64_t)tid * s.slot_stride;
     uint64_t v = ld_acquire_sys_u64(hp);
     if (s.wait && !UNSCATTER) {
@@ -914,15 +918,18 @@ __global__ void __launch_bounds__(GK_THREADS) k_scatter(GkSrc s, GkCtrl* ctrl, f
     if (tid == 0) atomicExch(&ctrl->err, 1u);
     return;
   }
-  for (int r = 0; r < s.nsrc; ++r) {
+  if (!UNSCATTER && ctrl->err) return;   // an earlier slot of this exchange timed out: leave grad alone
+  for (int r = r_begin; r < r_end; ++r) {
     const uint64_t* pairs = base + (uint64_t)r * s.slot_stride + GK_SLOT_HDR;
     const uint32_t n = scnt[r];
     for (uint32_t j = blockIdx.x * T + tid; j < n; j += gridDim.x * T) {
       const uint64_t p = __ldcg(pairs + j);
       const uint32_t idx = (uint32_t)p;
       if (idx < (uint32_t)nelem) {
+        const float v = __uint_as_float((uint32_t)(p >> 32)) * scale;
         if (UNSCATTER) grad[idx] = 0.f;
-        else atomicAdd(grad + idx, __uint_as_float((uint32_t)(p >> 32)) * scale);
+        else if (ORDERED) grad[idx] += v;
+        else atomicAdd(grad + idx, v);
       }
     }
   }
@@ -1354,7 +1361,15 @@ int gk_scatter(const GkSrc* src, GkCtrl* ctrl, float* grad, float scale, int32_t
   int grid = (int)((cap + T - 1) / T);
   if (grid > 296) grid = 296;
   if (grid < 1) grid = 1;
-  k_scatter<false><<<grid, T, 0, S(stream)>>>(*src, ctrl, grad, scale, nelem);
+  if (src->nsrc <= 2) {
+    // 0 + a + b is the same in either order: one launch with atomics is already bit-reproducible
+    k_scatter<false, false><<<grid, T, 0, S(stream)>>>(*src, ctrl, grad, scale, nelem, 0, src->nsrc);
+  } else {
+    // three or more contributions per coordinate: fixed rank order, one (tiny) launch per source rank;
+    // launch r only waits for rank r's header, so early arrivals are applied while later ones are in flight
+    for (int r = 0; r < src->nsrc; ++r)
+      k_scatter<false, true><<<grid, T, 0, S(stream)>>>(*src, ctrl, grad, scale, nelem, r, r + 1);
+  }
   GK_RET();
 }
 
@@ -1364,7 +1379,7 @@ int gk_unscatter(const GkSrc* src, GkCtrl* ctrl, float* grad, int32_t nelem, voi
   int grid = (int)((cap + T - 1) / T);
   if (grid > 296) grid = 296;
   if (grid < 1) grid = 1;
-  k_scatter<true><<<grid, T, 0, S(stream)>>>(*src, ctrl, grad, 0.f, nelem);
+  k_scatter<true, false><<<grid, T, 0, S(stream)>>>(*src, ctrl, grad, 0.f, nelem, 0, src->nsrc);
   GK_RET();
 }
 

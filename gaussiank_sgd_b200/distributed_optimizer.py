@@ -401,6 +401,16 @@ class _DistributedOptimizer(torch.optim.Optimizer):
             ch.scale_(self._arena.grad, self._tables, out[1:2])
         return out
 
+    @property
+    def graph_safe(self) -> bool:
+        """True when a training step contains no host-issued collective, i.e. it can be captured in a
+        CUDA graph: the P2P / local transports communicate from inside the kernels."""
+        if not self._active:
+            return True
+        if not self._sparse:
+            return size() == 1
+        return all(g.transport is not None and g.transport.name in ("p2p", "local") for g in self._groups)
+
     def check_errors(self) -> None:
         """Host-side check of the device error flags (receive timeouts).  Synchronises."""
         for g in self._groups:

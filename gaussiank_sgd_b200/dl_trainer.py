@@ -739,7 +739,8 @@ class DLTrainer:
     def _run_step(self, staged, hidden, clip_norm):
         from .ops.chain import LAUNCHES
         use_graph = (self.is_cuda and settings.CUDA_GRAPH and self.dnn != 'lstman4'
-                     and getattr(self.optimizer, '_fused_kind', None) is not None)
+                     and getattr(self.optimizer, '_fused_kind', None) is not None
+                     and getattr(self.optimizer, 'graph_safe', False))
         n0 = LAUNCHES["n"]
         if use_graph:
             if self._graph is None:

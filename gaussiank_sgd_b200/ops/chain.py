@@ -305,8 +305,9 @@ class CompressChain:
 
 # ------------------------------------------------------------------- receive side / optimizer
 def scatter(src: N.GkSrc, ctrl: torch.Tensor, grad: torch.Tensor, scale: float) -> None:
-    """grad[idx] += val*scale over every slot (distributed_optimizer.py:468-482)."""
-    LAUNCHES["n"] += 1
+    """grad[idx] += val*scale over every slot, in rank order (distributed_optimizer.py:468-482): one launch
+    for up to two sources, one launch per source rank beyond that (bit-identical sums on every replica)."""
+    LAUNCHES["n"] += src.nsrc if (src.nsrc > 2 and grad.device.type == "cuda") else 1
     if grad.device.type == "cuda":
         N.check(N.cuda_lib().gk_scatter(C.byref(src), ctrl.data_ptr(), grad.data_ptr(), C.c_float(scale),
                                         grad.numel(), _stream_ptr(grad.device)), "gk_scatter")
