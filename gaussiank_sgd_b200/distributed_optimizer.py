@@ -338,10 +338,16 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         try:
             if self._sparse:
                 comp = self._compressor
+                dump = (settings.LOGGING_GRADIENTS and self._gradient_path and rank() == 0
+                        and self.train_iter % max(settings.GRADIENT_DUMP_EVERY, 1) == 0)
                 if comp.startswith("randomk"):
                     seed = self._random_seed if comp.startswith("randomksame") else self._random_seed * 1000003 + rank() + 1
                     g.chain.randomk_send(g.transport.dst(), seed)
                 else:
+                    if dump:
+                        # opt-in gradient-distribution study (the reference does this every iteration by
+                        # default, distributed_optimizer.py:422-424)
+                        self._dump_gradients(g)
                     g.chain.compress(g.transport.dst())
                 g.transport.exchange()
             elif self._compressor == "bucket":
@@ -354,6 +360,29 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         finally:
             if stream_ctx is not None:
                 stream_ctx.__exit__(None, None, None)
+
+    def _dump_gradients(self, g: _Group) -> None:
+        """``<gradient_path>/r<rank>_gradients_iter_<i>.npy`` = acc (gradient + residual) of the group in the
+        reference's dense order, for logs/plot_cdf-style distribution plots.  Host copy: debugging only."""
+        if not hasattr(g, "_dense_map"):
+            g._dense_map = self._arena.dense_index_map(g.names).to(self.device)
+        acc = self._arena.grad.index_select(0, g._dense_map)
+        if g.chain.use_residual:
+            acc = acc + self._resid.index_select(0, g._dense_map)
+        acc = acc.cpu().numpy()
+        os.makedirs(self._gradient_path, exist_ok=True)
+        np.save('%s/r%d_gradients_iter_%d' % (self._gradient_path, rank(), self.train_iter), acc)
+
+    def gradient_histogram(self, lo: float, hi: float, nbins: int = 256) -> torch.Tensor:
+        """On-device histogram of the residual arena (acc right after a compress) — the cheap alternative
+        to dumping the whole tensor; returns an int32 tensor of ``nbins`` counts."""
+        import ctypes as C
+        assert self._resid is not None and self.device.type == "cuda"
+        out = torch.zeros(nbins, dtype=torch.int32, device=self.device)
+        ch.N.check(ch.N.cuda_lib().gk_histogram(self._resid.data_ptr(), self._resid.numel(), C.c_float(lo),
+                                                C.c_float(hi), nbins, out.data_ptr(),
+                                                torch.cuda.current_stream(self.device).cuda_stream), "gk_histogram")
+        return out
 
     # ------------------------------------------------------------------ receive side
     def synchronize(self):
