@@ -62,12 +62,13 @@ void accumulate_segment(const GkChain* c, const GkSeg& sg, double& sum, double& 
   mx = 0.f;
   for (int b = sg.blk_begin; b < sg.blk_end; ++b) {
     const GkBlk& B = c->blk[b];
+    const float* src = c->gsrc ? c->gsrc[b] : c->grad + B.start;
     for (int i = 0; i < B.len; ++i) {
       const int j = B.start + i;
-      float x = c->grad[j];
+      float x = src[i];
       if (c->use_residual) x += c->resid[j];
       c->resid[j] = x;
-      if (c->zero_grad) c->grad[j] = 0.f;
+      if (c->zero_grad && !c->gsrc) c->grad[j] = 0.f;
       const double xd = (double)x;
       sum += xd;
       sq += xd * xd;

@@ -271,7 +271,7 @@ __global__ void __launch_bounds__(GK_THREADS) k_accumulate(GkChain c) {
     for (int i = tid; i < GK_HIST_BINS; i += T) shist[i] = 0;
     __syncthreads();
   }
-  const bool user = c.use_residual != 0, zg = c.zero_grad != 0;
+  const bool user = c.use_residual != 0, zg = c.zero_grad != 0 && c.gsrc == nullptr;
   const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
   double ds = 0, dq = 0, da = 0;   // this thread's share of the current run
   float mx = 0.f;
@@ -279,7 +279,7 @@ __global__ void __launch_bounds__(GK_THREADS) k_accumulate(GkChain c) {
     const GkBlk B = c.blk[eidx];
     const int enext = eidx + gridDim.x;
     const bool last_of_run = (enext >= c.nblk) || (c.blk[enext].seg != B.seg);   // block-uniform
-    const float* __restrict__ g = c.grad + B.start;
+    const float* __restrict__ g = c.gsrc ? c.gsrc[eidx] : c.grad + B.start;
     float* __restrict__ r = c.resid + B.start;
     // fp32 partials over one entry (<= chunk/256 elements per thread), fp64 across entries
     float s = 0.f, q = 0.f, sa = 0.f;

@@ -81,7 +81,7 @@ class _DistributedOptimizer(torch.optim.Optimizer):
     def __init__(self, params, named_parameters, compression, is_sparse=False, density=0.001,
                  seq_layernames=None, layerwise_times=None, norm_clip=None, threshold=0, writer=None,
                  gradient_path=None, fused=True, transport=None, dynamic_densities="default",
-                 force_compress=False, chunk=ch.DEFAULT_CHUNK, overlap=None):
+                 force_compress=False, chunk=ch.DEFAULT_CHUNK, overlap=None, steal_grads=None):
         super(self.__class__, self).__init__(params)
         self._compression = compression
         self._compressor = _compressor_name(compression)
@@ -107,6 +107,7 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         self._chunk = chunk
         self._transport_kind = transport
         self._random_seed = 0
+        self._steal_req = settings.STEAL_GRADS if steal_grads is None else bool(steal_grads)
 
         named_parameters = list(named_parameters) if named_parameters is not None else []
         if any(not isinstance(p, tuple) for p in named_parameters):
@@ -126,6 +127,7 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         self.device = self._arena.device
         self._resid = self._arena.new_arena() if self._sparse or self._compressor == "bucket" else None
         self._active = size() > 1 or self._force_compress   # distributed_optimizer.py:97: 1 worker => plain optimizer
+        self._steal = self._steal_req and self._active and self._sparse
         group_of_tensor = self._param_group_index()
         self._tables = ch.FlatTables(self._arena.extents(), group_of_tensor, self.device, chunk)
         self._fused_kind = self._detect_fused(fused)
@@ -266,6 +268,50 @@ class _DistributedOptimizer(torch.optim.Optimizer):
             self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(p)))
         for g in self._groups:
             g.pending = len(g.names)
+        if self._steal:
+            # Gradients are taken over from autograd instead of being accumulated into the arena: with
+            # p.grad unset, AccumulateGrad hands the freshly computed tensor to p.grad without a kernel and
+            # K1 reads it in place (GkChain.gsrc).  Saves one add kernel per parameter tensor and step
+            # (161 for ResNet-50) and the zeroing of the gradient arena.
+            for p in self._arena.params:
+                p.grad = None
+
+    def _collect_grad_sources(self, g: _Group) -> None:
+        """Point K1 at the tensors autograd produced for group ``g`` (arena layout required: same strides
+        as the parameter, which AccumulateGrad guarantees for dense parameters; anything else is copied into
+        the arena first)."""
+        arena = self._arena
+        ptrs, dirty = [], []
+        for n in g.names:
+            i = arena.index[n]
+            p = arena.params[i]
+            view = arena.grad_views[i]
+            gr = p.grad
+            if gr is None:
+                ptrs.append(view.data_ptr())                      # no gradient this step: arena zeros
+            elif gr.data_ptr() == view.data_ptr():
+                ptrs.append(view.data_ptr())
+                dirty.append(view)
+            elif (gr.dtype == torch.float32 and gr.device == p.device and gr.stride() == p.stride()
+                  and gr.data_ptr() % 16 == 0):
+                ptrs.append(gr.data_ptr())
+            else:
+                view.copy_(gr)
+                ptrs.append(view.data_ptr())
+                dirty.append(view)
+        g.chain.set_grad_sources(ptrs)
+        g._dirty_views = dirty
+
+    def _release_grad_sources(self, g: _Group) -> None:
+        """After the chain is enqueued: the arena views become the visible gradients again (they will hold
+        the averaged sparse gradient); arena regions that served as a dense source are cleared."""
+        arena = self._arena
+        for v in getattr(g, "_dirty_views", ()):
+            v.zero_()
+        g._dirty_views = []
+        for n in g.names:
+            i = arena.index[n]
+            arena.params[i].grad = arena.grad_views[i]
 
     def _make_hook(self, p):
         group = self._group_of_param[p]
@@ -344,11 +390,15 @@ class _DistributedOptimizer(torch.optim.Optimizer):
                     seed = self._random_seed if comp.startswith("randomksame") else self._random_seed * 1000003 + rank() + 1
                     g.chain.randomk_send(g.transport.dst(), seed)
                 else:
+                    if self._steal:
+                        self._collect_grad_sources(g)
                     if dump:
                         # opt-in gradient-distribution study (the reference does this every iteration by
                         # default, distributed_optimizer.py:422-424)
                         self._dump_gradients(g)
                     g.chain.compress(g.transport.dst())
+                    if self._steal:
+                        self._release_grad_sources(g)
                 g.transport.exchange()
             elif self._compressor == "bucket":
                 g.chain.bucket_means(g.means)
@@ -366,7 +416,16 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         reference's dense order, for logs/plot_cdf-style distribution plots.  Host copy: debugging only."""
         if not hasattr(g, "_dense_map"):
             g._dense_map = self._arena.dense_index_map(g.names).to(self.device)
-        acc = self._arena.grad.index_select(0, g._dense_map)
+        if self._steal:
+            arena = self._arena
+            flat = torch.zeros_like(arena.grad)
+            for n in g.names:
+                i = arena.index[n]
+                if arena.params[i].grad is not None:
+                    arena.view(flat, i).copy_(arena.params[i].grad)
+            acc = flat.index_select(0, g._dense_map)
+        else:
+            acc = self._arena.grad.index_select(0, g._dense_map)
         if g.chain.use_residual:
             acc = acc + self._resid.index_select(0, g._dense_map)
         acc = acc.cpu().numpy()
@@ -501,7 +560,11 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         elif self._grad_state != "zero" or not self._active:
             a.grad.zero_()
         self._grad_state = "zero"
-        a.rebind_grads()
+        if self._steal:
+            for p in a.params:
+                p.grad = None          # the next backward hands its gradient tensors over (no accumulate kernels)
+        else:
+            a.rebind_grads()
 
     # ------------------------------------------------------------------ state
     def residual_state(self) -> Optional[torch.Tensor]:

@@ -163,6 +163,8 @@ class CompressChain:
         self.compressor = compressor
         self.mode, self.nloops = MODES[compressor]
         self.use_residual, self.zero_grad = use_residual, zero_grad
+        self._segments = [list(e) for e in segments]
+        self.chunk = chunk
         blk, segs = build_tables(segments, chunk)
         self.blk_np, self.seg_np = blk, segs
         self.nblk, self.nseg = blk.shape[0], segs.shape[0]
@@ -219,6 +221,59 @@ class CompressChain:
             self.seg.copy_(self._seg_pinned, non_blocking=True)
         else:
             self.seg.copy_(host)
+
+    # ------------------------------------------------------------- external gradient sources
+    def _extent_of_blocks(self):
+        """For every table entry: (index of its tensor extent in flattened segment order, element offset
+        inside that extent)."""
+        if getattr(self, "_blk_extent", None) is None:
+            ext, off, e = [], [], 0
+            for extents in self._segments:
+                for (_start, numel) in extents:
+                    o = 0
+                    while o < numel:
+                        ext.append(e)
+                        off.append(o)
+                        o += min(self.chunk, numel - o)
+                    e += 1
+            self._blk_extent = np.asarray(ext, dtype=np.int64)
+            self._blk_eoff = np.asarray(off, dtype=np.int64)
+            self.n_extents = e
+        return self._blk_extent, self._blk_eoff
+
+    def set_grad_sources(self, extent_ptrs: Optional[Sequence[int]]) -> None:
+        """Make K1 read the gradient of tensor extent e from device address ``extent_ptrs[e]`` (flattened
+        segment order) instead of the gradient arena — e.g. the tensors autograd just produced.  The table
+        of per-entry pointers is staged in rotating pinned buffers and copied on the current stream, so it
+        may be refreshed every iteration (eager mode) or captured once (CUDA graph).  ``None`` switches back
+        to the arena."""
+        if extent_ptrs is None:
+            self._desc.gsrc = None
+            return
+        be, bo = self._extent_of_blocks()
+        ptrs = np.asarray(extent_ptrs, dtype=np.int64)
+        assert ptrs.shape[0] == self.n_extents
+        table = ptrs[be] + 4 * bo
+        if not self.is_cuda:
+            self._gsrc_dev = torch.from_numpy(table.copy())
+            self._desc.gsrc = self._gsrc_dev.data_ptr()
+            return
+        if getattr(self, "_gsrc_dev", None) is None:
+            self._gsrc_dev = torch.zeros(max(self.nblk, 1), dtype=torch.int64, device=self.device)
+            self._gsrc_pin = [torch.zeros(max(self.nblk, 1), dtype=torch.int64).pin_memory() for _ in range(4)]
+            self._gsrc_evt = [None] * 4
+            self._gsrc_i = 0
+        i = self._gsrc_i
+        self._gsrc_i = (i + 1) % 4
+        if self._gsrc_evt[i] is not None:
+            self._gsrc_evt[i].synchronize()      # the copy that last used this staging buffer has run
+        self._gsrc_pin[i].numpy()[:table.shape[0]] = table
+        self._gsrc_dev.copy_(self._gsrc_pin[i], non_blocking=True)
+        if not torch.cuda.is_current_stream_capturing():
+            ev = torch.cuda.Event()
+            ev.record()
+            self._gsrc_evt[i] = ev
+        self._desc.gsrc = self._gsrc_dev.data_ptr()
 
     def _make_desc(self) -> N.GkChain:
         return N.GkChain(self.grad.data_ptr(), self.resid.data_ptr(), self.blk.data_ptr(), self.seg.data_ptr(),

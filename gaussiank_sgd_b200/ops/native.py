@@ -58,7 +58,8 @@ class GkChain(C.Structure):
                 ("part", C.c_void_p), ("stat", C.c_void_p), ("bcnt", C.c_void_p), ("boff", C.c_void_p),
                 ("hist", C.c_void_p), ("ctrl", C.c_void_p),
                 ("nblk", C.c_int32), ("nseg", C.c_int32), ("mode", C.c_int32), ("nloops", C.c_int32),
-                ("use_residual", C.c_int32), ("zero_grad", C.c_int32), ("cap", C.c_uint32), ("rsv", C.c_int32)]
+                ("use_residual", C.c_int32), ("zero_grad", C.c_int32), ("cap", C.c_uint32), ("rsv", C.c_int32),
+                ("gsrc", C.c_void_p)]
 
 
 class GkDst(C.Structure):

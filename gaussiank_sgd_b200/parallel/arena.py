@@ -48,13 +48,15 @@ class ParamArena:
         self._cl = [_is_channels_last(p.data) for p in self.params]
         self.param = torch.zeros(self.total, dtype=torch.float32, device=dev)
         self.grad = torch.zeros(self.total, dtype=torch.float32, device=dev) if with_grad else None
+        self.grad_views = []
         with torch.no_grad():
             for i, p in enumerate(self.params):
                 v = self.view(self.param, i)
                 v.copy_(p.data)
                 p.data = v
                 if with_grad:
-                    p.grad = self.view(self.grad, i)
+                    self.grad_views.append(self.view(self.grad, i))
+                    p.grad = self.grad_views[i]
 
     def view(self, arena: torch.Tensor, i: int) -> torch.Tensor:
         """Tensor i's window of ``arena`` with the parameter's shape and memory format."""
@@ -81,7 +83,7 @@ class ParamArena:
         for i, p in enumerate(self.params):
             g = p.grad
             if g is None or g.data_ptr() != self.grad.data_ptr() + 4 * self.offsets[i]:
-                p.grad = self.view(self.grad, i)
+                p.grad = self.grad_views[i]
 
     def num_params(self) -> int:
         return sum(self.numels)

@@ -59,6 +59,7 @@ MAX_EPOCHS = int(os.environ.get("GK_MAX_EPOCHS", "10"))
 # ---- switches that exist only here -------------------------------------------------------------
 DYNAMIC_DENSITIES = _floats("DYNAMIC_DENSITIES", [0.015625, 0.004, 0.001])  # distributed_optimizer.py:60
 COMPRESS_SINGLE = _flag("COMPRESS_SINGLE", False)   # run the chain with one worker too
+STEAL_GRADS = _flag("STEAL_GRADS", True)            # K1 reads autograd's gradient tensors in place (no arena accumulate)
 SPARSE_ZERO = _flag("SPARSE_ZERO", True)            # zero_grad clears only the received coordinates
 PROFILE_PHASES = _flag("PROFILE_PHASES", False)     # CUDA-event timers for compress / comm / update
 CUDA_GRAPH = _flag("CUDA_GRAPH", True)              # capture the training step in a CUDA graph on GPUs

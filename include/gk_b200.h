@@ -108,7 +108,11 @@ typedef struct GkChain {
   int32_t use_residual; /* 1: acc = grad + resid (error feedback); 0: acc = grad     */
   int32_t zero_grad;    /* 1: write 0 into grad after it is consumed                 */
   uint32_t cap;         /* max pairs emitted per send (receive-slot capacity)        */
-  int32_t rsv;
+  int32_t rsv;          /* experiment switches (tools/bench_chain.py); 0 in production */
+  const float* const* gsrc; /* optional [nblk] device array: where K1 reads each table entry's gradient
+                               from.  NULL = grad + start.  Lets K1 consume the tensors autograd
+                               produced (p.grad stolen, no accumulate-into-arena kernels); those
+                               sources are read only — zero_grad does not apply to them            */
 } GkChain;
 
 /* Where the compaction kernel stores this rank's pairs: one slot per destination.
