@@ -1,0 +1,656 @@
+// gk_bn.cu — fused training-mode batch norm for NHWC fp32 activations (sm_100a).
+//
+// Why it exists: on a B200 the ResNet-50 step of the benchmark spends 29 % of its kernel time in cuDNN's
+// NHWC batch norm and another 9 % in the stand-alone ReLU / residual-add kernels around it
+// (profiles/step_breakdown_resnet50_v1.txt) — all of it HBM-bound elementwise work.  The reference gets
+// these ops from torch.nn; here y = relu(bn(x) [+ residual]) is ONE pass after the
+// statistics pass, and the backward recomputes the ReLU mask instead of reading a saved activation:
+//   forward : stats pass reads x (4 B/elem), apply pass reads x (+ residual) and writes y (8-12 B/elem)
+//   backward: reduce pass reads dy, x (8 B/elem), dx pass reads dy, x and writes dx (12 B/elem)
+// versus 20-32 B/elem forward and 32+ B/elem backward for the unfused sequence.
+//
+// Layout: x is [M = N*H*W rows][C channels], C innermost, C % 4 == 0.  A thread owns one quad of channels
+// (float4) and walks rows; 16 or 32 consecutive threads cover consecutive quads (coalesced 256-512 B).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../include/gk_b200.h"
+
+#define BN_T 256
+
+__device__ __forceinline__ float4 bn_ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ void bn_st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ float4 f4_add(float4 a, float4 b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+__device__ __forceinline__ float4 f4_fma(float4 a, float4 b, float4 c) {
+  return make_float4(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y), fmaf(a.z, b.z, c.z), fmaf(a.w, b.w, c.w));
+}
+
+// true in the last block to arrive (self-resetting ticket), same pattern as gk_cuda.cu
+__device__ __forceinline__ bool bn_last_block(uint32_t* ticket, uint32_t nblocks) {
+  __shared__ int s_last;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const uint32_t t = atomicAdd(ticket, 1u);
+    s_last = (t == nblocks - 1);
+    if (s_last) *ticket = 0;
+  }
+  __syncthreads();
+  if (s_last) __threadfence();
+  return s_last != 0;
+}
+
+// Two per-channel sums over this block's rows, added into accum[0/1][C] (fp64, zero between uses).
+// MODE 0 (forward): (sum x, sum x^2).
+// MODE 1 (backward): (sum g, sum g*xhat) with g = dy masked by the ReLU of the forward output.
+template <int MODE>
+__device__ __forceinline__ void bn_block_sums(const float* __restrict__ x, const float* __restrict__ dy,
+                                              const float* __restrict__ y, int64_t M, int C, int rows_per_block,
+                                              int qpb, float4 mean, float4 istd, float4 scale, float4 shift,
+                                              int relu, double* __restrict__ partial,
+                                              float* __restrict__ gout) {
+  __shared__ float4 sm[2][BN_T];
+  const int tid = threadIdx.x;
+  const int ql = tid % qpb, rl = tid / qpb, RL = BN_T / qpb;   // threads with rl >= RL idle (qpb need not divide BN_T)
+  const int q = blockIdx.y * qpb + ql;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = (r0 + rows_per_block < M) ? r0 + rows_per_block : M;
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+#pragma unroll 4
+  for (int64_t r = (rl < RL) ? r0 + rl : r1; r < r1; r += RL) {
+    const float4 xv = bn_ld4(x + r * C + 4 * q);
+    if (MODE == 0) {
+      a = f4_add(a, xv);
+      b = f4_fma(xv, xv, b);
+    } else {
+      float4 g = bn_ld4(dy + r * C + 4 * q);
+      if (relu) {
+        if (y != nullptr) {                       // residual case: the mask comes from the saved output
+          const float4 yv = bn_ld4(y + r * C + 4 * q);
+          g.x = yv.x > 0.f ? g.x : 0.f; g.y = yv.y > 0.f ? g.y : 0.f;
+          g.z = yv.z > 0.f ? g.z : 0.f; g.w = yv.w > 0.f ? g.w : 0.f;
+        } else {                                  // recompute z = x*scale + shift instead of reading y
+          g.x = fmaf(xv.x, scale.x, shift.x) > 0.f ? g.x : 0.f; g.y = fmaf(xv.y, scale.y, shift.y) > 0.f ? g.y : 0.f;
+          g.z = fmaf(xv.z, scale.z, shift.z) > 0.f ? g.z : 0.f; g.w = fmaf(xv.w, scale.w, shift.w) > 0.f ? g.w : 0.f;
+        }
+      }
+      if (gout != nullptr) bn_st4(gout + r * C + 4 * q, g);   // masked gradient = gradient of the residual branch
+      const float4 xh = make_float4((xv.x - mean.x) * istd.x, (xv.y - mean.y) * istd.y, (xv.z - mean.z) * istd.z,
+                                    (xv.w - mean.w) * istd.w);
+      a = f4_add(a, g);
+      b = f4_fma(g, xh, b);
+    }
+  }
+  sm[0][tid] = a;
+  sm[1][tid] = b;
+  __syncthreads();
+  if (rl == 0) {
+    for (int i = 1; i < RL; ++i) {
+      a = f4_add(a, sm[0][i * qpb + ql]);
+      b = f4_add(b, sm[1][i * qpb + ql]);
+    }
+    // fp64 atomics into accum[0..C) / accum[C..2C): one pair per channel and block.  The order of the adds
+    // varies, but at 2^-53 relative the sums round to the same fp32 statistics in practice, and the last
+    // block needs O(1) work instead of a serial sweep over per-block partials.
+    double* acc = partial;
+    atomicAdd(acc + 4 * q + 0, (double)a.x); atomicAdd(acc + 4 * q + 1, (double)a.y);
+    atomicAdd(acc + 4 * q + 2, (double)a.z); atomicAdd(acc + 4 * q + 3, (double)a.w);
+    atomicAdd(acc + C + 4 * q + 0, (double)b.x); atomicAdd(acc + C + 4 * q + 1, (double)b.y);
+    atomicAdd(acc + C + 4 * q + 2, (double)b.z); atomicAdd(acc + C + 4 * q + 3, (double)b.w);
+  }
+}
+
+// ------------------------------------------------------------------------------- forward
+// Pass 1: per-channel sum / sum of squares; the last block turns them into mean, 1/std, updates the running
+// statistics (torch semantics: biased variance for normalisation, unbiased for running_var) and bumps
+// num_batches_tracked.
+__global__ void __launch_bounds__(BN_T) k_bn_stats(const float* __restrict__ x, int64_t M, int C, int rows_per_block,
+                                                    int qpb, double* __restrict__ partial, uint32_t* ticket,
+                                                    float* __restrict__ save_mean, float* __restrict__ save_istd,
+                                                    float* running_mean, float* running_var, int64_t* num_batches,
+                                                    float eps, float momentum) {
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  bn_block_sums<0>(x, nullptr, nullptr, M, C, rows_per_block, qpb, z, z, z, z, 0, partial, nullptr);
+  if (bn_last_block(ticket, gridDim.x * gridDim.y)) {
+    for (int c = threadIdx.x; c < C; c += BN_T) {
+      const double s = __ldcg(partial + c), ss = __ldcg(partial + C + c);
+      partial[c] = 0;                 // ready for the next use
+      partial[C + c] = 0;
+      const double mean = s / (double)M;
+      double var = ss / (double)M - mean * mean;
+      if (var < 0) var = 0;
+      save_mean[c] = (float)mean;
+      save_istd[c] = (float)(1.0 / sqrt(var + (double)eps));
+      if (running_mean != nullptr) {
+        const double unbiased = M > 1 ? var * (double)M / (double)(M - 1) : var;
+        running_mean[c] = (float)((1.0 - momentum) * (double)running_mean[c] + momentum * mean);
+        running_var[c] = (float)((1.0 - momentum) * (double)running_var[c] + momentum * unbiased);
+      }
+    }
+    if (threadIdx.x == 0 && num_batches != nullptr) *num_batches += 1;
+  }
+}
+
+// Pass 2: y = [relu]( (x - mean) * istd * gamma + beta [+ residual] )
+__global__ void __launch_bounds__(BN_T) k_bn_apply(const float* __restrict__ x, const float* __restrict__ res,
+                                                    float* __restrict__ y, const float* __restrict__ gamma,
+                                                    const float* __restrict__ beta, const float* __restrict__ save_mean,
+                                                    const float* __restrict__ save_istd, int64_t M, int C,
+                                                    int rows_per_block, int qpb, int relu) {
+  const int tid = threadIdx.x;
+  const int ql = tid % qpb, rl = tid / qpb, RL = BN_T / qpb;
+  const int q = blockIdx.y * qpb + ql;
+  const float4 g = bn_ld4(gamma + 4 * q), bt = bn_ld4(beta + 4 * q);
+  const float4 mu = bn_ld4(save_mean + 4 * q), is = bn_ld4(save_istd + 4 * q);
+  const float4 sc = make_float4(g.x * is.x, g.y * is.y, g.z * is.z, g.w * is.w);
+  const float4 sh = make_float4(fmaf(-mu.x, sc.x, bt.x), fmaf(-mu.y, sc.y, bt.y), fmaf(-mu.z, sc.z, bt.z),
+                                fmaf(-mu.w, sc.w, bt.w));
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = (r0 + rows_per_block < M) ? r0 + rows_per_block : M;
+#pragma unroll 4
+  for (int64_t r = (rl < RL) ? r0 + rl : r1; r < r1; r += RL) {
+    const float4 xv = bn_ld4(x + r * C + 4 * q);
+    float4 o = make_float4(fmaf(xv.x, sc.x, sh.x), fmaf(xv.y, sc.y, sh.y), fmaf(xv.z, sc.z, sh.z), fmaf(xv.w, sc.w, sh.w));
+    if (res != nullptr) o = f4_add(o, bn_ld4(res + r * C + 4 * q));
+    if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+    bn_st4(y + r * C + 4 * q, o);
+  }
+}
+
+// ------------------------------------------------------------------------------ backward
+__device__ __forceinline__ void bn_load_channel_consts(const float* gamma, const float* beta, const float* save_mean,
+                                                       const float* save_istd, int q, float4& mu, float4& is,
+                                                       float4& sc, float4& sh) {
+  const float4 g = bn_ld4(gamma + 4 * q), bt = bn_ld4(beta + 4 * q);
+  mu = bn_ld4(save_mean + 4 * q);
+  is = bn_ld4(save_istd + 4 * q);
+  sc = make_float4(g.x * is.x, g.y * is.y, g.z * is.z, g.w * is.w);      // same expressions as the forward,
+  sh = make_float4(fmaf(-mu.x, sc.x, bt.x), fmaf(-mu.y, sc.y, bt.y),      // so the recomputed ReLU mask is
+                   fmaf(-mu.z, sc.z, bt.z), fmaf(-mu.w, sc.w, bt.w));     // exactly the forward's
+}
+
+// Pass 1: per-channel sum g and sum g*xhat; the last block writes dgamma, dbeta and the two means pass 2 needs.
+__global__ void __launch_bounds__(BN_T) k_bn_bwd_reduce(const float* __restrict__ dy, const float* __restrict__ x,
+                                                         const float* __restrict__ y, const float* __restrict__ gamma,
+                                                         const float* __restrict__ beta,
+                                                         const float* __restrict__ save_mean,
+                                                         const float* __restrict__ save_istd, int64_t M, int C,
+                                                         int rows_per_block, int qpb, int relu,
+                                                         double* __restrict__ accum, uint32_t* ticket,
+                                                         float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                         float* __restrict__ coef /* [2][C]: mean g, mean g*xhat */,
+                                                         float* __restrict__ gout /* masked g or null */) {
+  float4 mu, is, sc, sh;
+  bn_load_channel_consts(gamma, beta, save_mean, save_istd, blockIdx.y * qpb + threadIdx.x % qpb, mu, is, sc, sh);
+  bn_block_sums<1>(x, dy, y, M, C, rows_per_block, qpb, mu, is, sc, sh, relu, accum, gout);
+  if (bn_last_block(ticket, gridDim.x * gridDim.y)) {
+    for (int c = threadIdx.x; c < C; c += BN_T) {
+      const double sg = __ldcg(accum + c), sgx = __ldcg(accum + C + c);
+      accum[c] = 0;
+      accum[C + c] = 0;
+      dbeta[c] = (float)sg;
+      dgamma[c] = (float)sgx;
+      coef[c] = (float)(sg / (double)M);
+      coef[C + c] = (float)(sgx / (double)M);
+    }
+  }
+}
+
+// Pass 2: dx = gamma*istd * (g - mean(g) - xhat * mean(g*xhat)).  With a residual branch pass 1 has already
+// written the masked gradient (= dres); the host then passes it here as dy with relu = 0.
+__global__ void __launch_bounds__(BN_T) k_bn_bwd_dx(const float* __restrict__ dy, const float* __restrict__ x,
+                                                     const float* __restrict__ y, const float* __restrict__ gamma,
+                                                     const float* __restrict__ beta, const float* __restrict__ save_mean,
+                                                     const float* __restrict__ save_istd, const float* __restrict__ coef,
+                                                     float* __restrict__ dx, int64_t M, int C, int rows_per_block,
+                                                     int qpb, int relu) {
+  const int tid = threadIdx.x;
+  const int ql = tid % qpb, rl = tid / qpb, RL = BN_T / qpb;
+  const int q = blockIdx.y * qpb + ql;
+  float4 mu, is, sc, sh;
+  bn_load_channel_consts(gamma, beta, save_mean, save_istd, q, mu, is, sc, sh);
+  const float4 mg = bn_ld4(coef + 4 * q), mgx = bn_ld4(coef + C + 4 * q);
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = (r0 + rows_per_block < M) ? r0 + rows_per_block : M;
+#pragma unroll 4
+  for (int64_t r = (rl < RL) ? r0 + rl : r1; r < r1; r += RL) {
+    const float4 xv = bn_ld4(x + r * C + 4 * q);
+    float4 g = bn_ld4(dy + r * C + 4 * q);
+    if (relu) {
+      if (y != nullptr) {
+        const float4 yv = bn_ld4(y + r * C + 4 * q);
+        g.x = yv.x > 0.f ? g.x : 0.f; g.y = yv.y > 0.f ? g.y : 0.f;
+        g.z = yv.z > 0.f ? g.z : 0.f; g.w = yv.w > 0.f ? g.w : 0.f;
+      } else {
+        g.x = fmaf(xv.x, sc.x, sh.x) > 0.f ? g.x : 0.f; g.y = fmaf(xv.y, sc.y, sh.y) > 0.f ? g.y : 0.f;
+        g.z = fmaf(xv.z, sc.z, sh.z) > 0.f ? g.z : 0.f; g.w = fmaf(xv.w, sc.w, sh.w) > 0.f ? g.w : 0.f;
+      }
+    }
+    float4 o;
+    o.x = sc.x * (g.x - mg.x - (xv.x - mu.x) * is.x * mgx.x);
+    o.y = sc.y * (g.y - mg.y - (xv.y - mu.y) * is.y * mgx.y);
+    o.z = sc.z * (g.z - mg.z - (xv.z - mu.z) * is.z * mgx.z);
+    o.w = sc.w * (g.w - mg.w - (xv.w - mu.w) * is.w * mgx.w);
+    bn_st4(dx + r * C + 4 * q, o);
+  }
+}
+
+// --------------------------------------------------------------------------------- host
+namespace {
+struct BnGeom {
+  int qpb, rpb;
+  dim3 grid;
+};
+
+int bn_sm_count() {
+  static int nsm[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (nsm[dev] == 0) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+    nsm[dev] = v;
+  }
+  return nsm[dev];
+}
+
+// qpb = the largest divisor of C/4 that is <= 32 (consecutive threads then read consecutive quads of one row);
+// about eight resident blocks per SM, but never fewer than four rows per thread.
+bool bn_geometry(int64_t M, int C, BnGeom* g) {
+  if (M <= 0 || C <= 0 || (C & 3)) return false;
+  const int quads = C / 4;
+  int qpb = quads < 32 ? quads : 32;
+  while (quads % qpb) --qpb;
+  const int RL = BN_T / qpb;
+  const int gy = quads / qpb;
+  int64_t gx_target = ((int64_t)bn_sm_count() * 8 + gy - 1) / gy;
+  if (gx_target < 1) gx_target = 1;
+  int64_t rpb = (M + gx_target - 1) / gx_target;
+  if (rpb < 4 * RL) rpb = 4 * RL;
+  if (rpb > (int64_t)1 << 30) return false;
+  const int64_t gx = (M + rpb - 1) / rpb;
+  g->qpb = qpb;
+  g->rpb = (int)rpb;
+  g->grid = dim3((unsigned)gx, (unsigned)gy, 1);
+  return true;
+}
+
+inline bool bn_aligned(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+}  // namespace
+
+extern "C" int gk_bn_fwd(const float* x, const float* res, float* y, const float* gamma, const float* beta,
+                         float* running_mean, float* running_var, int64_t* num_batches, float* save_mean,
+                         float* save_istd, double* accum, uint32_t* ticket, int64_t M, int C, float eps,
+                         float momentum, int relu, void* stream) {
+  BnGeom g;
+  if (!bn_geometry(M, C, &g)) return (int)cudaErrorInvalidValue;
+  if (!bn_aligned(x) || !bn_aligned(y) || !bn_aligned(res) || !bn_aligned(gamma) || !bn_aligned(beta) ||
+      !bn_aligned(save_mean) || !bn_aligned(save_istd))
+    return (int)cudaErrorMisalignedAddress;
+  cudaStream_t s = (cudaStream_t)stream;
+  k_bn_stats<<<g.grid, BN_T, 0, s>>>(x, M, C, g.rpb, g.qpb, accum, ticket, save_mean, save_istd, running_mean,
+                                     running_var, num_batches, eps, momentum);
+  k_bn_apply<<<g.grid, BN_T, 0, s>>>(x, res, y, gamma, beta, save_mean, save_istd, M, C, g.rpb, g.qpb, relu);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int gk_bn_bwd(const float* dy, const float* x, const float* y, const float* gamma, const float* beta,
+                         const float* save_mean, const float* save_istd, float* dx, float* dres, float* dgamma,
+                         float* dbeta, float* coef, double* accum, uint32_t* ticket, int64_t M, int C, int relu,
+                         void* stream) {
+  BnGeom g;
+  if (!bn_geometry(M, C, &g)) return (int)cudaErrorInvalidValue;
+  if (!bn_aligned(dy) || !bn_aligned(x) || !bn_aligned(y) || !bn_aligned(dx) || !bn_aligned(dres) ||
+      !bn_aligned(gamma) || !bn_aligned(beta) || !bn_aligned(save_mean) || !bn_aligned(save_istd) ||
+      !bn_aligned(coef))
+    return (int)cudaErrorMisalignedAddress;
+  cudaStream_t s = (cudaStream_t)stream;
+  // y != null: mask from the saved output (needed when a residual was added); dres != null: also emit masked g
+  k_bn_bwd_reduce<<<g.grid, BN_T, 0, s>>>(dy, x, y, gamma, beta, save_mean, save_istd, M, C, g.rpb, g.qpb, relu,
+                                          accum, ticket, dgamma, dbeta, coef, dres);
+  if (dres != nullptr)
+    k_bn_bwd_dx<<<g.grid, BN_T, 0, s>>>(dres, x, nullptr, gamma, beta, save_mean, save_istd, coef, dx, M, C, g.rpb,
+                                        g.qpb, 0);
+  else
+    k_bn_bwd_dx<<<g.grid, BN_T, 0, s>>>(dy, x, y, gamma, beta, save_mean, save_istd, coef, dx, M, C, g.rpb, g.qpb,
+                                        relu);
+  return (int)cudaGetLastError();
+}
+
+// ======================================================================= single-kernel variants
+// One cooperative kernel per direction: every block keeps its slab of the activation in shared memory,
+// the per-channel sums cross blocks through fp64 atomics and a per-channel-slab barrier, and the second
+// phase runs out of shared memory.  HBM traffic: forward read x (+res) once, write y; backward read dy, x
+// (+y with a residual) once, write dx (+dres).  The grid is (gx row slabs) x (gy channel slabs) with
+// gx*gy <= number of SMs, one block per SM, launched with cudaLaunchCooperativeKernel so that all blocks
+// are resident while they wait for each other.  Rows that do not fit in shared memory (the four largest
+// ResNet-50 shapes at batch 32) are re-read from L2/HBM in the second phase.
+#define BNF_T 512
+#define BNF_SMEM_BUDGET (200 * 1024)
+#define BNF_SPIN_LIMIT (1 << 22)
+
+__device__ __forceinline__ unsigned long long bnf_ld_acquire(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Barrier among the gridDim.x blocks that share blockIdx.y.  bar[y] only ever grows: generation g of a
+// column ends when it reaches (g+1)*gridDim.x, so nothing has to be reset and consecutive launches may
+// reuse the counter.  The wait is bounded: on expiry *err is set and the block carries on (wrong numbers,
+// no hang) — it can only expire if the blocks were not co-resident, which the cooperative launch rules out.
+__device__ __forceinline__ void bnf_column_barrier(unsigned long long* bar, unsigned long long gen, int* err) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(bar + blockIdx.y, 1ULL);
+    const unsigned long long target = (gen + 1ULL) * (unsigned long long)gridDim.x;
+    int spins = 0;
+    while (bnf_ld_acquire(bar + blockIdx.y) < target) {
+      if (++spins > BNF_SPIN_LIMIT) {
+        *err = 1;
+        break;
+      }
+      __nanosleep(32);
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+// block-level reduction of (a, b) over the row lanes that share a channel quad; result valid where rl == 0
+__device__ __forceinline__ void bnf_reduce_rows(float4 (*red)[BNF_T], float4& a, float4& b, int tid, int rl, int RL,
+                                                int qpb) {
+  red[0][tid] = a;
+  red[1][tid] = b;
+  __syncthreads();
+  for (int s = RL >> 1; s > 0; s >>= 1) {
+    if (rl < s) {
+      a = f4_add(a, red[0][tid + s * qpb]);
+      b = f4_add(b, red[1][tid + s * qpb]);
+      red[0][tid] = a;
+      red[1][tid] = b;
+    }
+    __syncthreads();
+  }
+}
+
+__device__ __forceinline__ void bnf_atomic_add8(double* acc, int C, int q, float4 a, float4 b) {
+  atomicAdd(acc + 4 * q + 0, (double)a.x); atomicAdd(acc + 4 * q + 1, (double)a.y);
+  atomicAdd(acc + 4 * q + 2, (double)a.z); atomicAdd(acc + 4 * q + 3, (double)a.w);
+  atomicAdd(acc + C + 4 * q + 0, (double)b.x); atomicAdd(acc + C + 4 * q + 1, (double)b.y);
+  atomicAdd(acc + C + 4 * q + 2, (double)b.z); atomicAdd(acc + C + 4 * q + 3, (double)b.w);
+}
+
+__global__ void __launch_bounds__(BNF_T, 1)
+k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float* __restrict__ y,
+               const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ save_mean,
+               float* __restrict__ save_istd, float* running_mean, float* running_var, int64_t* num_batches,
+               double* accum /* [2 parities][2][C] */, unsigned long long* bar, int* err, int64_t M, int C,
+               int rows_per_block, int qpb, int cached, float eps, float momentum, int relu) {
+  extern __shared__ float4 tile[];          // [cached][BNF_T]
+  __shared__ float4 red[2][BNF_T];
+  __shared__ unsigned long long s_gen;
+  const int tid = threadIdx.x;
+  const int ql = tid % qpb, rl = tid / qpb, RL = BNF_T / qpb;
+  const int q = blockIdx.y * qpb + ql;
+  if (tid == 0) s_gen = *(volatile unsigned long long*)(bar + blockIdx.y) / gridDim.x;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = (r0 + rows_per_block < M) ? r0 + rows_per_block : M;
+  const float* xp = x + 4 * q;
+
+  // phase 1: one read of x; sums and the shared-memory copy
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+  {
+    int i = 0;
+#pragma unroll 8
+    for (int64_t r = r0 + rl; r < r1; r += RL, ++i) {
+      const float4 xv = bn_ld4(xp + r * C);
+      a = f4_add(a, xv);
+      b = f4_fma(xv, xv, b);
+      if (i < cached) tile[i * BNF_T + tid] = xv;
+    }
+  }
+  bnf_reduce_rows(red, a, b, tid, rl, RL, qpb);
+  const unsigned long long gen = s_gen;
+  double* acc = accum + (gen & 1ULL) * 2 * (size_t)C;
+  if (rl == 0) bnf_atomic_add8(acc, C, q, a, b);
+  bnf_column_barrier(bar, gen, err);
+
+  // per-channel constants, recomputed by every thread for its own quad
+  float mu[4], is[4];
+  double varv[4], meanv[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const double s = __ldcg(acc + 4 * q + j), ss = __ldcg(acc + C + 4 * q + j);
+    const double mean = s / (double)M;
+    double var = ss / (double)M - mean * mean;
+    if (var < 0) var = 0;
+    meanv[j] = mean;
+    varv[j] = var;
+    mu[j] = (float)mean;
+    is[j] = (float)(1.0 / sqrt(var + (double)eps));
+  }
+  if (blockIdx.x == 0 && rl == 0) {
+    double* other = accum + ((gen + 1ULL) & 1ULL) * 2 * (size_t)C;   // dirty from the previous launch
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = 4 * q + j;
+      other[c] = 0;
+      other[C + c] = 0;
+      save_mean[c] = mu[j];
+      save_istd[c] = is[j];
+      if (running_mean != nullptr) {
+        const double unbiased = M > 1 ? varv[j] * (double)M / (double)(M - 1) : varv[j];
+        running_mean[c] = (float)((1.0 - momentum) * (double)running_mean[c] + momentum * meanv[j]);
+        running_var[c] = (float)((1.0 - momentum) * (double)running_var[c] + momentum * unbiased);
+      }
+    }
+    if (blockIdx.y == 0 && tid == 0 && num_batches != nullptr) *num_batches += 1;
+  }
+  const float4 g = bn_ld4(gamma + 4 * q), bt = bn_ld4(beta + 4 * q);
+  const float4 sc = make_float4(g.x * is[0], g.y * is[1], g.z * is[2], g.w * is[3]);
+  const float4 sh = make_float4(fmaf(-mu[0], sc.x, bt.x), fmaf(-mu[1], sc.y, bt.y), fmaf(-mu[2], sc.z, bt.z),
+                                fmaf(-mu[3], sc.w, bt.w));
+
+  // phase 2: normalise out of shared memory (rows beyond the cached part come from L2/HBM again)
+  {
+    int i = 0;
+#pragma unroll 4
+    for (int64_t r = r0 + rl; r < r1; r += RL, ++i) {
+      const float4 xv = (i < cached) ? tile[i * BNF_T + tid] : bn_ld4(xp + r * C);
+      float4 o = make_float4(fmaf(xv.x, sc.x, sh.x), fmaf(xv.y, sc.y, sh.y), fmaf(xv.z, sc.z, sh.z),
+                             fmaf(xv.w, sc.w, sh.w));
+      if (res != nullptr) o = f4_add(o, bn_ld4(res + r * C + 4 * q));
+      if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+      bn_st4(y + r * C + 4 * q, o);
+    }
+  }
+}
+
+__device__ __forceinline__ float4 bn_mask_pos(float4 g, float4 z) {
+  g.x = z.x > 0.f ? g.x : 0.f; g.y = z.y > 0.f ? g.y : 0.f;
+  g.z = z.z > 0.f ? g.z : 0.f; g.w = z.w > 0.f ? g.w : 0.f;
+  return g;
+}
+
+__global__ void __launch_bounds__(BNF_T, 1)
+k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ y,
+               const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ save_mean,
+               const float* __restrict__ save_istd, float* __restrict__ dx, float* __restrict__ dres,
+               float* __restrict__ dgamma, float* __restrict__ dbeta, double* accum, unsigned long long* bar,
+               int* err, int64_t M, int C, int rows_per_block, int qpb, int cached, int relu) {
+  extern __shared__ float4 tile[];          // [cached][2][BNF_T]: masked gradient, x
+  __shared__ float4 red[2][BNF_T];
+  __shared__ unsigned long long s_gen;
+  const int tid = threadIdx.x;
+  const int ql = tid % qpb, rl = tid / qpb, RL = BNF_T / qpb;
+  const int q = blockIdx.y * qpb + ql;
+  if (tid == 0) s_gen = *(volatile unsigned long long*)(bar + blockIdx.y) / gridDim.x;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = (r0 + rows_per_block < M) ? r0 + rows_per_block : M;
+  float4 mu, is, sc, sh;
+  bn_load_channel_consts(gamma, beta, save_mean, save_istd, q, mu, is, sc, sh);
+
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+  {
+    int i = 0;
+#pragma unroll 4
+    for (int64_t r = r0 + rl; r < r1; r += RL, ++i) {
+      const int64_t o = r * C + 4 * q;
+      const float4 xv = bn_ld4(x + o);
+      float4 g = bn_ld4(dy + o);
+      if (relu) g = bn_mask_pos(g, y != nullptr ? bn_ld4(y + o) : f4_fma(xv, sc, sh));
+      if (dres != nullptr) bn_st4(dres + o, g);
+      const float4 xh = make_float4((xv.x - mu.x) * is.x, (xv.y - mu.y) * is.y, (xv.z - mu.z) * is.z,
+                                    (xv.w - mu.w) * is.w);
+      a = f4_add(a, g);
+      b = f4_fma(g, xh, b);
+      if (i < cached) {
+        tile[(2 * i) * BNF_T + tid] = g;
+        tile[(2 * i + 1) * BNF_T + tid] = xv;
+      }
+    }
+  }
+  bnf_reduce_rows(red, a, b, tid, rl, RL, qpb);
+  const unsigned long long gen = s_gen;
+  double* acc = accum + (gen & 1ULL) * 2 * (size_t)C;
+  if (rl == 0) bnf_atomic_add8(acc, C, q, a, b);
+  bnf_column_barrier(bar, gen, err);
+
+  float mg[4], mgx[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const double sg = __ldcg(acc + 4 * q + j), sgx = __ldcg(acc + C + 4 * q + j);
+    mg[j] = (float)(sg / (double)M);
+    mgx[j] = (float)(sgx / (double)M);
+    if (blockIdx.x == 0 && rl == 0) {
+      double* other = accum + ((gen + 1ULL) & 1ULL) * 2 * (size_t)C;
+      other[4 * q + j] = 0;
+      other[C + 4 * q + j] = 0;
+      dbeta[4 * q + j] = (float)sg;
+      dgamma[4 * q + j] = (float)sgx;
+    }
+  }
+  {
+    int i = 0;
+#pragma unroll 4
+    for (int64_t r = r0 + rl; r < r1; r += RL, ++i) {
+      const int64_t o = r * C + 4 * q;
+      float4 g, xv;
+      if (i < cached) {
+        g = tile[(2 * i) * BNF_T + tid];
+        xv = tile[(2 * i + 1) * BNF_T + tid];
+      } else {
+        xv = bn_ld4(x + o);
+        if (dres != nullptr) {
+          g = bn_ld4(dres + o);            // already masked by phase 1 (written by this very thread)
+        } else {
+          g = bn_ld4(dy + o);
+          if (relu) g = bn_mask_pos(g, y != nullptr ? bn_ld4(y + o) : f4_fma(xv, sc, sh));
+        }
+      }
+      float4 d;
+      d.x = sc.x * (g.x - mg[0] - (xv.x - mu.x) * is.x * mgx[0]);
+      d.y = sc.y * (g.y - mg[1] - (xv.y - mu.y) * is.y * mgx[1]);
+      d.z = sc.z * (g.z - mg[2] - (xv.z - mu.z) * is.z * mgx[2]);
+      d.w = sc.w * (g.w - mg[3] - (xv.w - mu.w) * is.w * mgx[3]);
+      bn_st4(dx + o, d);
+    }
+  }
+}
+
+namespace {
+struct BnfGeom {
+  int qpb, rpb, iters;
+  dim3 grid;
+};
+
+#define BNF_MAX_COLUMNS 63   /* bar[0..62] column counters, bar[63] error word */
+
+bool bnf_geometry(int64_t M, int C, BnfGeom* g) {
+  if (M < 2 || C <= 0 || (C & 3)) return false;
+  const int quads = C / 4;
+  int qpb = 32;
+  while (quads % qpb) qpb >>= 1;
+  if (qpb < 8) return false;               // < 128 B contiguous per row: leave it to the two-kernel path
+  const int gy = quads / qpb;
+  const int nsm = bn_sm_count();
+  if (gy > nsm || gy > BNF_MAX_COLUMNS) return false;
+  const int RL = BNF_T / qpb;
+  int64_t gx = nsm / gy;
+  const int64_t useful = (M + RL - 1) / RL;
+  if (gx > useful) gx = useful;
+  int64_t rpb = (M + gx - 1) / gx;
+  rpb = (rpb + RL - 1) / RL * RL;
+  if (rpb > (int64_t)1 << 30) return false;
+  gx = (M + rpb - 1) / rpb;
+  g->qpb = qpb;
+  g->rpb = (int)rpb;
+  g->iters = (int)(rpb / RL);
+  g->grid = dim3((unsigned)gx, (unsigned)gy, 1);
+  return true;
+}
+
+int bnf_prepare() {
+  static bool ready[64] = {false};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
+  if (!ready[dev]) {
+    e = cudaFuncSetAttribute(k_bn_fwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(k_bn_bwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
+    if (e != cudaSuccess) return (int)e;
+    ready[dev] = true;
+  }
+  return 0;
+}
+}  // namespace
+
+extern "C" int gk_bn_fused_supported(int64_t M, int C) {
+  BnfGeom g;
+  return bnf_geometry(M, C, &g) ? 1 : 0;
+}
+
+extern "C" int gk_bn_fwd_fused(const float* x, const float* res, float* y, const float* gamma, const float* beta,
+                               float* running_mean, float* running_var, int64_t* num_batches, float* save_mean,
+                               float* save_istd, double* accum, unsigned long long* bar, int64_t M, int C,
+                               float eps, float momentum, int relu, void* stream) {
+  BnfGeom g;
+  if (!bnf_geometry(M, C, &g)) return (int)cudaErrorInvalidValue;
+  if (!bn_aligned(x) || !bn_aligned(y) || !bn_aligned(res) || !bn_aligned(gamma) || !bn_aligned(beta) ||
+      !bn_aligned(save_mean) || !bn_aligned(save_istd))
+    return (int)cudaErrorMisalignedAddress;
+  int rc = bnf_prepare();
+  if (rc) return rc;
+  int cached = g.iters < BNF_SMEM_BUDGET / (BNF_T * 16) ? g.iters : BNF_SMEM_BUDGET / (BNF_T * 16);
+  size_t smem = (size_t)cached * BNF_T * 16;
+  int* err = reinterpret_cast<int*>(bar + BNF_MAX_COLUMNS);
+  void* args[] = {&x, &res, &y, &gamma, &beta, &save_mean, &save_istd, &running_mean, &running_var, &num_batches,
+                  &accum, &bar, &err, &M, &C, &g.rpb, &g.qpb, &cached, &eps, &momentum, &relu};
+  return (int)cudaLaunchCooperativeKernel((void*)k_bn_fwd_fused, g.grid, dim3(BNF_T), args, smem,
+                                          (cudaStream_t)stream);
+}
+
+extern "C" int gk_bn_bwd_fused(const float* dy, const float* x, const float* y, const float* gamma,
+                               const float* beta, const float* save_mean, const float* save_istd, float* dx,
+                               float* dres, float* dgamma, float* dbeta, double* accum, unsigned long long* bar,
+                               int64_t M, int C, int relu, void* stream) {
+  BnfGeom g;
+  if (!bnf_geometry(M, C, &g)) return (int)cudaErrorInvalidValue;
+  if (!bn_aligned(dy) || !bn_aligned(x) || !bn_aligned(y) || !bn_aligned(dx) || !bn_aligned(dres) ||
+      !bn_aligned(gamma) || !bn_aligned(beta) || !bn_aligned(save_mean) || !bn_aligned(save_istd))
+    return (int)cudaErrorMisalignedAddress;
+  if (dres != nullptr && relu && y == nullptr) return (int)cudaErrorInvalidValue;
+  int rc = bnf_prepare();
+  if (rc) return rc;
+  int cached = g.iters < BNF_SMEM_BUDGET / (BNF_T * 32) ? g.iters : BNF_SMEM_BUDGET / (BNF_T * 32);
+  size_t smem = (size_t)cached * BNF_T * 32;
+  int* err = reinterpret_cast<int*>(bar + BNF_MAX_COLUMNS);
+  void* args[] = {&dy, &x, &y, &gamma, &beta, &save_mean, &save_istd, &dx, &dres, &dgamma, &dbeta, &accum,
+                  &bar, &err, &M, &C, &g.rpb, &g.qpb, &cached, &relu};
+  return (int)cudaLaunchCooperativeKernel((void*)k_bn_bwd_fused, g.grid, dim3(BNF_T), args, smem,
+                                          (cudaStream_t)stream);
+}

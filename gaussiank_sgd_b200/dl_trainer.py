@@ -194,6 +194,9 @@ class DLTrainer:
         self.net.to(self.device)
         if self.channels_last:
             self.net.to(memory_format=torch.channels_last)
+            if settings.FUSED_BN:
+                from .models.fuse import fuse_bn_act
+                self.fused_bn_sites = fuse_bn_act(self.net)
         self.accuracy = 0
         self.loss = 0.0
         self.train_iter = 0

@@ -10,6 +10,7 @@ import math
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
+from ..ops.bn import bn_act
 
 
 class PadShortcut(nn.Module):
@@ -36,10 +37,9 @@ class BasicBlock(nn.Module):
         self.downsample = shortcut
 
     def forward(self, x):
-        y = F.relu(self.bn_a(self.conv_a(x)), inplace=True)
-        y = self.bn_b(self.conv_b(y))
+        y = bn_act(self.bn_a, self.conv_a(x))
         s = x if self.downsample is None else self.downsample(x)
-        return F.relu(s + y, inplace=True)
+        return bn_act(self.bn_b, self.conv_b(y), residual=s)
 
 
 class PreActBlock(nn.Module):
@@ -54,10 +54,10 @@ class PreActBlock(nn.Module):
         self.downsample = shortcut
 
     def forward(self, x):
-        a = F.relu(self.bn_a(x), inplace=True)
+        a = bn_act(self.bn_a, x)
         s = x if self.downsample is None else self.downsample(a)
         y = self.conv_a(a)
-        y = self.conv_b(F.relu(self.bn_b(y), inplace=True))
+        y = self.conv_b(bn_act(self.bn_b, y))
         return s + y
 
 
@@ -100,11 +100,11 @@ class CifarResNet(nn.Module):
     def forward(self, x):
         x = self.conv_1_3x3(x)
         if self.final_bn is None:
-            x = F.relu(self.bn_1(x), inplace=True)
+            x = bn_act(self.bn_1, x)
         f1 = self.stage_1(x)
         f2 = self.stage_2(f1)
         f3 = self.stage_3(f2)
-        y = f3 if self.final_bn is None else F.relu(self.final_bn(f3), inplace=True)
+        y = f3 if self.final_bn is None else bn_act(self.final_bn, f3)
         y = self.avgpool(y).flatten(1)
         out = self.classifier(y)
         if self.return_features:

@@ -4,6 +4,7 @@ import math
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
+from ..ops.bn import bn_act
 
 
 class DenseLayer(nn.Module):
@@ -17,9 +18,9 @@ class DenseLayer(nn.Module):
         self.conv2 = nn.Conv2d(inter, growth, 3, padding=1, bias=False) if bottleneck else None
 
     def forward(self, x):
-        y = self.conv1(F.relu(self.bn1(x)))
+        y = self.conv1(bn_act(self.bn1, x))
         if self.conv2 is not None:
-            y = self.conv2(F.relu(self.bn2(y)))
+            y = self.conv2(bn_act(self.bn2, y))
         return torch.cat((x, y), 1)
 
 
@@ -30,7 +31,7 @@ class Transition(nn.Module):
         self.conv1 = nn.Conv2d(cin, cout, 1, bias=False)
 
     def forward(self, x):
-        return F.avg_pool2d(self.conv1(F.relu(self.bn1(x))), 2)
+        return F.avg_pool2d(self.conv1(bn_act(self.bn1, x)), 2)
 
 
 class DenseNet(nn.Module):
@@ -61,7 +62,7 @@ class DenseNet(nn.Module):
                 m.bias.data.zero_()
 
     def forward(self, x):
-        x = F.relu(self.bn1(self.dense(self.conv1(x))))
+        x = bn_act(self.bn1, self.dense(self.conv1(x)))
         return self.fc(F.adaptive_avg_pool2d(x, 1).flatten(1))
 
 

@@ -3,6 +3,7 @@ torchvision model it actually trains (models/imagenet_resnet.py:82-192).  Plan-d
 type plus the number of blocks per stage."""
 import torch.nn as nn
 import torch.nn.functional as F
+from ..ops.bn import bn_act
 
 PLANS = {18: ('basic', (2, 2, 2, 2)), 34: ('basic', (3, 4, 6, 3)), 50: ('bottleneck', (3, 4, 6, 3)),
          101: ('bottleneck', (3, 4, 23, 3)), 152: ('bottleneck', (3, 8, 36, 3))}
@@ -24,13 +25,11 @@ class Block(nn.Module):
             self.downsample = nn.Sequential(nn.Conv2d(cin, cout, 1, stride, bias=False), nn.BatchNorm2d(cout))
 
     def forward(self, x):
-        y = x
+        s = x if self.downsample is None else bn_act(self.downsample[1], self.downsample[0](x), relu=False)
+        y, last = x, len(self.convs) - 1
         for i, (conv, bn) in enumerate(zip(self.convs, self.bns)):
-            y = bn(conv(y))
-            if i + 1 < len(self.convs):
-                y = F.relu(y, inplace=True)
-        s = x if self.downsample is None else self.downsample(x)
-        return F.relu(y + s, inplace=True)
+            y = bn_act(bn, conv(y), residual=s if i == last else None)
+        return y
 
 
 class ResNet(nn.Module):
@@ -53,7 +52,7 @@ class ResNet(nn.Module):
                 nn.init.kaiming_normal_(m.weight, mode='fan_out', nonlinearity='relu')
 
     def forward(self, x):
-        x = F.max_pool2d(F.relu(self.bn1(self.conv1(x)), inplace=True), 3, 2, 1)
+        x = F.max_pool2d(bn_act(self.bn1, self.conv1(x)), 3, 2, 1)
         x = F.adaptive_avg_pool2d(self.layers(x), 1).flatten(1)
         return self.fc(x)
 

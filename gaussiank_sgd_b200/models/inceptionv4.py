@@ -8,6 +8,7 @@ Every block is described as a list of branches; a branch is a list of layer spec
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
+from ..ops.bn import bn_act
 
 
 class ConvBN(nn.Module):
@@ -17,7 +18,7 @@ class ConvBN(nn.Module):
         self.bn = nn.BatchNorm2d(cout, eps=0.001, momentum=0.1, affine=True)
 
     def forward(self, x):
-        return F.relu(self.bn(self.conv(x)), inplace=True)
+        return bn_act(self.bn, self.conv(x))
 
 
 def _chain(cin, specs):

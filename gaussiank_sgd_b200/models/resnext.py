@@ -2,6 +2,7 @@
 grouped 3x3 convolutions, cardinality 8 or 16, base width 64."""
 import torch.nn as nn
 import torch.nn.functional as F
+from ..ops.bn import bn_act
 
 
 class ResNeXtBottleneck(nn.Module):
@@ -22,11 +23,10 @@ class ResNeXtBottleneck(nn.Module):
             self.downsample = nn.Sequential(nn.Conv2d(cin, cout, 1, stride, bias=False), nn.BatchNorm2d(cout))
 
     def forward(self, x):
-        y = F.relu(self.bn_reduce(self.conv_reduce(x)), inplace=True)
-        y = F.relu(self.bn(self.conv_conv(y)), inplace=True)
-        y = self.bn_expand(self.conv_expand(y))
+        y = bn_act(self.bn_reduce, self.conv_reduce(x))
+        y = bn_act(self.bn, self.conv_conv(y))
         s = x if self.downsample is None else self.downsample(x)
-        return F.relu(s + y, inplace=True)
+        return bn_act(self.bn_expand, self.conv_expand(y), residual=s)
 
 
 class CifarResNeXt(nn.Module):
@@ -52,7 +52,7 @@ class CifarResNeXt(nn.Module):
                 m.bias.data.zero_()
 
     def forward(self, x):
-        x = F.relu(self.bn_1(self.conv_1_3x3(x)), inplace=True)
+        x = bn_act(self.bn_1, self.conv_1_3x3(x))
         return self.classifier(F.adaptive_avg_pool2d(self.stages(x), 1).flatten(1))
 
 

@@ -1,0 +1,150 @@
+"""Fused training-mode BatchNorm2d (+ residual add) (+ ReLU) on channels_last fp32 activations.
+
+The reference's CNNs take ``bn -> (+ identity) -> relu`` from torch.nn as separate modules
+(torchvision ResNet-50 through dl_trainer.py:90, models/resnet.py, models/vgg.py ...).  On a B200 those
+HBM-bound passes are 40 % of the ResNet-50 step (profiles/step_breakdown_resnet50_v1.txt), so here they
+are two kernels forward and two backward (csrc/gk_bn.cu: ``gk_bn_fwd`` / ``gk_bn_bwd``).
+
+``bn_act(bn, x, residual=None, relu=True)`` is the entry point: ``bn`` stays an ordinary
+``nn.BatchNorm2d`` (same parameters, buffers, state_dict keys); anything the kernels do not cover
+(CPU tensors, eval mode, non-fp32, NCHW-contiguous input, C % 4 != 0, momentum=None) takes the plain
+PyTorch path, so the numerics contract is "same as F.batch_norm + add + relu".
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+from torch.autograd.function import once_differentiable
+
+from .. import settings
+from . import native
+from . import chain as _chain
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _scratch(bn, device, C):
+    """Per-layer accumulators (2*C doubles) and ticket; zeroed once, the kernels leave them zero."""
+    sc = bn.__dict__.get("_gk_bn_scratch")
+    if sc is None or sc[0].device != device or sc[0].numel() != 2 * C:
+        sc = (torch.zeros(2 * C, dtype=torch.float64, device=device),
+              torch.zeros(1, dtype=torch.int32, device=device))
+        bn.__dict__["_gk_bn_scratch"] = sc
+    return sc
+
+
+def _scratch_coop(bn, device, C, M):
+    """Scratch of the single-kernel path, one per (layer, M): 4*C doubles and 64 barrier words, zero at
+    creation and never reset (include/gk_b200.h)."""
+    table = bn.__dict__.setdefault("_gk_bn_coop", {})
+    key = (str(device), C, M)
+    sc = table.get(key)
+    if sc is None:
+        sc = (torch.zeros(4 * C, dtype=torch.float64, device=device),
+              torch.zeros(64, dtype=torch.int64, device=device))
+        table[key] = sc
+    return sc
+
+
+def coop_errors(model) -> int:
+    """Number of layers whose barrier wait ever expired (0 on a healthy run)."""
+    bad = 0
+    for m in model.modules():
+        for _, bar in m.__dict__.get("_gk_bn_coop", {}).values():
+            bad += int(bar[63].item() != 0)
+    return bad
+
+
+def _rows_view_ok(t):
+    return t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last) and t.data_ptr() % 16 == 0
+
+
+def eligible(bn, x, residual=None) -> bool:
+    if not (x.is_cuda and x.dtype == torch.float32 and bn.training and bn.affine and x.dim() == 4):
+        return False
+    if bn.momentum is None or x.shape[1] % 4 or x.numel() == 0 or x.numel() // x.shape[1] < 2:
+        return False
+    if bn.weight.dtype != torch.float32 or not _rows_view_ok(x):
+        return False
+    if residual is not None and (residual.shape != x.shape or residual.dtype != x.dtype):
+        return False
+    return True
+
+
+class _BnAct(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, residual, weight, bias, bn, relu):
+        N, C, H, W = x.shape
+        M = N * H * W
+        if residual is not None and not _rows_view_ok(residual):
+            residual = residual.contiguous(memory_format=torch.channels_last)
+        y = torch.empty_like(x, memory_format=torch.channels_last)
+        stats = torch.empty(2, C, dtype=torch.float32, device=x.device)
+        track = bn.track_running_stats and bn.running_mean is not None
+        lib = native.cuda_lib()
+        ctx.coop = bool(settings.FUSED_BN_COOP and lib.gk_bn_fused_supported(M, C))
+        head = (_ptr(x), _ptr(residual), _ptr(y), _ptr(weight), _ptr(bias),
+                _ptr(bn.running_mean) if track else None, _ptr(bn.running_var) if track else None,
+                _ptr(bn.num_batches_tracked) if track else None, stats[0].data_ptr(), stats[1].data_ptr())
+        tail = (M, C, float(bn.eps), float(bn.momentum), int(relu), _stream())
+        if ctx.coop:
+            accum, bar = ctx.scratch = _scratch_coop(bn, x.device, C, M)
+            native.check(lib.gk_bn_fwd_fused(*head, accum.data_ptr(), bar.data_ptr(), *tail), "gk_bn_fwd_fused")
+            _chain.LAUNCHES["n"] += 1
+        else:
+            accum, ticket = ctx.scratch = _scratch(bn, x.device, C)
+            native.check(lib.gk_bn_fwd(*head, accum.data_ptr(), ticket.data_ptr(), *tail), "gk_bn_fwd")
+            _chain.LAUNCHES["n"] += 2
+        ctx.relu = bool(relu)
+        ctx.has_res = residual is not None
+        # the ReLU mask is recomputed from x unless a residual went into the activation
+        ctx.save_for_backward(x, weight, bias, stats, y if (relu and residual is not None) else None)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        x, weight, bias, stats, y = ctx.saved_tensors
+        N, C, H, W = x.shape
+        M = N * H * W
+        if not _rows_view_ok(dy):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dx = torch.empty_like(x, memory_format=torch.channels_last)
+        dres = torch.empty_like(x, memory_format=torch.channels_last) if (ctx.has_res and ctx.relu) else None
+        # separate tensors: autograd hands a fresh dense tensor to .grad without a copy, a view it would clone
+        dgamma = torch.empty(C, dtype=torch.float32, device=x.device)
+        dbeta = torch.empty(C, dtype=torch.float32, device=x.device)
+        lib = native.cuda_lib()
+        head = (_ptr(dy), _ptr(x), _ptr(y), _ptr(weight), _ptr(bias), stats[0].data_ptr(), stats[1].data_ptr(),
+                _ptr(dx), _ptr(dres), dgamma.data_ptr(), dbeta.data_ptr())
+        if ctx.coop:
+            accum, bar = ctx.scratch
+            native.check(lib.gk_bn_bwd_fused(*head, accum.data_ptr(), bar.data_ptr(), M, C, int(ctx.relu),
+                                             _stream()), "gk_bn_bwd_fused")
+            _chain.LAUNCHES["n"] += 1
+        else:
+            accum, ticket = ctx.scratch
+            coef = torch.empty(2, C, dtype=torch.float32, device=x.device)
+            native.check(lib.gk_bn_bwd(*head, coef.data_ptr(), accum.data_ptr(), ticket.data_ptr(), M, C,
+                                       int(ctx.relu), _stream()), "gk_bn_bwd")
+            _chain.LAUNCHES["n"] += 2
+        if ctx.has_res and dres is None:      # no ReLU: the residual branch receives dy unchanged
+            dres = dy
+        return dx, (dres if ctx.has_res else None), dgamma, dbeta, None, None
+
+
+def bn_act(bn, x, residual=None, relu=True):
+    """``relu(bn(x) + residual)`` with ``residual`` and ``relu`` optional; ``bn`` is an nn.BatchNorm2d."""
+    if settings.FUSED_BN and eligible(bn, x, residual):
+        return _BnAct.apply(x, residual, bn.weight, bn.bias, bn, relu)
+    # plain path; BatchNorm2d.forward directly because ``bn`` may be a FusedBNReLU (models/fuse.py)
+    y = torch.nn.BatchNorm2d.forward(bn, x) if isinstance(bn, torch.nn.BatchNorm2d) else bn(x)
+    if residual is not None:
+        y = y + residual
+    return F.relu(y, inplace=True) if relu else y

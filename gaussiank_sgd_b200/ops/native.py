@@ -100,12 +100,18 @@ def _nvcc() -> str:
     return "nvcc"
 
 
+CUDA_SOURCES = ("gk_cuda.cu", "gk_bn.cu")
+
+
+def _cuda_deps():
+    return [os.path.join(CSRC, f) for f in CUDA_SOURCES] + [os.path.join(INCLUDE, "gk_b200.h")]
+
+
 def build_cuda(force: bool = False, verbose: bool = False) -> str:
-    """Cross-compile csrc/gk_cuda.cu for sm_100a (works without a GPU)."""
-    src = os.path.join(CSRC, "gk_cuda.cu")
-    hdr = os.path.join(INCLUDE, "gk_b200.h")
-    if force or _stale(CUDA_SO, [src, hdr]):
-        cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", CUDA_SO + ".tmp", src]
+    """Cross-compile csrc/gk_cuda.cu + csrc/gk_bn.cu for sm_100a into one library (works without a GPU)."""
+    srcs = [os.path.join(CSRC, f) for f in CUDA_SOURCES]
+    if force or _stale(CUDA_SO, _cuda_deps()):
+        cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", CUDA_SO + ".tmp"] + srcs
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
@@ -145,7 +151,7 @@ def cuda_lib():
     is the only path."""
     with _lock:
         if "cuda" not in _libs:
-            if _stale(CUDA_SO, [os.path.join(CSRC, "gk_cuda.cu"), os.path.join(INCLUDE, "gk_b200.h")]):
+            if _stale(CUDA_SO, _cuda_deps()):
                 build_cuda()
             lib = C.CDLL(CUDA_SO)
             ch, ds, sr = C.POINTER(GkChain), C.POINTER(GkDst), C.POINTER(GkSrc)
@@ -166,6 +172,11 @@ def cuda_lib():
             _proto(lib, "gk_bucket_reconstruct", [ch, _P, _P, _P])
             _proto(lib, "gk_copy", [_P, _P, C.c_int64, _P])
             _proto(lib, "gk_histogram", [_P, C.c_int64, C.c_float, C.c_float, C.c_int32, _P, _P])
+            _proto(lib, "gk_bn_fwd", [_P] * 12 + [C.c_int64, C.c_int32, C.c_float, C.c_float, C.c_int32, _P])
+            _proto(lib, "gk_bn_bwd", [_P] * 14 + [C.c_int64, C.c_int32, C.c_int32, _P])
+            _proto(lib, "gk_bn_fused_supported", [C.c_int64, C.c_int32])
+            _proto(lib, "gk_bn_fwd_fused", [_P] * 12 + [C.c_int64, C.c_int32, C.c_float, C.c_float, C.c_int32, _P])
+            _proto(lib, "gk_bn_bwd_fused", [_P] * 13 + [C.c_int64, C.c_int32, C.c_int32, _P])
             _proto(lib, "gk_ipc_alloc", [C.c_uint64, C.POINTER(C.c_void_p), C.c_char_p])
             _proto(lib, "gk_ipc_open", [C.c_char_p, C.POINTER(C.c_void_p)])
             _proto(lib, "gk_ipc_close", [_P])

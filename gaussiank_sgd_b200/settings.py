@@ -65,6 +65,8 @@ PROFILE_PHASES = _flag("PROFILE_PHASES", False)     # CUDA-event timers for comp
 CUDA_GRAPH = _flag("CUDA_GRAPH", True)              # capture the training step in a CUDA graph on GPUs
 CHANNELS_LAST = _flag("CHANNELS_LAST", True)        # NHWC convolutions on GPUs
 SYNTHETIC_POOL = _flag("SYNTHETIC_POOL", True)      # pre-collated pinned batches for synthetic image data
+FUSED_BN = _flag("FUSED_BN", True)                  # BN(+residual)+ReLU through csrc/gk_bn.cu on GPUs (ops/bn.py)
+FUSED_BN_COOP = _flag("FUSED_BN_COOP", True)        # single cooperative kernel per direction where the shape allows
 CUDNN_BENCHMARK = _flag("CUDNN_BENCHMARK", True)    # the reference pins benchmark=False, deterministic=True
 
 hostname = socket.gethostname()

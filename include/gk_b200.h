@@ -237,6 +237,42 @@ int gk_copy(float* dst, const float* src, int64_t n, void* stream);
 int gk_histogram(const float* x, int64_t n, float lo, float hi, int32_t nbins, uint32_t* out,
                  void* stream);
 
+/* Fused training-mode batch norm on NHWC fp32 activations viewed as x[M = N*H*W][C], C % 4 == 0, every
+ * pointer 16-byte aligned (csrc/gk_bn.cu).  The reference takes BN, ReLU and the residual add from
+ * torch.nn as three to four separate passes (models/resnet.py via torchvision); here
+ *   gk_bn_fwd:  y = [relu]( (x - mean) * istd * gamma + beta [+ res] )     (res may be NULL)
+ *               save_mean / save_istd written, running stats (may be NULL) and *num_batches (may be NULL)
+ *               updated with torch.nn.BatchNorm2d semantics (biased batch variance, unbiased running)
+ *   gk_bn_bwd:  g = relu ? dy * (forward output > 0) : dy; dgamma = sum g*xhat, dbeta = sum g,
+ *               dx = gamma*istd * (g - mean g - xhat * mean g*xhat); if dres != NULL it receives g (the
+ *               residual branch's gradient) and y (the saved forward output) must be given; with y == NULL
+ *               the ReLU mask is recomputed from x.
+ * Scratch owned by the caller, per layer or per stream: accum = 2*C doubles and *ticket = one uint32, both
+ * zero before the first call (the kernels leave them zero), coef = 2*C floats.  Two launches each, no host
+ * synchronisation, no allocation. */
+int gk_bn_fwd(const float* x, const float* res, float* y, const float* gamma, const float* beta,
+              float* running_mean, float* running_var, int64_t* num_batches, float* save_mean, float* save_istd,
+              double* accum, uint32_t* ticket, int64_t M, int C, float eps, float momentum, int relu, void* stream);
+int gk_bn_bwd(const float* dy, const float* x, const float* y, const float* gamma, const float* beta,
+              const float* save_mean, const float* save_istd, float* dx, float* dres, float* dgamma, float* dbeta,
+              float* coef, double* accum, uint32_t* ticket, int64_t M, int C, int relu, void* stream);
+
+/* Single-kernel variants of the two calls above (one cooperative launch each; the activation slab of
+ * every block stays in shared memory between the statistics and the apply phase, so x / dy are read from
+ * HBM once).  Available when gk_bn_fused_supported(M, C) returns 1 (C/4 has a power-of-two factor >= 8 and
+ * the channel slabs fit the SM count).  Scratch, per (layer, M): accum = 4*C doubles (two parities) and
+ * bar = 64 uint64 (bar[0..62] column barriers that only grow, low word of bar[63] = error flag set if a
+ * barrier wait expired); both zero before the first call, never reset afterwards; the same scratch serves
+ * forward and backward of one layer as long as M and C stay the same. */
+int gk_bn_fused_supported(int64_t M, int C);
+int gk_bn_fwd_fused(const float* x, const float* res, float* y, const float* gamma, const float* beta,
+                    float* running_mean, float* running_var, int64_t* num_batches, float* save_mean,
+                    float* save_istd, double* accum, unsigned long long* bar, int64_t M, int C, float eps,
+                    float momentum, int relu, void* stream);
+int gk_bn_bwd_fused(const float* dy, const float* x, const float* y, const float* gamma, const float* beta,
+                    const float* save_mean, const float* save_istd, float* dx, float* dres, float* dgamma,
+                    float* dbeta, double* accum, unsigned long long* bar, int64_t M, int C, int relu, void* stream);
+
 /* Peer-memory plumbing of the P2P transport (set-up time only; the only allocating entry
  * points).  gk_ipc_alloc: cudaMalloc + zero + IPC handle (64 bytes) for the local receive arena;
  * gk_ipc_open maps a peer's arena into this process.  Replaces Horovod's allgather buffers

@@ -1,0 +1,226 @@
+"""Fused BN(+residual)(+ReLU): csrc/gk_bn.cu against F.batch_norm + add + relu in fp32, and the model
+rewiring of models/fuse.py (CPU: the rewired model must compute exactly what the original did)."""
+import copy
+
+import pytest
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from gaussiank_sgd_b200 import settings
+from gaussiank_sgd_b200.models.fuse import FusedBNReLU, fuse_bn_act
+from gaussiank_sgd_b200.ops.bn import bn_act, coop_errors, eligible
+
+
+# ------------------------------------------------------------------------------------- CPU
+def test_bn_act_cpu_fallback_matches_modules():
+    torch.manual_seed(0)
+    bn = nn.BatchNorm2d(8)
+    x, r = torch.randn(4, 8, 5, 5), torch.randn(4, 8, 5, 5)
+    ref_bn = copy.deepcopy(bn)
+    want = F.relu(ref_bn(x) + r)
+    got = bn_act(bn, x, residual=r, relu=True)
+    assert torch.equal(got, want)
+    assert torch.equal(bn.running_mean, ref_bn.running_mean)
+    assert int(bn.num_batches_tracked) == 1
+    assert not eligible(bn, x)
+
+
+def test_fuse_torchvision_resnet_cpu_equivalence():
+    tv = pytest.importorskip("torchvision")
+    torch.manual_seed(1)
+    for ctor in (tv.models.resnet18, tv.models.resnet50):
+        net = ctor(num_classes=10)
+        ref = copy.deepcopy(net)
+        keys = list(net.state_dict().keys())
+        sites = fuse_bn_act(net)
+        assert sites == sum(isinstance(m, nn.BatchNorm2d) for m in net.modules())
+        assert list(net.state_dict().keys()) == keys
+        x = torch.randn(2, 3, 64, 64)
+        out, want = net(x), ref(x)
+        assert torch.equal(out, want)
+        out.sum().backward()
+        want.sum().backward()
+        for (n, p), (_, q) in zip(net.named_parameters(), ref.named_parameters()):
+            assert torch.equal(p.grad, q.grad), n
+        net.eval(), ref.eval()
+        assert torch.equal(net(x), ref(x))
+        clone = copy.deepcopy(net)               # bound forwards follow the copy
+        assert torch.equal(clone(x), ref(x))
+
+
+def test_fuse_sequential_pattern_cpu():
+    torch.manual_seed(2)
+    from gaussiank_sgd_b200.models import VGG
+    net = VGG('VGG16')
+    ref = copy.deepcopy(net)
+    keys = list(net.state_dict().keys())
+    n_bn = sum(isinstance(m, nn.BatchNorm2d) for m in net.modules())
+    assert fuse_bn_act(net) == n_bn > 0
+    assert list(net.state_dict().keys()) == keys
+    assert sum(isinstance(m, FusedBNReLU) for m in net.modules()) == n_bn
+    x = torch.randn(2, 3, 32, 32)
+    assert torch.equal(net(x), ref(x))
+    net.load_state_dict(ref.state_dict())
+
+
+# ------------------------------------------------------------------------------------- GPU
+def _reference(bn, x, res, relu):
+    y = F.batch_norm(x, bn.running_mean, bn.running_var, bn.weight, bn.bias, True, bn.momentum, bn.eps)
+    if res is not None:
+        y = y + res
+    return F.relu(y) if relu else y
+
+
+CASES = [  # N, C, H, W
+    (32, 64, 28, 28), (8, 256, 14, 14), (4, 96, 9, 9), (2, 12, 5, 7), (16, 2048, 7, 7), (3, 512, 1, 1), (2, 4, 3, 3)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", CASES)
+@pytest.mark.parametrize("relu,with_res", [(True, False), (True, True), (False, False), (False, True)])
+@pytest.mark.parametrize("coop", [True, False])
+def test_fused_bn_matches_pytorch(shape, relu, with_res, coop, monkeypatch):
+    monkeypatch.setattr(settings, "FUSED_BN_COOP", coop)
+    torch.manual_seed(sum(shape))
+    dev = torch.device("cuda:0")
+    N, C, H, W = shape
+    bn = nn.BatchNorm2d(C).to(dev)
+    with torch.no_grad():
+        bn.weight.uniform_(0.5, 1.5)
+        bn.bias.uniform_(-0.5, 0.5)
+        bn.running_mean.normal_()
+        bn.running_var.uniform_(0.5, 2.0)
+    ref = copy.deepcopy(bn)
+    x = (torch.randn(N, C, H, W, device=dev) * 2 + 0.5).contiguous(memory_format=torch.channels_last)
+    res = torch.randn(N, C, H, W, device=dev).contiguous(memory_format=torch.channels_last) if with_res else None
+    x1, x2 = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    r1 = res.clone().requires_grad_(True) if with_res else None
+    r2 = res.clone().requires_grad_(True) if with_res else None
+    assert eligible(bn, x1, r1)
+    for rep in range(2):                       # twice: the scratch must come back zeroed
+        y = bn_act(bn, x1, residual=r1, relu=relu)
+        want = _reference(ref, x2, r2, relu)
+        assert y.is_contiguous(memory_format=torch.channels_last)
+        torch.testing.assert_close(y, want, rtol=1e-5, atol=2e-5)
+        torch.testing.assert_close(bn.running_mean, ref.running_mean, rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(bn.running_var, ref.running_var, rtol=1e-5, atol=1e-6)
+        ref.num_batches_tracked += 1           # F.batch_norm does not touch it, the module does
+        assert int(bn.num_batches_tracked) == int(ref.num_batches_tracked) == rep + 1
+        dy = torch.randn_like(y)
+        for t in (x1, x2, r1, r2, bn.weight, bn.bias, ref.weight, ref.bias):
+            if t is not None:
+                t.grad = None
+        y.backward(dy)
+        want.backward(dy)
+        scale = max(1.0, float(dy.abs().max()))
+        # an output within rounding of zero may land on either side of the ReLU in the two implementations
+        sure = (want.detach().abs() > 1e-5) if relu else torch.ones_like(want, dtype=torch.bool)
+        torch.testing.assert_close(x1.grad * sure, x2.grad * sure, rtol=1e-4, atol=2e-5 * scale)
+        M = N * H * W
+        torch.testing.assert_close(bn.weight.grad, ref.weight.grad, rtol=1e-4, atol=1e-5 * M ** 0.5 * 4)
+        torch.testing.assert_close(bn.bias.grad, ref.bias.grad, rtol=1e-4, atol=1e-5 * M ** 0.5 * 4)
+        if with_res:
+            assert torch.equal(r1.grad * sure, r2.grad * sure)
+    if "_gk_bn_scratch" in bn.__dict__:
+        sc = bn.__dict__["_gk_bn_scratch"]
+        assert float(sc[0].abs().sum()) == 0.0 and int(sc[1]) == 0
+    assert coop_errors(bn) == 0
+    if coop and C % 32 == 0:
+        assert "_gk_bn_coop" in bn.__dict__       # the single-kernel path really ran
+
+
+@pytest.mark.gpu
+def test_fused_bn_ineligible_inputs_fall_back():
+    dev = torch.device("cuda:0")
+    bn = nn.BatchNorm2d(6).to(dev)                       # C % 4 != 0
+    x = torch.randn(4, 6, 5, 5, device=dev).contiguous(memory_format=torch.channels_last)
+    assert not eligible(bn, x)
+    torch.testing.assert_close(bn_act(copy.deepcopy(bn), x), F.relu(copy.deepcopy(bn)(x)))
+    bn8 = nn.BatchNorm2d(8).to(dev)
+    xc = torch.randn(4, 8, 5, 5, device=dev)             # NCHW-contiguous
+    assert not eligible(bn8, xc)
+    bn8.eval()
+    xl = xc.contiguous(memory_format=torch.channels_last)
+    assert not eligible(bn8, xl)
+    torch.testing.assert_close(bn_act(bn8, xl), F.relu(bn8(xl)))
+
+
+@pytest.mark.gpu
+def test_fused_resnet50_step_matches_unfused():
+    tv = pytest.importorskip("torchvision")
+    torch.manual_seed(3)
+    dev = torch.device("cuda:0")
+    net = tv.models.resnet50(num_classes=100).to(dev).to(memory_format=torch.channels_last)
+    ref = copy.deepcopy(net)
+    assert fuse_bn_act(net) == 53
+    x = torch.randn(8, 3, 96, 96, device=dev).contiguous(memory_format=torch.channels_last)
+    t = torch.randint(0, 100, (8,), device=dev)
+    old = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    ref64 = copy.deepcopy(ref).double()          # what both fp32 runs are approximations of
+    try:
+        l1 = F.cross_entropy(net(x), t)
+        l2 = F.cross_entropy(ref(x), t)
+        l3 = F.cross_entropy(ref64(x.double()), t)
+        l1.backward()
+        l2.backward()
+        l3.backward()
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+    assert abs(l1.item() - l3.item()) < 1e-4 * max(1.0, abs(l3.item()))
+    ours = theirs = 0.0
+    for (n, p), (_, q), (_, d) in zip(net.named_parameters(), ref.named_parameters(), ref64.named_parameters()):
+        den = float(d.grad.norm()) + 1e-12
+        ours = max(ours, float((p.grad.double() - d.grad).norm()) / den)
+        theirs = max(theirs, float((q.grad.double() - d.grad).norm()) / den)
+    # fp32 round-off is amplified by 53 BN layers and ReLU masks; the fused path must not be worse than cuDNN's
+    assert ours < max(3.0 * theirs, 1e-3), (ours, theirs)
+    assert coop_errors(net) == 0
+    for (n, b), (_, c) in zip(net.named_buffers(), ref.named_buffers()):
+        torch.testing.assert_close(b.float(), c.float(), rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.gpu
+def test_fused_bn_switch_off():
+    dev = torch.device("cuda:0")
+    bn = nn.BatchNorm2d(8).to(dev)
+    x = torch.randn(4, 8, 5, 5, device=dev).contiguous(memory_format=torch.channels_last)
+    old = settings.FUSED_BN
+    settings.FUSED_BN = False
+    try:
+        bn_act(bn, x)
+        assert "_gk_bn_scratch" not in bn.__dict__
+    finally:
+        settings.FUSED_BN = old
+
+
+@pytest.mark.gpu
+def test_fused_bn_in_cuda_graph():
+    """The cooperative launches are capturable; replays keep producing what eager produces."""
+    torch.manual_seed(5)
+    dev = torch.device("cuda:0")
+    bn = nn.BatchNorm2d(64).to(dev)
+    ref = copy.deepcopy(bn)
+    x = torch.randn(8, 64, 14, 14, device=dev).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    r = torch.randn_like(x).requires_grad_(True)
+    dy = torch.randn_like(x)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(3):                              # warm-up: scratch allocation, attribute set-up
+            gx0, gr0, gw0, gb0 = torch.autograd.grad(bn_act(bn, x, residual=r), [x, r, bn.weight, bn.bias], dy)
+    torch.cuda.current_stream().wait_stream(side)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        y = bn_act(bn, x, residual=r)
+        gx, gr, gw, gb = torch.autograd.grad(y, [x, r, bn.weight, bn.bias], dy)
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    want = F.relu(F.batch_norm(x, ref.running_mean, ref.running_var, ref.weight, ref.bias, True, 0.1, ref.eps) + r)
+    torch.testing.assert_close(y, want, rtol=1e-5, atol=2e-5)
+    torch.testing.assert_close(gx, gx0, rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(gw, gw0, rtol=1e-6, atol=1e-5)
+    assert int(bn.num_batches_tracked) == 6
+    assert coop_errors(bn) == 0
