@@ -325,33 +325,53 @@ extern "C" int gk_bn_bwd(const float* dy, const float* x, const float* y, const 
 // gx*gy <= number of SMs, one block per SM, launched with cudaLaunchCooperativeKernel so that all blocks
 // are resident while they wait for each other.  Rows that do not fit in shared memory (the four largest
 // ResNet-50 shapes at batch 32) are re-read from L2/HBM in the second phase.
+//
+// Scratch words (uint64) of one layer: bar[2y] arrivals and bar[2y+1] generation of channel slab y
+// (y < BNF_MAX_COLUMNS), bar[96..111] optional phase time stamps, bar[127] error flag.
 #define BNF_T 512
 #define BNF_SMEM_BUDGET (200 * 1024)
 #define BNF_SPIN_LIMIT (1 << 22)
+#define BNF_MAX_COLUMNS 48
+#define BNF_STAMP_WORD 96
+#define BNF_ERR_WORD 127
 
-__device__ __forceinline__ unsigned long long bnf_ld_acquire(const unsigned long long* p) {
+__device__ __forceinline__ unsigned long long bnf_ld_relaxed(const unsigned long long* p) {
   unsigned long long v;
-  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ void bnf_st_release(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long bnf_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
 
-// Barrier among the gridDim.x blocks that share blockIdx.y.  bar[y] only ever grows: generation g of a
-// column ends when it reaches (g+1)*gridDim.x, so nothing has to be reset and consecutive launches may
-// reuse the counter.  The wait is bounded: on expiry *err is set and the block carries on (wrong numbers,
-// no hang) — it can only expire if the blocks were not co-resident, which the cooperative launch rules out.
-__device__ __forceinline__ void bnf_column_barrier(unsigned long long* bar, unsigned long long gen, int* err) {
+// Sense-reversing barrier among the gridDim.x blocks that share blockIdx.y.  `gen` is the generation word
+// as read when the block started (it cannot advance before this block arrives).  The last block to arrive
+// resets the arrival count and publishes gen+1; the others poll the generation word.  The wait is bounded:
+// on expiry the error word is set and the block carries on (wrong numbers, no hang) — that can only happen
+// if the blocks were not co-resident, which the cooperative launch rules out.
+__device__ __forceinline__ void bnf_column_barrier(unsigned long long* bar, unsigned long long gen) {
   __syncthreads();
   if (threadIdx.x == 0) {
+    unsigned long long* arrive = bar + 2 * blockIdx.y;
+    unsigned long long* genp = arrive + 1;
     __threadfence();
-    atomicAdd(bar + blockIdx.y, 1ULL);
-    const unsigned long long target = (gen + 1ULL) * (unsigned long long)gridDim.x;
-    int spins = 0;
-    while (bnf_ld_acquire(bar + blockIdx.y) < target) {
-      if (++spins > BNF_SPIN_LIMIT) {
-        *err = 1;
-        break;
+    const unsigned long long old = atomicAdd(arrive, 1ULL);
+    if (old == (unsigned long long)gridDim.x - 1ULL) {
+      *arrive = 0;
+      bnf_st_release(genp, gen + 1ULL);
+    } else {
+      int spins = 0;
+      while (bnf_ld_relaxed(genp) == gen) {
+        if (++spins > BNF_SPIN_LIMIT) {
+          *reinterpret_cast<int*>(bar + BNF_ERR_WORD) = 1;
+          break;
+        }
       }
-      __nanosleep(32);
     }
     __threadfence();
   }
@@ -382,57 +402,117 @@ __device__ __forceinline__ void bnf_atomic_add8(double* acc, int C, int q, float
   atomicAdd(acc + C + 4 * q + 2, (double)b.z); atomicAdd(acc + C + 4 * q + 3, (double)b.w);
 }
 
+// the eight totals of one channel quad, fetched from L2 in one batch
+__device__ __forceinline__ void bnf_load_totals(const double* acc, int C, int q, double* s, double* ss) {
+  const double2 s01 = __ldcg(reinterpret_cast<const double2*>(acc + 4 * q));
+  const double2 s23 = __ldcg(reinterpret_cast<const double2*>(acc + 4 * q + 2));
+  const double2 t01 = __ldcg(reinterpret_cast<const double2*>(acc + C + 4 * q));
+  const double2 t23 = __ldcg(reinterpret_cast<const double2*>(acc + C + 4 * q + 2));
+  s[0] = s01.x; s[1] = s01.y; s[2] = s23.x; s[3] = s23.y;
+  ss[0] = t01.x; ss[1] = t01.y; ss[2] = t23.x; ss[3] = t23.y;
+}
+
+__device__ __forceinline__ void bnf_cp_async16(void* smem, const void* gmem) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void bnf_cp_async_wait_all() {
+  asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+
+__device__ __forceinline__ float bnf_rsqrt(float a) {   // rsqrt.approx plus one Newton step: < 1 ulp
+  const float y = rsqrtf(a);
+  return y * fmaf(-0.5f * a * y, y, 1.5f);
+}
+
+// flags: bit 0 = ReLU, bit 1 = write phase time stamps (block 0,0 only; profiling aid)
 __global__ void __launch_bounds__(BNF_T, 1)
 k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float* __restrict__ y,
                const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ save_mean,
                float* __restrict__ save_istd, float* running_mean, float* running_var, int64_t* num_batches,
-               double* accum /* [2 parities][2][C] */, unsigned long long* bar, int* err, int64_t M, int C,
-               int rows_per_block, int qpb, int cached, float eps, float momentum, int relu) {
+               double* accum /* [2 parities][2][C] */, unsigned long long* bar, int64_t M, int C,
+               int rows_per_block, int qshift, int cached, float eps, float momentum, double inv_m, double unbias,
+               int flags) {
   extern __shared__ float4 tile[];          // [cached][BNF_T]
   __shared__ float4 red[2][BNF_T];
   __shared__ unsigned long long s_gen;
   const int tid = threadIdx.x;
-  const int ql = tid % qpb, rl = tid / qpb, RL = BNF_T / qpb;
+  const int qpb = 1 << qshift, ql = tid & (qpb - 1), rl = tid >> qshift, RL = BNF_T >> qshift;
   const int q = blockIdx.y * qpb + ql;
-  if (tid == 0) s_gen = *(volatile unsigned long long*)(bar + blockIdx.y) / gridDim.x;
+  const bool stamp = (flags & 2) && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0;
+  unsigned long long* ts = bar + BNF_STAMP_WORD;
+  if (stamp) ts[0] = bnf_now();
+  if (tid == 0 && gridDim.x > 1) s_gen = bnf_ld_relaxed(bar + 2 * blockIdx.y + 1);
+  const int relu = flags & 1;
   const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
   const int64_t r1 = (r0 + rows_per_block < M) ? r0 + rows_per_block : M;
   const float* xp = x + 4 * q;
 
-  // phase 1: one read of x; sums and the shared-memory copy
-  float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-  {
-    int i = 0;
-#pragma unroll 8
-    for (int64_t r = r0 + rl; r < r1; r += RL, ++i) {
-      const float4 xv = bn_ld4(xp + r * C);
-      a = f4_add(a, xv);
-      b = f4_fma(xv, xv, b);
-      if (i < cached) tile[i * BNF_T + tid] = xv;
-    }
+  // what the second phase needs besides the sums is fetched now, so its latency hides behind phase 1
+  const float4 gm = bn_ld4(gamma + 4 * q), bt = bn_ld4(beta + 4 * q);
+  const bool keeper = blockIdx.x == 0 && rl == 0;      // writes the per-channel results of its quad
+  float4 rm = make_float4(0.f, 0.f, 0.f, 0.f), rv = rm;
+  if (keeper && running_mean != nullptr) {
+    rm = bn_ld4(running_mean + 4 * q);
+    rv = bn_ld4(running_var + 4 * q);
   }
-  bnf_reduce_rows(red, a, b, tid, rl, RL, qpb);
-  const unsigned long long gen = s_gen;
-  double* acc = accum + (gen & 1ULL) * 2 * (size_t)C;
-  if (rl == 0) bnf_atomic_add8(acc, C, q, a, b);
-  bnf_column_barrier(bar, gen, err);
 
-  // per-channel constants, recomputed by every thread for its own quad
+  // phase 1: one read of x.  The rows that fit in shared memory are fetched with cp.async (all in flight
+  // at once, no register staging); the rest streams through registers meanwhile.
+  const int64_t rows = r1 - r0 - rl;
+  const int n_it = rows > 0 ? (int)((rows + RL - 1) >> (9 - qshift)) : 0;      // RL = 512 >> qshift
+  const int nc = n_it < cached ? n_it : cached;
+  for (int i = 0; i < nc; ++i) bnf_cp_async16(&tile[i * BNF_T + tid], xp + (r0 + rl + (int64_t)i * RL) * C);
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+#pragma unroll 8
+  for (int i = nc; i < n_it; ++i) {
+    const float4 xv = bn_ld4(xp + (r0 + rl + (int64_t)i * RL) * C);
+    a = f4_add(a, xv);
+    b = f4_fma(xv, xv, b);
+  }
+  bnf_cp_async_wait_all();
+#pragma unroll 8
+  for (int i = 0; i < nc; ++i) {
+    const float4 xv = tile[i * BNF_T + tid];
+    a = f4_add(a, xv);
+    b = f4_fma(xv, xv, b);
+  }
+  if (stamp) ts[1] = bnf_now();
+  bnf_reduce_rows(red, a, b, tid, rl, RL, qpb);
+  const bool alone = gridDim.x == 1;        // this block owns its channels: no atomics, no barrier
+  const unsigned long long gen = alone ? 0ULL : s_gen;
+  double* acc = accum + (gen & 1ULL) * 2 * (size_t)C;
+  double s[4], ss[4];
+  if (alone) {
+    const float4 ta = red[0][ql], tb = red[1][ql];
+    s[0] = ta.x; s[1] = ta.y; s[2] = ta.z; s[3] = ta.w;
+    ss[0] = tb.x; ss[1] = tb.y; ss[2] = tb.z; ss[3] = tb.w;
+    if (stamp) ts[2] = ts[3] = bnf_now();
+  } else {
+    if (rl == 0) bnf_atomic_add8(acc, C, q, a, b);
+    if (stamp) ts[2] = bnf_now();
+    bnf_column_barrier(bar, gen);
+    if (stamp) ts[3] = bnf_now();
+    bnf_load_totals(acc, C, q, s, ss);
+  }
+
+  // per-channel constants, recomputed by every thread for its own quad (no divisions, no fp64 sqrt)
   float mu[4], is[4];
   double varv[4], meanv[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
-    const double s = __ldcg(acc + 4 * q + j), ss = __ldcg(acc + C + 4 * q + j);
-    const double mean = s / (double)M;
-    double var = ss / (double)M - mean * mean;
+    const double mean = s[j] * inv_m;
+    double var = fma(ss[j], inv_m, -mean * mean);
     if (var < 0) var = 0;
     meanv[j] = mean;
     varv[j] = var;
     mu[j] = (float)mean;
-    is[j] = (float)(1.0 / sqrt(var + (double)eps));
+    is[j] = bnf_rsqrt((float)var + eps);
   }
-  if (blockIdx.x == 0 && rl == 0) {
+  if (keeper) {
     double* other = accum + ((gen + 1ULL) & 1ULL) * 2 * (size_t)C;   // dirty from the previous launch
+    if (alone) other = acc;                                           // (nothing is dirty: keep the stores valid)
+    const float rmv[4] = {rm.x, rm.y, rm.z, rm.w}, rvv[4] = {rv.x, rv.y, rv.z, rv.w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int c = 4 * q + j;
@@ -441,31 +521,31 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
       save_mean[c] = mu[j];
       save_istd[c] = is[j];
       if (running_mean != nullptr) {
-        const double unbiased = M > 1 ? varv[j] * (double)M / (double)(M - 1) : varv[j];
-        running_mean[c] = (float)((1.0 - momentum) * (double)running_mean[c] + momentum * meanv[j]);
-        running_var[c] = (float)((1.0 - momentum) * (double)running_var[c] + momentum * unbiased);
+        running_mean[c] = (float)((1.0 - momentum) * (double)rmv[j] + momentum * meanv[j]);
+        running_var[c] = (float)((1.0 - momentum) * (double)rvv[j] + momentum * (varv[j] * unbias));
       }
     }
     if (blockIdx.y == 0 && tid == 0 && num_batches != nullptr) *num_batches += 1;
   }
-  const float4 g = bn_ld4(gamma + 4 * q), bt = bn_ld4(beta + 4 * q);
-  const float4 sc = make_float4(g.x * is[0], g.y * is[1], g.z * is[2], g.w * is[3]);
+  const float4 sc = make_float4(gm.x * is[0], gm.y * is[1], gm.z * is[2], gm.w * is[3]);
   const float4 sh = make_float4(fmaf(-mu[0], sc.x, bt.x), fmaf(-mu[1], sc.y, bt.y), fmaf(-mu[2], sc.z, bt.z),
                                 fmaf(-mu[3], sc.w, bt.w));
+  if (stamp) ts[4] = bnf_now();
 
   // phase 2: normalise out of shared memory (rows beyond the cached part come from L2/HBM again)
+  // (last rows first: they are the ones most likely still in L2)
   {
-    int i = 0;
 #pragma unroll 4
-    for (int64_t r = r0 + rl; r < r1; r += RL, ++i) {
-      const float4 xv = (i < cached) ? tile[i * BNF_T + tid] : bn_ld4(xp + r * C);
-      float4 o = make_float4(fmaf(xv.x, sc.x, sh.x), fmaf(xv.y, sc.y, sh.y), fmaf(xv.z, sc.z, sh.z),
-                             fmaf(xv.w, sc.w, sh.w));
+    for (int i = n_it - 1; i >= 0; --i) {
+      const int64_t r = r0 + rl + (int64_t)i * RL;
+      const float4 xv = (i < nc) ? tile[i * BNF_T + tid] : bn_ld4(xp + r * C);
+      float4 o = f4_fma(xv, sc, sh);
       if (res != nullptr) o = f4_add(o, bn_ld4(res + r * C + 4 * q));
       if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
       bn_st4(y + r * C + 4 * q, o);
     }
   }
+  if (stamp) ts[5] = bnf_now();
 }
 
 __device__ __forceinline__ float4 bn_mask_pos(float4 g, float4 z) {
@@ -479,66 +559,103 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ x, const 
                const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ save_mean,
                const float* __restrict__ save_istd, float* __restrict__ dx, float* __restrict__ dres,
                float* __restrict__ dgamma, float* __restrict__ dbeta, double* accum, unsigned long long* bar,
-               int* err, int64_t M, int C, int rows_per_block, int qpb, int cached, int relu) {
+               int64_t M, int C, int rows_per_block, int qshift, int cached, double inv_m, int flags) {
   extern __shared__ float4 tile[];          // [cached][2][BNF_T]: masked gradient, x
   __shared__ float4 red[2][BNF_T];
   __shared__ unsigned long long s_gen;
   const int tid = threadIdx.x;
-  const int ql = tid % qpb, rl = tid / qpb, RL = BNF_T / qpb;
+  const int qpb = 1 << qshift, ql = tid & (qpb - 1), rl = tid >> qshift, RL = BNF_T >> qshift;
   const int q = blockIdx.y * qpb + ql;
-  if (tid == 0) s_gen = *(volatile unsigned long long*)(bar + blockIdx.y) / gridDim.x;
+  const bool stamp = (flags & 2) && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0;
+  unsigned long long* ts = bar + BNF_STAMP_WORD + 8;
+  if (stamp) ts[0] = bnf_now();
+  if (tid == 0 && gridDim.x > 1) s_gen = bnf_ld_relaxed(bar + 2 * blockIdx.y + 1);
+  const int relu = flags & 1;
   const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
   const int64_t r1 = (r0 + rows_per_block < M) ? r0 + rows_per_block : M;
   float4 mu, is, sc, sh;
   bn_load_channel_consts(gamma, beta, save_mean, save_istd, q, mu, is, sc, sh);
 
-  float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-  {
-    int i = 0;
-#pragma unroll 4
-    for (int64_t r = r0 + rl; r < r1; r += RL, ++i) {
-      const int64_t o = r * C + 4 * q;
-      const float4 xv = bn_ld4(x + o);
-      float4 g = bn_ld4(dy + o);
-      if (relu) g = bn_mask_pos(g, y != nullptr ? bn_ld4(y + o) : f4_fma(xv, sc, sh));
-      if (dres != nullptr) bn_st4(dres + o, g);
-      const float4 xh = make_float4((xv.x - mu.x) * is.x, (xv.y - mu.y) * is.y, (xv.z - mu.z) * is.z,
-                                    (xv.w - mu.w) * is.w);
-      a = f4_add(a, g);
-      b = f4_fma(g, xh, b);
-      if (i < cached) {
-        tile[(2 * i) * BNF_T + tid] = g;
-        tile[(2 * i + 1) * BNF_T + tid] = xv;
-      }
-    }
+  // phase 1: dy and x of the rows that fit go to shared memory with cp.async; the rest streams through
+  // registers meanwhile.  g = dy masked by the forward ReLU replaces dy in shared memory.
+  const int64_t rows = r1 - r0 - rl;
+  const int n_it = rows > 0 ? (int)((rows + RL - 1) >> (9 - qshift)) : 0;
+  const int nc = n_it < cached ? n_it : cached;
+  for (int i = 0; i < nc; ++i) {
+    const int64_t o = (r0 + rl + (int64_t)i * RL) * C + 4 * q;
+    bnf_cp_async16(&tile[(2 * i) * BNF_T + tid], dy + o);
+    bnf_cp_async16(&tile[(2 * i + 1) * BNF_T + tid], x + o);
   }
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+#pragma unroll 4
+  for (int i = nc; i < n_it; ++i) {
+    const int64_t o = (r0 + rl + (int64_t)i * RL) * C + 4 * q;
+    const float4 xv = bn_ld4(x + o);
+    float4 g = bn_ld4(dy + o);
+    if (relu) g = bn_mask_pos(g, y != nullptr ? bn_ld4(y + o) : f4_fma(xv, sc, sh));
+    if (dres != nullptr) bn_st4(dres + o, g);
+    const float4 xh = make_float4((xv.x - mu.x) * is.x, (xv.y - mu.y) * is.y, (xv.z - mu.z) * is.z,
+                                  (xv.w - mu.w) * is.w);
+    a = f4_add(a, g);
+    b = f4_fma(g, xh, b);
+  }
+  bnf_cp_async_wait_all();
+#pragma unroll 4
+  for (int i = 0; i < nc; ++i) {
+    const int64_t o = (r0 + rl + (int64_t)i * RL) * C + 4 * q;
+    const float4 xv = tile[(2 * i + 1) * BNF_T + tid];
+    float4 g = tile[(2 * i) * BNF_T + tid];
+    if (relu) {
+      g = bn_mask_pos(g, y != nullptr ? bn_ld4(y + o) : f4_fma(xv, sc, sh));
+      tile[(2 * i) * BNF_T + tid] = g;
+    }
+    if (dres != nullptr) bn_st4(dres + o, g);
+    const float4 xh = make_float4((xv.x - mu.x) * is.x, (xv.y - mu.y) * is.y, (xv.z - mu.z) * is.z,
+                                  (xv.w - mu.w) * is.w);
+    a = f4_add(a, g);
+    b = f4_fma(g, xh, b);
+  }
+  if (stamp) ts[1] = bnf_now();
   bnf_reduce_rows(red, a, b, tid, rl, RL, qpb);
-  const unsigned long long gen = s_gen;
+  const bool alone = gridDim.x == 1;
+  const unsigned long long gen = alone ? 0ULL : s_gen;
   double* acc = accum + (gen & 1ULL) * 2 * (size_t)C;
-  if (rl == 0) bnf_atomic_add8(acc, C, q, a, b);
-  bnf_column_barrier(bar, gen, err);
-
+  double sg[4], sgx[4];
+  if (alone) {
+    const float4 ta = red[0][ql], tb = red[1][ql];
+    sg[0] = ta.x; sg[1] = ta.y; sg[2] = ta.z; sg[3] = ta.w;
+    sgx[0] = tb.x; sgx[1] = tb.y; sgx[2] = tb.z; sgx[3] = tb.w;
+    if (stamp) ts[2] = ts[3] = bnf_now();
+  } else {
+    if (rl == 0) bnf_atomic_add8(acc, C, q, a, b);
+    if (stamp) ts[2] = bnf_now();
+    bnf_column_barrier(bar, gen);
+    if (stamp) ts[3] = bnf_now();
+    bnf_load_totals(acc, C, q, sg, sgx);
+  }
   float mg[4], mgx[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
-    const double sg = __ldcg(acc + 4 * q + j), sgx = __ldcg(acc + C + 4 * q + j);
-    mg[j] = (float)(sg / (double)M);
-    mgx[j] = (float)(sgx / (double)M);
-    if (blockIdx.x == 0 && rl == 0) {
-      double* other = accum + ((gen + 1ULL) & 1ULL) * 2 * (size_t)C;
+    mg[j] = (float)(sg[j] * inv_m);
+    mgx[j] = (float)(sgx[j] * inv_m);
+  }
+  if (blockIdx.x == 0 && rl == 0) {
+    double* other = alone ? acc : accum + ((gen + 1ULL) & 1ULL) * 2 * (size_t)C;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
       other[4 * q + j] = 0;
       other[C + 4 * q + j] = 0;
-      dbeta[4 * q + j] = (float)sg;
-      dgamma[4 * q + j] = (float)sgx;
+      dbeta[4 * q + j] = (float)sg[j];
+      dgamma[4 * q + j] = (float)sgx[j];
     }
   }
+  if (stamp) ts[4] = bnf_now();
   {
-    int i = 0;
 #pragma unroll 4
-    for (int64_t r = r0 + rl; r < r1; r += RL, ++i) {
-      const int64_t o = r * C + 4 * q;
+    for (int i = n_it - 1; i >= 0; --i) {      // last rows first: most likely still in L2
+      const int64_t o = (r0 + rl + (int64_t)i * RL) * C + 4 * q;
       float4 g, xv;
-      if (i < cached) {
+      if (i < nc) {
         g = tile[(2 * i) * BNF_T + tid];
         xv = tile[(2 * i + 1) * BNF_T + tid];
       } else {
@@ -558,24 +675,51 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ x, const 
       bn_st4(dx + o, d);
     }
   }
+  if (stamp) ts[5] = bnf_now();
 }
 
 namespace {
+int g_qcap = 9;           // upper bound on log2 of the channel slab width (in quads), cooperative path
+int g_private_kb = 128;   // largest per-block slab of the barrier-free path
+
 struct BnfGeom {
-  int qpb, rpb, iters;
+  int qshift, rpb, iters;
   dim3 grid;
 };
-
-#define BNF_MAX_COLUMNS 63   /* bar[0..62] column counters, bar[63] error word */
 
 bool bnf_geometry(int64_t M, int C, BnfGeom* g) {
   if (M < 2 || C <= 0 || (C & 3)) return false;
   const int quads = C / 4;
-  int qpb = 32;
-  while (quads % qpb) qpb >>= 1;
-  if (qpb < 8) return false;               // < 128 B contiguous per row: leave it to the two-kernel path
-  const int gy = quads / qpb;
+  int qmax = 9;                             // widest power-of-two quad slab that divides the row
+  while (quads % (1 << qmax)) --qmax;
   const int nsm = bn_sm_count();
+  // (a) small activations with many channels: one block owns a channel slab over ALL rows, so there is
+  //     nothing to exchange between blocks (>= 32 blocks of <= g_private_kb KB each, full 32 B sectors).
+  //     Only worth it while the slabs are small: a strided 32 B column is the worst DRAM access pattern.
+  int lg = 0;
+  while ((1 << (lg + 1)) <= quads) ++lg;
+  int qs = lg - 7 < 1 ? 1 : lg - 7;
+  while ((quads >> qs) > nsm && qs < qmax) ++qs;
+  if (qs <= qmax && (quads >> qs) >= 32 && (quads >> qs) <= nsm &&
+      M * (int64_t)(16 << qs) <= (int64_t)g_private_kb * 1024) {
+    const int RL = BNF_T >> qs;
+    int64_t rpb = (M + RL - 1) / RL * RL;
+    g->qshift = qs;
+    g->rpb = (int)rpb;
+    g->iters = (int)(rpb / RL);
+    g->grid = dim3(1, (unsigned)(quads >> qs), 1);
+    return true;
+  }
+  // (b) everything else: one block per SM, channel slabs chosen so that about eight (four for activations
+  //     beyond 64 MB, where longer contiguous runs pay) slabs share the SMs: fewer blocks per barrier and
+  //     per accumulator address than whole rows would give (measured: profiles/bn_geometry_sweep.txt)
+  const int target = M * (int64_t)C * 4 > ((int64_t)64 << 20) ? 2 : 3;
+  int qshift = lg - target < 3 ? 3 : lg - target;
+  if (qshift > qmax) qshift = qmax;
+  if (qshift > g_qcap) qshift = g_qcap;
+  if (qshift < 3) return false;            // < 128 B contiguous per row: leave it to the two-kernel path
+  const int qpb = 1 << qshift;
+  const int gy = quads / qpb;
   if (gy > nsm || gy > BNF_MAX_COLUMNS) return false;
   const int RL = BNF_T / qpb;
   int64_t gx = nsm / gy;
@@ -585,7 +729,7 @@ bool bnf_geometry(int64_t M, int C, BnfGeom* g) {
   rpb = (rpb + RL - 1) / RL * RL;
   if (rpb > (int64_t)1 << 30) return false;
   gx = (M + rpb - 1) / rpb;
-  g->qpb = qpb;
+  g->qshift = qshift;
   g->rpb = (int)rpb;
   g->iters = (int)(rpb / RL);
   g->grid = dim3((unsigned)gx, (unsigned)gy, 1);
@@ -609,6 +753,14 @@ int bnf_prepare() {
 }
 }  // namespace
 
+// Tuning knobs of the geometry heuristic (benchmarks only; not thread-safe, set before first use).
+extern "C" int gk_bn_set_tuning(int qcap_log2, int private_kb) {
+  if (qcap_log2 < 3 || qcap_log2 > 9 || private_kb < 0) return (int)cudaErrorInvalidValue;
+  g_qcap = qcap_log2;
+  g_private_kb = private_kb;
+  return 0;
+}
+
 extern "C" int gk_bn_fused_supported(int64_t M, int C) {
   BnfGeom g;
   return bnf_geometry(M, C, &g) ? 1 : 0;
@@ -617,19 +769,19 @@ extern "C" int gk_bn_fused_supported(int64_t M, int C) {
 extern "C" int gk_bn_fwd_fused(const float* x, const float* res, float* y, const float* gamma, const float* beta,
                                float* running_mean, float* running_var, int64_t* num_batches, float* save_mean,
                                float* save_istd, double* accum, unsigned long long* bar, int64_t M, int C,
-                               float eps, float momentum, int relu, void* stream) {
+                               float eps, float momentum, int flags, void* stream) {
   BnfGeom g;
   if (!bnf_geometry(M, C, &g)) return (int)cudaErrorInvalidValue;
   if (!bn_aligned(x) || !bn_aligned(y) || !bn_aligned(res) || !bn_aligned(gamma) || !bn_aligned(beta) ||
-      !bn_aligned(save_mean) || !bn_aligned(save_istd))
+      !bn_aligned(save_mean) || !bn_aligned(save_istd) || !bn_aligned(accum))
     return (int)cudaErrorMisalignedAddress;
   int rc = bnf_prepare();
   if (rc) return rc;
   int cached = g.iters < BNF_SMEM_BUDGET / (BNF_T * 16) ? g.iters : BNF_SMEM_BUDGET / (BNF_T * 16);
   size_t smem = (size_t)cached * BNF_T * 16;
-  int* err = reinterpret_cast<int*>(bar + BNF_MAX_COLUMNS);
+  double inv_m = 1.0 / (double)M, unbias = M > 1 ? (double)M / (double)(M - 1) : 1.0;
   void* args[] = {&x, &res, &y, &gamma, &beta, &save_mean, &save_istd, &running_mean, &running_var, &num_batches,
-                  &accum, &bar, &err, &M, &C, &g.rpb, &g.qpb, &cached, &eps, &momentum, &relu};
+                  &accum, &bar, &M, &C, &g.rpb, &g.qshift, &cached, &eps, &momentum, &inv_m, &unbias, &flags};
   return (int)cudaLaunchCooperativeKernel((void*)k_bn_fwd_fused, g.grid, dim3(BNF_T), args, smem,
                                           (cudaStream_t)stream);
 }
@@ -637,20 +789,21 @@ extern "C" int gk_bn_fwd_fused(const float* x, const float* res, float* y, const
 extern "C" int gk_bn_bwd_fused(const float* dy, const float* x, const float* y, const float* gamma,
                                const float* beta, const float* save_mean, const float* save_istd, float* dx,
                                float* dres, float* dgamma, float* dbeta, double* accum, unsigned long long* bar,
-                               int64_t M, int C, int relu, void* stream) {
+                               int64_t M, int C, int flags, void* stream) {
   BnfGeom g;
   if (!bnf_geometry(M, C, &g)) return (int)cudaErrorInvalidValue;
   if (!bn_aligned(dy) || !bn_aligned(x) || !bn_aligned(y) || !bn_aligned(dx) || !bn_aligned(dres) ||
-      !bn_aligned(gamma) || !bn_aligned(beta) || !bn_aligned(save_mean) || !bn_aligned(save_istd))
+      !bn_aligned(gamma) || !bn_aligned(beta) || !bn_aligned(save_mean) || !bn_aligned(save_istd) ||
+      !bn_aligned(accum))
     return (int)cudaErrorMisalignedAddress;
-  if (dres != nullptr && relu && y == nullptr) return (int)cudaErrorInvalidValue;
+  if (dres != nullptr && (flags & 1) && y == nullptr) return (int)cudaErrorInvalidValue;
   int rc = bnf_prepare();
   if (rc) return rc;
   int cached = g.iters < BNF_SMEM_BUDGET / (BNF_T * 32) ? g.iters : BNF_SMEM_BUDGET / (BNF_T * 32);
   size_t smem = (size_t)cached * BNF_T * 32;
-  int* err = reinterpret_cast<int*>(bar + BNF_MAX_COLUMNS);
+  double inv_m = 1.0 / (double)M;
   void* args[] = {&dy, &x, &y, &gamma, &beta, &save_mean, &save_istd, &dx, &dres, &dgamma, &dbeta, &accum,
-                  &bar, &err, &M, &C, &g.rpb, &g.qpb, &cached, &relu};
+                  &bar, &M, &C, &g.rpb, &g.qshift, &cached, &inv_m, &flags};
   return (int)cudaLaunchCooperativeKernel((void*)k_bn_bwd_fused, g.grid, dim3(BNF_T), args, smem,
                                           (cudaStream_t)stream);
 }

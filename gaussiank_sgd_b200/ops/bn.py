@@ -39,17 +39,30 @@ def _scratch(bn, device, C):
     return sc
 
 
-def _scratch_coop(bn, device, C, M):
-    """Scratch of the single-kernel path, one per (layer, M): 4*C doubles and 64 barrier words, zero at
+ERR_WORD, STAMP_WORD = 127, 96
+
+
+def _scratch_coop(bn, device, C):
+    """Scratch of the single-kernel path, one per layer: 4*C doubles and 128 barrier words, zero at
     creation and never reset (include/gk_b200.h)."""
     table = bn.__dict__.setdefault("_gk_bn_coop", {})
-    key = (str(device), C, M)
+    key = (str(device), C)
     sc = table.get(key)
     if sc is None:
         sc = (torch.zeros(4 * C, dtype=torch.float64, device=device),
-              torch.zeros(64, dtype=torch.int64, device=device))
+              torch.zeros(128, dtype=torch.int64, device=device))
         table[key] = sc
     return sc
+
+
+def phase_stamps(bn):
+    """[forward, backward] phase boundaries in ns relative to kernel start (needs GK_BN_STAMPS=1):
+    start, loads done, sums posted, barrier passed, constants ready, end."""
+    out = []
+    for _, bar in bn.__dict__.get("_gk_bn_coop", {}).values():
+        w = bar[STAMP_WORD:STAMP_WORD + 16].tolist()
+        out = [[v - w[0] for v in w[0:6]], [v - w[8] for v in w[8:14]]]
+    return out
 
 
 def coop_errors(model) -> int:
@@ -57,7 +70,7 @@ def coop_errors(model) -> int:
     bad = 0
     for m in model.modules():
         for _, bar in m.__dict__.get("_gk_bn_coop", {}).values():
-            bad += int(bar[63].item() != 0)
+            bad += int(bar[ERR_WORD].item() != 0)
     return bad
 
 
@@ -92,9 +105,9 @@ class _BnAct(torch.autograd.Function):
         head = (_ptr(x), _ptr(residual), _ptr(y), _ptr(weight), _ptr(bias),
                 _ptr(bn.running_mean) if track else None, _ptr(bn.running_var) if track else None,
                 _ptr(bn.num_batches_tracked) if track else None, stats[0].data_ptr(), stats[1].data_ptr())
-        tail = (M, C, float(bn.eps), float(bn.momentum), int(relu), _stream())
+        tail = (M, C, float(bn.eps), float(bn.momentum), int(relu) | (2 if settings.BN_STAMPS else 0), _stream())
         if ctx.coop:
-            accum, bar = ctx.scratch = _scratch_coop(bn, x.device, C, M)
+            accum, bar = ctx.scratch = _scratch_coop(bn, x.device, C)
             native.check(lib.gk_bn_fwd_fused(*head, accum.data_ptr(), bar.data_ptr(), *tail), "gk_bn_fwd_fused")
             _chain.LAUNCHES["n"] += 1
         else:
@@ -125,8 +138,9 @@ class _BnAct(torch.autograd.Function):
                 _ptr(dx), _ptr(dres), dgamma.data_ptr(), dbeta.data_ptr())
         if ctx.coop:
             accum, bar = ctx.scratch
-            native.check(lib.gk_bn_bwd_fused(*head, accum.data_ptr(), bar.data_ptr(), M, C, int(ctx.relu),
-                                             _stream()), "gk_bn_bwd_fused")
+            native.check(lib.gk_bn_bwd_fused(*head, accum.data_ptr(), bar.data_ptr(), M, C,
+                                             int(ctx.relu) | (2 if settings.BN_STAMPS else 0), _stream()),
+                         "gk_bn_bwd_fused")
             _chain.LAUNCHES["n"] += 1
         else:
             accum, ticket = ctx.scratch

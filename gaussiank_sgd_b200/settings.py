@@ -67,6 +67,7 @@ CHANNELS_LAST = _flag("CHANNELS_LAST", True)        # NHWC convolutions on GPUs
 SYNTHETIC_POOL = _flag("SYNTHETIC_POOL", True)      # pre-collated pinned batches for synthetic image data
 FUSED_BN = _flag("FUSED_BN", True)                  # BN(+residual)+ReLU through csrc/gk_bn.cu on GPUs (ops/bn.py)
 FUSED_BN_COOP = _flag("FUSED_BN_COOP", True)        # single cooperative kernel per direction where the shape allows
+BN_STAMPS = _flag("BN_STAMPS", False)                # fused BN kernels record phase time stamps (profiling aid)
 CUDNN_BENCHMARK = _flag("CUDNN_BENCHMARK", True)    # the reference pins benchmark=False, deterministic=True
 
 hostname = socket.gethostname()

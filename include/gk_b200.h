@@ -260,18 +260,22 @@ int gk_bn_bwd(const float* dy, const float* x, const float* y, const float* gamm
 /* Single-kernel variants of the two calls above (one cooperative launch each; the activation slab of
  * every block stays in shared memory between the statistics and the apply phase, so x / dy are read from
  * HBM once).  Available when gk_bn_fused_supported(M, C) returns 1 (C/4 has a power-of-two factor >= 8 and
- * the channel slabs fit the SM count).  Scratch, per (layer, M): accum = 4*C doubles (two parities) and
- * bar = 64 uint64 (bar[0..62] column barriers that only grow, low word of bar[63] = error flag set if a
- * barrier wait expired); both zero before the first call, never reset afterwards; the same scratch serves
- * forward and backward of one layer as long as M and C stay the same. */
+ * the channel slabs fit the SM count).  Scratch, per layer: accum = 4*C doubles (two parities) and
+ * bar = 128 uint64 (bar[2y], bar[2y+1]: arrival count and generation of channel slab y; bar[96..111]:
+ * phase time stamps in ns when flags bit 1 is set; low word of bar[127]: error flag, set if a barrier wait
+ * expired); both zero before the first call, never reset afterwards; one scratch serves forward and
+ * backward of a layer.  flags: bit 0 = ReLU, bit 1 = time stamps. */
 int gk_bn_fused_supported(int64_t M, int C);
+/* Geometry knobs for benchmarks (defaults 9 = no cap, 128): cap on log2 of the channel slab in float4 quads, and the
+ * largest per-block slab in KB for which one block takes a channel slab over all rows (no barrier). */
+int gk_bn_set_tuning(int qcap_log2, int private_kb);
 int gk_bn_fwd_fused(const float* x, const float* res, float* y, const float* gamma, const float* beta,
                     float* running_mean, float* running_var, int64_t* num_batches, float* save_mean,
                     float* save_istd, double* accum, unsigned long long* bar, int64_t M, int C, float eps,
-                    float momentum, int relu, void* stream);
+                    float momentum, int flags, void* stream);
 int gk_bn_bwd_fused(const float* dy, const float* x, const float* y, const float* gamma, const float* beta,
                     const float* save_mean, const float* save_istd, float* dx, float* dres, float* dgamma,
-                    float* dbeta, double* accum, unsigned long long* bar, int64_t M, int C, int relu, void* stream);
+                    float* dbeta, double* accum, unsigned long long* bar, int64_t M, int C, int flags, void* stream);
 
 /* Peer-memory plumbing of the P2P transport (set-up time only; the only allocating entry
  * points).  gk_ipc_alloc: cudaMalloc + zero + IPC handle (64 bytes) for the local receive arena;

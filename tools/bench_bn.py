@@ -15,7 +15,8 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from gaussiank_sgd_b200.ops.bn import bn_act  # noqa: E402
+from gaussiank_sgd_b200 import settings  # noqa: E402
+from gaussiank_sgd_b200.ops.bn import bn_act, phase_stamps  # noqa: E402
 
 SHAPES = [  # C, HW, residual, count in ResNet-50
     (64, 112, False, 1), (64, 56, False, 6), (256, 56, False, 1), (256, 56, True, 3),
@@ -57,7 +58,15 @@ def main():
     ap.add_argument("--batch", type=int, default=32)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--out", default=None)
+    ap.add_argument("--once", action="store_true", help="one profiled forward+backward per shape (for ncu)")
+    ap.add_argument("--qcap", type=int, default=None, help="geometry knob: log2 of the widest channel slab (quads)")
+    ap.add_argument("--private-kb", type=int, default=None, help="geometry knob: barrier-free path up to this slab")
+    ap.add_argument("--quiet", action="store_true", help="print one line per shape: graph ms fused / torch")
     a = ap.parse_args()
+    if a.qcap is not None or a.private_kb is not None:
+        from gaussiank_sgd_b200.ops import native
+        native.check(native.cuda_lib().gk_bn_set_tuning(9 if a.qcap is None else a.qcap,
+                                                        128 if a.private_kb is None else a.private_kb))
     dev = torch.device("cuda:0")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev).view(torch.float32)
     bw = peak_bw()
@@ -81,6 +90,16 @@ def main():
                 y = y + r
             out["y"] = F.relu(y, inplace=True)
 
+        if a.once:          # for ncu --profile-from-start off: exactly one fused forward + backward per shape
+            fused_f()
+            fused_b()
+            torch.cuda.synchronize()
+            torch.cuda.cudart().cudaProfilerStart()
+            fused_f()
+            fused_b()
+            torch.cuda.synchronize()
+            torch.cuda.cudart().cudaProfilerStop()
+            continue
         rec = {"C": C, "HW": HW, "residual": res, "count": cnt, "elems": x.numel()}
         for name, f, b in (("fused", fused_f, fused_b), ("torch", torch_f, fused_b)):
             tf = timeit(f, a.iters, flush)
@@ -103,13 +122,23 @@ def main():
             rec[name + "_graph_ms"] = round(timeit(gr.replay, a.iters, flush), 4)
             tot[name + "_graph"] = tot.get(name + "_graph", 0.0) + cnt * rec[name + "_graph_ms"]
             del gr, keep
+        if settings.BN_STAMPS:      # GK_BN_STAMPS=1: where inside the kernels the time goes (ns from kernel start)
+            fused_f()
+            fused_b()
+            torch.cuda.synchronize()
+            rec["stamps_fwd_bwd_ns"] = phase_stamps(bn)
         n = x.numel() * 4
-        fb = n * (3 + (1 if res else 0))                       # stats read + apply read(+res) + write
+        fb =n * (3 + (1 if res else 0))                       # stats read + apply read(+res) + write
         bb = n * ((3 if res else 2) + 1 + (3 if res else 3))   # reduce reads (+dres write) + dx reads + write
         rec["fused_fwd_roofline"] = round(fb / bw / (rec["fused_fwd_ms"] * 1e-3), 3)
         rec["fused_bwd_roofline"] = round(bb / bw / (rec["fused_bwd_ms"] * 1e-3), 3)
         rows.append(rec)
-        print(json.dumps(rec), flush=True)
+        if a.quiet:
+            print(C, HW, int(res), "x%d" % cnt, rec["fused_graph_ms"], rec["torch_graph_ms"], flush=True)
+        else:
+            print(json.dumps(rec), flush=True)
+    if a.once:
+        return
     summary = {"per_step_ms_fused": round(tot["fused"], 3), "per_step_ms_torch": round(tot["torch"], 3),
                "per_step_graph_ms_fused": round(tot["fused_graph"], 3),
                "per_step_graph_ms_torch": round(tot["torch_graph"], 3),

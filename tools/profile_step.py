@@ -23,6 +23,8 @@ DATASET = {'resnet50': 'imagenet', 'resnet20': 'cifar10', 'vgg16': 'cifar10', 'l
 
 def category(name: str) -> str:
     n = name.lower()
+    if n.startswith('k_bn'):
+        return 'ours (fused bn+relu)'
     if n.startswith('k_') or 'gkchain' in n:
         return 'ours (gk_*)'
     if 'bn_' in n or 'batch_norm' in n or 'batchnorm' in n:
