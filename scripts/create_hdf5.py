@@ -34,6 +34,11 @@ def main():
     classes = sorted(os.listdir(os.path.join(a.root, 'train')))
     class_to_idx = {c: i for i, c in enumerate(classes)}
     rng = random.Random(a.seed)
+    # the class-directory -> label table next to the HDF5 file, one "wnid index" pair per line
+    # (scripts/imagenet_label_mapping.csv of the reference is the output of create_hdf5.py:53-57)
+    with open(os.path.join(os.path.dirname(os.path.abspath(a.out)), 'imagenet_label_mapping.csv'), 'w') as m:
+        for c in classes:
+            m.write('%s %d\n' % (c, class_to_idx[c]))
     with h5py.File(a.out, 'w') as f:
         for split in ('train', 'val'):
             items = list_split(a.root, split, class_to_idx)
