@@ -532,6 +532,8 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
                                 fmaf(-mu[3], sc.w, bt.w));
   if (stamp) ts[4] = bnf_now();
 
+  if (y == nullptr) return;   // statistics only (the caller applies them itself, e.g. fused with a max pool)
+
   // phase 2: normalise out of shared memory (rows beyond the cached part come from L2/HBM again)
   // (last rows first: they are the ones most likely still in L2)
   {
@@ -554,12 +556,51 @@ __device__ __forceinline__ float4 bn_mask_pos(float4 g, float4 z) {
   return g;
 }
 
+// Gradient arriving through a 3x3 / stride 2 / padding 1 max pool that followed the BN+ReLU (ResNet stem):
+// the pooled gradient dy[N][OH][OW][C] and the window position (0..8, kh*3+kw) of each maximum.
+struct BnPool {
+  const float* dy;
+  const unsigned char* idx;
+  int H, W, OH, OW;
+};
+
+// gradient of one input pixel's channel quad = sum over the (1, 2 or 4) windows that contain it and whose
+// maximum sits exactly there
+__device__ __forceinline__ float4 bn_pool_gather(const BnPool& P, int64_t r, int C, int q) {
+  const int hw = P.H * P.W;
+  const int n = (int)(r / hw), rem = (int)(r - (int64_t)n * hw);
+  const int h = rem / P.W, w = rem - h * P.W;
+  float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int oh0 = h >> 1, ow0 = w >> 1;                 // window oh covers rows 2*oh-1 .. 2*oh+1
+#pragma unroll
+  for (int dh = 0; dh < 2; ++dh) {
+    const int oh = oh0 + dh;
+    if (oh >= P.OH || (dh == 1 && !(h & 1))) continue;  // even rows belong to one window only
+#pragma unroll
+    for (int dw = 0; dw < 2; ++dw) {
+      const int ow = ow0 + dw;
+      if (ow >= P.OW || (dw == 1 && !(w & 1))) continue;
+      const unsigned code = (unsigned)((h - (2 * oh - 1)) * 3 + (w - (2 * ow - 1)));
+      const int64_t o = (((int64_t)n * P.OH + oh) * P.OW + ow) * C + 4 * q;
+      const uchar4 id = *reinterpret_cast<const uchar4*>(P.idx + o);
+      const float4 d = bn_ld4(P.dy + o);
+      g.x += id.x == code ? d.x : 0.f; g.y += id.y == code ? d.y : 0.f;
+      g.z += id.z == code ? d.z : 0.f; g.w += id.w == code ? d.w : 0.f;
+    }
+  }
+  return g;
+}
+
+// dy2: optional second gradient of the same output (the output was handed out twice, see ops/bn.py), added
+// on the fly.  POOL: the gradient comes through the max pool described by P instead of dy.
+template <bool POOL>
 __global__ void __launch_bounds__(BNF_T, 1)
-k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ y,
-               const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ save_mean,
-               const float* __restrict__ save_istd, float* __restrict__ dx, float* __restrict__ dres,
-               float* __restrict__ dgamma, float* __restrict__ dbeta, double* accum, unsigned long long* bar,
-               int64_t M, int C, int rows_per_block, int qshift, int cached, double inv_m, int flags) {
+k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, const float* __restrict__ x,
+               const float* __restrict__ y, const float* __restrict__ gamma, const float* __restrict__ beta,
+               const float* __restrict__ save_mean, const float* __restrict__ save_istd, float* __restrict__ dx,
+               float* __restrict__ dres, float* __restrict__ dgamma, float* __restrict__ dbeta, double* accum,
+               unsigned long long* bar, int64_t M, int C, int rows_per_block, int qshift, int cached,
+               double inv_m, int flags, BnPool P) {
   extern __shared__ float4 tile[];          // [cached][2][BNF_T]: masked gradient, x
   __shared__ float4 red[2][BNF_T];
   __shared__ unsigned long long s_gen;
@@ -581,17 +622,24 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ x, const 
   const int64_t rows = r1 - r0 - rl;
   const int n_it = rows > 0 ? (int)((rows + RL - 1) >> (9 - qshift)) : 0;
   const int nc = n_it < cached ? n_it : cached;
+  auto load_g = [&](int64_t r, int64_t o) -> float4 {
+    if (POOL) return bn_pool_gather(P, r, C, q);
+    float4 g = bn_ld4(dy + o);
+    if (dy2 != nullptr) g = f4_add(g, bn_ld4(dy2 + o));
+    return g;
+  };
   for (int i = 0; i < nc; ++i) {
     const int64_t o = (r0 + rl + (int64_t)i * RL) * C + 4 * q;
-    bnf_cp_async16(&tile[(2 * i) * BNF_T + tid], dy + o);
+    if (!POOL) bnf_cp_async16(&tile[(2 * i) * BNF_T + tid], dy + o);
     bnf_cp_async16(&tile[(2 * i + 1) * BNF_T + tid], x + o);
   }
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
 #pragma unroll 4
   for (int i = nc; i < n_it; ++i) {
-    const int64_t o = (r0 + rl + (int64_t)i * RL) * C + 4 * q;
+    const int64_t r = r0 + rl + (int64_t)i * RL;
+    const int64_t o = r * C + 4 * q;
     const float4 xv = bn_ld4(x + o);
-    float4 g = bn_ld4(dy + o);
+    float4 g = load_g(r, o);
     if (relu) g = bn_mask_pos(g, y != nullptr ? bn_ld4(y + o) : f4_fma(xv, sc, sh));
     if (dres != nullptr) bn_st4(dres + o, g);
     const float4 xh = make_float4((xv.x - mu.x) * is.x, (xv.y - mu.y) * is.y, (xv.z - mu.z) * is.z,
@@ -602,13 +650,18 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ x, const 
   bnf_cp_async_wait_all();
 #pragma unroll 4
   for (int i = 0; i < nc; ++i) {
-    const int64_t o = (r0 + rl + (int64_t)i * RL) * C + 4 * q;
+    const int64_t r = r0 + rl + (int64_t)i * RL;
+    const int64_t o = r * C + 4 * q;
     const float4 xv = tile[(2 * i + 1) * BNF_T + tid];
-    float4 g = tile[(2 * i) * BNF_T + tid];
-    if (relu) {
-      g = bn_mask_pos(g, y != nullptr ? bn_ld4(y + o) : f4_fma(xv, sc, sh));
-      tile[(2 * i) * BNF_T + tid] = g;
+    float4 g;
+    if (POOL) {
+      g = bn_pool_gather(P, r, C, q);
+    } else {
+      g = tile[(2 * i) * BNF_T + tid];
+      if (dy2 != nullptr) g = f4_add(g, bn_ld4(dy2 + o));
     }
+    if (relu) g = bn_mask_pos(g, y != nullptr ? bn_ld4(y + o) : f4_fma(xv, sc, sh));
+    if (POOL || relu || dy2 != nullptr) tile[(2 * i) * BNF_T + tid] = g;
     if (dres != nullptr) bn_st4(dres + o, g);
     const float4 xh = make_float4((xv.x - mu.x) * is.x, (xv.y - mu.y) * is.y, (xv.z - mu.z) * is.z,
                                   (xv.w - mu.w) * is.w);
@@ -653,7 +706,8 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ x, const 
   {
 #pragma unroll 4
     for (int i = n_it - 1; i >= 0; --i) {      // last rows first: most likely still in L2
-      const int64_t o = (r0 + rl + (int64_t)i * RL) * C + 4 * q;
+      const int64_t r = r0 + rl + (int64_t)i * RL;
+      const int64_t o = r * C + 4 * q;
       float4 g, xv;
       if (i < nc) {
         g = tile[(2 * i) * BNF_T + tid];
@@ -663,7 +717,7 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ x, const 
         if (dres != nullptr) {
           g = bn_ld4(dres + o);            // already masked by phase 1 (written by this very thread)
         } else {
-          g = bn_ld4(dy + o);
+          g = load_g(r, o);
           if (relu) g = bn_mask_pos(g, y != nullptr ? bn_ld4(y + o) : f4_fma(xv, sc, sh));
         }
       }
@@ -745,7 +799,9 @@ int bnf_prepare() {
   if (!ready[dev]) {
     e = cudaFuncSetAttribute(k_bn_fwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(k_bn_bwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
+    e = cudaFuncSetAttribute(k_bn_bwd_fused<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(k_bn_bwd_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
     if (e != cudaSuccess) return (int)e;
     ready[dev] = true;
   }
@@ -786,15 +842,16 @@ extern "C" int gk_bn_fwd_fused(const float* x, const float* res, float* y, const
                                           (cudaStream_t)stream);
 }
 
-extern "C" int gk_bn_bwd_fused(const float* dy, const float* x, const float* y, const float* gamma,
-                               const float* beta, const float* save_mean, const float* save_istd, float* dx,
-                               float* dres, float* dgamma, float* dbeta, double* accum, unsigned long long* bar,
-                               int64_t M, int C, int flags, void* stream) {
+namespace {
+int bn_bwd_fused_launch(const float* dy, const float* dy2, const float* x, const float* y, const float* gamma,
+                        const float* beta, const float* save_mean, const float* save_istd, float* dx, float* dres,
+                        float* dgamma, float* dbeta, double* accum, unsigned long long* bar, int64_t M, int C,
+                        int flags, BnPool P, bool pool, void* stream) {
   BnfGeom g;
   if (!bnf_geometry(M, C, &g)) return (int)cudaErrorInvalidValue;
-  if (!bn_aligned(dy) || !bn_aligned(x) || !bn_aligned(y) || !bn_aligned(dx) || !bn_aligned(dres) ||
-      !bn_aligned(gamma) || !bn_aligned(beta) || !bn_aligned(save_mean) || !bn_aligned(save_istd) ||
-      !bn_aligned(accum))
+  if (!bn_aligned(dy) || !bn_aligned(dy2) || !bn_aligned(x) || !bn_aligned(y) || !bn_aligned(dx) ||
+      !bn_aligned(dres) || !bn_aligned(gamma) || !bn_aligned(beta) || !bn_aligned(save_mean) ||
+      !bn_aligned(save_istd) || !bn_aligned(accum) || !bn_aligned(P.dy))
     return (int)cudaErrorMisalignedAddress;
   if (dres != nullptr && (flags & 1) && y == nullptr) return (int)cudaErrorInvalidValue;
   int rc = bnf_prepare();
@@ -802,8 +859,136 @@ extern "C" int gk_bn_bwd_fused(const float* dy, const float* x, const float* y, 
   int cached = g.iters < BNF_SMEM_BUDGET / (BNF_T * 32) ? g.iters : BNF_SMEM_BUDGET / (BNF_T * 32);
   size_t smem = (size_t)cached * BNF_T * 32;
   double inv_m = 1.0 / (double)M;
-  void* args[] = {&dy, &x, &y, &gamma, &beta, &save_mean, &save_istd, &dx, &dres, &dgamma, &dbeta, &accum,
-                  &bar, &M, &C, &g.rpb, &g.qshift, &cached, &inv_m, &flags};
-  return (int)cudaLaunchCooperativeKernel((void*)k_bn_bwd_fused, g.grid, dim3(BNF_T), args, smem,
-                                          (cudaStream_t)stream);
+  void* args[] = {&dy, &dy2, &x, &y, &gamma, &beta, &save_mean, &save_istd, &dx, &dres, &dgamma, &dbeta, &accum,
+                  &bar, &M, &C, &g.rpb, &g.qshift, &cached, &inv_m, &flags, &P};
+  void* fn = pool ? (void*)k_bn_bwd_fused<true> : (void*)k_bn_bwd_fused<false>;
+  return (int)cudaLaunchCooperativeKernel(fn, g.grid, dim3(BNF_T), args, smem, (cudaStream_t)stream);
+}
+}  // namespace
+
+extern "C" int gk_bn_bwd_fused(const float* dy, const float* x, const float* y, const float* gamma,
+                               const float* beta, const float* save_mean, const float* save_istd, float* dx,
+                               float* dres, float* dgamma, float* dbeta, double* accum, unsigned long long* bar,
+                               int64_t M, int C, int flags, void* stream) {
+  BnPool none = {nullptr, nullptr, 0, 0, 0, 0};
+  return bn_bwd_fused_launch(dy, nullptr, x, y, gamma, beta, save_mean, save_istd, dx, dres, dgamma, dbeta, accum,
+                             bar, M, C, flags, none, false, stream);
+}
+
+extern "C" int gk_bn_bwd_fused2(const float* dy, const float* dy2, const float* x, const float* y,
+                                const float* gamma, const float* beta, const float* save_mean,
+                                const float* save_istd, float* dx, float* dres, float* dgamma, float* dbeta,
+                                double* accum, unsigned long long* bar, int64_t M, int C, int flags, void* stream) {
+  BnPool none = {nullptr, nullptr, 0, 0, 0, 0};
+  return bn_bwd_fused_launch(dy, dy2, x, y, gamma, beta, save_mean, save_istd, dx, dres, dgamma, dbeta, accum, bar,
+                             M, C, flags, none, false, stream);
+}
+
+// ------------------------------------------------------------- BN + ReLU + 3x3/2 max pool (ResNet stem)
+// Forward: statistics with k_bn_stats, then one pass that normalises the nine inputs of every pooled pixel
+// on the fly (they are still in L2 from the statistics pass), writes the pooled activation and the window
+// position of each maximum (first maximum in scan order, like at::max_pool2d).  The full-resolution
+// activation is never written.  Backward: k_bn_bwd_fused<true> gathers the pooled gradient back.
+__global__ void __launch_bounds__(256) k_bn_pool_apply(const float* __restrict__ x, float* __restrict__ yp,
+                                                       unsigned char* __restrict__ pidx,
+                                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                       const float* __restrict__ save_mean,
+                                                       const float* __restrict__ save_istd, int N, int H, int W, int C,
+                                                       int OH, int OW) {
+  const int quads = C >> 2;
+  const int64_t total = (int64_t)N * OH * OW * quads;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int q = (int)(t % quads);
+    int64_t p = t / quads;
+    const int ow = (int)(p % OW); p /= OW;
+    const int oh = (int)(p % OH);
+    const int n = (int)(p / OH);
+    float4 mu, is, sc, sh;
+    bn_load_channel_consts(gamma, beta, save_mean, save_istd, q, mu, is, sc, sh);
+    float4 best = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+    uchar4 bi = make_uchar4(255, 255, 255, 255);
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+      const int h = 2 * oh - 1 + kh;
+      if (h < 0 || h >= H) continue;
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int w = 2 * ow - 1 + kw;
+        if (w < 0 || w >= W) continue;
+        const float4 z = f4_fma(bn_ld4(x + (((int64_t)n * H + h) * W + w) * C + 4 * q), sc, sh);
+        const unsigned char code = (unsigned char)(kh * 3 + kw);
+        if (z.x > best.x || bi.x == 255) { best.x = z.x; bi.x = code; }
+        if (z.y > best.y || bi.y == 255) { best.y = z.y; bi.y = code; }
+        if (z.z > best.z || bi.z == 255) { best.z = z.z; bi.z = code; }
+        if (z.w > best.w || bi.w == 255) { best.w = z.w; bi.w = code; }
+      }
+    }
+    const int64_t o = (((int64_t)n * OH + oh) * OW + ow) * C + 4 * q;
+    bn_st4(yp + o, make_float4(fmaxf(best.x, 0.f), fmaxf(best.y, 0.f), fmaxf(best.z, 0.f), fmaxf(best.w, 0.f)));
+    *reinterpret_cast<uchar4*>(pidx + o) = bi;
+  }
+}
+
+extern "C" int gk_bn_pool_fwd(const float* x, float* yp, unsigned char* pidx, const float* gamma, const float* beta,
+                              float* running_mean, float* running_var, int64_t* num_batches, float* save_mean,
+                              float* save_istd, double* accum, uint32_t* ticket, unsigned long long* bar, int N,
+                              int H, int W, int C, float eps, float momentum, void* stream) {
+  const int64_t M = (int64_t)N * H * W;
+  const int OH = (H - 1) / 2 + 1, OW = (W - 1) / 2 + 1;
+  BnGeom g;
+  if (!bn_geometry(M, C, &g) || H < 2 || W < 2) return (int)cudaErrorInvalidValue;
+  if (!bn_aligned(x) || !bn_aligned(yp) || !bn_aligned(gamma) || !bn_aligned(beta) || !bn_aligned(save_mean) ||
+      !bn_aligned(save_istd) || (reinterpret_cast<uintptr_t>(pidx) & 3))
+    return (int)cudaErrorMisalignedAddress;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (bar != nullptr && gk_bn_fused_supported(M, C)) {
+    // statistics through the cooperative kernel (y = NULL: phase 1 and the per-channel results only)
+    int rc = gk_bn_fwd_fused(x, nullptr, nullptr, gamma, beta, running_mean, running_var, num_batches, save_mean,
+                             save_istd, accum, bar, M, C, eps, momentum, 0, stream);
+    if (rc) return rc;
+  } else {
+    k_bn_stats<<<g.grid, BN_T, 0, s>>>(x, M, C, g.rpb, g.qpb, accum, ticket, save_mean, save_istd, running_mean,
+                                       running_var, num_batches, eps, momentum);
+  }
+  const int64_t total = (int64_t)N * OH * OW * (C / 4);
+  int64_t blocks = (total + 255) / 256;
+  const int64_t cap = (int64_t)bn_sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  k_bn_pool_apply<<<(unsigned)blocks, 256, 0, s>>>(x, yp, pidx, gamma, beta, save_mean, save_istd, N, H, W, C, OH, OW);
+  return (int)cudaGetLastError();
+}
+
+// Full-resolution gradient of the max pool (dense gather, one thread per input pixel and channel quad): the
+// BN backward then runs on it like on any other gradient.  Cheaper than gathering inside the cooperative
+// kernel, which has one 512-thread block per SM and would evaluate the windows twice.
+__global__ void __launch_bounds__(256) k_pool_gather(BnPool P, float* __restrict__ g, int64_t M, int C) {
+  const int quads = C >> 2;
+  const int64_t total = M * quads;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = t / quads;
+    const int q = (int)(t - r * quads);
+    bn_st4(g + r * C + 4 * q, bn_pool_gather(P, r, C, q));
+  }
+}
+
+extern "C" int gk_bn_pool_bwd(const float* dyp, const unsigned char* pidx, const float* x, const float* gamma,
+                              const float* beta, const float* save_mean, const float* save_istd, float* dx,
+                              float* gfull, float* dgamma, float* dbeta, double* accum, unsigned long long* bar,
+                              int N, int H, int W, int C, int flags, void* stream) {
+  const int OH = (H - 1) / 2 + 1, OW = (W - 1) / 2 + 1;
+  const int64_t M = (int64_t)N * H * W;
+  BnPool P = {dyp, pidx, H, W, OH, OW};
+  if (gfull == nullptr)      // gather inside the cooperative kernel (no extra buffer)
+    return bn_bwd_fused_launch(nullptr, nullptr, x, nullptr, gamma, beta, save_mean, save_istd, dx, nullptr, dgamma,
+                               dbeta, accum, bar, M, C, flags | 1, P, true, stream);
+  if (!bn_aligned(gfull) || !bn_aligned(dyp) || (reinterpret_cast<uintptr_t>(pidx) & 3) || (C & 3))
+    return (int)cudaErrorMisalignedAddress;
+  const int64_t total = M * (C / 4);
+  int64_t blocks = (total + 255) / 256;
+  const int64_t cap = (int64_t)bn_sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  k_pool_gather<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(P, gfull, M, C);
+  BnPool none = {nullptr, nullptr, 0, 0, 0, 0};
+  return bn_bwd_fused_launch(gfull, nullptr, x, nullptr, gamma, beta, save_mean, save_istd, dx, nullptr, dgamma,
+                             dbeta, accum, bar, M, C, flags | 1, none, false, stream);
 }

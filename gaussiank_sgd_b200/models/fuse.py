@@ -16,7 +16,8 @@ import types
 import torch
 import torch.nn as nn
 
-from ..ops.bn import bn_act
+from .. import settings
+from ..ops.bn import bn_act, bn_relu_maxpool
 
 
 class FusedBNReLU(nn.BatchNorm2d):
@@ -35,22 +36,42 @@ def _downsample(mod, x):
     return ds(x)
 
 
+def _split(x):
+    """A block input is either one tensor or (convolution input, identity shortcut): the same activation
+    handed out twice by the previous block so that its two gradients are not pre-added by autograd."""
+    return x if isinstance(x, tuple) else (x, x)
+
+
 def _bottleneck_forward(self, x):
-    s = _downsample(self, x)
-    y = bn_act(self.bn1, self.conv1(x))
+    xc, xi = _split(x)
+    s = xi if self.downsample is None else _downsample(self, xc)
+    y = bn_act(self.bn1, self.conv1(xc))
     y = bn_act(self.bn2, self.conv2(y))
-    return bn_act(self.bn3, self.conv3(y), residual=s)
+    return bn_act(self.bn3, self.conv3(y), residual=s, twice=getattr(self, "_gk_twice", False))
 
 
 def _basic_forward(self, x):
-    s = _downsample(self, x)
-    y = bn_act(self.bn1, self.conv1(x))
-    return bn_act(self.bn2, self.conv2(y), residual=s)
+    xc, xi = _split(x)
+    s = xi if self.downsample is None else _downsample(self, xc)
+    y = bn_act(self.bn1, self.conv1(xc))
+    return bn_act(self.bn2, self.conv2(y), residual=s, twice=getattr(self, "_gk_twice", False))
+
+
+def _is_stem_pool(m):
+    def two(v):
+        return tuple(v) if isinstance(v, (tuple, list)) else (v, v)
+    return (type(m) is nn.MaxPool2d and two(m.kernel_size) == (3, 3) and two(m.stride) == (2, 2)
+            and two(m.padding) == (1, 1) and two(m.dilation) == (1, 1) and not m.ceil_mode and not m.return_indices)
 
 
 def _resnet_forward(self, x):
-    x = self.maxpool(bn_act(self.bn1, self.conv1(x)))
+    if _is_stem_pool(self.maxpool):
+        x = bn_relu_maxpool(self.bn1, self.conv1(x), self.maxpool)
+    else:
+        x = self.maxpool(bn_act(self.bn1, self.conv1(x)))
     x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
+    if isinstance(x, tuple):
+        x = x[0]
     return self.fc(torch.flatten(self.avgpool(x), 1))
 
 
@@ -72,6 +93,10 @@ def fuse_bn_act(model: nn.Module) -> int:
             m.forward = types.MethodType(_resnet_forward, m)
             sites += 1
         elif isinstance(m, nn.Sequential):
+            blocks = list(m)
+            if tv is not None and blocks and all(type(b) in (tv.Bottleneck, tv.BasicBlock) for b in blocks):
+                for b, nxt in zip(blocks, blocks[1:] + [None]):      # a ResNet stage
+                    b._gk_twice = bool(settings.FUSED_BN_TWICE and nxt is not None and nxt.downsample is None)
             for i in range(len(m) - 1):
                 if type(m[i]) is nn.BatchNorm2d and type(m[i + 1]) is nn.ReLU:
                     m[i].__class__ = FusedBNReLU

@@ -92,7 +92,7 @@ def eligible(bn, x, residual=None) -> bool:
 
 class _BnAct(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, residual, weight, bias, bn, relu):
+    def forward(ctx, x, residual, weight, bias, bn, relu, twice=False):
         N, C, H, W = x.shape
         M = N * H * W
         if residual is not None and not _rows_view_ok(residual):
@@ -118,16 +118,30 @@ class _BnAct(torch.autograd.Function):
         ctx.has_res = residual is not None
         # the ReLU mask is recomputed from x unless a residual went into the activation
         ctx.save_for_backward(x, weight, bias, stats, y if (relu and residual is not None) else None)
+        if twice:
+            # the same activation handed out twice (convolution input + identity shortcut of the next block):
+            # autograd then delivers the two gradients separately and the backward kernel adds them on the
+            # fly instead of autograd running an add kernel over the whole activation first
+            ctx.set_materialize_grads(False)
+            return y, y.view_as(y)
         return y
 
     @staticmethod
     @once_differentiable
-    def backward(ctx, dy):
+    def backward(ctx, dy, dy2=None):
         x, weight, bias, stats, y = ctx.saved_tensors
         N, C, H, W = x.shape
         M = N * H * W
+        if dy is None:
+            dy, dy2 = dy2, None
+        if dy is None:
+            return None, None, None, None, None, None, None
         if not _rows_view_ok(dy):
             dy = dy.contiguous(memory_format=torch.channels_last)
+        if dy2 is not None and not _rows_view_ok(dy2):
+            dy2 = dy2.contiguous(memory_format=torch.channels_last)
+        if dy2 is not None and not ctx.coop:
+            dy, dy2 = dy + dy2, None
         dx = torch.empty_like(x, memory_format=torch.channels_last)
         dres = torch.empty_like(x, memory_format=torch.channels_last) if (ctx.has_res and ctx.relu) else None
         # separate tensors: autograd hands a fresh dense tensor to .grad without a copy, a view it would clone
@@ -138,9 +152,9 @@ class _BnAct(torch.autograd.Function):
                 _ptr(dx), _ptr(dres), dgamma.data_ptr(), dbeta.data_ptr())
         if ctx.coop:
             accum, bar = ctx.scratch
-            native.check(lib.gk_bn_bwd_fused(*head, accum.data_ptr(), bar.data_ptr(), M, C,
-                                             int(ctx.relu) | (2 if settings.BN_STAMPS else 0), _stream()),
-                         "gk_bn_bwd_fused")
+            native.check(lib.gk_bn_bwd_fused2(head[0], _ptr(dy2), *head[1:], accum.data_ptr(), bar.data_ptr(), M, C,
+                                              int(ctx.relu) | (2 if settings.BN_STAMPS else 0), _stream()),
+                         "gk_bn_bwd_fused2")
             _chain.LAUNCHES["n"] += 1
         else:
             accum, ticket = ctx.scratch
@@ -149,15 +163,75 @@ class _BnAct(torch.autograd.Function):
                                        int(ctx.relu), _stream()), "gk_bn_bwd")
             _chain.LAUNCHES["n"] += 2
         if ctx.has_res and dres is None:      # no ReLU: the residual branch receives dy unchanged
-            dres = dy
-        return dx, (dres if ctx.has_res else None), dgamma, dbeta, None, None
+            dres = dy if dy2 is None else dy + dy2
+        return dx, (dres if ctx.has_res else None), dgamma, dbeta, None, None, None
 
 
-def bn_act(bn, x, residual=None, relu=True):
-    """``relu(bn(x) + residual)`` with ``residual`` and ``relu`` optional; ``bn`` is an nn.BatchNorm2d."""
+class _BnReluPool(torch.autograd.Function):
+    """relu(bn(x)) followed by max_pool2d(3, stride 2, padding 1): the full-resolution activation is never
+    written; the backward gathers the pooled gradient through the saved window positions."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, bn):
+        N, C, H, W = x.shape
+        OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+        yp = torch.empty((N, C, OH, OW), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+        pidx = torch.empty((N, OH, OW, C), dtype=torch.uint8, device=x.device)
+        stats = torch.empty(2, C, dtype=torch.float32, device=x.device)
+        track = bn.track_running_stats and bn.running_mean is not None
+        accum, bar = ctx.scratch = _scratch_coop(bn, x.device, C)
+        lib = native.cuda_lib()
+        native.check(lib.gk_bn_pool_fwd(_ptr(x), _ptr(yp), _ptr(pidx), _ptr(weight), _ptr(bias),
+                                        _ptr(bn.running_mean) if track else None,
+                                        _ptr(bn.running_var) if track else None,
+                                        _ptr(bn.num_batches_tracked) if track else None,
+                                        stats[0].data_ptr(), stats[1].data_ptr(), accum.data_ptr(), None,
+                                        bar.data_ptr(), N, H, W, C, float(bn.eps), float(bn.momentum), _stream()),
+                     "gk_bn_pool_fwd")
+        _chain.LAUNCHES["n"] += 2
+        ctx.save_for_backward(x, weight, bias, stats, pidx)
+        return yp
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dyp):
+        x, weight, bias, stats, pidx = ctx.saved_tensors
+        N, C, H, W = x.shape
+        if not _rows_view_ok(dyp):
+            dyp = dyp.contiguous(memory_format=torch.channels_last)
+        dx = torch.empty_like(x, memory_format=torch.channels_last)
+        dgamma = torch.empty(C, dtype=torch.float32, device=x.device)
+        dbeta = torch.empty(C, dtype=torch.float32, device=x.device)
+        accum, bar = ctx.scratch
+        native.check(native.cuda_lib().gk_bn_pool_bwd(
+            _ptr(dyp), _ptr(pidx), _ptr(x), _ptr(weight), _ptr(bias), stats[0].data_ptr(), stats[1].data_ptr(),
+            _ptr(dx), _ptr(dx), dgamma.data_ptr(), dbeta.data_ptr(), accum.data_ptr(), bar.data_ptr(), N, H, W, C,
+            2 if settings.BN_STAMPS else 0, _stream()), "gk_bn_pool_bwd")     # dx doubles as the gather buffer
+        _chain.LAUNCHES["n"] += 2
+        return dx, dgamma, dbeta, None
+
+
+def bn_act(bn, x, residual=None, relu=True, twice=False):
+    """``relu(bn(x) + residual)`` with ``residual`` and ``relu`` optional; ``bn`` is an nn.BatchNorm2d.
+    ``twice=True`` returns the result as two tensors sharing one storage (see _BnAct.forward)."""
     if settings.FUSED_BN and eligible(bn, x, residual):
-        return _BnAct.apply(x, residual, bn.weight, bn.bias, bn, relu)
-    # plain path; BatchNorm2d.forward directly because ``bn`` may be a FusedBNReLU (models/fuse.py)
+        return _BnAct.apply(x, residual, bn.weight, bn.bias, bn, relu, twice)
+    y = _bn_act_plain(bn, x, residual, relu)
+    return (y, y) if twice else y
+
+
+def bn_relu_maxpool(bn, x, pool=None):
+    """``max_pool2d(relu(bn(x)), 3, 2, 1)`` (the ResNet stem) through the fused kernels when possible."""
+    N, C, H, W = x.shape if x.dim() == 4 else (0, 0, 0, 0)
+    if (settings.FUSED_BN and settings.FUSED_BN_POOL and eligible(bn, x) and H >= 2 and W >= 2
+            and N * H * W < 2 ** 31 and native.cuda_lib().gk_bn_fused_supported(N * H * W, C)):
+        return _BnReluPool.apply(x, bn.weight, bn.bias, bn)
+    y = bn_act(bn, x, relu=True)
+    return pool(y) if pool is not None else F.max_pool2d(y, 3, 2, 1)
+
+
+def _bn_act_plain(bn, x, residual, relu):
+    """The PyTorch sequence; BatchNorm2d.forward directly because ``bn`` may be a FusedBNReLU (models/fuse.py)."""
     y = torch.nn.BatchNorm2d.forward(bn, x) if isinstance(bn, torch.nn.BatchNorm2d) else bn(x)
     if residual is not None:
         y = y + residual

@@ -67,6 +67,8 @@ CHANNELS_LAST = _flag("CHANNELS_LAST", True)        # NHWC convolutions on GPUs
 SYNTHETIC_POOL = _flag("SYNTHETIC_POOL", True)      # pre-collated pinned batches for synthetic image data
 FUSED_BN = _flag("FUSED_BN", True)                  # BN(+residual)+ReLU through csrc/gk_bn.cu on GPUs (ops/bn.py)
 FUSED_BN_COOP = _flag("FUSED_BN_COOP", True)        # single cooperative kernel per direction where the shape allows
+FUSED_BN_POOL = _flag("FUSED_BN_POOL", True)        # stem: BN+ReLU+maxpool(3,2,1) without the full-resolution write
+FUSED_BN_TWICE = _flag("FUSED_BN_TWICE", True)      # block outputs handed out twice: no autograd add at the junctions
 BN_STAMPS = _flag("BN_STAMPS", False)                # fused BN kernels record phase time stamps (profiling aid)
 CUDNN_BENCHMARK = _flag("CUDNN_BENCHMARK", True)    # the reference pins benchmark=False, deterministic=True
 

@@ -266,6 +266,29 @@ int gk_bn_bwd(const float* dy, const float* x, const float* y, const float* gamm
  * expired); both zero before the first call, never reset afterwards; one scratch serves forward and
  * backward of a layer.  flags: bit 0 = ReLU, bit 1 = time stamps. */
 int gk_bn_fused_supported(int64_t M, int C);
+/* gk_bn_bwd_fused with a second gradient of the same output (dy + dy2 is formed on the fly; dy2 may be NULL):
+ * saves the separate add kernel when a block output feeds both a convolution and an identity shortcut. */
+int gk_bn_bwd_fused2(const float* dy, const float* dy2, const float* x, const float* y, const float* gamma,
+                     const float* beta, const float* save_mean, const float* save_istd, float* dx, float* dres,
+                     float* dgamma, float* dbeta, double* accum, unsigned long long* bar, int64_t M, int C,
+                     int flags, void* stream);
+/* BN + ReLU + max pool 3x3 / stride 2 / padding 1 in one (the ResNet stem; torch.nn runs three modules and
+ * writes the full-resolution activation twice).  x is [N][H][W][C]; the forward writes the pooled activation
+ * yp[N][OH][OW][C] (OH = (H-1)/2+1) and pidx, one byte per pooled element: kh*3+kw of the first maximum of its
+ * window; scratch as gk_bn_fwd (accum 2*C doubles + ticket).  The backward takes the pooled gradient and pidx
+ * and produces dx, dgamma, dbeta; scratch as gk_bn_bwd_fused; needs gk_bn_fused_supported(N*H*W, C). */
+int gk_bn_pool_fwd(const float* x, float* yp, unsigned char* pidx, const float* gamma, const float* beta,
+                   float* running_mean, float* running_var, int64_t* num_batches, float* save_mean, float* save_istd,
+                   double* accum, uint32_t* ticket, unsigned long long* bar, int N, int H, int W, int C, float eps,
+                   float momentum, void* stream);
+/* forward scratch: with bar != NULL (and a supported shape) the statistics come from the cooperative kernel and
+ * accum / bar are the gk_bn_fwd_fused scratch; with bar == NULL accum / ticket are the gk_bn_fwd scratch.
+ * backward: gfull = N*H*W*C floats receives the full-resolution pool gradient first (it may be the same
+ * buffer as dx); gfull == NULL gathers inside the cooperative kernel instead (slower, no buffer). */
+int gk_bn_pool_bwd(const float* dyp, const unsigned char* pidx, const float* x, const float* gamma, const float* beta,
+                   const float* save_mean, const float* save_istd, float* dx, float* gfull, float* dgamma,
+                   float* dbeta, double* accum, unsigned long long* bar, int N, int H, int W, int C, int flags,
+                   void* stream);
 /* Geometry knobs for benchmarks (defaults 9 = no cap, 128): cap on log2 of the channel slab in float4 quads, and the
  * largest per-block slab in KB for which one block takes a channel slab over all rows (no barrier). */
 int gk_bn_set_tuning(int qcap_log2, int private_kb);

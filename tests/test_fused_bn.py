@@ -224,3 +224,69 @@ def test_fused_bn_in_cuda_graph():
     torch.testing.assert_close(gw, gw0, rtol=1e-6, atol=1e-5)
     assert int(bn.num_batches_tracked) == 6
     assert coop_errors(bn) == 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(4, 64, 32, 32), (2, 64, 17, 23), (3, 32, 8, 6), (32, 64, 112, 112)])
+def test_bn_relu_maxpool_matches_pytorch(shape):
+    from gaussiank_sgd_b200.ops.bn import bn_relu_maxpool
+    torch.manual_seed(7)
+    dev = torch.device("cuda:0")
+    N, C, H, W = shape
+    bn = nn.BatchNorm2d(C).to(dev)
+    with torch.no_grad():
+        bn.weight.uniform_(-1.0, 1.5)          # negative scales too: the maximum must be taken after BN
+        bn.bias.uniform_(-0.5, 0.5)
+    ref = copy.deepcopy(bn)
+    x = (torch.randn(N, C, H, W, device=dev) * 2 + 0.3).contiguous(memory_format=torch.channels_last)
+    x1, x2 = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    for rep in range(2):
+        y = bn_relu_maxpool(bn, x1)
+        want = F.max_pool2d(F.relu(ref(x2)), 3, 2, 1)
+        assert y.shape == want.shape and y.is_contiguous(memory_format=torch.channels_last)
+        torch.testing.assert_close(y, want, rtol=1e-5, atol=2e-5)
+        torch.testing.assert_close(bn.running_var, ref.running_var, rtol=1e-5, atol=1e-6)
+        assert int(bn.num_batches_tracked) == rep + 1
+        dy = torch.randn_like(y)
+        for t in (x1, x2, bn.weight, bn.bias, ref.weight, ref.bias):
+            t.grad = None
+        y.backward(dy)
+        want.backward(dy)
+        # a pooled value within rounding of a tie (or of zero) may pick another window position
+        close = (x1.grad - x2.grad).abs() <= 1e-4 + 1e-4 * x2.grad.abs()
+        assert float(close.float().mean()) > 0.999
+        M = N * H * W
+        torch.testing.assert_close(bn.weight.grad, ref.weight.grad, rtol=2e-3, atol=2e-4 * M ** 0.5)
+        torch.testing.assert_close(bn.bias.grad, ref.bias.grad, rtol=2e-3, atol=2e-4 * M ** 0.5)
+    assert "_gk_bn_coop" in bn.__dict__ and coop_errors(bn) == 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("with_res,relu", [(True, True), (False, True), (True, False)])
+def test_bn_act_twice_adds_the_two_gradients(with_res, relu):
+    torch.manual_seed(9)
+    dev = torch.device("cuda:0")
+    bn = nn.BatchNorm2d(64).to(dev)
+    ref = copy.deepcopy(bn)
+    x = torch.randn(8, 64, 14, 14, device=dev).contiguous(memory_format=torch.channels_last)
+    r = torch.randn_like(x) if with_res else None
+    x1, x2 = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    r1 = r.clone().requires_grad_(True) if with_res else None
+    r2 = r.clone().requires_grad_(True) if with_res else None
+    ya, yb = bn_act(bn, x1, residual=r1, relu=relu, twice=True)
+    assert ya.data_ptr() == yb.data_ptr()
+    want = bn_act(ref, x2, residual=r2, relu=relu)
+    d1, d2 = torch.randn_like(want), torch.randn_like(want)
+    (ya * d1).sum().backward(retain_graph=True)          # only one of the two gradients present
+    gx_single = x1.grad.clone()
+    x1.grad = None
+    bn.weight.grad = bn.bias.grad = None
+    if with_res:
+        r1.grad = None
+    ((ya * d1).sum() + (yb * d2).sum()).backward()
+    want.backward(d1 + d2)
+    torch.testing.assert_close(x1.grad, x2.grad, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(bn.weight.grad, ref.weight.grad, rtol=1e-4, atol=1e-4)
+    if with_res:
+        torch.testing.assert_close(r1.grad, r2.grad, rtol=1e-5, atol=1e-6)
+    assert not torch.equal(gx_single, x1.grad)

@@ -23,7 +23,7 @@ DATASET = {'resnet50': 'imagenet', 'resnet20': 'cifar10', 'vgg16': 'cifar10', 'l
 
 def category(name: str) -> str:
     n = name.lower()
-    if n.startswith('k_bn'):
+    if 'k_bn' in n or 'k_pool_gather' in n:
         return 'ours (fused bn+relu)'
     if n.startswith('k_') or 'gkchain' in n:
         return 'ours (gk_*)'
