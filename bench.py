@@ -330,6 +330,8 @@ def main():
     ap.add_argument("--transport", default=None)
     ap.add_argument("--no-graph", action="store_true")
     args = ap.parse_args()
+    # stdout carries exactly one JSON line: NCCL's banner ("NCCL version ...") and debug output go to stderr
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     if args.gpus > 1 and "RANK" not in os.environ:
         # convenience: re-launch ourselves under torchrun
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",

@@ -329,6 +329,20 @@ extern "C" int gk_bn_bwd(const float* dy, const float* x, const float* y, const 
 // Scratch words (uint64) of one layer: bar[2y] arrivals and bar[2y+1] generation of channel slab y
 // (y < BNF_MAX_COLUMNS), bar[96..111] optional phase time stamps, bar[127] error flag.
 #define BNF_T 512
+// unroll depths of the streaming loops = loads in flight per thread (tuned on a B200, profiles/bn_unroll_sweep.txt)
+#ifndef BNF_U_F1
+#define BNF_U_F1 8
+#endif
+#ifndef BNF_U_F2
+#define BNF_U_F2 4
+#endif
+#ifndef BNF_U_B1
+#define BNF_U_B1 4
+#endif
+#ifndef BNF_U_B2
+#define BNF_U_B2 4
+#endif
+static constexpr int kUF1 = BNF_U_F1, kUF2 = BNF_U_F2, kUB1 = BNF_U_B1, kUB2 = BNF_U_B2;
 #define BNF_SMEM_BUDGET (200 * 1024)
 #define BNF_SPIN_LIMIT (1 << 22)
 #define BNF_MAX_COLUMNS 48
@@ -464,7 +478,7 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
   const int nc = n_it < cached ? n_it : cached;
   for (int i = 0; i < nc; ++i) bnf_cp_async16(&tile[i * BNF_T + tid], xp + (r0 + rl + (int64_t)i * RL) * C);
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-#pragma unroll 8
+#pragma unroll kUF1
   for (int i = nc; i < n_it; ++i) {
     const float4 xv = bn_ld4(xp + (r0 + rl + (int64_t)i * RL) * C);
     a = f4_add(a, xv);
@@ -537,7 +551,7 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
   // phase 2: normalise out of shared memory (rows beyond the cached part come from L2/HBM again)
   // (last rows first: they are the ones most likely still in L2)
   {
-#pragma unroll 4
+#pragma unroll kUF2
     for (int i = n_it - 1; i >= 0; --i) {
       const int64_t r = r0 + rl + (int64_t)i * RL;
       const float4 xv = (i < nc) ? tile[i * BNF_T + tid] : bn_ld4(xp + r * C);
@@ -593,7 +607,7 @@ __device__ __forceinline__ float4 bn_pool_gather(const BnPool& P, int64_t r, int
 
 // dy2: optional second gradient of the same output (the output was handed out twice, see ops/bn.py), added
 // on the fly.  POOL: the gradient comes through the max pool described by P instead of dy.
-template <bool POOL>
+template <bool POOL, bool DUAL>
 __global__ void __launch_bounds__(BNF_T, 1)
 k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, const float* __restrict__ x,
                const float* __restrict__ y, const float* __restrict__ gamma, const float* __restrict__ beta,
@@ -625,7 +639,7 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
   auto load_g = [&](int64_t r, int64_t o) -> float4 {
     if (POOL) return bn_pool_gather(P, r, C, q);
     float4 g = bn_ld4(dy + o);
-    if (dy2 != nullptr) g = f4_add(g, bn_ld4(dy2 + o));
+    if (DUAL) g = f4_add(g, bn_ld4(dy2 + o));
     return g;
   };
   for (int i = 0; i < nc; ++i) {
@@ -634,7 +648,7 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
     bnf_cp_async16(&tile[(2 * i + 1) * BNF_T + tid], x + o);
   }
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-#pragma unroll 4
+#pragma unroll kUB1
   for (int i = nc; i < n_it; ++i) {
     const int64_t r = r0 + rl + (int64_t)i * RL;
     const int64_t o = r * C + 4 * q;
@@ -648,7 +662,7 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
     b = f4_fma(g, xh, b);
   }
   bnf_cp_async_wait_all();
-#pragma unroll 4
+#pragma unroll kUB1
   for (int i = 0; i < nc; ++i) {
     const int64_t r = r0 + rl + (int64_t)i * RL;
     const int64_t o = r * C + 4 * q;
@@ -658,10 +672,10 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
       g = bn_pool_gather(P, r, C, q);
     } else {
       g = tile[(2 * i) * BNF_T + tid];
-      if (dy2 != nullptr) g = f4_add(g, bn_ld4(dy2 + o));
+      if (DUAL) g = f4_add(g, bn_ld4(dy2 + o));
     }
     if (relu) g = bn_mask_pos(g, y != nullptr ? bn_ld4(y + o) : f4_fma(xv, sc, sh));
-    if (POOL || relu || dy2 != nullptr) tile[(2 * i) * BNF_T + tid] = g;
+    if (POOL || DUAL || relu) tile[(2 * i) * BNF_T + tid] = g;
     if (dres != nullptr) bn_st4(dres + o, g);
     const float4 xh = make_float4((xv.x - mu.x) * is.x, (xv.y - mu.y) * is.y, (xv.z - mu.z) * is.z,
                                   (xv.w - mu.w) * is.w);
@@ -704,7 +718,7 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
   }
   if (stamp) ts[4] = bnf_now();
   {
-#pragma unroll 4
+#pragma unroll kUB2
     for (int i = n_it - 1; i >= 0; --i) {      // last rows first: most likely still in L2
       const int64_t r = r0 + rl + (int64_t)i * RL;
       const int64_t o = r * C + 4 * q;
@@ -799,9 +813,11 @@ int bnf_prepare() {
   if (!ready[dev]) {
     e = cudaFuncSetAttribute(k_bn_fwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(k_bn_bwd_fused<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
+    e = cudaFuncSetAttribute(k_bn_bwd_fused<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(k_bn_bwd_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
+    e = cudaFuncSetAttribute(k_bn_bwd_fused<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(k_bn_bwd_fused<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
     if (e != cudaSuccess) return (int)e;
     ready[dev] = true;
   }
@@ -861,7 +877,8 @@ int bn_bwd_fused_launch(const float* dy, const float* dy2, const float* x, const
   double inv_m = 1.0 / (double)M;
   void* args[] = {&dy, &dy2, &x, &y, &gamma, &beta, &save_mean, &save_istd, &dx, &dres, &dgamma, &dbeta, &accum,
                   &bar, &M, &C, &g.rpb, &g.qshift, &cached, &inv_m, &flags, &P};
-  void* fn = pool ? (void*)k_bn_bwd_fused<true> : (void*)k_bn_bwd_fused<false>;
+  void* fn = pool ? (void*)k_bn_bwd_fused<true, false>
+                  : (dy2 != nullptr ? (void*)k_bn_bwd_fused<false, true> : (void*)k_bn_bwd_fused<false, false>);
   return (int)cudaLaunchCooperativeKernel(fn, g.grid, dim3(BNF_T), args, smem, (cudaStream_t)stream);
 }
 }  // namespace

@@ -18,7 +18,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(os.path.dirname(_HERE))
 CSRC = os.path.join(_ROOT, "csrc")
 INCLUDE = os.path.join(_ROOT, "include")
-CUDA_SO = os.path.join(_HERE, "libgk_cuda.so")
+# GK_CUDA_SO points at an alternative build (tuning sweeps: same sources, other -D flags)
+CUDA_SO = os.environ.get("GK_CUDA_SO") or os.path.join(_HERE, "libgk_cuda.so")
 CPU_SO = os.path.join(_HERE, "libgk_cpu.so")
 
 GK_NC = 16
