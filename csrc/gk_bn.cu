@@ -342,6 +342,25 @@ extern "C" int gk_bn_bwd(const float* dy, const float* x, const float* y, const 
 #ifndef BNF_U_B2
 #define BNF_U_B2 4
 #endif
+// Row assignment.  Interleaved (default): in iteration i block b handles rows (i*gridDim.x + b)*RL .. +RL-1, so
+// at any moment the blocks of a channel slab read one contiguous region (the access pattern of a streaming
+// copy: all DRAM channels busy, blocks finish together) and the rows read last — the ones phase 2 starts with —
+// are the tail of the tensor for every block.  BNF_INTERLEAVE=0: each block owns a contiguous slab of rows.
+#ifndef BNF_INTERLEAVE
+#define BNF_INTERLEAVE 1
+#endif
+#if BNF_INTERLEAVE
+#define BNF_ROWS_DECL                                                                     \
+  const int64_t rstep = (int64_t)gridDim.x * RL, rbase = (int64_t)blockIdx.x * RL + rl;   \
+  const int n_it = rbase < M ? (int)((M - rbase + rstep - 1) / rstep) : 0;                \
+  (void)rows_per_block;
+#else
+#define BNF_ROWS_DECL                                                                     \
+  const int64_t rstep = RL, r0_ = (int64_t)blockIdx.x * rows_per_block;                   \
+  const int64_t r1_ = (r0_ + rows_per_block < M) ? r0_ + rows_per_block : M;              \
+  const int64_t rbase = r0_ + rl;                                                         \
+  const int n_it = rbase < r1_ ? (int)((r1_ - rbase + RL - 1) / RL) : 0;
+#endif
 static constexpr int kUF1 = BNF_U_F1, kUF2 = BNF_U_F2, kUB1 = BNF_U_B1, kUB2 = BNF_U_B2;
 #define BNF_SMEM_BUDGET (200 * 1024)
 #define BNF_SPIN_LIMIT (1 << 22)
@@ -458,8 +477,7 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
   if (stamp) ts[0] = bnf_now();
   if (tid == 0 && gridDim.x > 1) s_gen = bnf_ld_relaxed(bar + 2 * blockIdx.y + 1);
   const int relu = flags & 1;
-  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
-  const int64_t r1 = (r0 + rows_per_block < M) ? r0 + rows_per_block : M;
+  BNF_ROWS_DECL
   const float* xp = x + 4 * q;
 
   // what the second phase needs besides the sums is fetched now, so its latency hides behind phase 1
@@ -473,14 +491,12 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
 
   // phase 1: one read of x.  The rows that fit in shared memory are fetched with cp.async (all in flight
   // at once, no register staging); the rest streams through registers meanwhile.
-  const int64_t rows = r1 - r0 - rl;
-  const int n_it = rows > 0 ? (int)((rows + RL - 1) >> (9 - qshift)) : 0;      // RL = 512 >> qshift
   const int nc = n_it < cached ? n_it : cached;
-  for (int i = 0; i < nc; ++i) bnf_cp_async16(&tile[i * BNF_T + tid], xp + (r0 + rl + (int64_t)i * RL) * C);
+  for (int i = 0; i < nc; ++i) bnf_cp_async16(&tile[i * BNF_T + tid], xp + (rbase + (int64_t)i * rstep) * C);
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
 #pragma unroll kUF1
   for (int i = nc; i < n_it; ++i) {
-    const float4 xv = bn_ld4(xp + (r0 + rl + (int64_t)i * RL) * C);
+    const float4 xv = bn_ld4(xp + (rbase + (int64_t)i * rstep) * C);
     a = f4_add(a, xv);
     b = f4_fma(xv, xv, b);
   }
@@ -523,6 +539,27 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
     mu[j] = (float)mean;
     is[j] = bnf_rsqrt((float)var + eps);
   }
+  const float4 sc = make_float4(gm.x * is[0], gm.y * is[1], gm.z * is[2], gm.w * is[3]);
+  const float4 sh = make_float4(fmaf(-mu[0], sc.x, bt.x), fmaf(-mu[1], sc.y, bt.y), fmaf(-mu[2], sc.z, bt.z),
+                                fmaf(-mu[3], sc.w, bt.w));
+  if (stamp) ts[4] = bnf_now();
+
+  // y == NULL: statistics only (the caller applies them itself, e.g. fused with a max pool)
+
+  // phase 2: normalise out of shared memory (rows beyond the cached part come from L2/HBM again)
+  // (last rows first: they are the ones most likely still in L2)
+  if (y != nullptr) {
+#pragma unroll kUF2
+    for (int i = n_it - 1; i >= 0; --i) {
+      const int64_t r = rbase + (int64_t)i * rstep;
+      const float4 xv = (i < nc) ? tile[i * BNF_T + tid] : bn_ld4(xp + r * C);
+      float4 o = f4_fma(xv, sc, sh);
+      if (res != nullptr) o = f4_add(o, bn_ld4(res + r * C + 4 * q));
+      if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+      bn_st4(y + r * C + 4 * q, o);
+    }
+  }
+  // per-channel results last: their latency (running statistics are read-modify-write) is off the critical path
   if (keeper) {
     double* other = accum + ((gen + 1ULL) & 1ULL) * 2 * (size_t)C;   // dirty from the previous launch
     if (alone) other = acc;                                           // (nothing is dirty: keep the stores valid)
@@ -540,26 +577,6 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
       }
     }
     if (blockIdx.y == 0 && tid == 0 && num_batches != nullptr) *num_batches += 1;
-  }
-  const float4 sc = make_float4(gm.x * is[0], gm.y * is[1], gm.z * is[2], gm.w * is[3]);
-  const float4 sh = make_float4(fmaf(-mu[0], sc.x, bt.x), fmaf(-mu[1], sc.y, bt.y), fmaf(-mu[2], sc.z, bt.z),
-                                fmaf(-mu[3], sc.w, bt.w));
-  if (stamp) ts[4] = bnf_now();
-
-  if (y == nullptr) return;   // statistics only (the caller applies them itself, e.g. fused with a max pool)
-
-  // phase 2: normalise out of shared memory (rows beyond the cached part come from L2/HBM again)
-  // (last rows first: they are the ones most likely still in L2)
-  {
-#pragma unroll kUF2
-    for (int i = n_it - 1; i >= 0; --i) {
-      const int64_t r = r0 + rl + (int64_t)i * RL;
-      const float4 xv = (i < nc) ? tile[i * BNF_T + tid] : bn_ld4(xp + r * C);
-      float4 o = f4_fma(xv, sc, sh);
-      if (res != nullptr) o = f4_add(o, bn_ld4(res + r * C + 4 * q));
-      if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
-      bn_st4(y + r * C + 4 * q, o);
-    }
   }
   if (stamp) ts[5] = bnf_now();
 }
@@ -626,15 +643,12 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
   if (stamp) ts[0] = bnf_now();
   if (tid == 0 && gridDim.x > 1) s_gen = bnf_ld_relaxed(bar + 2 * blockIdx.y + 1);
   const int relu = flags & 1;
-  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
-  const int64_t r1 = (r0 + rows_per_block < M) ? r0 + rows_per_block : M;
+  BNF_ROWS_DECL
   float4 mu, is, sc, sh;
   bn_load_channel_consts(gamma, beta, save_mean, save_istd, q, mu, is, sc, sh);
 
   // phase 1: dy and x of the rows that fit go to shared memory with cp.async; the rest streams through
   // registers meanwhile.  g = dy masked by the forward ReLU replaces dy in shared memory.
-  const int64_t rows = r1 - r0 - rl;
-  const int n_it = rows > 0 ? (int)((rows + RL - 1) >> (9 - qshift)) : 0;
   const int nc = n_it < cached ? n_it : cached;
   auto load_g = [&](int64_t r, int64_t o) -> float4 {
     if (POOL) return bn_pool_gather(P, r, C, q);
@@ -643,14 +657,14 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
     return g;
   };
   for (int i = 0; i < nc; ++i) {
-    const int64_t o = (r0 + rl + (int64_t)i * RL) * C + 4 * q;
+    const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
     if (!POOL) bnf_cp_async16(&tile[(2 * i) * BNF_T + tid], dy + o);
     bnf_cp_async16(&tile[(2 * i + 1) * BNF_T + tid], x + o);
   }
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
 #pragma unroll kUB1
   for (int i = nc; i < n_it; ++i) {
-    const int64_t r = r0 + rl + (int64_t)i * RL;
+    const int64_t r = rbase + (int64_t)i * rstep;
     const int64_t o = r * C + 4 * q;
     const float4 xv = bn_ld4(x + o);
     float4 g = load_g(r, o);
@@ -664,7 +678,7 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
   bnf_cp_async_wait_all();
 #pragma unroll kUB1
   for (int i = 0; i < nc; ++i) {
-    const int64_t r = r0 + rl + (int64_t)i * RL;
+    const int64_t r = rbase + (int64_t)i * rstep;
     const int64_t o = r * C + 4 * q;
     const float4 xv = tile[(2 * i + 1) * BNF_T + tid];
     float4 g;
@@ -720,7 +734,7 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
   {
 #pragma unroll kUB2
     for (int i = n_it - 1; i >= 0; --i) {      // last rows first: most likely still in L2
-      const int64_t r = r0 + rl + (int64_t)i * RL;
+      const int64_t r = rbase + (int64_t)i * rstep;
       const int64_t o = r * C + 4 * q;
       float4 g, xv;
       if (i < nc) {

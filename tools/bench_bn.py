@@ -29,7 +29,7 @@ def peak_bw():
     p = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")
     try:
         d = json.load(open(p))
-        for k in ("copy_bandwidth_GBps", "hbm_copy_GBps", "copy_GBps"):
+        for k in ("hbm_gbs", "copy_bandwidth_GBps", "hbm_copy_GBps", "copy_GBps"):
             if k in d:
                 return float(d[k]) * 1e9
     except Exception:
