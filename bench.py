@@ -330,14 +330,23 @@ def main():
     ap.add_argument("--transport", default=None)
     ap.add_argument("--no-graph", action="store_true")
     args = ap.parse_args()
-    # stdout carries exactly one JSON line: NCCL's banner ("NCCL version ...") and debug output go to stderr
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     if args.gpus > 1 and "RANK" not in os.environ:
         # convenience: re-launch ourselves under torchrun
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 400), os.path.abspath(__file__)] + sys.argv[1:]
         sys.exit(subprocess.call(cmd))
-    res = run_reference(args) if args.impl == "reference" else run_ours(args)
+    # stdout carries exactly one JSON line.  Native libraries write there too (NCCL prints its version banner
+    # to file descriptor 1), so descriptor 1 points at stderr while the benchmark runs and the JSON line goes
+    # to a private copy of the real stdout.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        res = run_reference(args) if args.impl == "reference" else run_ours(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
     if res is not None and (int(os.environ.get("RANK", "0")) == 0 or "unavailable" not in res):
         print(json.dumps(res), flush=True)
 
