@@ -453,6 +453,39 @@ __device__ __forceinline__ void bnf_cp_async_wait_all() {
   asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
 }
 
+// ---- optional: TMA bulk copies (cp.async.bulk, SASS UBLKCP) into the shared-memory slab, completion on an
+// mbarrier.  One thread per row lane issues one copy per cached row (the row's channel slab, 32-512 B
+// contiguous) instead of every thread issuing a 16-byte cp.async.  Built with -DBNF_TMA=1; measured on a
+// B200 it LOSES against cp.async (sum over the 53 ResNet-50 layers 3.65 ms vs 3.45 ms, the 7x7 layers with
+// their 32-64 B rows 35 % slower, the 100 MB layers equal; profiles/bn_unroll_sweep.txt), because the rows of
+// an NHWC channel slab are far below the size where one bulk copy beats sixteen vector copies — so the
+// default stays cp.async.
+#ifndef BNF_TMA
+#define BNF_TMA 0
+#endif
+__device__ __forceinline__ unsigned bnf_saddr(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bnf_mbar_init(unsigned long long* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bnf_saddr(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void bnf_mbar_expect(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bnf_saddr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bnf_bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(bnf_saddr(dst)), "l"(src), "r"(bytes), "r"(bnf_saddr(bar)) : "memory");
+}
+__device__ __forceinline__ void bnf_mbar_wait(unsigned long long* bar, unsigned parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "BNF_WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra BNF_DONE_%=;\n\t"
+      "bra BNF_WAIT_%=;\n\t"
+      "BNF_DONE_%=:\n\t}"
+      ::"r"(bnf_saddr(bar)), "r"(parity) : "memory");
+}
+
 __device__ __forceinline__ float bnf_rsqrt(float a) {   // rsqrt.approx plus one Newton step: < 1 ulp
   const float y = rsqrtf(a);
   return y * fmaf(-0.5f * a * y, y, 1.5f);
@@ -469,6 +502,9 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
   extern __shared__ float4 tile[];          // [cached][BNF_T]
   __shared__ float4 red[2][BNF_T];
   __shared__ unsigned long long s_gen;
+#if BNF_TMA
+  __shared__ __align__(8) unsigned long long s_mbar;
+#endif
   const int tid = threadIdx.x;
   const int qpb = 1 << qshift, ql = tid & (qpb - 1), rl = tid >> qshift, RL = BNF_T >> qshift;
   const int q = blockIdx.y * qpb + ql;
@@ -476,6 +512,10 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
   unsigned long long* ts = bar + BNF_STAMP_WORD;
   if (stamp) ts[0] = bnf_now();
   if (tid == 0 && gridDim.x > 1) s_gen = bnf_ld_relaxed(bar + 2 * blockIdx.y + 1);
+#if BNF_TMA
+  if (tid == 0) bnf_mbar_init(&s_mbar, (unsigned)RL);      // one arrival per row lane
+  __syncthreads();
+#endif
   const int relu = flags & 1;
   BNF_ROWS_DECL
   const float* xp = x + 4 * q;
@@ -492,7 +532,15 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
   // phase 1: one read of x.  The rows that fit in shared memory are fetched with cp.async (all in flight
   // at once, no register staging); the rest streams through registers meanwhile.
   const int nc = n_it < cached ? n_it : cached;
+#if BNF_TMA
+  if (ql == 0) {
+    bnf_mbar_expect(&s_mbar, (unsigned)(nc * qpb * 16));
+    for (int i = 0; i < nc; ++i)
+      bnf_bulk_g2s(&tile[i * BNF_T + tid], xp + (rbase + (int64_t)i * rstep) * C, (unsigned)(qpb * 16), &s_mbar);
+  }
+#else
   for (int i = 0; i < nc; ++i) bnf_cp_async16(&tile[i * BNF_T + tid], xp + (rbase + (int64_t)i * rstep) * C);
+#endif
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
 #pragma unroll kUF1
   for (int i = nc; i < n_it; ++i) {
@@ -500,7 +548,11 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
     a = f4_add(a, xv);
     b = f4_fma(xv, xv, b);
   }
+#if BNF_TMA
+  bnf_mbar_wait(&s_mbar, 0);
+#else
   bnf_cp_async_wait_all();
+#endif
 #pragma unroll 8
   for (int i = 0; i < nc; ++i) {
     const float4 xv = tile[i * BNF_T + tid];
@@ -635,6 +687,9 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
   extern __shared__ float4 tile[];          // [cached][2][BNF_T]: masked gradient, x
   __shared__ float4 red[2][BNF_T];
   __shared__ unsigned long long s_gen;
+#if BNF_TMA
+  __shared__ __align__(8) unsigned long long s_mbar;
+#endif
   const int tid = threadIdx.x;
   const int qpb = 1 << qshift, ql = tid & (qpb - 1), rl = tid >> qshift, RL = BNF_T >> qshift;
   const int q = blockIdx.y * qpb + ql;
@@ -642,6 +697,10 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
   unsigned long long* ts = bar + BNF_STAMP_WORD + 8;
   if (stamp) ts[0] = bnf_now();
   if (tid == 0 && gridDim.x > 1) s_gen = bnf_ld_relaxed(bar + 2 * blockIdx.y + 1);
+#if BNF_TMA
+  if (tid == 0) bnf_mbar_init(&s_mbar, (unsigned)RL);
+  __syncthreads();
+#endif
   const int relu = flags & 1;
   BNF_ROWS_DECL
   float4 mu, is, sc, sh;
@@ -656,11 +715,22 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
     if (DUAL) g = f4_add(g, bn_ld4(dy2 + o));
     return g;
   };
+#if BNF_TMA
+  if (ql == 0) {
+    bnf_mbar_expect(&s_mbar, (unsigned)(nc * qpb * 16 * (POOL ? 1 : 2)));
+    for (int i = 0; i < nc; ++i) {
+      const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
+      if (!POOL) bnf_bulk_g2s(&tile[(2 * i) * BNF_T + tid], dy + o, (unsigned)(qpb * 16), &s_mbar);
+      bnf_bulk_g2s(&tile[(2 * i + 1) * BNF_T + tid], x + o, (unsigned)(qpb * 16), &s_mbar);
+    }
+  }
+#else
   for (int i = 0; i < nc; ++i) {
     const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
     if (!POOL) bnf_cp_async16(&tile[(2 * i) * BNF_T + tid], dy + o);
     bnf_cp_async16(&tile[(2 * i + 1) * BNF_T + tid], x + o);
   }
+#endif
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
 #pragma unroll kUB1
   for (int i = nc; i < n_it; ++i) {
@@ -675,7 +745,11 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
     a = f4_add(a, g);
     b = f4_fma(g, xh, b);
   }
+#if BNF_TMA
+  bnf_mbar_wait(&s_mbar, 0);
+#else
   bnf_cp_async_wait_all();
+#endif
 #pragma unroll kUB1
   for (int i = 0; i < nc; ++i) {
     const int64_t r = rbase + (int64_t)i * rstep;

@@ -165,6 +165,8 @@ class DLTrainer:
         self.is_cuda = self.device.type == 'cuda'
         if self.is_cuda:
             torch.backends.cudnn.benchmark = settings.CUDNN_BENCHMARK
+            if settings.CUDNN_BENCHMARK_LIMIT is not None:      # how many algorithms the autotuner tries (0 = all)
+                torch.backends.cudnn.benchmark_limit = settings.CUDNN_BENCHMARK_LIMIT
         self.trainset = self.testset = self.trainloader = self.testloader = self.train_sampler = None
         self.vocab_size = 10000
         self.decoder = None

@@ -72,6 +72,9 @@ FUSED_BN_TWICE = _flag("FUSED_BN_TWICE", True)      # block outputs handed out t
 BN_STAMPS = _flag("BN_STAMPS", False)                # fused BN kernels record phase time stamps (profiling aid)
 CUDNN_BENCHMARK = _flag("CUDNN_BENCHMARK", True)    # the reference pins benchmark=False, deterministic=True
 
+CUDNN_BENCHMARK_LIMIT = (int(os.environ["GK_CUDNN_BENCHMARK_LIMIT"])
+                         if os.environ.get("GK_CUDNN_BENCHMARK_LIMIT") else None)   # None = torch's default (10)
+
 hostname = socket.gethostname()
 logger = logging.getLogger(hostname)
 
