@@ -290,3 +290,20 @@ def test_bn_act_twice_adds_the_two_gradients(with_res, relu):
     if with_res:
         torch.testing.assert_close(r1.grad, r2.grad, rtol=1e-5, atol=1e-6)
     assert not torch.equal(gx_single, x1.grad)
+
+
+def test_stem_space_to_depth_rewrite_is_exact():
+    """7x7/2 convolution on 3 channels == 4x4/1 convolution on the space-to-depth image (models/fuse.py)."""
+    from gaussiank_sgd_b200.models.fuse import _stem_conv_s2d
+    torch.manual_seed(4)
+    conv = nn.Conv2d(3, 16, 7, 2, 3, bias=False).double()
+    ref = copy.deepcopy(conv)
+    x = torch.randn(2, 3, 20, 28, dtype=torch.float64).contiguous(memory_format=torch.channels_last)
+    y, want = _stem_conv_s2d(conv, x), ref(x)
+    assert y.shape == want.shape
+    torch.testing.assert_close(y, want, rtol=1e-12, atol=1e-12)
+    d = torch.randn_like(want)
+    y.backward(d)
+    want.backward(d)
+    assert conv.weight.grad.shape == (16, 3, 7, 7)
+    torch.testing.assert_close(conv.weight.grad, ref.weight.grad, rtol=1e-11, atol=1e-11)
