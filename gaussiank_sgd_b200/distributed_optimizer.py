@@ -292,8 +292,10 @@ class _DistributedOptimizer(torch.optim.Optimizer):
             elif gr.data_ptr() == view.data_ptr():
                 ptrs.append(view.data_ptr())
                 dirty.append(view)
-            elif (gr.dtype == torch.float32 and gr.device == p.device and gr.stride() == p.stride()
-                  and gr.data_ptr() % 16 == 0):
+            elif (gr.dtype == torch.float32 and gr.device == p.device and gr.data_ptr() % 16 == 0
+                  and all(a == b or n == 1 for a, b, n in zip(gr.stride(), p.stride(), p.shape))):
+                # same element order in memory (strides of size-1 dimensions are arbitrary: the gradient of a
+                # 1x1 convolution weight comes back with other ones than the channels_last parameter has)
                 ptrs.append(gr.data_ptr())
             else:
                 view.copy_(gr)
