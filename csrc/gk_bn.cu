@@ -1097,3 +1097,341 @@ extern "C" int gk_bn_pool_bwd(const float* dyp, const unsigned char* pidx, const
   return bn_bwd_fused_launch(gfull, nullptr, x, nullptr, gamma, beta, save_mean, save_istd, dx, nullptr, dgamma,
                              dbeta, accum, bar, M, C, flags | 1, none, false, stream);
 }
+
+// ===================================================== two batch norms into one activation (downsample blocks)
+// y = relu( bnA(xa) + bnB(xb) ): the last BN of a bottleneck and the BN of its 1x1 downsample shortcut.  Done
+// separately the shortcut's normalised activation is written and read back (and its gradient too); here both
+// statistics are taken in one pass over xa and xb, and y / dxa / dxb come out of one kernel per direction.
+// Accumulator rows per parity: forward [sum xa, sum xa^2, sum xb, sum xb^2], backward [sum g, sum g*xhat_a,
+// sum g*xhat_b, unused]; scratch = 2 parities x 4 x C doubles + the usual 128 barrier words.
+struct Bn2Side {
+  const float* x;
+  const float* gamma;
+  const float* beta;
+  float* save_mean;
+  float* save_istd;
+  float* running_mean;
+  float* running_var;
+  int64_t* num_batches;
+  float eps, momentum;
+};
+
+__device__ __forceinline__ void bn2_consts(const double* s, const double* ss, double inv_m, float eps, float* mu,
+                                           float* is, double* meanv, double* varv) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const double mean = s[j] * inv_m;
+    double var = fma(ss[j], inv_m, -mean * mean);
+    if (var < 0) var = 0;
+    meanv[j] = mean;
+    varv[j] = var;
+    mu[j] = (float)mean;
+    is[j] = bnf_rsqrt((float)var + eps);
+  }
+}
+
+__device__ __forceinline__ void bn2_keep(const Bn2Side& S, int q, const float* mu, const float* is, const double* meanv,
+                                         const double* varv, float4 rm, float4 rv, double unbias) {
+  const float rmv[4] = {rm.x, rm.y, rm.z, rm.w}, rvv[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int c = 4 * q + j;
+    S.save_mean[c] = mu[j];
+    S.save_istd[c] = is[j];
+    if (S.running_mean != nullptr) {
+      S.running_mean[c] = (float)((1.0 - S.momentum) * (double)rmv[j] + S.momentum * meanv[j]);
+      S.running_var[c] = (float)((1.0 - S.momentum) * (double)rvv[j] + S.momentum * (varv[j] * unbias));
+    }
+  }
+}
+
+__global__ void __launch_bounds__(BNF_T, 1)
+k_bn2_fwd_fused(Bn2Side A, Bn2Side B, float* __restrict__ y, double* accum, unsigned long long* bar, int64_t M, int C,
+                int rows_per_block, int qshift, int cached, double inv_m, double unbias, int flags) {
+  extern __shared__ float4 tile[];          // [cached][2][BNF_T]: xa, xb
+  __shared__ float4 red[2][BNF_T];
+  __shared__ unsigned long long s_gen;
+  const int tid = threadIdx.x;
+  const int qpb = 1 << qshift, ql = tid & (qpb - 1), rl = tid >> qshift, RL = BNF_T >> qshift;
+  const int q = blockIdx.y * qpb + ql;
+  if (tid == 0 && gridDim.x > 1) s_gen = bnf_ld_relaxed(bar + 2 * blockIdx.y + 1);
+  const int relu = flags & 1;
+  BNF_ROWS_DECL
+  const float4 gmA = bn_ld4(A.gamma + 4 * q), btA = bn_ld4(A.beta + 4 * q);
+  const float4 gmB = bn_ld4(B.gamma + 4 * q), btB = bn_ld4(B.beta + 4 * q);
+  const bool keeper = blockIdx.x == 0 && rl == 0;
+  float4 rmA = make_float4(0.f, 0.f, 0.f, 0.f), rvA = rmA, rmB = rmA, rvB = rmA;
+  if (keeper && A.running_mean != nullptr) { rmA = bn_ld4(A.running_mean + 4 * q); rvA = bn_ld4(A.running_var + 4 * q); }
+  if (keeper && B.running_mean != nullptr) { rmB = bn_ld4(B.running_mean + 4 * q); rvB = bn_ld4(B.running_var + 4 * q); }
+
+  const int nc = n_it < cached ? n_it : cached;
+  for (int i = 0; i < nc; ++i) {
+    const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
+    bnf_cp_async16(&tile[(2 * i) * BNF_T + tid], A.x + o);
+    bnf_cp_async16(&tile[(2 * i + 1) * BNF_T + tid], B.x + o);
+  }
+  float4 a1 = make_float4(0.f, 0.f, 0.f, 0.f), a2 = a1, b1 = a1, b2 = a1;
+#pragma unroll 4
+  for (int i = nc; i < n_it; ++i) {
+    const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
+    const float4 xa = bn_ld4(A.x + o), xb = bn_ld4(B.x + o);
+    a1 = f4_add(a1, xa); a2 = f4_fma(xa, xa, a2);
+    b1 = f4_add(b1, xb); b2 = f4_fma(xb, xb, b2);
+  }
+  bnf_cp_async_wait_all();
+#pragma unroll 4
+  for (int i = 0; i < nc; ++i) {
+    const float4 xa = tile[(2 * i) * BNF_T + tid], xb = tile[(2 * i + 1) * BNF_T + tid];
+    a1 = f4_add(a1, xa); a2 = f4_fma(xa, xa, a2);
+    b1 = f4_add(b1, xb); b2 = f4_fma(xb, xb, b2);
+  }
+  const bool alone = gridDim.x == 1;
+  double sA[4], ssA[4], sB[4], ssB[4];
+  bnf_reduce_rows(red, a1, a2, tid, rl, RL, qpb);
+  if (alone) {
+    const float4 ta = red[0][ql], tb = red[1][ql];
+    sA[0] = ta.x; sA[1] = ta.y; sA[2] = ta.z; sA[3] = ta.w;
+    ssA[0] = tb.x; ssA[1] = tb.y; ssA[2] = tb.z; ssA[3] = tb.w;
+  }
+  __syncthreads();
+  bnf_reduce_rows(red, b1, b2, tid, rl, RL, qpb);
+  const unsigned long long gen = alone ? 0ULL : s_gen;
+  double* acc = accum + (gen & 1ULL) * 4 * (size_t)C;
+  if (alone) {
+    const float4 ta = red[0][ql], tb = red[1][ql];
+    sB[0] = ta.x; sB[1] = ta.y; sB[2] = ta.z; sB[3] = ta.w;
+    ssB[0] = tb.x; ssB[1] = tb.y; ssB[2] = tb.z; ssB[3] = tb.w;
+  } else {
+    if (rl == 0) {
+      bnf_atomic_add8(acc, C, q, a1, a2);
+      bnf_atomic_add8(acc + 2 * (size_t)C, C, q, b1, b2);
+    }
+    bnf_column_barrier(bar, gen);
+    bnf_load_totals(acc, C, q, sA, ssA);
+    bnf_load_totals(acc + 2 * (size_t)C, C, q, sB, ssB);
+  }
+  float muA[4], isA[4], muB[4], isB[4];
+  double meanA[4], varA[4], meanB[4], varB[4];
+  bn2_consts(sA, ssA, inv_m, A.eps, muA, isA, meanA, varA);
+  bn2_consts(sB, ssB, inv_m, B.eps, muB, isB, meanB, varB);
+  const float4 scA = make_float4(gmA.x * isA[0], gmA.y * isA[1], gmA.z * isA[2], gmA.w * isA[3]);
+  const float4 shA = make_float4(fmaf(-muA[0], scA.x, btA.x), fmaf(-muA[1], scA.y, btA.y), fmaf(-muA[2], scA.z, btA.z),
+                                 fmaf(-muA[3], scA.w, btA.w));
+  const float4 scB = make_float4(gmB.x * isB[0], gmB.y * isB[1], gmB.z * isB[2], gmB.w * isB[3]);
+  const float4 shB = make_float4(fmaf(-muB[0], scB.x, btB.x), fmaf(-muB[1], scB.y, btB.y), fmaf(-muB[2], scB.z, btB.z),
+                                 fmaf(-muB[3], scB.w, btB.w));
+#pragma unroll 4
+  for (int i = n_it - 1; i >= 0; --i) {
+    const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
+    const float4 xa = (i < nc) ? tile[(2 * i) * BNF_T + tid] : bn_ld4(A.x + o);
+    const float4 xb = (i < nc) ? tile[(2 * i + 1) * BNF_T + tid] : bn_ld4(B.x + o);
+    float4 v = f4_add(f4_fma(xa, scA, shA), f4_fma(xb, scB, shB));
+    if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+    bn_st4(y + o, v);
+  }
+  if (keeper) {
+    if (!alone) {
+      double* other = accum + ((gen + 1ULL) & 1ULL) * 4 * (size_t)C;
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) other[r * (size_t)C + 4 * q + j] = 0;
+    }
+    bn2_keep(A, q, muA, isA, meanA, varA, rmA, rvA, unbias);
+    bn2_keep(B, q, muB, isB, meanB, varB, rmB, rvB, unbias);
+    if (blockIdx.y == 0 && tid == 0) {
+      if (A.num_batches != nullptr) *A.num_batches += 1;
+      if (B.num_batches != nullptr) *B.num_batches += 1;
+    }
+  }
+}
+
+struct Bn2Back {
+  const float* x;
+  const float* gamma;
+  const float* beta;
+  const float* save_mean;
+  const float* save_istd;
+  float* dx;
+  float* dgamma;
+  float* dbeta;
+};
+
+// g = (dy [+ dy2]) masked by y > 0; dxa, dxb, dgamma/dbeta of both sides.  The masked gradient of the rows that do
+// not fit in shared memory is parked in A.dx between the phases (same thread, same address).
+__global__ void __launch_bounds__(BNF_T, 1)
+k_bn2_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, const float* __restrict__ y, Bn2Back A,
+                Bn2Back B, double* accum, unsigned long long* bar, int64_t M, int C, int rows_per_block, int qshift,
+                int cached, double inv_m, int flags) {
+  extern __shared__ float4 tile[];          // [cached][3][BNF_T]: g, xa, xb
+  __shared__ float4 red[2][BNF_T];
+  __shared__ unsigned long long s_gen;
+  const int tid = threadIdx.x;
+  const int qpb = 1 << qshift, ql = tid & (qpb - 1), rl = tid >> qshift, RL = BNF_T >> qshift;
+  const int q = blockIdx.y * qpb + ql;
+  if (tid == 0 && gridDim.x > 1) s_gen = bnf_ld_relaxed(bar + 2 * blockIdx.y + 1);
+  const int relu = flags & 1;
+  BNF_ROWS_DECL
+  float4 muA, isA, scA, shA, muB, isB, scB, shB;
+  bn_load_channel_consts(A.gamma, A.beta, A.save_mean, A.save_istd, q, muA, isA, scA, shA);
+  bn_load_channel_consts(B.gamma, B.beta, B.save_mean, B.save_istd, q, muB, isB, scB, shB);
+
+  const int nc = n_it < cached ? n_it : cached;
+  for (int i = 0; i < nc; ++i) {
+    const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
+    bnf_cp_async16(&tile[(3 * i) * BNF_T + tid], dy + o);
+    bnf_cp_async16(&tile[(3 * i + 1) * BNF_T + tid], A.x + o);
+    bnf_cp_async16(&tile[(3 * i + 2) * BNF_T + tid], B.x + o);
+  }
+  float4 sg = make_float4(0.f, 0.f, 0.f, 0.f), sa = sg, sb = sg;
+  auto xhat = [](float4 x, float4 mu, float4 is) {
+    return make_float4((x.x - mu.x) * is.x, (x.y - mu.y) * is.y, (x.z - mu.z) * is.z, (x.w - mu.w) * is.w);
+  };
+#pragma unroll 2
+  for (int i = nc; i < n_it; ++i) {
+    const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
+    const float4 xa = bn_ld4(A.x + o), xb = bn_ld4(B.x + o);
+    float4 g = bn_ld4(dy + o);
+    if (dy2 != nullptr) g = f4_add(g, bn_ld4(dy2 + o));
+    if (relu) g = bn_mask_pos(g, bn_ld4(y + o));
+    bn_st4(A.dx + o, g);
+    sg = f4_add(sg, g);
+    sa = f4_fma(g, xhat(xa, muA, isA), sa);
+    sb = f4_fma(g, xhat(xb, muB, isB), sb);
+  }
+  bnf_cp_async_wait_all();
+#pragma unroll 2
+  for (int i = 0; i < nc; ++i) {
+    const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
+    const float4 xa = tile[(3 * i + 1) * BNF_T + tid], xb = tile[(3 * i + 2) * BNF_T + tid];
+    float4 g = tile[(3 * i) * BNF_T + tid];
+    if (dy2 != nullptr) g = f4_add(g, bn_ld4(dy2 + o));
+    if (relu) g = bn_mask_pos(g, bn_ld4(y + o));
+    tile[(3 * i) * BNF_T + tid] = g;
+    sg = f4_add(sg, g);
+    sa = f4_fma(g, xhat(xa, muA, isA), sa);
+    sb = f4_fma(g, xhat(xb, muB, isB), sb);
+  }
+  const bool alone = gridDim.x == 1;
+  float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+  double tg[4], ta_[4], tb_[4], dummy[4];
+  bnf_reduce_rows(red, sg, sa, tid, rl, RL, qpb);
+  if (alone) {
+    const float4 u = red[0][ql], v = red[1][ql];
+    tg[0] = u.x; tg[1] = u.y; tg[2] = u.z; tg[3] = u.w;
+    ta_[0] = v.x; ta_[1] = v.y; ta_[2] = v.z; ta_[3] = v.w;
+  }
+  __syncthreads();
+  bnf_reduce_rows(red, sb, zero, tid, rl, RL, qpb);
+  const unsigned long long gen = alone ? 0ULL : s_gen;
+  double* acc = accum + (gen & 1ULL) * 4 * (size_t)C;
+  if (alone) {
+    const float4 u = red[0][ql];
+    tb_[0] = u.x; tb_[1] = u.y; tb_[2] = u.z; tb_[3] = u.w;
+  } else {
+    if (rl == 0) {
+      bnf_atomic_add8(acc, C, q, sg, sa);
+      atomicAdd(acc + 2 * (size_t)C + 4 * q + 0, (double)sb.x); atomicAdd(acc + 2 * (size_t)C + 4 * q + 1, (double)sb.y);
+      atomicAdd(acc + 2 * (size_t)C + 4 * q + 2, (double)sb.z); atomicAdd(acc + 2 * (size_t)C + 4 * q + 3, (double)sb.w);
+    }
+    bnf_column_barrier(bar, gen);
+    bnf_load_totals(acc, C, q, tg, ta_);
+    bnf_load_totals(acc + 2 * (size_t)C, C, q, tb_, dummy);
+  }
+  float mg[4], mga[4], mgb[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    mg[j] = (float)(tg[j] * inv_m);
+    mga[j] = (float)(ta_[j] * inv_m);
+    mgb[j] = (float)(tb_[j] * inv_m);
+  }
+#pragma unroll 2
+  for (int i = n_it - 1; i >= 0; --i) {
+    const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
+    float4 g, xa, xb;
+    if (i < nc) {
+      g = tile[(3 * i) * BNF_T + tid];
+      xa = tile[(3 * i + 1) * BNF_T + tid];
+      xb = tile[(3 * i + 2) * BNF_T + tid];
+    } else {
+      g = bn_ld4(A.dx + o);
+      xa = bn_ld4(A.x + o);
+      xb = bn_ld4(B.x + o);
+    }
+    float4 da, db;
+    da.x = scA.x * (g.x - mg[0] - (xa.x - muA.x) * isA.x * mga[0]);
+    da.y = scA.y * (g.y - mg[1] - (xa.y - muA.y) * isA.y * mga[1]);
+    da.z = scA.z * (g.z - mg[2] - (xa.z - muA.z) * isA.z * mga[2]);
+    da.w = scA.w * (g.w - mg[3] - (xa.w - muA.w) * isA.w * mga[3]);
+    db.x = scB.x * (g.x - mg[0] - (xb.x - muB.x) * isB.x * mgb[0]);
+    db.y = scB.y * (g.y - mg[1] - (xb.y - muB.y) * isB.y * mgb[1]);
+    db.z = scB.z * (g.z - mg[2] - (xb.z - muB.z) * isB.z * mgb[2]);
+    db.w = scB.w * (g.w - mg[3] - (xb.w - muB.w) * isB.w * mgb[3]);
+    bn_st4(A.dx + o, da);
+    bn_st4(B.dx + o, db);
+  }
+  if (blockIdx.x == 0 && rl == 0) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = 4 * q + j;
+      if (!alone) {
+        double* other = accum + ((gen + 1ULL) & 1ULL) * 4 * (size_t)C;
+        other[c] = 0; other[C + c] = 0; other[2 * (size_t)C + c] = 0; other[3 * (size_t)C + c] = 0;
+      }
+      A.dbeta[c] = (float)tg[j];
+      B.dbeta[c] = (float)tg[j];
+      A.dgamma[c] = (float)ta_[j];
+      B.dgamma[c] = (float)tb_[j];
+    }
+  }
+}
+
+extern "C" int gk_bn2_fwd_fused(void* const* a, void* const* b, float eps_a, float mom_a, float eps_b, float mom_b,
+                                float* y, double* accum, unsigned long long* bar, int64_t M, int C, int flags,
+                                void* stream) {
+  BnfGeom g;
+  if (!bnf_geometry(M, C, &g)) return (int)cudaErrorInvalidValue;
+  for (int i = 0; i < 5; ++i)
+    if (!bn_aligned(a[i]) || !bn_aligned(b[i])) return (int)cudaErrorMisalignedAddress;
+  if (!bn_aligned(y) || !bn_aligned(accum)) return (int)cudaErrorMisalignedAddress;
+  static bool ready[64] = {false};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
+  if (!ready[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(k_bn2_fwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(k_bn2_bwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
+    if (e != cudaSuccess) return (int)e;
+    ready[dev] = true;
+  }
+  Bn2Side A = {(const float*)a[0], (const float*)a[1], (const float*)a[2], (float*)a[3], (float*)a[4], (float*)a[5],
+               (float*)a[6], (int64_t*)a[7], eps_a, mom_a};
+  Bn2Side B = {(const float*)b[0], (const float*)b[1], (const float*)b[2], (float*)b[3], (float*)b[4], (float*)b[5],
+               (float*)b[6], (int64_t*)b[7], eps_b, mom_b};
+  int cached = g.iters < BNF_SMEM_BUDGET / (BNF_T * 32) ? g.iters : BNF_SMEM_BUDGET / (BNF_T * 32);
+  size_t smem = (size_t)cached * BNF_T * 32;
+  double inv_m = 1.0 / (double)M, unbias = M > 1 ? (double)M / (double)(M - 1) : 1.0;
+  void* args[] = {&A, &B, &y, &accum, &bar, &M, &C, &g.rpb, &g.qshift, &cached, &inv_m, &unbias, &flags};
+  return (int)cudaLaunchCooperativeKernel((void*)k_bn2_fwd_fused, g.grid, dim3(BNF_T), args, smem,
+                                          (cudaStream_t)stream);
+}
+
+extern "C" int gk_bn2_bwd_fused(const float* dy, const float* dy2, const float* y, void* const* a, void* const* b,
+                                double* accum, unsigned long long* bar, int64_t M, int C, int flags, void* stream) {
+  BnfGeom g;
+  if (!bnf_geometry(M, C, &g)) return (int)cudaErrorInvalidValue;
+  for (int i = 0; i < 8; ++i)
+    if (!bn_aligned(a[i]) || !bn_aligned(b[i])) return (int)cudaErrorMisalignedAddress;
+  if (!bn_aligned(dy) || !bn_aligned(dy2) || !bn_aligned(y) || !bn_aligned(accum)) return (int)cudaErrorMisalignedAddress;
+  if ((flags & 1) && y == nullptr) return (int)cudaErrorInvalidValue;
+  Bn2Back A = {(const float*)a[0], (const float*)a[1], (const float*)a[2], (const float*)a[3], (const float*)a[4],
+               (float*)a[5], (float*)a[6], (float*)a[7]};
+  Bn2Back B = {(const float*)b[0], (const float*)b[1], (const float*)b[2], (const float*)b[3], (const float*)b[4],
+               (float*)b[5], (float*)b[6], (float*)b[7]};
+  int cached = g.iters < BNF_SMEM_BUDGET / (BNF_T * 48) ? g.iters : BNF_SMEM_BUDGET / (BNF_T * 48);
+  size_t smem = (size_t)cached * BNF_T * 48;
+  double inv_m = 1.0 / (double)M;
+  void* args[] = {&dy, &dy2, &y, &A, &B, &accum, &bar, &M, &C, &g.rpb, &g.qshift, &cached, &inv_m, &flags};
+  return (int)cudaLaunchCooperativeKernel((void*)k_bn2_bwd_fused, g.grid, dim3(BNF_T), args, smem,
+                                          (cudaStream_t)stream);
+}

@@ -18,7 +18,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from .. import settings
-from ..ops.bn import bn_act, bn_relu_maxpool
+from ..ops.bn import bn2_act, bn_act, bn_relu_maxpool
 
 
 class FusedBNReLU(nn.BatchNorm2d):
@@ -43,19 +43,30 @@ def _split(x):
     return x if isinstance(x, tuple) else (x, x)
 
 
+def _plain_shortcut(mod):
+    ds = mod.downsample
+    return isinstance(ds, nn.Sequential) and len(ds) == 2 and type(ds[1]) is nn.BatchNorm2d
+
+
 def _bottleneck_forward(self, x):
     xc, xi = _split(x)
-    s = xi if self.downsample is None else _downsample(self, xc)
     y = bn_act(self.bn1, self.conv1(xc))
     y = bn_act(self.bn2, self.conv2(y))
-    return bn_act(self.bn3, self.conv3(y), residual=s, twice=getattr(self, "_gk_twice", False))
+    twice = getattr(self, "_gk_twice", False)
+    if self.downsample is not None and _plain_shortcut(self):      # both BNs of the junction in one kernel
+        return bn2_act(self.bn3, self.conv3(y), self.downsample[1], self.downsample[0](xc), twice=twice)
+    s = xi if self.downsample is None else self.downsample(xc)
+    return bn_act(self.bn3, self.conv3(y), residual=s, twice=twice)
 
 
 def _basic_forward(self, x):
     xc, xi = _split(x)
-    s = xi if self.downsample is None else _downsample(self, xc)
     y = bn_act(self.bn1, self.conv1(xc))
-    return bn_act(self.bn2, self.conv2(y), residual=s, twice=getattr(self, "_gk_twice", False))
+    twice = getattr(self, "_gk_twice", False)
+    if self.downsample is not None and _plain_shortcut(self):
+        return bn2_act(self.bn2, self.conv2(y), self.downsample[1], self.downsample[0](xc), twice=twice)
+    s = xi if self.downsample is None else self.downsample(xc)
+    return bn_act(self.bn2, self.conv2(y), residual=s, twice=twice)
 
 
 def _is_stem_pool(m):

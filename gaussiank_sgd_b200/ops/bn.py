@@ -211,6 +211,82 @@ class _BnReluPool(torch.autograd.Function):
         return dx, dgamma, dbeta, None
 
 
+def _ptr_table(ptrs):
+    arr = (native.C.c_void_p * len(ptrs))(*[p if p else None for p in ptrs])
+    return arr
+
+
+class _Bn2Act(torch.autograd.Function):
+    """relu(bn_a(xa) + bn_b(xb)): last BN of a residual block plus the BN of its downsample shortcut."""
+
+    @staticmethod
+    def forward(ctx, xa, xb, wa, ba, wb, bb, bna, bnb, relu, twice):
+        N, C, H, W = xa.shape
+        M = N * H * W
+        y = torch.empty_like(xa, memory_format=torch.channels_last)
+        stats = torch.empty(4, C, dtype=torch.float32, device=xa.device)
+        table = bna.__dict__.setdefault("_gk_bn_coop", {})
+        key = (str(xa.device), C, "pair")
+        if key not in table:
+            table[key] = (torch.zeros(8 * C, dtype=torch.float64, device=xa.device),
+                          torch.zeros(128, dtype=torch.int64, device=xa.device))
+        accum, bar = ctx.scratch = table[key]
+
+        def side(x, w, b, bn, row):
+            track = bn.track_running_stats and bn.running_mean is not None
+            return _ptr_table([_ptr(x), _ptr(w), _ptr(b), stats[row].data_ptr(), stats[row + 1].data_ptr(),
+                               _ptr(bn.running_mean) if track else None, _ptr(bn.running_var) if track else None,
+                               _ptr(bn.num_batches_tracked) if track else None])
+        ta, tb = side(xa, wa, ba, bna, 0), side(xb, wb, bb, bnb, 2)
+        native.check(native.cuda_lib().gk_bn2_fwd_fused(ta, tb, float(bna.eps), float(bna.momentum), float(bnb.eps),
+                                                        float(bnb.momentum), _ptr(y), accum.data_ptr(), bar.data_ptr(),
+                                                        M, C, int(relu), _stream()), "gk_bn2_fwd_fused")
+        _chain.LAUNCHES["n"] += 1
+        ctx.relu = bool(relu)
+        ctx.save_for_backward(xa, xb, wa, ba, wb, bb, stats, y)
+        if twice:
+            ctx.set_materialize_grads(False)
+            return y, y.view_as(y)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy, dy2=None):
+        xa, xb, wa, ba, wb, bb, stats, y = ctx.saved_tensors
+        N, C, H, W = xa.shape
+        M = N * H * W
+        if dy is None:
+            dy, dy2 = dy2, None
+        if dy is None:
+            return (None,) * 10
+        if not _rows_view_ok(dy):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        if dy2 is not None and not _rows_view_ok(dy2):
+            dy2 = dy2.contiguous(memory_format=torch.channels_last)
+        dxa = torch.empty_like(xa, memory_format=torch.channels_last)
+        dxb = torch.empty_like(xb, memory_format=torch.channels_last)
+        dga, dba, dgb, dbb = (torch.empty(C, dtype=torch.float32, device=xa.device) for _ in range(4))
+        accum, bar = ctx.scratch
+        ta = _ptr_table([_ptr(xa), _ptr(wa), _ptr(ba), stats[0].data_ptr(), stats[1].data_ptr(), _ptr(dxa), _ptr(dga),
+                         _ptr(dba)])
+        tb = _ptr_table([_ptr(xb), _ptr(wb), _ptr(bb), stats[2].data_ptr(), stats[3].data_ptr(), _ptr(dxb), _ptr(dgb),
+                         _ptr(dbb)])
+        native.check(native.cuda_lib().gk_bn2_bwd_fused(_ptr(dy), _ptr(dy2), _ptr(y), ta, tb, accum.data_ptr(),
+                                                        bar.data_ptr(), M, C, int(ctx.relu), _stream()),
+                     "gk_bn2_bwd_fused")
+        _chain.LAUNCHES["n"] += 1
+        return dxa, dxb, dga, dba, dgb, dbb, None, None, None, None
+
+
+def bn2_act(bna, xa, bnb, xb, relu=True, twice=False):
+    """``relu(bna(xa) + bnb(xb))`` — e.g. ``bn3(conv3(.)) + downsample_bn(downsample_conv(.))`` of a ResNet block."""
+    if (settings.FUSED_BN and settings.FUSED_BN_PAIR and settings.FUSED_BN_COOP and xa.shape == xb.shape
+            and eligible(bna, xa) and eligible(bnb, xb)
+            and native.cuda_lib().gk_bn_fused_supported(xa.numel() // xa.shape[1], xa.shape[1])):
+        return _Bn2Act.apply(xa, xb, bna.weight, bna.bias, bnb.weight, bnb.bias, bna, bnb, relu, twice)
+    return bn_act(bna, xa, residual=bn_act(bnb, xb, relu=False), relu=relu, twice=twice)
+
+
 def bn_act(bn, x, residual=None, relu=True, twice=False):
     """``relu(bn(x) + residual)`` with ``residual`` and ``relu`` optional; ``bn`` is an nn.BatchNorm2d.
     ``twice=True`` returns the result as two tensors sharing one storage (see _BnAct.forward)."""

@@ -289,6 +289,18 @@ int gk_bn_pool_bwd(const float* dyp, const unsigned char* pidx, const float* x, 
                    const float* save_mean, const float* save_istd, float* dx, float* gfull, float* dgamma,
                    float* dbeta, double* accum, unsigned long long* bar, int N, int H, int W, int C, int flags,
                    void* stream);
+/* Two batch norms into one activation: y = relu(bn_a(xa) + bn_b(xb)) — the last BN of a residual block and the
+ * BN of its 1x1 downsample shortcut — in one cooperative kernel per direction (the shortcut's normalised
+ * activation and its gradient are never materialised).  Pointer tables, 8 entries each:
+ *   forward  a[] / b[] = { x, gamma, beta, save_mean, save_istd, running_mean|NULL, running_var|NULL, num_batches|NULL }
+ *   backward a[] / b[] = { x, gamma, beta, save_mean, save_istd, dx, dgamma, dbeta }
+ * dy2 may be NULL (second gradient of y, added on the fly); y is the saved forward output (ReLU mask).
+ * Scratch per pair of layers: accum = 8*C doubles (two parities of four rows), bar as for gk_bn_fwd_fused;
+ * needs gk_bn_fused_supported(M, C).  flags bit 0 = ReLU. */
+int gk_bn2_fwd_fused(void* const* a, void* const* b, float eps_a, float mom_a, float eps_b, float mom_b, float* y,
+                     double* accum, unsigned long long* bar, int64_t M, int C, int flags, void* stream);
+int gk_bn2_bwd_fused(const float* dy, const float* dy2, const float* y, void* const* a, void* const* b, double* accum,
+                     unsigned long long* bar, int64_t M, int C, int flags, void* stream);
 /* Geometry knobs for benchmarks (defaults 9 = no cap, 128): cap on log2 of the channel slab in float4 quads, and the
  * largest per-block slab in KB for which one block takes a channel slab over all rows (no barrier). */
 int gk_bn_set_tuning(int qcap_log2, int private_kb);

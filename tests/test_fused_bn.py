@@ -307,3 +307,53 @@ def test_stem_space_to_depth_rewrite_is_exact():
     want.backward(d)
     assert conv.weight.grad.shape == (16, 3, 7, 7)
     torch.testing.assert_close(conv.weight.grad, ref.weight.grad, rtol=1e-11, atol=1e-11)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(32, 256, 28, 28), (8, 2048, 7, 7), (4, 96, 9, 9), (16, 512, 14, 14)])
+@pytest.mark.parametrize("twice", [False, True])
+def test_two_bns_into_one_activation(shape, twice):
+    from gaussiank_sgd_b200.ops.bn import bn2_act
+    torch.manual_seed(sum(shape))
+    dev = torch.device("cuda:0")
+    N, C, H, W = shape
+    bna, bnb = nn.BatchNorm2d(C).to(dev), nn.BatchNorm2d(C, momentum=0.2).to(dev)
+    with torch.no_grad():
+        for bn in (bna, bnb):
+            bn.weight.uniform_(0.5, 1.5)
+            bn.bias.uniform_(-0.5, 0.5)
+    ra, rb = copy.deepcopy(bna), copy.deepcopy(bnb)
+    xa = (torch.randn(N, C, H, W, device=dev) * 2 + 0.5).contiguous(memory_format=torch.channels_last)
+    xb = (torch.randn(N, C, H, W, device=dev) - 0.3).contiguous(memory_format=torch.channels_last)
+    a1, b1 = xa.clone().requires_grad_(True), xb.clone().requires_grad_(True)
+    a2, b2 = xa.clone().requires_grad_(True), xb.clone().requires_grad_(True)
+    for rep in range(2):
+        out = bn2_act(bna, a1, bnb, b1, twice=twice)
+        want = F.relu(ra(a2) + rb(b2))
+        d1 = torch.randn_like(want)
+        for t in (a1, b1, a2, b2, bna.weight, bna.bias, bnb.weight, bnb.bias, ra.weight, ra.bias, rb.weight, rb.bias):
+            t.grad = None
+        if twice:
+            ya, yb = out
+            assert ya.data_ptr() == yb.data_ptr()
+            d2 = torch.randn_like(want)
+            torch.testing.assert_close(ya, want, rtol=1e-5, atol=3e-5)
+            ((ya * d1).sum() + (yb * d2).sum()).backward()
+            want.backward(d1 + d2)
+        else:
+            torch.testing.assert_close(out, want, rtol=1e-5, atol=3e-5)
+            out.backward(d1)
+            want.backward(d1)
+        sure = want.detach().abs() > 1e-5
+        torch.testing.assert_close(a1.grad * sure, a2.grad * sure, rtol=1e-4, atol=5e-5)
+        torch.testing.assert_close(b1.grad * sure, b2.grad * sure, rtol=1e-4, atol=5e-5)
+        M = N * H * W
+        for p, r in ((bna.weight, ra.weight), (bna.bias, ra.bias), (bnb.weight, rb.weight), (bnb.bias, rb.bias)):
+            torch.testing.assert_close(p.grad, r.grad, rtol=1e-4, atol=1e-5 * M ** 0.5 * 6)
+        for bn, r in ((bna, ra), (bnb, rb)):
+            torch.testing.assert_close(bn.running_mean, r.running_mean, rtol=1e-5, atol=1e-6)
+            torch.testing.assert_close(bn.running_var, r.running_var, rtol=1e-5, atol=1e-6)
+            assert int(bn.num_batches_tracked) == rep + 1
+    assert coop_errors(bna) == 0
+    if C % 32 == 0:
+        assert any(k[-1] == "pair" for k in bna.__dict__["_gk_bn_coop"])
