@@ -54,8 +54,8 @@ def _bottleneck_forward(self, x):
     y = bn_act(self.bn2, self.conv2(y))
     twice = getattr(self, "_gk_twice", False)
     if self.downsample is not None and _plain_shortcut(self):      # both BNs of the junction in one kernel
-        return bn2_act(self.bn3, self.conv3(y), self.downsample[1], self.downsample[0](xc), twice=twice)
-    s = xi if self.downsample is None else self.downsample(xc)
+        return bn2_act(self.bn3, self.conv3(y), self.downsample[1], self.downsample[0](xi), twice=twice)
+    s = xi if self.downsample is None else self.downsample(xi)
     return bn_act(self.bn3, self.conv3(y), residual=s, twice=twice)
 
 
@@ -64,8 +64,8 @@ def _basic_forward(self, x):
     y = bn_act(self.bn1, self.conv1(xc))
     twice = getattr(self, "_gk_twice", False)
     if self.downsample is not None and _plain_shortcut(self):
-        return bn2_act(self.bn2, self.conv2(y), self.downsample[1], self.downsample[0](xc), twice=twice)
-    s = xi if self.downsample is None else self.downsample(xc)
+        return bn2_act(self.bn2, self.conv2(y), self.downsample[1], self.downsample[0](xi), twice=twice)
+    s = xi if self.downsample is None else self.downsample(xi)
     return bn_act(self.bn2, self.conv2(y), residual=s, twice=twice)
 
 
@@ -141,11 +141,18 @@ def fuse_bn_act(model: nn.Module) -> int:
         elif tv is not None and type(m) is tv.ResNet and type(m.bn1) is nn.BatchNorm2d:
             m.forward = types.MethodType(_resnet_forward, m)
             sites += 1
+            # the last block of a stage feeds the next stage's first convolution and its downsample convolution
+            stages = [m.layer1, m.layer2, m.layer3, m.layer4]
+            for la, lb in zip(stages, stages[1:]):
+                if (settings.FUSED_BN_TWICE and len(la) and len(lb)
+                        and type(la[-1]) in (tv.Bottleneck, tv.BasicBlock) and type(lb[0]) in (tv.Bottleneck, tv.BasicBlock)):
+                    la[-1]._gk_stage_twice = True
         elif isinstance(m, nn.Sequential):
             blocks = list(m)
             if tv is not None and blocks and all(type(b) in (tv.Bottleneck, tv.BasicBlock) for b in blocks):
                 for b, nxt in zip(blocks, blocks[1:] + [None]):      # a ResNet stage
-                    b._gk_twice = bool(settings.FUSED_BN_TWICE and nxt is not None and nxt.downsample is None)
+                    b._gk_twice = bool(settings.FUSED_BN_TWICE and ((nxt is not None and nxt.downsample is None)
+                                                                      or getattr(b, "_gk_stage_twice", False)))
             for i in range(len(m) - 1):
                 if type(m[i]) is nn.BatchNorm2d and type(m[i + 1]) is nn.ReLU:
                     m[i].__class__ = FusedBNReLU
