@@ -25,6 +25,20 @@ __device__ __forceinline__ float4 f4_fma(float4 a, float4 b, float4 c) {
   return make_float4(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y), fmaf(a.z, b.z, c.z), fmaf(a.w, b.w, c.w));
 }
 
+// What decides the ReLU mask of a saved forward output: the output itself or, with flag bit 2 (value 4), one
+// byte per channel quad written by the forward kernel (bit j = output j of the quad was positive) — a sixteenth
+// of the bytes.
+__device__ __forceinline__ float4 bn_mask_src(const float* y, int64_t o, int64_t r, int C, int q, bool bits) {
+  if (bits) {
+    const unsigned b = reinterpret_cast<const unsigned char*>(y)[r * (C >> 2) + q];
+    return make_float4((b & 1u) ? 1.f : 0.f, (b & 2u) ? 1.f : 0.f, (b & 4u) ? 1.f : 0.f, (b & 8u) ? 1.f : 0.f);
+  }
+  return bn_ld4(y + o);
+}
+__device__ __forceinline__ unsigned char bn_mask_bits(float4 v) {
+  return (unsigned char)((v.x > 0.f ? 1u : 0u) | (v.y > 0.f ? 2u : 0u) | (v.z > 0.f ? 4u : 0u) | (v.w > 0.f ? 8u : 0u));
+}
+
 // true in the last block to arrive (self-resetting ticket), same pattern as gk_cuda.cu
 __device__ __forceinline__ bool bn_last_block(uint32_t* ticket, uint32_t nblocks) {
   __shared__ int s_last;
@@ -498,7 +512,7 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
                float* __restrict__ save_istd, float* running_mean, float* running_var, int64_t* num_batches,
                double* accum /* [2 parities][2][C] */, unsigned long long* bar, int64_t M, int C,
                int rows_per_block, int qshift, int cached, float eps, float momentum, double inv_m, double unbias,
-               int flags) {
+               int flags, unsigned char* __restrict__ mask /* optional: ReLU bits, one byte per channel quad */) {
   extern __shared__ float4 tile[];          // [cached][BNF_T]
   __shared__ float4 red[2][BNF_T];
   __shared__ unsigned long long s_gen;
@@ -607,6 +621,7 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
       const float4 xv = (i < nc) ? tile[i * BNF_T + tid] : bn_ld4(xp + r * C);
       float4 o = f4_fma(xv, sc, sh);
       if (res != nullptr) o = f4_add(o, bn_ld4(res + r * C + 4 * q));
+      if (mask != nullptr) mask[r * (C >> 2) + q] = bn_mask_bits(o);
       if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
       bn_st4(y + r * C + 4 * q, o);
     }
@@ -702,6 +717,7 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
   __syncthreads();
 #endif
   const int relu = flags & 1;
+  const bool mbits = (flags & 4) != 0;
   BNF_ROWS_DECL
   float4 mu, is, sc, sh;
   bn_load_channel_consts(gamma, beta, save_mean, save_istd, q, mu, is, sc, sh);
@@ -738,7 +754,7 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
     const int64_t o = r * C + 4 * q;
     const float4 xv = bn_ld4(x + o);
     float4 g = load_g(r, o);
-    if (relu) g = bn_mask_pos(g, y != nullptr ? bn_ld4(y + o) : f4_fma(xv, sc, sh));
+    if (relu) g = bn_mask_pos(g, y != nullptr ? bn_mask_src(y, o, r, C, q, mbits) : f4_fma(xv, sc, sh));
     if (dres != nullptr) bn_st4(dres + o, g);
     const float4 xh = make_float4((xv.x - mu.x) * is.x, (xv.y - mu.y) * is.y, (xv.z - mu.z) * is.z,
                                   (xv.w - mu.w) * is.w);
@@ -762,7 +778,7 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
       g = tile[(2 * i) * BNF_T + tid];
       if (DUAL) g = f4_add(g, bn_ld4(dy2 + o));
     }
-    if (relu) g = bn_mask_pos(g, y != nullptr ? bn_ld4(y + o) : f4_fma(xv, sc, sh));
+    if (relu) g = bn_mask_pos(g, y != nullptr ? bn_mask_src(y, o, r, C, q, mbits) : f4_fma(xv, sc, sh));
     if (POOL || DUAL || relu) tile[(2 * i) * BNF_T + tid] = g;
     if (dres != nullptr) bn_st4(dres + o, g);
     const float4 xh = make_float4((xv.x - mu.x) * is.x, (xv.y - mu.y) * is.y, (xv.z - mu.z) * is.z,
@@ -820,7 +836,7 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
           g = bn_ld4(dres + o);            // already masked by phase 1 (written by this very thread)
         } else {
           g = load_g(r, o);
-          if (relu) g = bn_mask_pos(g, y != nullptr ? bn_ld4(y + o) : f4_fma(xv, sc, sh));
+          if (relu) g = bn_mask_pos(g, y != nullptr ? bn_mask_src(y, o, r, C, q, mbits) : f4_fma(xv, sc, sh));
         }
       }
       float4 d;
@@ -926,10 +942,23 @@ extern "C" int gk_bn_fused_supported(int64_t M, int C) {
   return bnf_geometry(M, C, &g) ? 1 : 0;
 }
 
+extern "C" int gk_bn_fwd_fused_m(const float* x, const float* res, float* y, const float* gamma, const float* beta,
+                                 float* running_mean, float* running_var, int64_t* num_batches, float* save_mean,
+                                 float* save_istd, double* accum, unsigned long long* bar, int64_t M, int C,
+                                 float eps, float momentum, int flags, unsigned char* mask, void* stream);
+
 extern "C" int gk_bn_fwd_fused(const float* x, const float* res, float* y, const float* gamma, const float* beta,
                                float* running_mean, float* running_var, int64_t* num_batches, float* save_mean,
                                float* save_istd, double* accum, unsigned long long* bar, int64_t M, int C,
                                float eps, float momentum, int flags, void* stream) {
+  return gk_bn_fwd_fused_m(x, res, y, gamma, beta, running_mean, running_var, num_batches, save_mean, save_istd, accum,
+                           bar, M, C, eps, momentum, flags, nullptr, stream);
+}
+
+extern "C" int gk_bn_fwd_fused_m(const float* x, const float* res, float* y, const float* gamma, const float* beta,
+                                 float* running_mean, float* running_var, int64_t* num_batches, float* save_mean,
+                                 float* save_istd, double* accum, unsigned long long* bar, int64_t M, int C,
+                                 float eps, float momentum, int flags, unsigned char* mask, void* stream) {
   BnfGeom g;
   if (!bnf_geometry(M, C, &g)) return (int)cudaErrorInvalidValue;
   if (!bn_aligned(x) || !bn_aligned(y) || !bn_aligned(res) || !bn_aligned(gamma) || !bn_aligned(beta) ||
@@ -941,7 +970,7 @@ extern "C" int gk_bn_fwd_fused(const float* x, const float* res, float* y, const
   size_t smem = (size_t)cached * BNF_T * 16;
   double inv_m = 1.0 / (double)M, unbias = M > 1 ? (double)M / (double)(M - 1) : 1.0;
   void* args[] = {&x, &res, &y, &gamma, &beta, &save_mean, &save_istd, &running_mean, &running_var, &num_batches,
-                  &accum, &bar, &M, &C, &g.rpb, &g.qshift, &cached, &eps, &momentum, &inv_m, &unbias, &flags};
+                  &accum, &bar, &M, &C, &g.rpb, &g.qshift, &cached, &eps, &momentum, &inv_m, &unbias, &flags, &mask};
   return (int)cudaLaunchCooperativeKernel((void*)k_bn_fwd_fused, g.grid, dim3(BNF_T), args, smem,
                                           (cudaStream_t)stream);
 }
@@ -1147,7 +1176,8 @@ __device__ __forceinline__ void bn2_keep(const Bn2Side& S, int q, const float* m
 
 __global__ void __launch_bounds__(BNF_T, 1)
 k_bn2_fwd_fused(Bn2Side A, Bn2Side B, float* __restrict__ y, double* accum, unsigned long long* bar, int64_t M, int C,
-                int rows_per_block, int qshift, int cached, double inv_m, double unbias, int flags) {
+                int rows_per_block, int qshift, int cached, double inv_m, double unbias, int flags,
+                unsigned char* __restrict__ mask) {
   extern __shared__ float4 tile[];          // [cached][2][BNF_T]: xa, xb
   __shared__ float4 red[2][BNF_T];
   __shared__ unsigned long long s_gen;
@@ -1226,6 +1256,7 @@ k_bn2_fwd_fused(Bn2Side A, Bn2Side B, float* __restrict__ y, double* accum, unsi
     const float4 xa = (i < nc) ? tile[(2 * i) * BNF_T + tid] : bn_ld4(A.x + o);
     const float4 xb = (i < nc) ? tile[(2 * i + 1) * BNF_T + tid] : bn_ld4(B.x + o);
     float4 v = f4_add(f4_fma(xa, scA, shA), f4_fma(xb, scB, shB));
+    if (mask != nullptr) mask[(rbase + (int64_t)i * rstep) * (C >> 2) + q] = bn_mask_bits(v);
     if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
     bn_st4(y + o, v);
   }
@@ -1271,6 +1302,7 @@ k_bn2_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, con
   const int q = blockIdx.y * qpb + ql;
   if (tid == 0 && gridDim.x > 1) s_gen = bnf_ld_relaxed(bar + 2 * blockIdx.y + 1);
   const int relu = flags & 1;
+  const bool mbits = (flags & 4) != 0;
   BNF_ROWS_DECL
   float4 muA, isA, scA, shA, muB, isB, scB, shB;
   bn_load_channel_consts(A.gamma, A.beta, A.save_mean, A.save_istd, q, muA, isA, scA, shA);
@@ -1293,7 +1325,7 @@ k_bn2_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, con
     const float4 xa = bn_ld4(A.x + o), xb = bn_ld4(B.x + o);
     float4 g = bn_ld4(dy + o);
     if (dy2 != nullptr) g = f4_add(g, bn_ld4(dy2 + o));
-    if (relu) g = bn_mask_pos(g, bn_ld4(y + o));
+    if (relu) g = bn_mask_pos(g, bn_mask_src(y, o, rbase + (int64_t)i * rstep, C, q, mbits));
     bn_st4(A.dx + o, g);
     sg = f4_add(sg, g);
     sa = f4_fma(g, xhat(xa, muA, isA), sa);
@@ -1306,7 +1338,7 @@ k_bn2_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, con
     const float4 xa = tile[(3 * i + 1) * BNF_T + tid], xb = tile[(3 * i + 2) * BNF_T + tid];
     float4 g = tile[(3 * i) * BNF_T + tid];
     if (dy2 != nullptr) g = f4_add(g, bn_ld4(dy2 + o));
-    if (relu) g = bn_mask_pos(g, bn_ld4(y + o));
+    if (relu) g = bn_mask_pos(g, bn_mask_src(y, o, rbase + (int64_t)i * rstep, C, q, mbits));
     tile[(3 * i) * BNF_T + tid] = g;
     sg = f4_add(sg, g);
     sa = f4_fma(g, xhat(xa, muA, isA), sa);
@@ -1387,8 +1419,8 @@ k_bn2_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, con
 }
 
 extern "C" int gk_bn2_fwd_fused(void* const* a, void* const* b, float eps_a, float mom_a, float eps_b, float mom_b,
-                                float* y, double* accum, unsigned long long* bar, int64_t M, int C, int flags,
-                                void* stream) {
+                                float* y, unsigned char* mask, double* accum, unsigned long long* bar, int64_t M, int C,
+                                int flags, void* stream) {
   BnfGeom g;
   if (!bnf_geometry(M, C, &g)) return (int)cudaErrorInvalidValue;
   for (int i = 0; i < 5; ++i)
@@ -1411,7 +1443,7 @@ extern "C" int gk_bn2_fwd_fused(void* const* a, void* const* b, float eps_a, flo
   int cached = g.iters < BNF_SMEM_BUDGET / (BNF_T * 32) ? g.iters : BNF_SMEM_BUDGET / (BNF_T * 32);
   size_t smem = (size_t)cached * BNF_T * 32;
   double inv_m = 1.0 / (double)M, unbias = M > 1 ? (double)M / (double)(M - 1) : 1.0;
-  void* args[] = {&A, &B, &y, &accum, &bar, &M, &C, &g.rpb, &g.qshift, &cached, &inv_m, &unbias, &flags};
+  void* args[] = {&A, &B, &y, &accum, &bar, &M, &C, &g.rpb, &g.qshift, &cached, &inv_m, &unbias, &flags, &mask};
   return (int)cudaLaunchCooperativeKernel((void*)k_bn2_fwd_fused, g.grid, dim3(BNF_T), args, smem,
                                           (cudaStream_t)stream);
 }

@@ -106,9 +106,14 @@ class _BnAct(torch.autograd.Function):
                 _ptr(bn.running_mean) if track else None, _ptr(bn.running_var) if track else None,
                 _ptr(bn.num_batches_tracked) if track else None, stats[0].data_ptr(), stats[1].data_ptr())
         tail = (M, C, float(bn.eps), float(bn.momentum), int(relu) | (2 if settings.BN_STAMPS else 0), _stream())
+        mask = None
         if ctx.coop:
             accum, bar = ctx.scratch = _scratch_coop(bn, x.device, C)
-            native.check(lib.gk_bn_fwd_fused(*head, accum.data_ptr(), bar.data_ptr(), *tail), "gk_bn_fwd_fused")
+            if relu and residual is not None and settings.FUSED_BN_MASK:
+                # the backward needs to know where the ReLU was active: one byte per channel quad instead of y
+                mask = torch.empty(M * (C // 4), dtype=torch.uint8, device=x.device)
+            native.check(lib.gk_bn_fwd_fused_m(*head, accum.data_ptr(), bar.data_ptr(), *tail[:-1], _ptr(mask),
+                                               tail[-1]), "gk_bn_fwd_fused")
             _chain.LAUNCHES["n"] += 1
         else:
             accum, ticket = ctx.scratch = _scratch(bn, x.device, C)
@@ -117,7 +122,9 @@ class _BnAct(torch.autograd.Function):
         ctx.relu = bool(relu)
         ctx.has_res = residual is not None
         # the ReLU mask is recomputed from x unless a residual went into the activation
-        ctx.save_for_backward(x, weight, bias, stats, y if (relu and residual is not None) else None)
+        ctx.has_mask = mask is not None
+        ctx.save_for_backward(x, weight, bias, stats,
+                              mask if mask is not None else (y if (relu and residual is not None) else None))
         if twice:
             # the same activation handed out twice (convolution input + identity shortcut of the next block):
             # autograd then delivers the two gradients separately and the backward kernel adds them on the
@@ -153,7 +160,8 @@ class _BnAct(torch.autograd.Function):
         if ctx.coop:
             accum, bar = ctx.scratch
             native.check(lib.gk_bn_bwd_fused2(head[0], _ptr(dy2), *head[1:], accum.data_ptr(), bar.data_ptr(), M, C,
-                                              int(ctx.relu) | (2 if settings.BN_STAMPS else 0), _stream()),
+                                              int(ctx.relu) | (2 if settings.BN_STAMPS else 0)
+                                              | (4 if ctx.has_mask else 0), _stream()),
                          "gk_bn_bwd_fused2")
             _chain.LAUNCHES["n"] += 1
         else:
@@ -238,12 +246,15 @@ class _Bn2Act(torch.autograd.Function):
                                _ptr(bn.running_mean) if track else None, _ptr(bn.running_var) if track else None,
                                _ptr(bn.num_batches_tracked) if track else None])
         ta, tb = side(xa, wa, ba, bna, 0), side(xb, wb, bb, bnb, 2)
+        mask = (torch.empty(M * (C // 4), dtype=torch.uint8, device=xa.device)
+                if (relu and settings.FUSED_BN_MASK) else None)
         native.check(native.cuda_lib().gk_bn2_fwd_fused(ta, tb, float(bna.eps), float(bna.momentum), float(bnb.eps),
-                                                        float(bnb.momentum), _ptr(y), accum.data_ptr(), bar.data_ptr(),
-                                                        M, C, int(relu), _stream()), "gk_bn2_fwd_fused")
+                                                        float(bnb.momentum), _ptr(y), _ptr(mask), accum.data_ptr(),
+                                                        bar.data_ptr(), M, C, int(relu), _stream()), "gk_bn2_fwd_fused")
         _chain.LAUNCHES["n"] += 1
         ctx.relu = bool(relu)
-        ctx.save_for_backward(xa, xb, wa, ba, wb, bb, stats, y)
+        ctx.has_mask = mask is not None
+        ctx.save_for_backward(xa, xb, wa, ba, wb, bb, stats, mask if mask is not None else y)
         if twice:
             ctx.set_materialize_grads(False)
             return y, y.view_as(y)
@@ -272,7 +283,8 @@ class _Bn2Act(torch.autograd.Function):
         tb = _ptr_table([_ptr(xb), _ptr(wb), _ptr(bb), stats[2].data_ptr(), stats[3].data_ptr(), _ptr(dxb), _ptr(dgb),
                          _ptr(dbb)])
         native.check(native.cuda_lib().gk_bn2_bwd_fused(_ptr(dy), _ptr(dy2), _ptr(y), ta, tb, accum.data_ptr(),
-                                                        bar.data_ptr(), M, C, int(ctx.relu), _stream()),
+                                                        bar.data_ptr(), M, C,
+                                                        int(ctx.relu) | (4 if ctx.has_mask else 0), _stream()),
                      "gk_bn2_bwd_fused")
         _chain.LAUNCHES["n"] += 1
         return dxa, dxb, dga, dba, dgb, dbb, None, None, None, None

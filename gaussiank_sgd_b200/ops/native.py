@@ -178,8 +178,9 @@ def cuda_lib():
             _proto(lib, "gk_bn_fused_supported", [C.c_int64, C.c_int32])
             _proto(lib, "gk_bn_set_tuning", [C.c_int32, C.c_int32])
             _proto(lib, "gk_bn_bwd_fused2", [_P] * 14 + [C.c_int64, C.c_int32, C.c_int32, _P])
-            _proto(lib, "gk_bn2_fwd_fused", [_P, _P, C.c_float, C.c_float, C.c_float, C.c_float, _P, _P, _P, C.c_int64,
+            _proto(lib, "gk_bn2_fwd_fused", [_P, _P, C.c_float, C.c_float, C.c_float, C.c_float, _P, _P, _P, _P, C.c_int64,
                                              C.c_int32, C.c_int32, _P])
+            _proto(lib, "gk_bn_fwd_fused_m", [_P] * 12 + [C.c_int64, C.c_int32, C.c_float, C.c_float, C.c_int32, _P, _P])
             _proto(lib, "gk_bn2_bwd_fused", [_P, _P, _P, _P, _P, _P, _P, C.c_int64, C.c_int32, C.c_int32, _P])
             _proto(lib, "gk_bn_pool_fwd", [_P] * 13 + [C.c_int32] * 4 + [C.c_float, C.c_float, _P])
             _proto(lib, "gk_bn_pool_bwd", [_P] * 13 + [C.c_int32] * 5 + [_P])

@@ -68,6 +68,7 @@ SYNTHETIC_POOL = _flag("SYNTHETIC_POOL", True)      # pre-collated pinned batche
 FUSED_BN = _flag("FUSED_BN", True)                  # BN(+residual)+ReLU through csrc/gk_bn.cu on GPUs (ops/bn.py)
 FUSED_BN_COOP = _flag("FUSED_BN_COOP", True)        # single cooperative kernel per direction where the shape allows
 FUSED_BN_POOL = _flag("FUSED_BN_POOL", True)        # stem: BN+ReLU+maxpool(3,2,1) without the full-resolution write
+FUSED_BN_MASK = _flag("FUSED_BN_MASK", True)        # residual junctions: ReLU bit mask for the backward instead of y
 FUSED_BN_PAIR = _flag("FUSED_BN_PAIR", True)        # downsample blocks: bn3 and the shortcut's BN in one kernel
 FUSED_BN_TWICE = _flag("FUSED_BN_TWICE", True)      # block outputs handed out twice: no autograd add at the junctions
 STEM_S2D = _flag("STEM_S2D", True)                  # ResNet stem as a 4x4 convolution on the space-to-depth image

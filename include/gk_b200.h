@@ -298,7 +298,16 @@ int gk_bn_pool_bwd(const float* dyp, const unsigned char* pidx, const float* x, 
  * Scratch per pair of layers: accum = 8*C doubles (two parities of four rows), bar as for gk_bn_fwd_fused;
  * needs gk_bn_fused_supported(M, C).  flags bit 0 = ReLU. */
 int gk_bn2_fwd_fused(void* const* a, void* const* b, float eps_a, float mom_a, float eps_b, float mom_b, float* y,
-                     double* accum, unsigned long long* bar, int64_t M, int C, int flags, void* stream);
+                     unsigned char* mask, double* accum, unsigned long long* bar, int64_t M, int C, int flags,
+                     void* stream);
+/* ReLU bit masks: a forward call given mask != NULL also writes one byte per channel quad (M*C/4 bytes, bit j =
+ * output j of the quad was positive); the backward calls take that buffer in place of y when flags has bit 2
+ * (value 4) set — a sixteenth of the bytes of re-reading the activation.  gk_bn_fwd_fused_m is gk_bn_fwd_fused
+ * with the extra mask argument. */
+int gk_bn_fwd_fused_m(const float* x, const float* res, float* y, const float* gamma, const float* beta,
+                      float* running_mean, float* running_var, int64_t* num_batches, float* save_mean,
+                      float* save_istd, double* accum, unsigned long long* bar, int64_t M, int C, float eps,
+                      float momentum, int flags, unsigned char* mask, void* stream);
 int gk_bn2_bwd_fused(const float* dy, const float* dy2, const float* y, void* const* a, void* const* b, double* accum,
                      unsigned long long* bar, int64_t M, int C, int flags, void* stream);
 /* Geometry knobs for benchmarks (defaults 9 = no cap, 128): cap on log2 of the channel slab in float4 quads, and the
