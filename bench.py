@@ -218,6 +218,10 @@ def run_ours(args):
                        "density": DENSITY, "optimizer": "sgd momentum 0.875 wd 6.1e-5", "lr": LR,
                        "transport": transport.name + (":" + getattr(transport, "backend", "") if hasattr(transport, "backend") else ""),
                        "cuda_graph": graphed, "channels_last": trainer.channels_last,
+                       "fused_bn_sites": getattr(trainer, "fused_bn_sites", 0),
+                       "model_rewrites": "own BN(+residual)(+ReLU)(+maxpool) kernels at every BatchNorm2d, stem 7x7/2 "
+                                         "convolution computed as 4x4 on the space-to-depth image (exact); same "
+                                         "parameters, same arithmetic as torchvision resnet50",
                        "conv_math": "fp32 storage, cuDNN TF32 convolutions allowed (torch default), fp32 matmul",
                        "l2": "no explicit flush: every step streams ~0.4 GB of arenas plus GBs of activations, "
                              "far larger than the 126 MB L2"},
