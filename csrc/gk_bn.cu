@@ -851,6 +851,14 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
 }
 
 namespace {
+// cudaLaunchCooperativeKernel reports e.g. cudaErrorCooperativeLaunchTooLarge synchronously; the error is not
+// sticky, but it stays in the runtime's "last error" slot where the next launch check of the host framework
+// would find it.  Take it out so that the caller can fall back to the two-kernel path.
+inline int bn_coop_result(cudaError_t e) {
+  if (e != cudaSuccess) (void)cudaGetLastError();
+  return (int)e;
+}
+
 int g_qcap = 9;           // upper bound on log2 of the channel slab width (in quads), cooperative path
 int g_private_kb = 128;   // largest per-block slab of the barrier-free path
 
@@ -971,8 +979,8 @@ extern "C" int gk_bn_fwd_fused_m(const float* x, const float* res, float* y, con
   double inv_m = 1.0 / (double)M, unbias = M > 1 ? (double)M / (double)(M - 1) : 1.0;
   void* args[] = {&x, &res, &y, &gamma, &beta, &save_mean, &save_istd, &running_mean, &running_var, &num_batches,
                   &accum, &bar, &M, &C, &g.rpb, &g.qshift, &cached, &eps, &momentum, &inv_m, &unbias, &flags, &mask};
-  return (int)cudaLaunchCooperativeKernel((void*)k_bn_fwd_fused, g.grid, dim3(BNF_T), args, smem,
-                                          (cudaStream_t)stream);
+  return bn_coop_result(cudaLaunchCooperativeKernel((void*)k_bn_fwd_fused, g.grid, dim3(BNF_T), args, smem,
+                                          (cudaStream_t)stream));
 }
 
 namespace {
@@ -996,7 +1004,7 @@ int bn_bwd_fused_launch(const float* dy, const float* dy2, const float* x, const
                   &bar, &M, &C, &g.rpb, &g.qshift, &cached, &inv_m, &flags, &P};
   void* fn = pool ? (void*)k_bn_bwd_fused<true, false>
                   : (dy2 != nullptr ? (void*)k_bn_bwd_fused<false, true> : (void*)k_bn_bwd_fused<false, false>);
-  return (int)cudaLaunchCooperativeKernel(fn, g.grid, dim3(BNF_T), args, smem, (cudaStream_t)stream);
+  return bn_coop_result(cudaLaunchCooperativeKernel(fn, g.grid, dim3(BNF_T), args, smem, (cudaStream_t)stream));
 }
 }  // namespace
 
@@ -1444,8 +1452,8 @@ extern "C" int gk_bn2_fwd_fused(void* const* a, void* const* b, float eps_a, flo
   size_t smem = (size_t)cached * BNF_T * 32;
   double inv_m = 1.0 / (double)M, unbias = M > 1 ? (double)M / (double)(M - 1) : 1.0;
   void* args[] = {&A, &B, &y, &accum, &bar, &M, &C, &g.rpb, &g.qshift, &cached, &inv_m, &unbias, &flags, &mask};
-  return (int)cudaLaunchCooperativeKernel((void*)k_bn2_fwd_fused, g.grid, dim3(BNF_T), args, smem,
-                                          (cudaStream_t)stream);
+  return bn_coop_result(cudaLaunchCooperativeKernel((void*)k_bn2_fwd_fused, g.grid, dim3(BNF_T), args, smem,
+                                          (cudaStream_t)stream));
 }
 
 extern "C" int gk_bn2_bwd_fused(const float* dy, const float* dy2, const float* y, void* const* a, void* const* b,
@@ -1464,6 +1472,6 @@ extern "C" int gk_bn2_bwd_fused(const float* dy, const float* dy2, const float* 
   size_t smem = (size_t)cached * BNF_T * 48;
   double inv_m = 1.0 / (double)M;
   void* args[] = {&dy, &dy2, &y, &A, &B, &accum, &bar, &M, &C, &g.rpb, &g.qshift, &cached, &inv_m, &flags};
-  return (int)cudaLaunchCooperativeKernel((void*)k_bn2_bwd_fused, g.grid, dim3(BNF_T), args, smem,
-                                          (cudaStream_t)stream);
+  return bn_coop_result(cudaLaunchCooperativeKernel((void*)k_bn2_bwd_fused, g.grid, dim3(BNF_T), args, smem,
+                                          (cudaStream_t)stream));
 }

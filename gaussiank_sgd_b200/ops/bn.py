@@ -40,6 +40,8 @@ def _scratch(bn, device, C):
 
 
 ERR_WORD, STAMP_WORD = 127, 96
+_COOP_OFF = {"off": False}
+_COOP_LAUNCH_ERRORS = (720, 701)   # cudaErrorCooperativeLaunchTooLarge, cudaErrorLaunchOutOfResources
 
 
 def _scratch_coop(bn, device, C):
@@ -101,7 +103,7 @@ class _BnAct(torch.autograd.Function):
         stats = torch.empty(2, C, dtype=torch.float32, device=x.device)
         track = bn.track_running_stats and bn.running_mean is not None
         lib = native.cuda_lib()
-        ctx.coop = bool(settings.FUSED_BN_COOP and lib.gk_bn_fused_supported(M, C))
+        ctx.coop = bool(settings.FUSED_BN_COOP and not _COOP_OFF["off"] and lib.gk_bn_fused_supported(M, C))
         head = (_ptr(x), _ptr(residual), _ptr(y), _ptr(weight), _ptr(bias),
                 _ptr(bn.running_mean) if track else None, _ptr(bn.running_var) if track else None,
                 _ptr(bn.num_batches_tracked) if track else None, stats[0].data_ptr(), stats[1].data_ptr())
@@ -112,10 +114,17 @@ class _BnAct(torch.autograd.Function):
             if relu and residual is not None and settings.FUSED_BN_MASK:
                 # the backward needs to know where the ReLU was active: one byte per channel quad instead of y
                 mask = torch.empty(M * (C // 4), dtype=torch.uint8, device=x.device)
-            native.check(lib.gk_bn_fwd_fused_m(*head, accum.data_ptr(), bar.data_ptr(), *tail[:-1], _ptr(mask),
-                                               tail[-1]), "gk_bn_fwd_fused")
-            _chain.LAUNCHES["n"] += 1
-        else:
+            rc = lib.gk_bn_fwd_fused_m(*head, accum.data_ptr(), bar.data_ptr(), *tail[:-1], _ptr(mask), tail[-1])
+            if rc in _COOP_LAUNCH_ERRORS:
+                # the device cannot keep one block per SM resident (SM share limited by MPS, ...): use the
+                # two-kernel variant from now on
+                _COOP_OFF["off"] = True
+                ctx.coop, mask = False, None
+                settings.logger.warning("cooperative launch refused (cudaError %d): fused BN falls back to two kernels", rc)
+            else:
+                native.check(rc, "gk_bn_fwd_fused")
+                _chain.LAUNCHES["n"] += 1
+        if not ctx.coop:
             accum, ticket = ctx.scratch = _scratch(bn, x.device, C)
             native.check(lib.gk_bn_fwd(*head, accum.data_ptr(), ticket.data_ptr(), *tail), "gk_bn_fwd")
             _chain.LAUNCHES["n"] += 2
@@ -292,7 +301,8 @@ class _Bn2Act(torch.autograd.Function):
 
 def bn2_act(bna, xa, bnb, xb, relu=True, twice=False):
     """``relu(bna(xa) + bnb(xb))`` — e.g. ``bn3(conv3(.)) + downsample_bn(downsample_conv(.))`` of a ResNet block."""
-    if (settings.FUSED_BN and settings.FUSED_BN_PAIR and settings.FUSED_BN_COOP and xa.shape == xb.shape
+    if (settings.FUSED_BN and settings.FUSED_BN_PAIR and settings.FUSED_BN_COOP and not _COOP_OFF["off"]
+            and xa.shape == xb.shape
             and eligible(bna, xa) and eligible(bnb, xb)
             and native.cuda_lib().gk_bn_fused_supported(xa.numel() // xa.shape[1], xa.shape[1])):
         return _Bn2Act.apply(xa, xb, bna.weight, bna.bias, bnb.weight, bnb.bias, bna, bnb, relu, twice)
@@ -311,7 +321,8 @@ def bn_act(bn, x, residual=None, relu=True, twice=False):
 def bn_relu_maxpool(bn, x, pool=None):
     """``max_pool2d(relu(bn(x)), 3, 2, 1)`` (the ResNet stem) through the fused kernels when possible."""
     N, C, H, W = x.shape if x.dim() == 4 else (0, 0, 0, 0)
-    if (settings.FUSED_BN and settings.FUSED_BN_POOL and eligible(bn, x) and H >= 2 and W >= 2
+    if (settings.FUSED_BN and settings.FUSED_BN_POOL and settings.FUSED_BN_COOP and not _COOP_OFF["off"]
+            and eligible(bn, x) and H >= 2 and W >= 2
             and N * H * W < 2 ** 31 and native.cuda_lib().gk_bn_fused_supported(N * H * W, C)):
         return _BnReluPool.apply(x, bn.weight, bn.bias, bn)
     y = bn_act(bn, x, relu=True)
