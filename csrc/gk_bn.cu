@@ -342,7 +342,8 @@ extern "C" int gk_bn_bwd(const float* dy, const float* x, const float* y, const 
 //
 // Scratch words (uint64) of one layer: bar[2y] arrivals and bar[2y+1] generation of channel slab y
 // (y < BNF_MAX_COLUMNS), bar[96..111] optional phase time stamps, bar[127] error flag.
-#define BNF_T 512
+// threads per block of the cooperative kernels: template parameter T_ (512 or 1024, chosen per layer by
+// bnf_geometry)
 // unroll depths of the streaming loops = loads in flight per thread (tuned on a B200, profiles/bn_unroll_sweep.txt)
 #ifndef BNF_U_F1
 #define BNF_U_F1 8
@@ -376,7 +377,6 @@ extern "C" int gk_bn_bwd(const float* dy, const float* x, const float* y, const 
   const int n_it = rbase < r1_ ? (int)((r1_ - rbase + RL - 1) / RL) : 0;
 #endif
 static constexpr int kUF1 = BNF_U_F1, kUF2 = BNF_U_F2, kUB1 = BNF_U_B1, kUB2 = BNF_U_B2;
-#define BNF_SMEM_BUDGET (200 * 1024)
 #define BNF_SPIN_LIMIT (1 << 22)
 #define BNF_MAX_COLUMNS 48
 #define BNF_STAMP_WORD 96
@@ -426,7 +426,8 @@ __device__ __forceinline__ void bnf_column_barrier(unsigned long long* bar, unsi
 }
 
 // block-level reduction of (a, b) over the row lanes that share a channel quad; result valid where rl == 0
-__device__ __forceinline__ void bnf_reduce_rows(float4 (*red)[BNF_T], float4& a, float4& b, int tid, int rl, int RL,
+template <int T_>
+__device__ __forceinline__ void bnf_reduce_rows(float4 (*red)[T_], float4& a, float4& b, int tid, int rl, int RL,
                                                 int qpb) {
   red[0][tid] = a;
   red[1][tid] = b;
@@ -506,27 +507,28 @@ __device__ __forceinline__ float bnf_rsqrt(float a) {   // rsqrt.approx plus one
 }
 
 // flags: bit 0 = ReLU, bit 1 = write phase time stamps (block 0,0 only; profiling aid)
-__global__ void __launch_bounds__(BNF_T, 1)
+template <int T_>
+__global__ void __launch_bounds__(T_, 1)
 k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float* __restrict__ y,
                const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ save_mean,
                float* __restrict__ save_istd, float* running_mean, float* running_var, int64_t* num_batches,
                double* accum /* [2 parities][2][C] */, unsigned long long* bar, int64_t M, int C,
                int rows_per_block, int qshift, int cached, float eps, float momentum, double inv_m, double unbias,
                int flags, unsigned char* __restrict__ mask /* optional: ReLU bits, one byte per channel quad */) {
-  extern __shared__ float4 tile[];          // [cached][BNF_T]
-  __shared__ float4 red[2][BNF_T];
+  extern __shared__ float4 tile[];          // [cached][T_]
+  __shared__ float4 red[2][T_];
   __shared__ unsigned long long s_gen;
-#if BNF_TMA
+#if T_MA
   __shared__ __align__(8) unsigned long long s_mbar;
 #endif
   const int tid = threadIdx.x;
-  const int qpb = 1 << qshift, ql = tid & (qpb - 1), rl = tid >> qshift, RL = BNF_T >> qshift;
+  const int qpb = 1 << qshift, ql = tid & (qpb - 1), rl = tid >> qshift, RL = T_ >> qshift;
   const int q = blockIdx.y * qpb + ql;
   const bool stamp = (flags & 2) && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0;
   unsigned long long* ts = bar + BNF_STAMP_WORD;
   if (stamp) ts[0] = bnf_now();
   if (tid == 0 && gridDim.x > 1) s_gen = bnf_ld_relaxed(bar + 2 * blockIdx.y + 1);
-#if BNF_TMA
+#if T_MA
   if (tid == 0) bnf_mbar_init(&s_mbar, (unsigned)RL);      // one arrival per row lane
   __syncthreads();
 #endif
@@ -546,14 +548,14 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
   // phase 1: one read of x.  The rows that fit in shared memory are fetched with cp.async (all in flight
   // at once, no register staging); the rest streams through registers meanwhile.
   const int nc = n_it < cached ? n_it : cached;
-#if BNF_TMA
+#if T_MA
   if (ql == 0) {
     bnf_mbar_expect(&s_mbar, (unsigned)(nc * qpb * 16));
     for (int i = 0; i < nc; ++i)
-      bnf_bulk_g2s(&tile[i * BNF_T + tid], xp + (rbase + (int64_t)i * rstep) * C, (unsigned)(qpb * 16), &s_mbar);
+      bnf_bulk_g2s(&tile[i * T_ + tid], xp + (rbase + (int64_t)i * rstep) * C, (unsigned)(qpb * 16), &s_mbar);
   }
 #else
-  for (int i = 0; i < nc; ++i) bnf_cp_async16(&tile[i * BNF_T + tid], xp + (rbase + (int64_t)i * rstep) * C);
+  for (int i = 0; i < nc; ++i) bnf_cp_async16(&tile[i * T_ + tid], xp + (rbase + (int64_t)i * rstep) * C);
 #endif
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
 #pragma unroll kUF1
@@ -562,14 +564,14 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
     a = f4_add(a, xv);
     b = f4_fma(xv, xv, b);
   }
-#if BNF_TMA
+#if T_MA
   bnf_mbar_wait(&s_mbar, 0);
 #else
   bnf_cp_async_wait_all();
 #endif
 #pragma unroll 8
   for (int i = 0; i < nc; ++i) {
-    const float4 xv = tile[i * BNF_T + tid];
+    const float4 xv = tile[i * T_ + tid];
     a = f4_add(a, xv);
     b = f4_fma(xv, xv, b);
   }
@@ -618,7 +620,7 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
 #pragma unroll kUF2
     for (int i = n_it - 1; i >= 0; --i) {
       const int64_t r = rbase + (int64_t)i * rstep;
-      const float4 xv = (i < nc) ? tile[i * BNF_T + tid] : bn_ld4(xp + r * C);
+      const float4 xv = (i < nc) ? tile[i * T_ + tid] : bn_ld4(xp + r * C);
       float4 o = f4_fma(xv, sc, sh);
       if (res != nullptr) o = f4_add(o, bn_ld4(res + r * C + 4 * q));
       if (mask != nullptr) mask[r * (C >> 2) + q] = bn_mask_bits(o);
@@ -691,28 +693,28 @@ __device__ __forceinline__ float4 bn_pool_gather(const BnPool& P, int64_t r, int
 
 // dy2: optional second gradient of the same output (the output was handed out twice, see ops/bn.py), added
 // on the fly.  POOL: the gradient comes through the max pool described by P instead of dy.
-template <bool POOL, bool DUAL>
-__global__ void __launch_bounds__(BNF_T, 1)
+template <int T_, bool POOL, bool DUAL>
+__global__ void __launch_bounds__(T_, 1)
 k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, const float* __restrict__ x,
                const float* __restrict__ y, const float* __restrict__ gamma, const float* __restrict__ beta,
                const float* __restrict__ save_mean, const float* __restrict__ save_istd, float* __restrict__ dx,
                float* __restrict__ dres, float* __restrict__ dgamma, float* __restrict__ dbeta, double* accum,
                unsigned long long* bar, int64_t M, int C, int rows_per_block, int qshift, int cached,
                double inv_m, int flags, BnPool P) {
-  extern __shared__ float4 tile[];          // [cached][2][BNF_T]: masked gradient, x
-  __shared__ float4 red[2][BNF_T];
+  extern __shared__ float4 tile[];          // [cached][2][T_]: masked gradient, x
+  __shared__ float4 red[2][T_];
   __shared__ unsigned long long s_gen;
-#if BNF_TMA
+#if T_MA
   __shared__ __align__(8) unsigned long long s_mbar;
 #endif
   const int tid = threadIdx.x;
-  const int qpb = 1 << qshift, ql = tid & (qpb - 1), rl = tid >> qshift, RL = BNF_T >> qshift;
+  const int qpb = 1 << qshift, ql = tid & (qpb - 1), rl = tid >> qshift, RL = T_ >> qshift;
   const int q = blockIdx.y * qpb + ql;
   const bool stamp = (flags & 2) && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0;
   unsigned long long* ts = bar + BNF_STAMP_WORD + 8;
   if (stamp) ts[0] = bnf_now();
   if (tid == 0 && gridDim.x > 1) s_gen = bnf_ld_relaxed(bar + 2 * blockIdx.y + 1);
-#if BNF_TMA
+#if T_MA
   if (tid == 0) bnf_mbar_init(&s_mbar, (unsigned)RL);
   __syncthreads();
 #endif
@@ -731,20 +733,20 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
     if (DUAL) g = f4_add(g, bn_ld4(dy2 + o));
     return g;
   };
-#if BNF_TMA
+#if T_MA
   if (ql == 0) {
     bnf_mbar_expect(&s_mbar, (unsigned)(nc * qpb * 16 * (POOL ? 1 : 2)));
     for (int i = 0; i < nc; ++i) {
       const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
-      if (!POOL) bnf_bulk_g2s(&tile[(2 * i) * BNF_T + tid], dy + o, (unsigned)(qpb * 16), &s_mbar);
-      bnf_bulk_g2s(&tile[(2 * i + 1) * BNF_T + tid], x + o, (unsigned)(qpb * 16), &s_mbar);
+      if (!POOL) bnf_bulk_g2s(&tile[(2 * i) * T_ + tid], dy + o, (unsigned)(qpb * 16), &s_mbar);
+      bnf_bulk_g2s(&tile[(2 * i + 1) * T_ + tid], x + o, (unsigned)(qpb * 16), &s_mbar);
     }
   }
 #else
   for (int i = 0; i < nc; ++i) {
     const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
-    if (!POOL) bnf_cp_async16(&tile[(2 * i) * BNF_T + tid], dy + o);
-    bnf_cp_async16(&tile[(2 * i + 1) * BNF_T + tid], x + o);
+    if (!POOL) bnf_cp_async16(&tile[(2 * i) * T_ + tid], dy + o);
+    bnf_cp_async16(&tile[(2 * i + 1) * T_ + tid], x + o);
   }
 #endif
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
@@ -761,7 +763,7 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
     a = f4_add(a, g);
     b = f4_fma(g, xh, b);
   }
-#if BNF_TMA
+#if T_MA
   bnf_mbar_wait(&s_mbar, 0);
 #else
   bnf_cp_async_wait_all();
@@ -770,16 +772,16 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
   for (int i = 0; i < nc; ++i) {
     const int64_t r = rbase + (int64_t)i * rstep;
     const int64_t o = r * C + 4 * q;
-    const float4 xv = tile[(2 * i + 1) * BNF_T + tid];
+    const float4 xv = tile[(2 * i + 1) * T_ + tid];
     float4 g;
     if (POOL) {
       g = bn_pool_gather(P, r, C, q);
     } else {
-      g = tile[(2 * i) * BNF_T + tid];
+      g = tile[(2 * i) * T_ + tid];
       if (DUAL) g = f4_add(g, bn_ld4(dy2 + o));
     }
     if (relu) g = bn_mask_pos(g, y != nullptr ? bn_mask_src(y, o, r, C, q, mbits) : f4_fma(xv, sc, sh));
-    if (POOL || DUAL || relu) tile[(2 * i) * BNF_T + tid] = g;
+    if (POOL || DUAL || relu) tile[(2 * i) * T_ + tid] = g;
     if (dres != nullptr) bn_st4(dres + o, g);
     const float4 xh = make_float4((xv.x - mu.x) * is.x, (xv.y - mu.y) * is.y, (xv.z - mu.z) * is.z,
                                   (xv.w - mu.w) * is.w);
@@ -828,8 +830,8 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
       const int64_t o = r * C + 4 * q;
       float4 g, xv;
       if (i < nc) {
-        g = tile[(2 * i) * BNF_T + tid];
-        xv = tile[(2 * i + 1) * BNF_T + tid];
+        g = tile[(2 * i) * T_ + tid];
+        xv = tile[(2 * i + 1) * T_ + tid];
       } else {
         xv = bn_ld4(x + o);
         if (dres != nullptr) {
@@ -863,13 +865,21 @@ int g_qcap = 9;           // upper bound on log2 of the channel slab width (in q
 int g_private_kb = 128;   // largest per-block slab of the barrier-free path
 
 struct BnfGeom {
-  int qshift, rpb, iters;
+  int qshift, rpb, iters, threads;
   dim3 grid;
 };
+
+int g_big_mb = 40;        // activations of at least this many MB run 1024 threads per block (else 512)
+inline size_t bnf_smem_budget(int threads) { return (size_t)216 * 1024 - (size_t)2 * threads * 16; }
 
 bool bnf_geometry(int64_t M, int C, BnfGeom* g) {
   if (M < 2 || C <= 0 || (C & 3)) return false;
   const int quads = C / 4;
+  // 1024 threads per block hide the load latency of the big streaming layers better (-15 % on the 100 MB
+  // shapes although the kernels then spill a few registers), 512 win on the small ones
+  // (profiles/bn_unroll_sweep.txt)
+  const int T = (M * (int64_t)C * 4 >= (int64_t)g_big_mb << 20) ? 1024 : 512;
+  g->threads = T;
   int qmax = 9;                             // widest power-of-two quad slab that divides the row
   while (quads % (1 << qmax)) --qmax;
   const int nsm = bn_sm_count();
@@ -882,7 +892,7 @@ bool bnf_geometry(int64_t M, int C, BnfGeom* g) {
   while ((quads >> qs) > nsm && qs < qmax) ++qs;
   if (qs <= qmax && (quads >> qs) >= 32 && (quads >> qs) <= nsm &&
       M * (int64_t)(16 << qs) <= (int64_t)g_private_kb * 1024) {
-    const int RL = BNF_T >> qs;
+    const int RL = T >> qs;
     int64_t rpb = (M + RL - 1) / RL * RL;
     g->qshift = qs;
     g->rpb = (int)rpb;
@@ -901,7 +911,7 @@ bool bnf_geometry(int64_t M, int C, BnfGeom* g) {
   const int qpb = 1 << qshift;
   const int gy = quads / qpb;
   if (gy > nsm || gy > BNF_MAX_COLUMNS) return false;
-  const int RL = BNF_T / qpb;
+  const int RL = T / qpb;
   int64_t gx = nsm / gy;
   const int64_t useful = (M + RL - 1) / RL;
   if (gx > useful) gx = useful;
@@ -923,14 +933,18 @@ int bnf_prepare() {
   if (e != cudaSuccess) return (int)e;
   if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
   if (!ready[dev]) {
-    e = cudaFuncSetAttribute(k_bn_fwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(k_bn_bwd_fused<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(k_bn_bwd_fused<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(k_bn_bwd_fused<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
-    if (e != cudaSuccess) return (int)e;
+#define BNF_SET_ATTR(fn, threads)                                                                                  \
+  e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bnf_smem_budget(threads));      \
+  if (e != cudaSuccess) return (int)e;
+    BNF_SET_ATTR(k_bn_fwd_fused<512>, 512)
+    BNF_SET_ATTR(k_bn_fwd_fused<1024>, 1024)
+    BNF_SET_ATTR((k_bn_bwd_fused<512, false, false>), 512)
+    BNF_SET_ATTR((k_bn_bwd_fused<512, false, true>), 512)
+    BNF_SET_ATTR((k_bn_bwd_fused<512, true, false>), 512)
+    BNF_SET_ATTR((k_bn_bwd_fused<1024, false, false>), 1024)
+    BNF_SET_ATTR((k_bn_bwd_fused<1024, false, true>), 1024)
+    BNF_SET_ATTR((k_bn_bwd_fused<1024, true, false>), 1024)
+#undef BNF_SET_ATTR
     ready[dev] = true;
   }
   return 0;
@@ -942,6 +956,12 @@ extern "C" int gk_bn_set_tuning(int qcap_log2, int private_kb) {
   if (qcap_log2 < 3 || qcap_log2 > 9 || private_kb < 0) return (int)cudaErrorInvalidValue;
   g_qcap = qcap_log2;
   g_private_kb = private_kb;
+  return 0;
+}
+
+extern "C" int gk_bn_set_big_mb(int mb) {      // activations of at least mb MB run 1024 threads per block
+  if (mb < 0) return (int)cudaErrorInvalidValue;
+  g_big_mb = mb;
   return 0;
 }
 
@@ -974,12 +994,15 @@ extern "C" int gk_bn_fwd_fused_m(const float* x, const float* res, float* y, con
     return (int)cudaErrorMisalignedAddress;
   int rc = bnf_prepare();
   if (rc) return rc;
-  int cached = g.iters < BNF_SMEM_BUDGET / (BNF_T * 16) ? g.iters : BNF_SMEM_BUDGET / (BNF_T * 16);
-  size_t smem = (size_t)cached * BNF_T * 16;
+  const int T = g.threads;
+  int cached = (int)(bnf_smem_budget(T) / ((size_t)T * 16));
+  if (g.iters < cached) cached = g.iters;
+  size_t smem = (size_t)cached * T * 16;
   double inv_m = 1.0 / (double)M, unbias = M > 1 ? (double)M / (double)(M - 1) : 1.0;
   void* args[] = {&x, &res, &y, &gamma, &beta, &save_mean, &save_istd, &running_mean, &running_var, &num_batches,
                   &accum, &bar, &M, &C, &g.rpb, &g.qshift, &cached, &eps, &momentum, &inv_m, &unbias, &flags, &mask};
-  return bn_coop_result(cudaLaunchCooperativeKernel((void*)k_bn_fwd_fused, g.grid, dim3(BNF_T), args, smem,
+  void* fn = T == 1024 ? (void*)k_bn_fwd_fused<1024> : (void*)k_bn_fwd_fused<512>;
+  return bn_coop_result(cudaLaunchCooperativeKernel(fn, g.grid, dim3(T), args, smem,
                                           (cudaStream_t)stream));
 }
 
@@ -997,14 +1020,21 @@ int bn_bwd_fused_launch(const float* dy, const float* dy2, const float* x, const
   if (dres != nullptr && (flags & 1) && y == nullptr) return (int)cudaErrorInvalidValue;
   int rc = bnf_prepare();
   if (rc) return rc;
-  int cached = g.iters < BNF_SMEM_BUDGET / (BNF_T * 32) ? g.iters : BNF_SMEM_BUDGET / (BNF_T * 32);
-  size_t smem = (size_t)cached * BNF_T * 32;
+  const int T = g.threads;
+  int cached = (int)(bnf_smem_budget(T) / ((size_t)T * 32));
+  if (g.iters < cached) cached = g.iters;
+  size_t smem = (size_t)cached * T * 32;
   double inv_m = 1.0 / (double)M;
   void* args[] = {&dy, &dy2, &x, &y, &gamma, &beta, &save_mean, &save_istd, &dx, &dres, &dgamma, &dbeta, &accum,
                   &bar, &M, &C, &g.rpb, &g.qshift, &cached, &inv_m, &flags, &P};
-  void* fn = pool ? (void*)k_bn_bwd_fused<true, false>
-                  : (dy2 != nullptr ? (void*)k_bn_bwd_fused<false, true> : (void*)k_bn_bwd_fused<false, false>);
-  return bn_coop_result(cudaLaunchCooperativeKernel(fn, g.grid, dim3(BNF_T), args, smem, (cudaStream_t)stream));
+  void* fn;
+  if (T == 1024)
+    fn = pool ? (void*)k_bn_bwd_fused<1024, true, false>
+              : (dy2 != nullptr ? (void*)k_bn_bwd_fused<1024, false, true> : (void*)k_bn_bwd_fused<1024, false, false>);
+  else
+    fn = pool ? (void*)k_bn_bwd_fused<512, true, false>
+              : (dy2 != nullptr ? (void*)k_bn_bwd_fused<512, false, true> : (void*)k_bn_bwd_fused<512, false, false>);
+  return bn_coop_result(cudaLaunchCooperativeKernel(fn, g.grid, dim3(T), args, smem, (cudaStream_t)stream));
 }
 }  // namespace
 
@@ -1182,15 +1212,16 @@ __device__ __forceinline__ void bn2_keep(const Bn2Side& S, int q, const float* m
   }
 }
 
-__global__ void __launch_bounds__(BNF_T, 1)
+template <int T_>
+__global__ void __launch_bounds__(T_, 1)
 k_bn2_fwd_fused(Bn2Side A, Bn2Side B, float* __restrict__ y, double* accum, unsigned long long* bar, int64_t M, int C,
                 int rows_per_block, int qshift, int cached, double inv_m, double unbias, int flags,
                 unsigned char* __restrict__ mask) {
-  extern __shared__ float4 tile[];          // [cached][2][BNF_T]: xa, xb
-  __shared__ float4 red[2][BNF_T];
+  extern __shared__ float4 tile[];          // [cached][2][T_]: xa, xb
+  __shared__ float4 red[2][T_];
   __shared__ unsigned long long s_gen;
   const int tid = threadIdx.x;
-  const int qpb = 1 << qshift, ql = tid & (qpb - 1), rl = tid >> qshift, RL = BNF_T >> qshift;
+  const int qpb = 1 << qshift, ql = tid & (qpb - 1), rl = tid >> qshift, RL = T_ >> qshift;
   const int q = blockIdx.y * qpb + ql;
   if (tid == 0 && gridDim.x > 1) s_gen = bnf_ld_relaxed(bar + 2 * blockIdx.y + 1);
   const int relu = flags & 1;
@@ -1205,8 +1236,8 @@ k_bn2_fwd_fused(Bn2Side A, Bn2Side B, float* __restrict__ y, double* accum, unsi
   const int nc = n_it < cached ? n_it : cached;
   for (int i = 0; i < nc; ++i) {
     const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
-    bnf_cp_async16(&tile[(2 * i) * BNF_T + tid], A.x + o);
-    bnf_cp_async16(&tile[(2 * i + 1) * BNF_T + tid], B.x + o);
+    bnf_cp_async16(&tile[(2 * i) * T_ + tid], A.x + o);
+    bnf_cp_async16(&tile[(2 * i + 1) * T_ + tid], B.x + o);
   }
   float4 a1 = make_float4(0.f, 0.f, 0.f, 0.f), a2 = a1, b1 = a1, b2 = a1;
 #pragma unroll 4
@@ -1219,7 +1250,7 @@ k_bn2_fwd_fused(Bn2Side A, Bn2Side B, float* __restrict__ y, double* accum, unsi
   bnf_cp_async_wait_all();
 #pragma unroll 4
   for (int i = 0; i < nc; ++i) {
-    const float4 xa = tile[(2 * i) * BNF_T + tid], xb = tile[(2 * i + 1) * BNF_T + tid];
+    const float4 xa = tile[(2 * i) * T_ + tid], xb = tile[(2 * i + 1) * T_ + tid];
     a1 = f4_add(a1, xa); a2 = f4_fma(xa, xa, a2);
     b1 = f4_add(b1, xb); b2 = f4_fma(xb, xb, b2);
   }
@@ -1261,8 +1292,8 @@ k_bn2_fwd_fused(Bn2Side A, Bn2Side B, float* __restrict__ y, double* accum, unsi
 #pragma unroll 4
   for (int i = n_it - 1; i >= 0; --i) {
     const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
-    const float4 xa = (i < nc) ? tile[(2 * i) * BNF_T + tid] : bn_ld4(A.x + o);
-    const float4 xb = (i < nc) ? tile[(2 * i + 1) * BNF_T + tid] : bn_ld4(B.x + o);
+    const float4 xa = (i < nc) ? tile[(2 * i) * T_ + tid] : bn_ld4(A.x + o);
+    const float4 xb = (i < nc) ? tile[(2 * i + 1) * T_ + tid] : bn_ld4(B.x + o);
     float4 v = f4_add(f4_fma(xa, scA, shA), f4_fma(xb, scB, shB));
     if (mask != nullptr) mask[(rbase + (int64_t)i * rstep) * (C >> 2) + q] = bn_mask_bits(v);
     if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
@@ -1298,15 +1329,16 @@ struct Bn2Back {
 
 // g = (dy [+ dy2]) masked by y > 0; dxa, dxb, dgamma/dbeta of both sides.  The masked gradient of the rows that do
 // not fit in shared memory is parked in A.dx between the phases (same thread, same address).
-__global__ void __launch_bounds__(BNF_T, 1)
+template <int T_>
+__global__ void __launch_bounds__(T_, 1)
 k_bn2_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, const float* __restrict__ y, Bn2Back A,
                 Bn2Back B, double* accum, unsigned long long* bar, int64_t M, int C, int rows_per_block, int qshift,
                 int cached, double inv_m, int flags) {
-  extern __shared__ float4 tile[];          // [cached][3][BNF_T]: g, xa, xb
-  __shared__ float4 red[2][BNF_T];
+  extern __shared__ float4 tile[];          // [cached][3][T_]: g, xa, xb
+  __shared__ float4 red[2][T_];
   __shared__ unsigned long long s_gen;
   const int tid = threadIdx.x;
-  const int qpb = 1 << qshift, ql = tid & (qpb - 1), rl = tid >> qshift, RL = BNF_T >> qshift;
+  const int qpb = 1 << qshift, ql = tid & (qpb - 1), rl = tid >> qshift, RL = T_ >> qshift;
   const int q = blockIdx.y * qpb + ql;
   if (tid == 0 && gridDim.x > 1) s_gen = bnf_ld_relaxed(bar + 2 * blockIdx.y + 1);
   const int relu = flags & 1;
@@ -1319,9 +1351,9 @@ k_bn2_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, con
   const int nc = n_it < cached ? n_it : cached;
   for (int i = 0; i < nc; ++i) {
     const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
-    bnf_cp_async16(&tile[(3 * i) * BNF_T + tid], dy + o);
-    bnf_cp_async16(&tile[(3 * i + 1) * BNF_T + tid], A.x + o);
-    bnf_cp_async16(&tile[(3 * i + 2) * BNF_T + tid], B.x + o);
+    bnf_cp_async16(&tile[(3 * i) * T_ + tid], dy + o);
+    bnf_cp_async16(&tile[(3 * i + 1) * T_ + tid], A.x + o);
+    bnf_cp_async16(&tile[(3 * i + 2) * T_ + tid], B.x + o);
   }
   float4 sg = make_float4(0.f, 0.f, 0.f, 0.f), sa = sg, sb = sg;
   auto xhat = [](float4 x, float4 mu, float4 is) {
@@ -1343,11 +1375,11 @@ k_bn2_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, con
 #pragma unroll 2
   for (int i = 0; i < nc; ++i) {
     const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
-    const float4 xa = tile[(3 * i + 1) * BNF_T + tid], xb = tile[(3 * i + 2) * BNF_T + tid];
-    float4 g = tile[(3 * i) * BNF_T + tid];
+    const float4 xa = tile[(3 * i + 1) * T_ + tid], xb = tile[(3 * i + 2) * T_ + tid];
+    float4 g = tile[(3 * i) * T_ + tid];
     if (dy2 != nullptr) g = f4_add(g, bn_ld4(dy2 + o));
     if (relu) g = bn_mask_pos(g, bn_mask_src(y, o, rbase + (int64_t)i * rstep, C, q, mbits));
-    tile[(3 * i) * BNF_T + tid] = g;
+    tile[(3 * i) * T_ + tid] = g;
     sg = f4_add(sg, g);
     sa = f4_fma(g, xhat(xa, muA, isA), sa);
     sb = f4_fma(g, xhat(xb, muB, isB), sb);
@@ -1390,9 +1422,9 @@ k_bn2_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, con
     const int64_t o = (rbase + (int64_t)i * rstep) * C + 4 * q;
     float4 g, xa, xb;
     if (i < nc) {
-      g = tile[(3 * i) * BNF_T + tid];
-      xa = tile[(3 * i + 1) * BNF_T + tid];
-      xb = tile[(3 * i + 2) * BNF_T + tid];
+      g = tile[(3 * i) * T_ + tid];
+      xa = tile[(3 * i + 1) * T_ + tid];
+      xb = tile[(3 * i + 2) * T_ + tid];
     } else {
       g = bn_ld4(A.dx + o);
       xa = bn_ld4(A.x + o);
@@ -1426,6 +1458,27 @@ k_bn2_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, con
   }
 }
 
+namespace {
+int bn2_prepare() {
+  static bool ready[64] = {false};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
+  if (!ready[dev]) {
+    void* fns[4] = {(void*)k_bn2_fwd_fused<512>, (void*)k_bn2_bwd_fused<512>, (void*)k_bn2_fwd_fused<1024>,
+                    (void*)k_bn2_bwd_fused<1024>};
+    for (int i = 0; i < 4; ++i) {
+      e = cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)bnf_smem_budget(i < 2 ? 512 : 1024));
+      if (e != cudaSuccess) return (int)e;
+    }
+    ready[dev] = true;
+  }
+  return 0;
+}
+}  // namespace
+
 extern "C" int gk_bn2_fwd_fused(void* const* a, void* const* b, float eps_a, float mom_a, float eps_b, float mom_b,
                                 float* y, unsigned char* mask, double* accum, unsigned long long* bar, int64_t M, int C,
                                 int flags, void* stream) {
@@ -1434,25 +1487,20 @@ extern "C" int gk_bn2_fwd_fused(void* const* a, void* const* b, float eps_a, flo
   for (int i = 0; i < 5; ++i)
     if (!bn_aligned(a[i]) || !bn_aligned(b[i])) return (int)cudaErrorMisalignedAddress;
   if (!bn_aligned(y) || !bn_aligned(accum)) return (int)cudaErrorMisalignedAddress;
-  static bool ready[64] = {false};
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
-  if (!ready[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(k_bn2_fwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(k_bn2_bwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, BNF_SMEM_BUDGET);
-    if (e != cudaSuccess) return (int)e;
-    ready[dev] = true;
-  }
+  int rc = bn2_prepare();
+  if (rc) return rc;
   Bn2Side A = {(const float*)a[0], (const float*)a[1], (const float*)a[2], (float*)a[3], (float*)a[4], (float*)a[5],
                (float*)a[6], (int64_t*)a[7], eps_a, mom_a};
   Bn2Side B = {(const float*)b[0], (const float*)b[1], (const float*)b[2], (float*)b[3], (float*)b[4], (float*)b[5],
                (float*)b[6], (int64_t*)b[7], eps_b, mom_b};
-  int cached = g.iters < BNF_SMEM_BUDGET / (BNF_T * 32) ? g.iters : BNF_SMEM_BUDGET / (BNF_T * 32);
-  size_t smem = (size_t)cached * BNF_T * 32;
+  const int T = g.threads;
+  int cached = (int)(bnf_smem_budget(T) / ((size_t)T * 32));
+  if (g.iters < cached) cached = g.iters;
+  size_t smem = (size_t)cached * T * 32;
   double inv_m = 1.0 / (double)M, unbias = M > 1 ? (double)M / (double)(M - 1) : 1.0;
   void* args[] = {&A, &B, &y, &accum, &bar, &M, &C, &g.rpb, &g.qshift, &cached, &inv_m, &unbias, &flags, &mask};
-  return bn_coop_result(cudaLaunchCooperativeKernel((void*)k_bn2_fwd_fused, g.grid, dim3(BNF_T), args, smem,
+  void* fn = T == 1024 ? (void*)k_bn2_fwd_fused<1024> : (void*)k_bn2_fwd_fused<512>;
+  return bn_coop_result(cudaLaunchCooperativeKernel(fn, g.grid, dim3(T), args, smem,
                                           (cudaStream_t)stream));
 }
 
@@ -1464,14 +1512,19 @@ extern "C" int gk_bn2_bwd_fused(const float* dy, const float* dy2, const float* 
     if (!bn_aligned(a[i]) || !bn_aligned(b[i])) return (int)cudaErrorMisalignedAddress;
   if (!bn_aligned(dy) || !bn_aligned(dy2) || !bn_aligned(y) || !bn_aligned(accum)) return (int)cudaErrorMisalignedAddress;
   if ((flags & 1) && y == nullptr) return (int)cudaErrorInvalidValue;
+  int rc = bn2_prepare();
+  if (rc) return rc;
   Bn2Back A = {(const float*)a[0], (const float*)a[1], (const float*)a[2], (const float*)a[3], (const float*)a[4],
                (float*)a[5], (float*)a[6], (float*)a[7]};
   Bn2Back B = {(const float*)b[0], (const float*)b[1], (const float*)b[2], (const float*)b[3], (const float*)b[4],
                (float*)b[5], (float*)b[6], (float*)b[7]};
-  int cached = g.iters < BNF_SMEM_BUDGET / (BNF_T * 48) ? g.iters : BNF_SMEM_BUDGET / (BNF_T * 48);
-  size_t smem = (size_t)cached * BNF_T * 48;
+  const int T = g.threads;
+  int cached = (int)(bnf_smem_budget(T) / ((size_t)T * 48));
+  if (g.iters < cached) cached = g.iters;
+  size_t smem = (size_t)cached * T * 48;
   double inv_m = 1.0 / (double)M;
   void* args[] = {&dy, &dy2, &y, &A, &B, &accum, &bar, &M, &C, &g.rpb, &g.qshift, &cached, &inv_m, &flags};
-  return bn_coop_result(cudaLaunchCooperativeKernel((void*)k_bn2_bwd_fused, g.grid, dim3(BNF_T), args, smem,
+  void* fn = T == 1024 ? (void*)k_bn2_bwd_fused<1024> : (void*)k_bn2_bwd_fused<512>;
+  return bn_coop_result(cudaLaunchCooperativeKernel(fn, g.grid, dim3(T), args, smem,
                                           (cudaStream_t)stream));
 }

@@ -61,12 +61,16 @@ def main():
     ap.add_argument("--once", action="store_true", help="one profiled forward+backward per shape (for ncu)")
     ap.add_argument("--qcap", type=int, default=None, help="geometry knob: log2 of the widest channel slab (quads)")
     ap.add_argument("--private-kb", type=int, default=None, help="geometry knob: barrier-free path up to this slab")
+    ap.add_argument("--big-mb", type=int, default=None, help="geometry knob: 1024 threads per block from this many MB")
     ap.add_argument("--quiet", action="store_true", help="print one line per shape: graph ms fused / torch")
     a = ap.parse_args()
     if a.qcap is not None or a.private_kb is not None:
         from gaussiank_sgd_b200.ops import native
         native.check(native.cuda_lib().gk_bn_set_tuning(9 if a.qcap is None else a.qcap,
                                                         128 if a.private_kb is None else a.private_kb))
+    if a.big_mb is not None:
+        from gaussiank_sgd_b200.ops import native
+        native.check(native.cuda_lib().gk_bn_set_big_mb(a.big_mb))
     dev = torch.device("cuda:0")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev).view(torch.float32)
     bw = peak_bw()
