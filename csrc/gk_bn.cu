@@ -376,7 +376,23 @@ extern "C" int gk_bn_bwd(const float* dy, const float* x, const float* y, const 
   const int64_t rbase = r0_ + rl;                                                         \
   const int n_it = rbase < r1_ ? (int)((r1_ - rbase + RL - 1) / RL) : 0;
 #endif
-static constexpr int kUF1 = BNF_U_F1, kUF2 = BNF_U_F2, kUB1 = BNF_U_B1, kUB2 = BNF_U_B2;
+// the 1024-thread instantiations have 64 registers per thread: their own (smaller) depths
+#ifndef BNF_U_F1_BIG
+#define BNF_U_F1_BIG 4
+#endif
+#ifndef BNF_U_F2_BIG
+#define BNF_U_F2_BIG 4
+#endif
+#ifndef BNF_U_B1_BIG
+#define BNF_U_B1_BIG 2
+#endif
+#ifndef BNF_U_B2_BIG
+#define BNF_U_B2_BIG 4
+#endif
+template <int T_> struct BnfUnroll {
+  static constexpr int F1 = T_ >= 1024 ? BNF_U_F1_BIG : BNF_U_F1, F2 = T_ >= 1024 ? BNF_U_F2_BIG : BNF_U_F2,
+                       B1 = T_ >= 1024 ? BNF_U_B1_BIG : BNF_U_B1, B2 = T_ >= 1024 ? BNF_U_B2_BIG : BNF_U_B2;
+};
 #define BNF_SPIN_LIMIT (1 << 22)
 #define BNF_MAX_COLUMNS 48
 #define BNF_STAMP_WORD 96
@@ -558,7 +574,7 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
   for (int i = 0; i < nc; ++i) bnf_cp_async16(&tile[i * T_ + tid], xp + (rbase + (int64_t)i * rstep) * C);
 #endif
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-#pragma unroll kUF1
+#pragma unroll BnfUnroll<T_>::F1
   for (int i = nc; i < n_it; ++i) {
     const float4 xv = bn_ld4(xp + (rbase + (int64_t)i * rstep) * C);
     a = f4_add(a, xv);
@@ -617,7 +633,7 @@ k_bn_fwd_fused(const float* __restrict__ x, const float* __restrict__ res, float
   // phase 2: normalise out of shared memory (rows beyond the cached part come from L2/HBM again)
   // (last rows first: they are the ones most likely still in L2)
   if (y != nullptr) {
-#pragma unroll kUF2
+#pragma unroll BnfUnroll<T_>::F2
     for (int i = n_it - 1; i >= 0; --i) {
       const int64_t r = rbase + (int64_t)i * rstep;
       const float4 xv = (i < nc) ? tile[i * T_ + tid] : bn_ld4(xp + r * C);
@@ -750,7 +766,7 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
   }
 #endif
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-#pragma unroll kUB1
+#pragma unroll BnfUnroll<T_>::B1
   for (int i = nc; i < n_it; ++i) {
     const int64_t r = rbase + (int64_t)i * rstep;
     const int64_t o = r * C + 4 * q;
@@ -768,7 +784,7 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
 #else
   bnf_cp_async_wait_all();
 #endif
-#pragma unroll kUB1
+#pragma unroll BnfUnroll<T_>::B1
   for (int i = 0; i < nc; ++i) {
     const int64_t r = rbase + (int64_t)i * rstep;
     const int64_t o = r * C + 4 * q;
@@ -824,7 +840,7 @@ k_bn_bwd_fused(const float* __restrict__ dy, const float* __restrict__ dy2, cons
   }
   if (stamp) ts[4] = bnf_now();
   {
-#pragma unroll kUB2
+#pragma unroll BnfUnroll<T_>::B2
     for (int i = n_it - 1; i >= 0; --i) {      // last rows first: most likely still in L2
       const int64_t r = rbase + (int64_t)i * rstep;
       const int64_t o = r * C + 4 * q;
