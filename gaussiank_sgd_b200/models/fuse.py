@@ -28,15 +28,6 @@ class FusedBNReLU(nn.BatchNorm2d):
         return bn_act(self, x, relu=True)
 
 
-def _downsample(mod, x):
-    ds = mod.downsample
-    if ds is None:
-        return x
-    if isinstance(ds, nn.Sequential) and len(ds) == 2 and type(ds[1]) is nn.BatchNorm2d:
-        return bn_act(ds[1], ds[0](x), relu=False)
-    return ds(x)
-
-
 def _split(x):
     """A block input is either one tensor or (convolution input, identity shortcut): the same activation
     handed out twice by the previous block so that its two gradients are not pre-added by autograd."""
