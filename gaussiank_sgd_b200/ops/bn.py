@@ -3,7 +3,9 @@
 The reference's CNNs take ``bn -> (+ identity) -> relu`` from torch.nn as separate modules
 (torchvision ResNet-50 through dl_trainer.py:90, models/resnet.py, models/vgg.py ...).  On a B200 those
 HBM-bound passes are 40 % of the ResNet-50 step (profiles/step_breakdown_resnet50_v1.txt), so here they
-are two kernels forward and two backward (csrc/gk_bn.cu: ``gk_bn_fwd`` / ``gk_bn_bwd``).
+are one cooperative kernel per direction (csrc/gk_bn.cu: ``gk_bn_fwd_fused`` / ``gk_bn_bwd_fused``; two
+kernels each, ``gk_bn_fwd`` / ``gk_bn_bwd``, for shapes the cooperative tiling does not cover), plus the
+variants for the ResNet stem (``bn_relu_maxpool``) and for the downsample junctions (``bn2_act``).
 
 ``bn_act(bn, x, residual=None, relu=True)`` is the entry point: ``bn`` stays an ordinary
 ``nn.BatchNorm2d`` (same parameters, buffers, state_dict keys); anything the kernels do not cover
@@ -126,7 +128,8 @@ class _BnAct(torch.autograd.Function):
                 _chain.LAUNCHES["n"] += 1
         if not ctx.coop:
             accum, ticket = ctx.scratch = _scratch(bn, x.device, C)
-            native.check(lib.gk_bn_fwd(*head, accum.data_ptr(), ticket.data_ptr(), *tail), "gk_bn_fwd")
+            native.check(lib.gk_bn_fwd(*head, accum.data_ptr(), ticket.data_ptr(), *tail[:4], int(relu), tail[5]),
+                         "gk_bn_fwd")
             _chain.LAUNCHES["n"] += 2
         ctx.relu = bool(relu)
         ctx.has_res = residual is not None
