@@ -886,15 +886,16 @@ struct BnfGeom {
 };
 
 int g_big_mb = 40;        // activations of at least this many MB run 1024 threads per block (else 512)
+int g_pair_big_mb = 40;   // same for the two-BN kernels (per input tensor)
 inline size_t bnf_smem_budget(int threads) { return (size_t)216 * 1024 - (size_t)2 * threads * 16; }
 
-bool bnf_geometry(int64_t M, int C, BnfGeom* g) {
+bool bnf_geometry(int64_t M, int C, BnfGeom* g, bool pair = false) {
   if (M < 2 || C <= 0 || (C & 3)) return false;
   const int quads = C / 4;
   // 1024 threads per block hide the load latency of the big streaming layers better (-15 % on the 100 MB
   // shapes although the kernels then spill a few registers), 512 win on the small ones
   // (profiles/bn_unroll_sweep.txt)
-  const int T = (M * (int64_t)C * 4 >= (int64_t)g_big_mb << 20) ? 1024 : 512;
+  const int T = (M * (int64_t)C * 4 >= (int64_t)(pair ? g_pair_big_mb : g_big_mb) << 20) ? 1024 : 512;
   g->threads = T;
   int qmax = 9;                             // widest power-of-two quad slab that divides the row
   while (quads % (1 << qmax)) --qmax;
@@ -978,6 +979,12 @@ extern "C" int gk_bn_set_tuning(int qcap_log2, int private_kb) {
 extern "C" int gk_bn_set_big_mb(int mb) {      // activations of at least mb MB run 1024 threads per block
   if (mb < 0) return (int)cudaErrorInvalidValue;
   g_big_mb = mb;
+  return 0;
+}
+
+extern "C" int gk_bn_set_pair_big_mb(int mb) {  // the same threshold for gk_bn2_fwd_fused / gk_bn2_bwd_fused
+  if (mb < 0) return (int)cudaErrorInvalidValue;
+  g_pair_big_mb = mb;
   return 0;
 }
 
@@ -1499,7 +1506,7 @@ extern "C" int gk_bn2_fwd_fused(void* const* a, void* const* b, float eps_a, flo
                                 float* y, unsigned char* mask, double* accum, unsigned long long* bar, int64_t M, int C,
                                 int flags, void* stream) {
   BnfGeom g;
-  if (!bnf_geometry(M, C, &g)) return (int)cudaErrorInvalidValue;
+  if (!bnf_geometry(M, C, &g, true)) return (int)cudaErrorInvalidValue;
   for (int i = 0; i < 5; ++i)
     if (!bn_aligned(a[i]) || !bn_aligned(b[i])) return (int)cudaErrorMisalignedAddress;
   if (!bn_aligned(y) || !bn_aligned(accum)) return (int)cudaErrorMisalignedAddress;
@@ -1523,7 +1530,7 @@ extern "C" int gk_bn2_fwd_fused(void* const* a, void* const* b, float eps_a, flo
 extern "C" int gk_bn2_bwd_fused(const float* dy, const float* dy2, const float* y, void* const* a, void* const* b,
                                 double* accum, unsigned long long* bar, int64_t M, int C, int flags, void* stream) {
   BnfGeom g;
-  if (!bnf_geometry(M, C, &g)) return (int)cudaErrorInvalidValue;
+  if (!bnf_geometry(M, C, &g, true)) return (int)cudaErrorInvalidValue;
   for (int i = 0; i < 8; ++i)
     if (!bn_aligned(a[i]) || !bn_aligned(b[i])) return (int)cudaErrorMisalignedAddress;
   if (!bn_aligned(dy) || !bn_aligned(dy2) || !bn_aligned(y) || !bn_aligned(accum)) return (int)cudaErrorMisalignedAddress;

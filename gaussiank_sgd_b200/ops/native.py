@@ -178,6 +178,10 @@ def cuda_lib():
             _proto(lib, "gk_bn_fused_supported", [C.c_int64, C.c_int32])
             _proto(lib, "gk_bn_set_tuning", [C.c_int32, C.c_int32])
             _proto(lib, "gk_bn_set_big_mb", [C.c_int32])
+            _proto(lib, "gk_bn_set_pair_big_mb", [C.c_int32])
+            for env, fn in (("GK_BN_BIG_MB", lib.gk_bn_set_big_mb), ("GK_BN_PAIR_BIG_MB", lib.gk_bn_set_pair_big_mb)):
+                if os.environ.get(env):          # tuning knobs of the fused BN geometry (include/gk_b200.h)
+                    check(fn(int(os.environ[env])), env)
             _proto(lib, "gk_bn_bwd_fused2", [_P] * 14 + [C.c_int64, C.c_int32, C.c_int32, _P])
             _proto(lib, "gk_bn2_fwd_fused", [_P, _P, C.c_float, C.c_float, C.c_float, C.c_float, _P, _P, _P, _P, C.c_int64,
                                              C.c_int32, C.c_int32, _P])

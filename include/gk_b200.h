@@ -316,6 +316,7 @@ int gk_bn_set_tuning(int qcap_log2, int private_kb);
 /* Activations of at least mb MB run the cooperative kernels with 1024 threads per block, smaller ones with 512
  * (default 40). */
 int gk_bn_set_big_mb(int mb);
+int gk_bn_set_pair_big_mb(int mb); /* the same threshold for the two-BN kernels (default 40) */
 int gk_bn_fwd_fused(const float* x, const float* res, float* y, const float* gamma, const float* beta,
                     float* running_mean, float* running_var, int64_t* num_batches, float* save_mean,
                     float* save_istd, double* accum, unsigned long long* bar, int64_t M, int C, float eps,
