@@ -1155,7 +1155,7 @@ extern "C" int gk_bn_pool_fwd(const float* x, float* yp, unsigned char* pidx, co
 
 // Full-resolution gradient of the max pool (dense gather, one thread per input pixel and channel quad): the
 // BN backward then runs on it like on any other gradient.  Cheaper than gathering inside the cooperative
-// kernel, which has one 512-thread block per SM and would evaluate the windows twice.
+// kernel, which has one block per SM (16-32 warps) and would evaluate the windows twice.
 __global__ void __launch_bounds__(256) k_pool_gather(BnPool P, float* __restrict__ g, int64_t M, int C) {
   const int quads = C >> 2;
   const int64_t total = M * quads;
