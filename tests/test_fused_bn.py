@@ -357,3 +357,16 @@ def test_two_bns_into_one_activation(shape, twice):
     assert coop_errors(bna) == 0
     if C % 32 == 0:
         assert any(k[-1] == "pair" for k in bna.__dict__["_gk_bn_coop"])
+
+
+def test_fuse_marks_which_blocks_hand_their_output_out_twice():
+    tv = pytest.importorskip("torchvision")
+    net = tv.models.resnet50(num_classes=10)
+    fuse_bn_act(net)
+    flags = [[bool(getattr(b, "_gk_twice", False)) for b in stage] for stage in (net.layer1, net.layer2, net.layer3, net.layer4)]
+    # every block whose output feeds another block (identity shortcut, or the next stage's two convolutions);
+    # only the very last block of the network returns a plain tensor
+    assert flags == [[True] * 3, [True] * 4, [True] * 6, [True, True, False]]
+    x = torch.randn(2, 3, 64, 64)
+    out = net(x)                                   # CPU: plain path, tuples pass through the stages
+    assert out.shape == (2, 10)
