@@ -83,10 +83,11 @@ def _stem_conv_s2d(conv, x):
 
 
 def _stem_conv(conv, x):
-    """The 7x7 stem convolution with its 3 input channels padded to 4 (zeros in the image and in the weight:
-    same result).  With C_in = 3 the NHWC rows are 12 bytes and cuDNN falls back to its pre-Hopper indexed
-    kernels (162 us forward + 176 us weight gradient at batch 32 on a B200); with 4 channels it can use the
-    aligned tensor-core implicit-GEMM kernels.  The parameter itself keeps its [C_out, 3, 7, 7] shape."""
+    """The stem convolution in a shape cuDNN has aligned kernels for: the space-to-depth rewrite when the
+    convolution is the 7x7 / stride 2 / padding 3 one on an even-sized image (_stem_conv_s2d), else the 3 input
+    channels padded to 4 (zeros in the image and in the weight: same result), else the module as it is.  With
+    C_in = 3 the NHWC rows are 12 bytes and cuDNN falls back to its pre-Hopper indexed kernels.  The parameter
+    keeps its [C_out, 3, k, k] shape in every case."""
     if (settings.STEM_S2D and x.is_cuda and x.dim() == 4 and x.shape[1] == 3 and conv.in_channels == 3
             and conv.groups == 1 and conv.bias is None and conv.padding_mode == 'zeros'
             and tuple(conv.kernel_size) == (7, 7) and tuple(conv.stride) == (2, 2) and tuple(conv.padding) == (3, 3)
