@@ -87,11 +87,69 @@ uint32_t count_gt(const GkChain* c, const GkSeg& sg, float thr) {
   return n;
 }
 
+
+// exact k largest (or smallest) keys of a segment, ties towards the lowest index: emits in table order
+void emit_exact_topk(const GkChain* c, const GkSeg& sg, GkSegStat& st, Emit& em, bool mink) {
+  std::vector<uint32_t> keys;
+  keys.reserve(sg.n);
+  for (int b = sg.blk_begin; b < sg.blk_end; ++b) {
+    const GkBlk& B = c->blk[b];
+    for (int i = 0; i < B.len; ++i) keys.push_back(sel_key(c->resid[B.start + i], mink));
+  }
+  const size_t kk = std::min<size_t>((size_t)sg.k, keys.size());
+  std::vector<uint32_t> tmp(keys);
+  std::nth_element(tmp.begin(), tmp.begin() + (kk - 1), tmp.end(), std::greater<uint32_t>());
+  const uint32_t Tk = tmp[kk - 1];
+  size_t ngt = 0;
+  for (uint32_t v : keys) ngt += v > Tk;
+  uint32_t ties = (uint32_t)(kk - ngt);
+  st.tbits = Tk;
+  st.ties = ties;
+  st.chosen = 0;
+  size_t pos = 0;
+  for (int b = sg.blk_begin; b < sg.blk_end; ++b) {
+    const GkBlk& B = c->blk[b];
+    for (int i = 0; i < B.len; ++i, ++pos) {
+      const uint32_t key = keys[pos];
+      bool take = key > Tk;
+      if (!take && key == Tk && ties > 0) { take = true; --ties; }
+      if (take) {
+        const int j = B.start + i;
+        if (em.put((uint32_t)j, c->resid[j])) c->resid[j] = 0.f;
+      }
+    }
+  }
+}
+
+static inline uint32_t mix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return x;
+}
+static inline uint32_t feistel_perm(uint32_t j, uint32_t n, uint64_t seed) {
+  int bits = 2;
+  while ((1ull << bits) < (uint64_t)n) bits += 2;
+  const int half = bits / 2;
+  const uint32_t mask = (1u << half) - 1u;
+  uint32_t x = j;
+  do {
+    uint32_t l = x >> half, r = x & mask;
+    for (int round = 0; round < 4; ++round) {
+      const uint32_t f = mix32(r ^ (uint32_t)(seed >> (round * 8)) ^ (0x9e3779b9u * (round + 1))) & mask;
+      const uint32_t nl = r;
+      r = l ^ f;
+      l = nl;
+    }
+    x = (l << half) | r;
+  } while (x >= n);
+  return x;
+}
+
+
 }  // namespace
 
 extern "C" {
 
-const char* gkcpu_version(void) { return "gk_b200 cpu 0.1"; }
+const char* gkcpu_version(void) { return "gk_b200 cpu 0.2"; }
 
 int gkcpu_compress(const GkChain* c, const GkDst* dst) {
   if (dst->ndst < 1 || dst->ndst > GK_MAXP) return 1;
@@ -116,36 +174,7 @@ int gkcpu_compress(const GkChain* c, const GkDst* dst) {
     st.out_base = em.total;
     const uint32_t before = em.total;
     if (c->mode == GK_MODE_TOPK || mink) {
-      // exact k-th key via nth_element, ties resolved towards the lowest index
-      std::vector<uint32_t> keys;
-      keys.reserve(sg.n);
-      for (int b = sg.blk_begin; b < sg.blk_end; ++b) {
-        const GkBlk& B = c->blk[b];
-        for (int i = 0; i < B.len; ++i) keys.push_back(sel_key(c->resid[B.start + i], mink));
-      }
-      const size_t kk = std::min<size_t>((size_t)sg.k, keys.size());
-      std::vector<uint32_t> tmp(keys);
-      std::nth_element(tmp.begin(), tmp.begin() + (kk - 1), tmp.end(), std::greater<uint32_t>());
-      const uint32_t Tk = tmp[kk - 1];
-      size_t ngt = 0;
-      for (uint32_t v : keys) ngt += v > Tk;
-      uint32_t ties = (uint32_t)(kk - ngt);
-      st.tbits = Tk;
-      st.ties = ties;
-      st.chosen = 0;
-      size_t pos = 0;
-      for (int b = sg.blk_begin; b < sg.blk_end; ++b) {
-        const GkBlk& B = c->blk[b];
-        for (int i = 0; i < B.len; ++i, ++pos) {
-          const uint32_t key = keys[pos];
-          bool take = key > Tk;
-          if (!take && key == Tk && ties > 0) { take = true; --ties; }
-          if (take) {
-            const int j = B.start + i;
-            if (em.put((uint32_t)j, c->resid[j])) c->resid[j] = 0.f;
-          }
-        }
-      }
+      emit_exact_topk(c, sg, st, em, mink);
     } else {
       float thr = 0.f;
       int chosen = 0;
@@ -285,6 +314,73 @@ int gkcpu_sgd(float* param, const float* grad, float* mom, const GkBlk* blk, int
   return 0;
 }
 
+int gkcpu_sgd_recv(const GkRecvUpd* u, const GkSrc* src) {
+  // Folded receive + SGD (twin of k_sgd_recv): dense pass with a zero gradient, then the received pairs are
+  // summed per coordinate in rank order inside u->mask (read as floats here) and folded in.  Same result as
+  // gkcpu_scatter + gkcpu_sgd up to the rounding of the split FMA on the touched coordinates.
+  if (src->nsrc < 1 || src->nsrc > GK_MAXP) return 1;
+  if (!u->skip_dense) {
+    for (int b = 0; b < u->nblk; ++b) {
+      const GkBlk& B = u->blk[b];
+      const GkHyper& h = u->hyper[B.seg];
+      const bool has_m = h.momentum != 0.f && u->mom != nullptr;
+      for (int i = 0; i < B.len; ++i) {
+        const int j = B.start + i;
+        float g = 0.f;
+        if (h.weight_decay != 0.f) g = std::fmaf(h.weight_decay, u->param[j], g);
+        float up = g;
+        if (has_m) {
+          float m = u->mom[j];
+          m = h.first_step ? g : std::fmaf(1.f - h.dampening, g, h.momentum * m);
+          u->mom[j] = m;
+          up = h.nesterov ? std::fmaf(h.momentum, m, g) : m;
+        }
+        u->param[j] = std::fmaf(-h.lr, up, u->param[j]);
+      }
+    }
+  }
+  const uint32_t seq = u->ctrl->seq;
+  const uint64_t* base = src->arena + (uint64_t)(seq & 1u) * src->parity_stride;
+  const uint32_t cap = (uint32_t)(src->slot_stride - GK_SLOT_HDR);
+  float* tot = reinterpret_cast<float*>(u->mask);
+  uint32_t cnt[GK_MAXP];
+  for (int r = 0; r < src->nsrc; ++r) {
+    const uint64_t* slot = base + (uint64_t)r * src->slot_stride;
+    if (src->wait && (uint32_t)(slot[0] >> 32) != seq) { u->ctrl->err = 1; return 2; }
+    cnt[r] = std::min((uint32_t)slot[0], cap);
+  }
+  std::vector<uint32_t> touched;
+  for (int r = 0; r < src->nsrc; ++r) {
+    const uint64_t* slot = base + (uint64_t)r * src->slot_stride;
+    for (uint32_t j = 0; j < cnt[r]; ++j) {
+      const uint64_t p = slot[GK_SLOT_HDR + j];
+      const uint32_t idx = (uint32_t)p;
+      if (idx >= (uint32_t)u->nelem) continue;
+      const uint32_t vb = (uint32_t)(p >> 32);
+      float v;
+      std::memcpy(&v, &vb, 4);
+      tot[idx] = tot[idx] + v * u->scale;
+      touched.push_back(idx);
+    }
+  }
+  for (uint32_t idx : touched) {
+    const float g = tot[idx];
+    if (fbits(g) == 0u) continue;        // already folded in (coordinate sent by several ranks) or exact zero
+    tot[idx] = 0.f;
+    const GkHyper& h = u->hyper[u->gmap ? u->gmap[idx >> 6] : 0];
+    const bool has_m = h.momentum != 0.f && u->mom != nullptr;
+    float du = g;
+    if (has_m) {
+      const float dm = h.first_step ? g : (1.f - h.dampening) * g;
+      u->mom[idx] = u->mom[idx] + dm;
+      du = h.nesterov ? std::fmaf(h.momentum, dm, g) : dm;
+    }
+    u->param[idx] = std::fmaf(-h.lr, du, u->param[idx]);
+  }
+  for (uint32_t idx : touched) tot[idx] = 0.f;   // -0.0 leftovers
+  return 0;
+}
+
 int gkcpu_lars(float* param, const float* grad, float* mom, const GkBlk* blk, int32_t nblk, const GkSeg* tens,
                int32_t ntens, const GkHyper* hyper, double* part, float* ratio) {
   (void)part;
@@ -330,29 +426,6 @@ int gkcpu_grad_norm(const float* grad, const GkBlk* blk, int32_t nblk, float max
   out[0] = norm;
   out[1] = (max_norm > 0.f && coef < 1.f) ? coef : 1.f;
   return 0;
-}
-
-static inline uint32_t mix32(uint32_t x) {
-  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
-  return x;
-}
-static inline uint32_t feistel_perm(uint32_t j, uint32_t n, uint64_t seed) {
-  int bits = 2;
-  while ((1ull << bits) < (uint64_t)n) bits += 2;
-  const int half = bits / 2;
-  const uint32_t mask = (1u << half) - 1u;
-  uint32_t x = j;
-  do {
-    uint32_t l = x >> half, r = x & mask;
-    for (int round = 0; round < 4; ++round) {
-      const uint32_t f = mix32(r ^ (uint32_t)(seed >> (round * 8)) ^ (0x9e3779b9u * (round + 1))) & mask;
-      const uint32_t nl = r;
-      r = l ^ f;
-      l = nl;
-    }
-    x = (l << half) | r;
-  } while (x >= n);
-  return x;
 }
 
 int gkcpu_randomk_send(const GkChain* c, const GkDst* dst, uint64_t seed) {
@@ -411,6 +484,66 @@ int gkcpu_bucket_reconstruct(const GkChain* c, const float* lm, const float* gm)
       x = (x >= 0.f) ? (x - lm[2 * B.seg]) + gm[2 * B.seg] : (x - lm[2 * B.seg + 1]) + gm[2 * B.seg + 1];
     }
   }
+  return 0;
+}
+
+int gkcpu_dgc_compress(const GkChain* c, const GkDst* dst, uint64_t seed) {
+  // compression.py:576-606 with the sample drawn by the keyed bijection of the random-k kernels (same
+  // coordinates as csrc/gk_cuda.cu for the same seed): k-th largest |acc| of int(0.01 n) sampled coordinates
+  // is the threshold; more than 4k/3 above it => exact top-k instead.
+  if (dst->ndst < 1 || dst->ndst > GK_MAXP) return 1;
+  const uint32_t seqn = c->ctrl->seq + 1u;
+  Emit em{dst, (uint64_t)(seqn & 1u) * dst->parity_stride, c->cap};
+  for (int s = 0; s < c->nseg; ++s) {
+    const GkSeg& sg = c->seg[s];
+    GkSegStat& st = c->stat[s];
+    double sum, sq, sa;
+    float mx;
+    accumulate_segment(c, sg, sum, sq, sa, mx);
+    const double n = (double)sg.n;
+    const double mean = sum / n;
+    double var = sg.n > 1 ? (sq - sum * mean) / (n - 1.0) : 0.0;
+    if (var < 0) var = 0;
+    st.mean = (float)mean; st.std = (float)std::sqrt(var); st.meanabs = (float)(sa / n); st.maxabs = mx;
+    st.out_base = em.total;
+    const uint32_t before = em.total;
+    const int fk = (int)((double)sg.n * 0.01);
+    uint32_t tb = 0;
+    if (fk >= sg.k && fk >= 1) {
+      const uint64_t sd = seed + 0x632be59bd9b4e019ull * (uint64_t)(s + 1) + 0x9e3779b97f4a7c15ull * (uint64_t)seqn;
+      std::vector<uint32_t> keys((size_t)fk);
+      for (int j = 0; j < fk; ++j) {
+        const uint32_t li = feistel_perm((uint32_t)j, (uint32_t)sg.n, sd);
+        int lo = sg.blk_begin, hi = sg.blk_end - 1;
+        while (lo < hi) {
+          const int mid = (lo + hi + 1) >> 1;
+          if ((uint32_t)c->blk[mid].soff <= li) lo = mid; else hi = mid - 1;
+        }
+        const GkBlk& B = c->blk[lo];
+        keys[(size_t)j] = absbits(c->resid[(uint32_t)B.start + (li - (uint32_t)B.soff)]);
+      }
+      std::nth_element(keys.begin(), keys.begin() + (sg.k - 1), keys.end(), std::greater<uint32_t>());
+      tb = keys[(size_t)sg.k - 1];
+    }
+    size_t passed = 0;
+    for (int b = sg.blk_begin; b < sg.blk_end; ++b)
+      for (int i = 0; i < c->blk[b].len; ++i) passed += absbits(c->resid[c->blk[b].start + i]) > tb;
+    if ((double)passed > 4.0 * (double)sg.k / 3.0) {
+      emit_exact_topk(c, sg, st, em, false);
+    } else {
+      st.tbits = tb; st.ties = 0; st.chosen = 0;
+      for (int b = sg.blk_begin; b < sg.blk_end; ++b) {
+        const GkBlk& B = c->blk[b];
+        for (int i = 0; i < B.len; ++i) {
+          const int j = B.start + i;
+          if (absbits(c->resid[j]) > tb)
+            if (em.put((uint32_t)j, c->resid[j])) c->resid[j] = 0.f;
+        }
+      }
+    }
+    st.count = em.total - before;
+  }
+  publish(c, dst, em.poff, seqn, em.total, em.pos);
   return 0;
 }
 

@@ -111,11 +111,111 @@ __device__ __forceinline__ uint32_t sel_key(float x) {
 // index of the gaussian refinement candidate reached after `a` halvings and `b` x1.5 steps
 __device__ __forceinline__ int tri_idx(int a, int b) { return (a + b) * (a + b + 1) / 2 + a; }
 
+// -------------------------------------------------------------- row maxima and gated reading
+// K1 has every element of acc in registers once; it leaves behind, per 128-element row of every table
+// entry, the largest |acc| bit pattern (GkChain.rowmax, n/128 words = 0.8 MB for ResNet-50).  All later
+// passes of the chain look for elements ABOVE some threshold, and at density 0.001 only about one row in
+// eight contains one: they read the row maxima and then only the rows that can contribute.  Counts and
+// selections stay exact — a skipped row provably holds nothing above the gate.
+#define GK_ROW 128           /* elements per row: one float4 per lane */
+#define GK_RC 5              /* candidates evaluated per counting round (>= the widest round of any mode) */
+
+__device__ __forceinline__ uint32_t ld_relaxed_gpu_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Gate for "|x| > thr" on row maxima: a row can hold such an element iff (int)rowmax_bits > gate.
+// Negative thresholds select everything (gate -1); the comparison of the elements themselves is done in
+// floating point, the gate only has to be conservative.
+__device__ __forceinline__ int gate_of(float thr) { return (thr < 0.f) ? -1 : __float_as_int(thr); }
+
+// One row of an entry as a float4 per lane; positions past the end of the entry read as NaN, which no
+// comparison selects.
+__device__ __forceinline__ float4 ld_row(const float* __restrict__ a, int row, int lane, int len) {
+  const int i0 = row * GK_ROW + lane * 4;
+  if (i0 + 3 < len) return ld4(a + i0);
+  const float qn = __int_as_float(0x7fc00000);
+  float4 v;
+  v.x = (i0 < len) ? a[i0] : qn;
+  v.y = (i0 + 1 < len) ? a[i0 + 1] : qn;
+  v.z = (i0 + 2 < len) ? a[i0 + 2] : qn;
+  v.w = qn;
+  return v;
+}
+
+// ----------------------------------------------------------------- K2 search state machine
+// The reference evaluates its candidate thresholds one after the other, each with a full pass and a host
+// synchronisation (compression.py:372-381, :653-672, :719-732).  Here the search is replayed on the device
+// on the totals known so far; when it needs a candidate that has not been counted yet, the next ROUND
+// counts that candidate together with the others the search could ask for at the same depth:
+//   gaussian (L evaluations): round a counts c*t0 for c = 0.5^a * 1.5^b, all b        (<= L rounds)
+//   redsync:                  round d counts the nodes of depth d of the bisection tree (<= 3 rounds)
+//   redsynctrim:              round r counts ratios 4r .. 4r+3                          (<= 4 rounds)
+// In the regime the method is built for the first round settles it.  Returns true when the search is
+// complete; otherwise st->rcand[0..nrc) / st->gate describe the next round.
+__device__ bool k2_advance(const GkChain& c, const GkSeg& sg, GkSegStat* st) {
+  const double k = (double)sg.k;
+  const uint32_t known = st->known;
+  int nrc = 0;
+  uint8_t rc[GK_RC];
+  if (c.mode == GK_MODE_GAUSSIAN) {
+    int a = 0, b = 0, need = -1;
+    for (int loop = 0; loop < c.nloops; ++loop) {
+      const int idx = tri_idx(a, b);
+      if (!((known >> idx) & 1u)) { need = a; break; }
+      const double cnt = (double)__ldcg(&st->tot[idx]);
+      if (cnt < 2.0 * k / 3.0) ++a;
+      else if (cnt > 4.0 * k / 3.0) ++b;
+      else break;
+    }
+    if (need >= 0)
+      for (int bb = 0; need + bb < c.nloops && nrc < GK_RC; ++bb) rc[nrc++] = (uint8_t)tri_idx(need, bb);
+  } else if (c.mode == GK_MODE_REDSYNC) {
+    double l = 0.0, r = 1.0;
+    int node = 0, need = -1;
+    while (r - l > 0.2) {
+      if (!((known >> node) & 1u)) { need = node; break; }
+      const double mid = l + (r - l) / 2;
+      const double nnz = (double)__ldcg(&st->tot[node]);
+      if (nnz > k && 2.0 * k > nnz) break;
+      else if (nnz < k / 2.0) { r = mid; node = 2 * node + 1; }
+      else { l = mid; node = 2 * node + 2; }
+      if (node >= 7) break;
+    }
+    if (need >= 0) {
+      const int first = (need == 0) ? 0 : (need < 3 ? 1 : 3), cntn = first + 1;   // depth 0: {0}, 1: {1,2}, 2: {3..6}
+      for (int j = 0; j < cntn && nrc < GK_RC; ++j) rc[nrc++] = (uint8_t)(first + j);
+    }
+  } else if (c.mode == GK_MODE_REDSYNCTRIM) {
+    for (int j = 0; j < GK_NC; ++j) {
+      if (!((known >> j) & 1u)) {
+        for (int q = j; q < GK_NC && q < j + 4; ++q) rc[nrc++] = (uint8_t)q;
+        break;
+      }
+      if ((double)__ldcg(&st->tot[j]) >= k) break;
+    }
+  } else {  // GK_MODE_THRESHOLD: one candidate, one round
+    if (!(known & 1u)) rc[nrc++] = 0;
+  }
+  if (nrc == 0) return true;
+  float cmin = st->cand[rc[0]];
+  for (int j = 1; j < nrc; ++j) cmin = fminf(cmin, st->cand[rc[j]]);   // fminf ignores NaN candidates
+  for (int j = 0; j < nrc; ++j) st->rcand[j] = rc[j];
+  st->nrc = nrc;
+  st->gate = gate_of(cmin);
+  return false;
+}
+
 // ----------------------------------------------------------------- K1 accumulate + moments
 // Epilogue of K1, run by the last block: per-segment moments (fixed-order warp reduction of
 // the per-block partials => deterministic), then the candidate thresholds of the counting
-// pass, or the first radix digit for top-k.
-// Leader work of the K1 epilogue for one segment: moments -> stat, candidate thresholds.
+// rounds, or the first radix digit for top-k.
+// Leader work of the K1 epilogue for one segment: moments -> stat, candidate thresholds, first round.
 __device__ void k1_finish_segment(const GkChain& c, int s, const GkSeg& sg, double sum, double sq, double sa, float mx) {
   GkSegStat* st = c.stat + s;
   for (int j = 0; j < GK_NC; ++j) st->tot[j] = 0;
@@ -157,29 +257,13 @@ __device__ void k1_finish_segment(const GkChain& c, int s, const GkSeg& sg, doub
   } else if (c.mode == GK_MODE_THRESHOLD) {
     st->cand[0] = sg.param;
   }
-  if (c.mode == GK_MODE_TOPK || c.mode == GK_MODE_MINK) {
+  if (c.mode == GK_MODE_TOPK || c.mode == GK_MODE_MINK || c.mode == GK_MODE_DGC) {
     c.stat[s].prefix = 0; c.stat[s].krem = (uint32_t)sg.k;
+    st->done = 0;
   } else {
-    // Sorted candidate order for the counting pass.  Candidates far in the tail ("high") are only
-    // evaluated in rows where the row maximum exceeds the smallest of them; the split is a speed
-    // heuristic (about 1 % expected exceedance), the counts are exact either way.
-    const int nc = (c.mode == GK_MODE_GAUSSIAN) ? c.nloops * (c.nloops + 1) / 2
-                 : (c.mode == GK_MODE_REDSYNC) ? 7 : (c.mode == GK_MODE_REDSYNCTRIM) ? GK_NC : 1;
-    uint8_t ord[GK_NC];
-    for (int j = 0; j < GK_NC; ++j) ord[j] = (uint8_t)j;
-    for (int j = 1; j < nc; ++j) {          // insertion sort, <= 16 items
-      const uint8_t key = ord[j];
-      const float kv = st->cand[key];
-      int i = j - 1;
-      while (i >= 0 && st->cand[ord[i]] > kv) { ord[i + 1] = ord[i]; --i; }
-      ord[i + 1] = key;
-    }
-    const float gate = (c.mode == GK_MODE_GAUSSIAN) ? fabsf(meanf) + 2.5f * stdf : 3.2f * meanabs;
-    int nlow = 0;
-    while (nlow < nc && !(st->cand[ord[nlow]] > gate)) ++nlow;
-    if (c.mode == GK_MODE_THRESHOLD) nlow = 1;
-    for (int j = 0; j < GK_NC; ++j) st->order[j] = ord[j];
-    st->nlow = nlow;
+    st->known = 0;
+    st->nrc = 0;
+    st->done = k2_advance(c, sg, st) ? 1 : 0;   // plans the first counting round
   }
 }
 
@@ -221,10 +305,8 @@ __device__ void k1_epilogue(const GkChain& c) {
 
 // One radix-select step on segment s by one warp: find the digit whose bucket contains the
 // krem-th largest key, update (prefix, krem), and clear the histogram for the next pass.
-__device__ void radix_pick_warp(const GkChain& c, int s, int shift, int nbins, int lane) {
-  uint32_t* h = c.hist + (size_t)s * GK_HIST_BINS;
-  GkSegStat* st = c.stat + s;
-  const uint32_t krem = st->krem;
+__device__ void radix_pick_warp_at(uint32_t* h, uint32_t* prefix_p, uint32_t* krem_p, int nbins, int lane) {
+  const uint32_t krem = *krem_p;
   const int per = nbins / 32;  // bins per lane; lane 31 owns the highest digits
   uint32_t mysum = 0;
   for (int j = 0; j < per; ++j) mysum += __ldcg(h + lane * per + j);
@@ -240,7 +322,7 @@ __device__ void radix_pick_warp(const GkChain& c, int s, int shift, int nbins, i
   const uint32_t ball = __ballot_sync(0xffffffffu, mine);
   if (ball == 0) {
     // fewer than krem keys matched the prefix (cannot happen when k <= n); take the lowest digit
-    if (lane == 0) st->prefix = st->prefix << ((nbins == 2048) ? 11 : 9);
+    if (lane == 0) *prefix_p = *prefix_p << ((nbins == 2048) ? 11 : 9);
   } else if (mine) {
     uint32_t run = above;
     int digit = lane * per;
@@ -250,17 +332,24 @@ __device__ void radix_pick_warp(const GkChain& c, int s, int shift, int nbins, i
       run += v;
     }
     const int width = (nbins == 2048) ? 11 : 9;
-    st->prefix = (st->prefix << width) | (uint32_t)digit;
-    st->krem = krem - run;  // rank inside the chosen bucket (1-based)
+    *prefix_p = (*prefix_p << width) | (uint32_t)digit;
+    *krem_p = krem - run;  // rank inside the chosen bucket (1-based)
   }
   __syncwarp();
   for (int j = lane; j < nbins; j += 32) h[j] = 0;
+}
+
+__device__ __forceinline__ void radix_pick_warp(const GkChain& c, int s, int shift, int nbins, int lane) {
+  (void)shift;
+  radix_pick_warp_at(c.hist + (size_t)s * GK_HIST_BINS, &c.stat[s].prefix, &c.stat[s].krem, nbins, lane);
 }
 
 // Persistent: a CUDA block walks the table entries blockIdx.x, blockIdx.x + gridDim.x, ... and keeps
 // its partial moments in registers for as long as consecutive entries belong to the same segment (a
 // "run"); only the last entry of a run pays for the block reduction, the others record zeros.  In the
 // merged-buffer mode (one segment) that is one reduction and one ticket per block.
+// A warp handles one 128-element row per step (rows warp, warp+8, ... of the entry), so the row maximum
+// is one REDUX on the bit patterns.
 template <bool HIST, bool MINK>
 __global__ void __launch_bounds__(GK_THREADS) k_accumulate(GkChain c) {
   __shared__ uint32_t shist[HIST ? GK_HIST_BINS : 1];
@@ -281,37 +370,59 @@ __global__ void __launch_bounds__(GK_THREADS) k_accumulate(GkChain c) {
     const bool last_of_run = (enext >= c.nblk) || (c.blk[enext].seg != B.seg);   // block-uniform
     const float* __restrict__ g = c.gsrc ? c.gsrc[eidx] : c.grad + B.start;
     float* __restrict__ r = c.resid + B.start;
+    uint32_t* __restrict__ rmx = c.rowmax ? c.rowmax + (size_t)eidx * c.rpb : nullptr;
     // fp32 partials over one entry (<= chunk/256 elements per thread), fp64 across entries
     float s = 0.f, q = 0.f, sa = 0.f;
-    const int n4 = B.len >> 2;
-    if (tid < GK_NC) c.bcnt[(size_t)eidx * GK_NC + tid] = 0;   // the counting pass accumulates with atomics
+    const int nrow = (B.len + GK_ROW - 1) / GK_ROW;
+    if (tid < GK_NC) c.bcnt[(size_t)eidx * GK_NC + tid] = 0;   // entries no counting round visits stay at zero
 #pragma unroll 2
-    for (int i = tid; i < n4; i += T) {
-      float4 x = ld4_stream(g + 4 * i);
-      if (user) {
-        const float4 rv = ld4_stream(r + 4 * i);
-        x.x += rv.x; x.y += rv.y; x.z += rv.z; x.w += rv.w;
+    for (int row = warp; row < nrow; row += NWARP) {
+      const int i0 = row * GK_ROW + lane * 4;
+      float4 x;
+      int nv = 4;                       // valid elements of this lane's quad
+      if (i0 + 3 < B.len) {
+        x = ld4_stream(g + i0);
+        if (user) {
+          const float4 rv = ld4_stream(r + i0);
+          x.x += rv.x; x.y += rv.y; x.z += rv.z; x.w += rv.w;
+        }
+        st4(r + i0, x);  // acc: default policy so that it can stay in L2 for the following passes
+        if (zg) st4_stream(const_cast<float*>(g) + i0, z4);
+      } else {                          // ragged end of a tensor whose size is not a multiple of 4
+        nv = B.len - i0;
+        nv = nv < 0 ? 0 : nv;
+        float e[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int j = 0; j < nv; ++j) {
+          float v = g[i0 + j];
+          if (user) v += r[i0 + j];
+          r[i0 + j] = v;
+          if (zg) const_cast<float*>(g)[i0 + j] = 0.f;
+          e[j] = v;
+        }
+        x = make_float4(e[0], e[1], e[2], e[3]);
       }
-      st4(r + 4 * i, x);  // acc: default policy so that it can stay in L2 for the following passes
-      if (zg) st4_stream(const_cast<float*>(g) + 4 * i, z4);
       s += (x.x + x.y) + (x.z + x.w);
       q = fmaf(x.x, x.x, q); q = fmaf(x.y, x.y, q); q = fmaf(x.z, x.z, q); q = fmaf(x.w, x.w, q);
       const float ax = fabsf(x.x), ay = fabsf(x.y), az = fabsf(x.z), aw = fabsf(x.w);
       sa += (ax + ay) + (az + aw);
-      mx = fmaxf(fmaxf(mx, fmaxf(ax, ay)), fmaxf(az, aw));
-      if (HIST) {
-        atomicAdd(&shist[sel_key<MINK>(x.x) >> 20], 1u); atomicAdd(&shist[sel_key<MINK>(x.y) >> 20], 1u);
-        atomicAdd(&shist[sel_key<MINK>(x.z) >> 20], 1u); atomicAdd(&shist[sel_key<MINK>(x.w) >> 20], 1u);
+      const float m4 = fmaxf(fmaxf(ax, ay), fmaxf(az, aw));
+      mx = fmaxf(mx, m4);
+      if (rmx) {
+        // bit patterns of non-negative floats order like the floats (NaN sorts above everything: such a row
+        // is always read); padding zeros cannot raise the maximum
+        const uint32_t mb = max(max(absbits(x.x), absbits(x.y)), max(absbits(x.z), absbits(x.w)));
+        const uint32_t rm = __reduce_max_sync(0xffffffffu, mb);
+        if (lane == 0) rmx[row] = rm;
       }
-    }
-    for (int i = 4 * n4 + tid; i < B.len; i += T) {  // tail of a tensor whose size % 4 != 0
-      float x = g[i];
-      if (user) x += r[i];
-      r[i] = x;
-      if (zg) const_cast<float*>(g)[i] = 0.f;
-      s += x; q = fmaf(x, x, q); sa += fabsf(x);
-      mx = fmaxf(mx, fabsf(x));
-      if (HIST) atomicAdd(&shist[sel_key<MINK>(x) >> 20], 1u);
+      if (HIST) {
+        if (nv == 4) {
+          atomicAdd(&shist[sel_key<MINK>(x.x) >> 20], 1u); atomicAdd(&shist[sel_key<MINK>(x.y) >> 20], 1u);
+          atomicAdd(&shist[sel_key<MINK>(x.z) >> 20], 1u); atomicAdd(&shist[sel_key<MINK>(x.w) >> 20], 1u);
+        } else {
+          const float e[4] = {x.x, x.y, x.z, x.w};
+          for (int j = 0; j < nv; ++j) atomicAdd(&shist[sel_key<MINK>(e[j]) >> 20], 1u);
+        }
+      }
     }
     ds += (double)s; dq += (double)q; da += (double)sa;
     double* p = c.part + 4 * (size_t)eidx;
@@ -349,6 +460,8 @@ __global__ void __launch_bounds__(GK_THREADS) k_accumulate(GkChain c) {
 // ------------------------------------------------------------- K4 radix-select digit passes
 // PASS 2: digit = key bits [19:9] of elements whose bits [30:20] equal the prefix.
 // PASS 3: digit = key bits [8:0]  of elements whose bits [30:9]  equal the prefix.
+// One block per table entry; a row whose maximum lies below the prefix cannot match and is not read
+// (largest-k only: for min-k the keys are reversed and every row is read).
 template <int PASS, bool MINK>
 __global__ void __launch_bounds__(GK_THREADS) k_radix_pass(GkChain c) {
   constexpr int NB = (PASS == 2) ? 2048 : 512;
@@ -357,27 +470,28 @@ __global__ void __launch_bounds__(GK_THREADS) k_radix_pass(GkChain c) {
   __shared__ uint32_t shist[NB];
   __shared__ int s_any;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const GkBlk B = c.blk[(PASS == 2) ? (c.nblk - 1 - (int)blockIdx.x) : (int)blockIdx.x];  // zig-zag
+  const int eidx = (int)blockIdx.x;
+  const GkBlk B = c.blk[eidx];
+  const GkSegStat* st = c.stat + B.seg;
+  const bool skip = st->done != 0;           // DGC: the sampled threshold was accepted, no exact select needed
   for (int i = tid; i < NB; i += T) shist[i] = 0;
   if (tid == 0) s_any = 0;
   __syncthreads();
-  const uint32_t prefix = c.stat[B.seg].prefix;
+  const uint32_t prefix = st->prefix;
   const float* __restrict__ a = c.resid + B.start;
-  const int n4 = B.len >> 2;
+  const uint32_t* __restrict__ rmx = (c.rowmax && !MINK) ? c.rowmax + (size_t)eidx * c.rpb : nullptr;
+  const int nrow = skip ? 0 : (B.len + GK_ROW - 1) / GK_ROW;
   bool any = false;
-#pragma unroll 4
-  for (int i = tid; i < n4; i += T) {
-    const float4 x = ld4(a + 4 * i);
+  for (int row = warp; row < nrow; row += NWARP) {
+    if (rmx && (rmx[row] >> SHIFT_MATCH) < prefix) continue;     // warp-uniform
+    const float4 x = ld_row(a, row, lane, B.len);
     const float e[4] = {x.x, x.y, x.z, x.w};
+    const int nv = B.len - (row * GK_ROW + lane * 4);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const uint32_t key = sel_key<MINK>(e[j]);
-      if ((key >> SHIFT_MATCH) == prefix) { atomicAdd(&shist[(key >> SHIFT_DIGIT) & (NB - 1)], 1u); any = true; }
+      if (j < nv && (key >> SHIFT_MATCH) == prefix) { atomicAdd(&shist[(key >> SHIFT_DIGIT) & (NB - 1)], 1u); any = true; }
     }
-  }
-  for (int i = 4 * n4 + tid; i < B.len; i += T) {
-    const uint32_t key = sel_key<MINK>(a[i]);
-    if ((key >> SHIFT_MATCH) == prefix) { atomicAdd(&shist[(key >> SHIFT_DIGIT) & (NB - 1)], 1u); any = true; }
   }
   if (any) s_any = 1;
   __syncthreads();
@@ -390,14 +504,15 @@ __global__ void __launch_bounds__(GK_THREADS) k_radix_pass(GkChain c) {
   }
   if (last_block_done(&c.ctrl->done[1])) {
     for (int s = warp; s < c.nseg; s += NWARP) {
+      if (c.stat[s].done) continue;
       radix_pick_warp(c, s, SHIFT_DIGIT, NB, lane);
       if (PASS == 3) {
         __syncwarp();
         if (lane == 0) {
-          GkSegStat* st = c.stat + s;
-          st->tbits = st->prefix;  // full 31-bit key of the k-th element
-          st->ties = st->krem;     // how many keys == T are still needed
-          st->chosen = 0;
+          GkSegStat* sst = c.stat + s;
+          sst->tbits = sst->prefix;  // full 31-bit key of the k-th element
+          sst->ties = sst->krem;     // how many keys == T are still needed
+          sst->chosen = 0;
         }
       }
     }
@@ -461,8 +576,6 @@ __device__ void k2_decide_segment(const GkChain& c, int s, const GkSeg& sg, cons
 __device__ void k2_epilogue(const GkChain& c, bool topk) {
   __shared__ uint32_t sscan[2][T];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const bool dbg = (c.rsv & 4) != 0;
-  if (dbg && tid == 0) c.ctrl->ring[40] = (uint32_t)globaltimer_ns();
   // phase 1: the counting pass already accumulated the per-candidate totals of every segment with
   // atomics (stat.tot); one thread per segment replays the refinement loop.  Thread t owns segments
   // [t*per, (t+1)*per) in phases 1 and 2, so nothing is read back from global memory in between.
@@ -479,7 +592,6 @@ __device__ void k2_epilogue(const GkChain& c, bool topk) {
     loc += c.stat[s].count;
     if (s == 0) s_chosen0 = c.stat[s].chosen;
   }
-  if (dbg && tid == 0) c.ctrl->ring[41] = (uint32_t)globaltimer_ns();
   // phase 2: exclusive scan of the per-segment counts -> out_base; total
   {
     sscan[0][tid] = loc;
@@ -503,7 +615,6 @@ __device__ void k2_epilogue(const GkChain& c, bool topk) {
     }
   }
   __syncthreads();
-  if (dbg && tid == 0) c.ctrl->ring[42] = (uint32_t)globaltimer_ns();
   // phase 3: global exclusive scans over the table entries of (gt, eq); K3 subtracts the value at the
   // first entry of its segment to make them segment-relative.  Each thread owns a contiguous run of
   // entries whose counts stay in registers between the two sweeps when the run is short.
@@ -581,288 +692,301 @@ __device__ void k2_epilogue(const GkChain& c, bool topk) {
     }
   }
   __syncthreads();
-  if (dbg && tid == 0) c.ctrl->ring[43] = (uint32_t)globaltimer_ns();
 }
 
-// Persistent and barrier-free: a block walks the table entries (backwards, see below); inside an entry
-// every warp owns a contiguous 1024-element slice per 8192-element sub-tile, counts its slice in
-// registers and adds its (non-zero) per-candidate counts to the entry's row of bcnt with integer atomics
-// (K1 zeroed the rows).  Integer adds commute, so the result is deterministic.
-template <int NCAND>
-__global__ void __launch_bounds__(GK_THREADS) k_count(GkChain c) {
-  constexpr bool SKIP_ROWS = NCAND > 6;   // gaussian (<= 6 candidates): the smallest is exceeded in every row
-  constexpr int NLOW = (NCAND + 1) / 2;    // candidates evaluated unconditionally
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  int cur_seg = -1;
-  float cs[NCAND];        // candidates of the current segment in ascending order
-  uint32_t ord[NCAND];    // their original indices
+
+// Counting rounds.  One warp per table entry: it reads the entry's row maxima, then only the rows that can
+// hold an element above the smallest candidate of the round, four rows in flight at a time, and leaves the
+// entry's count for every candidate of the round in its row of bcnt (plain stores: one writer per cell).
+// Totals go to stat.tot with integer atomics (commutative => deterministic).  Between rounds the blocks
+// meet at a grid-wide barrier (cooperative launch) whose last arrival replays the searches (k2_advance);
+// after the last round the last block to finish runs the prefix-sum epilogue for K3.
+template <int NR>
+__device__ __forceinline__ void count_rows(const float* __restrict__ a, const uint32_t* __restrict__ rmx, int len,
+                                           int gate, const float (&cs)[GK_RC], uint32_t (&cnt)[GK_RC], int lane) {
+  const int nrow = (len + GK_ROW - 1) / GK_ROW;
+  for (int rb = 0; rb < nrow; rb += 32) {
+    const int row = rb + lane;
+    const bool flag = row < nrow && (rmx == nullptr || (int)rmx[row] > gate);
+    uint32_t m = __ballot_sync(0xffffffffu, flag);
+    while (m) {                                     // warp-uniform: m is a ballot
+      int rr[4];
 #pragma unroll
-  for (int j = 0; j < NCAND; ++j) { cs[j] = 0.f; ord[j] = j; }
-  __shared__ uint32_t s_tot[GK_NC];
-  if (tid < GK_NC) s_tot[tid] = 0;
-  if ((c.rsv & 4) && blockIdx.x == 0 && tid == 0) c.ctrl->ring[44] = (uint32_t)globaltimer_ns();
-  __syncthreads();
-  uint32_t run[NCAND];     // this lane's counts since the last flush (current segment)
-#pragma unroll
-  for (int j = 0; j < NCAND; ++j) run[j] = 0;
-  for (int it = blockIdx.x; it < c.nblk; it += gridDim.x) {
-    // zig-zag: K1 walked the arena forwards, so its tail is what is still in L2 -> walk backwards here
-    const int eidx = c.nblk - 1 - it;
-    const GkBlk B = c.blk[eidx];
-    if (B.seg != cur_seg) {   // block-uniform
-      if (cur_seg >= 0) {     // segment change inside a block (multi-segment tables): flush straight to global
-#pragma unroll
-        for (int j = 0; j < NCAND; ++j) {
-          const uint32_t w = warp_sum_u(run[j]);
-          if (lane == 0 && w) atomicAdd(&c.stat[cur_seg].tot[ord[j]], w);
-          run[j] = 0;
-        }
+      for (int u = 0; u < 4; ++u) {
+        rr[u] = m ? rb + __ffs(m) - 1 : -1;
+        m &= m - 1u;                                // 0 stays 0
       }
-      cur_seg = B.seg;
-      const GkSegStat* st = c.stat + B.seg;
+      float4 v[4];
+      const float qn = __int_as_float(0x7fc00000);
 #pragma unroll
-      for (int j = 0; j < NCAND; ++j) { ord[j] = st->order[j]; cs[j] = st->cand[ord[j]]; }
+      for (int u = 0; u < 4; ++u) v[u] = (rr[u] >= 0) ? ld_row(a, rr[u], lane, len) : make_float4(qn, qn, qn, qn);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float e0 = fabsf(v[u].x), e1 = fabsf(v[u].y), e2 = fabsf(v[u].z), e3 = fabsf(v[u].w);
+#pragma unroll
+        for (int j = 0; j < NR; ++j)
+          cnt[j] += (uint32_t)(e0 > cs[j]) + (uint32_t)(e1 > cs[j]) + (uint32_t)(e2 > cs[j]) + (uint32_t)(e3 > cs[j]);
+      }
     }
-    uint32_t cnt[NCAND];
+  }
+}
+
+__global__ void __launch_bounds__(GK_THREADS) k_count_rounds(GkChain c) {
+  __shared__ uint32_t s_tot[GK_RC];
+  __shared__ uint32_t s_gen, s_more;
+  __shared__ int s_last;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int noct = (c.nblk + NWARP - 1) / NWARP;
+  uint32_t* bar = c.ctrl->rsv;      // [0] arrivals, [1] generation, [2] "another round is needed"
+  if (tid == 0) s_gen = ld_relaxed_gpu_u32(bar + 1);
+  const bool one_seg = c.nseg == 1;
+  for (int round = 0; round < GK_NC + 1; ++round) {
+    if (tid < GK_RC) s_tot[tid] = 0;
+    __syncthreads();
+    for (int oct = blockIdx.x; oct < noct; oct += gridDim.x) {
+      const int e = oct * NWARP + warp;
+      if (e >= c.nblk) continue;                    // warp-uniform
+      const GkBlk B = c.blk[e];
+      const GkSegStat* st = c.stat + B.seg;
+      if (__ldcg(&st->done)) continue;              // this segment's search is complete
+      const int nrc = __ldcg(&st->nrc), gate = __ldcg(&st->gate);
+      const uint2 rcw = __ldcg(reinterpret_cast<const uint2*>(st->rcand));   // rcand[0..7], 8-byte aligned
+      float cs[GK_RC];
+      uint32_t ci[GK_RC], cnt[GK_RC];
 #pragma unroll
-    for (int j = 0; j < NCAND; ++j) cnt[j] = 0;
-    const float* __restrict__ a = c.resid + B.start;
-    for (int t0 = 0; t0 < B.len; t0 += GK_SUB) {
-      const int wbeg = t0 + warp * 1024;
-      if (wbeg >= B.len) break;          // warp-uniform
-      if (wbeg + 1024 <= B.len) {        // warp-uniform fast path: a full 1024-element slice
-        const float* __restrict__ aw = a + wbeg + lane * 4;
+      for (int j = 0; j < GK_RC; ++j) {
+        ci[j] = ((j < 4 ? rcw.x >> (8 * j) : rcw.y >> (8 * (j - 4))) & 0xffu);
+        cs[j] = (j < nrc) ? __ldcg(&st->cand[ci[j] & (GK_NC - 1)]) : __int_as_float(0x7f800000);   // +inf: never exceeded
+        cnt[j] = 0;
+      }
+      const float* __restrict__ a = c.resid + B.start;
+      const uint32_t* __restrict__ rmx = c.rowmax ? c.rowmax + (size_t)e * c.rpb : nullptr;
+      if (nrc <= 1) count_rows<1>(a, rmx, B.len, gate, cs, cnt, lane);
+      else if (nrc <= 3) count_rows<3>(a, rmx, B.len, gate, cs, cnt, lane);
+      else count_rows<GK_RC>(a, rmx, B.len, gate, cs, cnt, lane);
+      uint32_t* brow = c.bcnt + (size_t)e * GK_NC;
 #pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          float4 v[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) v[i] = ld4(aw + (half * 4 + i) * 128);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const float e0 = fabsf(v[i].x), e1 = fabsf(v[i].y), e2 = fabsf(v[i].z), e3 = fabsf(v[i].w);
-            // Candidates are sorted ascending.  The lower half is evaluated for every element; the upper
-            // half (far-tail thresholds) only in rows where some lane exceeds the smallest of them — one
-            // row maximum + vote instead of 4 compares per candidate.  Exact either way.
-            const float m = fmaxf(fmaxf(e0, e1), fmaxf(e2, e3));
-            if (SKIP_ROWS && !__any_sync(0xffffffffu, m > cs[0])) continue;
-#pragma unroll
-            for (int j = 0; j < NLOW; ++j)
-              cnt[j] -= (gt_mask(e0, cs[j]) + gt_mask(e1, cs[j])) + (gt_mask(e2, cs[j]) + gt_mask(e3, cs[j]));
-            if (NLOW < NCAND && __any_sync(0xffffffffu, m > cs[NLOW < NCAND ? NLOW : 0])) {
-#pragma unroll
-              for (int j = NLOW; j < NCAND; ++j)
-                cnt[j] -= (gt_mask(e0, cs[j]) + gt_mask(e1, cs[j])) + (gt_mask(e2, cs[j]) + gt_mask(e3, cs[j]));
+      for (int j = 0; j < GK_RC; ++j) {
+        if (j < nrc) {                              // warp-uniform
+          const uint32_t w = warp_sum_u(cnt[j]);
+          if (lane == 0) {
+            brow[ci[j]] = w;
+            if (w) {
+              if (one_seg) atomicAdd(&s_tot[j], w);
+              else atomicAdd(&c.stat[B.seg].tot[ci[j]], w);
             }
           }
         }
-      } else {                            // ragged end of a tensor: plain scalar loop
-        const int wend = min(wbeg + 1024, B.len);
-        for (int i = wbeg + lane; i < wend; i += 32) {
-          const float x = fabsf(a[i]);
-#pragma unroll
-          for (int j = 0; j < NCAND; ++j) cnt[j] += (uint32_t)(x > cs[j]);
-        }
       }
     }
-    uint32_t* row = c.bcnt + (size_t)eidx * GK_NC;
-#pragma unroll
-    for (int j = 0; j < NCAND; ++j) {
-      run[j] += cnt[j];
-      const uint32_t w = warp_sum_u(cnt[j]);
-      if (lane == 0 && w) atomicAdd(row + ord[j], w);
+    __syncthreads();
+    if (one_seg && tid < GK_RC && s_tot[tid]) {
+      const GkSegStat* st = c.stat;
+      if (tid < __ldcg(&st->nrc)) atomicAdd(&c.stat[0].tot[__ldcg(&st->rcand[tid])], s_tot[tid]);
     }
-  }
-  // segment totals: lanes -> warp (REDUX) -> block (smem atomics) -> one global atomic per candidate and block
-  if (cur_seg >= 0) {
-#pragma unroll
-    for (int j = 0; j < NCAND; ++j) {
-      const uint32_t w = warp_sum_u(run[j]);
-      if (lane == 0 && w) atomicAdd(&s_tot[ord[j]], w);
+    // ---- grid barrier; the last block to arrive advances every segment's search before releasing it
+    __syncthreads();
+    if (tid == 0) {
+      __threadfence();
+      s_last = (atomicAdd(bar, 1u) == gridDim.x - 1u);
     }
+    __syncthreads();
+    if (s_last) {
+      __threadfence();
+      int more = 0;
+      for (int s = tid; s < c.nseg; s += T) {
+        GkSegStat* st = c.stat + s;
+        if (st->done) continue;
+        uint32_t known = st->known;
+        for (int j = 0; j < st->nrc; ++j) known |= 1u << st->rcand[j];
+        st->known = known;
+        if (k2_advance(c, c.seg[s], st)) st->done = 1; else more = 1;
+      }
+      more = __syncthreads_or(more);
+      if (tid == 0) {
+        bar[0] = 0;
+        bar[2] = (uint32_t)more;
+        __threadfence();
+        st_release_gpu_u32(bar + 1, s_gen + (uint32_t)round + 1u);
+      }
+    } else if (tid == 0) {
+      const uint64_t t0 = globaltimer_ns();
+      while (ld_relaxed_gpu_u32(bar + 1) == s_gen + (uint32_t)round) {
+        if (globaltimer_ns() - t0 > 2000000000ull) { atomicExch(&c.ctrl->err, 3u); break; }
+      }
+    }
+    __syncthreads();
+    if (tid == 0) {
+      __threadfence();
+      s_more = ld_relaxed_gpu_u32(bar + 2);
+    }
+    __syncthreads();
+    if (!s_more) break;
   }
-  __syncthreads();
-  if (tid < GK_NC && cur_seg >= 0 && s_tot[tid]) atomicAdd(&c.stat[cur_seg].tot[tid], s_tot[tid]);
-  if (c.rsv & 1) return;   // experiment switch (tools/bench_chain.py): skip the epilogue
-  if ((c.rsv & 4) && tid == 0) atomicMax(&c.ctrl->ring[45], (uint32_t)globaltimer_ns());
   if (last_block_done(&c.ctrl->done[2])) k2_epilogue(c, false);
 }
 
-// top-k: per-block counts of key > T (column 0) and key == T (column 1)
-template <bool MINK>
+// top-k / DGC: per-entry counts of key > T (column 0) and key == T (column 1), one warp per entry, rows below
+// T skipped.  FIRST (DGC only) is the pass with the sampled threshold: its epilogue accepts the threshold when
+// at most 4k/3 elements pass it (compression.py:598), otherwise the exact radix select runs.
+template <bool MINK, bool FIRST>
 __global__ void __launch_bounds__(GK_THREADS) k_count_topk(GkChain c) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int it = blockIdx.x; it < c.nblk; it += gridDim.x) {
-    const int eidx = c.nblk - 1 - it;  // zig-zag (see k_count)
-    const GkBlk B = c.blk[eidx];
-    const uint32_t tb = c.stat[B.seg].tbits;
+  const int e = (int)blockIdx.x * NWARP + warp;
+  if (e < c.nblk) {
+    const GkBlk B = c.blk[e];
+    GkSegStat* st = c.stat + B.seg;
+    const uint32_t tb = st->tbits;
     uint32_t gt = 0, eq = 0;
     const float* __restrict__ a = c.resid + B.start;
-    for (int t0 = 0; t0 < B.len; t0 += GK_SUB) {
-      const int wbeg = t0 + warp * 1024;
-      if (wbeg >= B.len) break;
-      if (wbeg + 1024 <= B.len) {
-        float4 v[8];
+    const uint32_t* __restrict__ rmx = (c.rowmax && !MINK) ? c.rowmax + (size_t)e * c.rpb : nullptr;
+    const int nrow = (B.len + GK_ROW - 1) / GK_ROW;
+    for (int rb = 0; rb < nrow; rb += 32) {
+      const int row = rb + lane;
+      const bool flag = row < nrow && (rmx == nullptr || rmx[row] >= tb);
+      uint32_t m = __ballot_sync(0xffffffffu, flag);
+      while (m) {
+        int rr[4];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) v[i] = ld4(a + wbeg + (i * 32 + lane) * 4);
+        for (int u = 0; u < 4; ++u) { rr[u] = m ? rb + __ffs(m) - 1 : -1; m &= m - 1u; }
+        float4 v[4];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float e[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+        for (int u = 0; u < 4; ++u) v[u] = (rr[u] >= 0) ? ld_row(a, rr[u], lane, B.len) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const float ev[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+          const int nv = (rr[u] >= 0) ? B.len - (rr[u] * GK_ROW + lane * 4) : 0;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const uint32_t key = sel_key<MINK>(e[j]);
-            gt += (uint32_t)(key > tb);
-            eq += (uint32_t)(key == tb);
+            const uint32_t key = sel_key<MINK>(ev[j]);
+            gt += (uint32_t)(j < nv && key > tb);
+            eq += (uint32_t)(j < nv && key == tb);
           }
-        }
-      } else {
-        for (int i = wbeg + lane; i < min(wbeg + 1024, B.len); i += 32) {
-          const uint32_t key = sel_key<MINK>(a[i]);
-          gt += (uint32_t)(key > tb);
-          eq += (uint32_t)(key == tb);
         }
       }
     }
     gt = warp_sum_u(gt); eq = warp_sum_u(eq);
-    uint32_t* row = c.bcnt + (size_t)eidx * GK_NC;
+    uint32_t* brow = c.bcnt + (size_t)e * GK_NC;
     if (lane == 0) {
-      if (gt) { atomicAdd(row, gt); atomicAdd(&c.stat[B.seg].tot[0], gt); }
-      if (eq) { atomicAdd(row + 1, eq); atomicAdd(&c.stat[B.seg].tot[1], eq); }
+      brow[0] = gt; brow[1] = eq;
+      if (gt) atomicAdd(&st->tot[0], gt);
+      if (eq) atomicAdd(&st->tot[1], eq);
     }
   }
-  if (last_block_done(&c.ctrl->done[2])) k2_epilogue(c, true);
+  if (last_block_done(&c.ctrl->done[2])) {
+    if (FIRST) {
+      for (int s = tid; s < c.nseg; s += T) {
+        GkSegStat* st = c.stat + s;
+        const double k = (double)c.seg[s].k;
+        const uint32_t passed = __ldcg(&st->tot[0]);
+        st->tot[0] = 0; st->tot[1] = 0;             // the final (gt, eq) pass counts again
+        if ((double)passed > 4.0 * k / 3.0) {       // too many: exact top-k of the whole segment instead
+          st->done = 0;
+        } else {
+          st->done = 1;                             // keep the sampled threshold: every element above it
+          st->ties = 0;
+        }
+      }
+    } else {
+      k2_epilogue(c, true);
+    }
+  }
 }
 
 // ------------------------------------------------------- K3 select + compact + residual + send
-// Every warp owns a contiguous 1024-element slice of the block's 8192-element sub-tile and keeps it
-// in registers (8 float4 per lane).  One block-level exchange of the per-warp counts gives every warp
-// its output base; inside a warp the order is recovered with ballots, and only for the (rare) float4
-// rows that contain a selected element.  One __syncthreads per sub-tile, no per-row scans.
-
+// One warp per table entry, rows without a selected element skipped via the row maxima.  The entry's first
+// output position comes from K2's prefix sums; inside the entry the single warp walks the rows in order and
+// ranks the selected elements of a row with ballots, so the pairs leave in ascending index order.
 template <bool TOPK, bool MINK>
 __global__ void __launch_bounds__(GK_THREADS) k_compact_send(GkChain c, GkDst d) {
-  __shared__ uint32_t s_wcnt[2][NWARP];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t seqn = c.ctrl->seq + 1u;  // every block reads it before the last block bumps it
   const uint64_t poff = (uint64_t)(seqn & 1u) * d.parity_stride;
   const uint32_t cap = c.cap;
   const uint32_t lt = (1u << lane) - 1u;
-  int par = 0;
-  for (int b = blockIdx.x; b < c.nblk; b += gridDim.x) {   // persistent over the table entries
-  const GkBlk B = c.blk[b];
-  const GkSegStat* st = c.stat + B.seg;
-  const float thr = st->thr;
-  const uint32_t tb = st->tbits, ties = st->ties;
-  const uint32_t seg_first = (uint32_t)c.seg[B.seg].blk_begin;
-  const uint2 off_b = *reinterpret_cast<const uint2*>(c.boff + 2 * (size_t)b);
-  const uint2 off_s = *reinterpret_cast<const uint2*>(c.boff + 2 * (size_t)seg_first);
-  const uint32_t base_gt = st->out_base + (off_b.x - off_s.x);
-  const uint32_t base_eq = TOPK ? (off_b.y - off_s.y) : 0u;
-  float* __restrict__ a = c.resid + B.start;
-  uint32_t run_gt = 0, run_eq = 0;  // selected before the current sub-tile, inside this entry
-  for (int t0 = 0; t0 < B.len; t0 += GK_SUB, par ^= 1) {
-    const int wbeg = t0 + warp * 1024;
-    float4 v[8];
-    uint32_t fg = 0, fe = 0;  // bit 4*i+j: element j of row i is gt / eq
-    if (wbeg + 1024 <= B.len) {  // warp-uniform fast path: the whole slice is in range
+  const int e = (int)blockIdx.x * NWARP + warp;
+  if (e < c.nblk) {
+    const GkBlk B = c.blk[e];
+    const GkSegStat* st = c.stat + B.seg;
+    const float thr = st->thr;
+    const uint32_t tb = st->tbits, ties = st->ties;
+    const uint32_t seg_first = (uint32_t)c.seg[B.seg].blk_begin;
+    const uint2 off_b = *reinterpret_cast<const uint2*>(c.boff + 2 * (size_t)e);
+    const uint2 off_s = *reinterpret_cast<const uint2*>(c.boff + 2 * (size_t)seg_first);
+    const uint32_t base_gt = st->out_base + (off_b.x - off_s.x);
+    uint32_t gb = 0;                                         // gt elements of this entry before the current row
+    uint32_t eb = TOPK ? (off_b.y - off_s.y) : 0u;           // eq elements of the segment before the current row
+    float* __restrict__ a = c.resid + B.start;
+    const uint32_t* __restrict__ rmx = (c.rowmax && !(TOPK && MINK)) ? c.rowmax + (size_t)e * c.rpb : nullptr;
+    const int gate = gate_of(thr);
+    const int nrow = (B.len + GK_ROW - 1) / GK_ROW;
+    for (int rb = 0; rb < nrow; rb += 32) {
+      const int row = rb + lane;
+      bool flag = row < nrow;
+      if (flag && rmx) flag = TOPK ? (ties ? rmx[row] >= tb : rmx[row] > tb) : ((int)rmx[row] > gate);
+      uint32_t m = __ballot_sync(0xffffffffu, flag);
+      while (m) {
+        int rr[4];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) v[i] = ld4(a + wbeg + (i * 32 + lane) * 4);
+        for (int u = 0; u < 4; ++u) { rr[u] = m ? rb + __ffs(m) - 1 : -1; m &= m - 1u; }
+        float4 v[4];
+        const float qn = __int_as_float(0x7fc00000);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float e[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+        for (int u = 0; u < 4; ++u) v[u] = (rr[u] >= 0) ? ld_row(a, rr[u], lane, B.len) : make_float4(qn, qn, qn, qn);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          if (TOPK) {
-            const uint32_t key = sel_key<MINK>(e[j]);
-            if (key > tb) fg |= 1u << (4 * i + j);
-            if (key == tb) fe |= 1u << (4 * i + j);
-          } else {
-            fg |= gt_mask(fabsf(e[j]), thr) & (1u << (4 * i + j));
-          }
-        }
-      }
-    } else {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int i0 = wbeg + (i * 32 + lane) * 4;
-        if (i0 + 3 < B.len) {
-          v[i] = ld4(a + i0);
-        } else {
-          v[i].x = (i0 < B.len) ? a[i0] : 0.f;
-          v[i].y = (i0 + 1 < B.len) ? a[i0 + 1] : 0.f;
-          v[i].z = (i0 + 2 < B.len) ? a[i0 + 2] : 0.f;
-          v[i].w = 0.f;
-        }
-        const float e[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const bool valid = (i0 + j) < B.len;
-          if (TOPK) {
-            const uint32_t key = sel_key<MINK>(e[j]);
-            if (valid && key > tb) fg |= 1u << (4 * i + j);
-            if (valid && key == tb) fe |= 1u << (4 * i + j);
-          } else {
-            if (valid && fabsf(e[j]) > thr) fg |= 1u << (4 * i + j);
-          }
-        }
-      }
-    }
-    const uint32_t wsum = warp_sum_u((uint32_t)__popc(fg) | ((uint32_t)__popc(fe) << 16));
-    if (lane == 0) s_wcnt[par][warp] = wsum;
-    __syncthreads();
-    uint32_t wbase = 0, total = 0;
-#pragma unroll
-    for (int w = 0; w < NWARP; ++w) {
-      const uint32_t x = s_wcnt[par][w];
-      if (w < warp) wbase += x;
-      total += x;
-    }
-    if (wsum != 0) {  // warp-uniform
-      uint32_t gb = run_gt + (wbase & 0xffffu);            // gt elements before the current row
-      uint32_t eb = base_eq + run_eq + (wbase >> 16);      // eq elements before the current row (segment-wide)
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const uint32_t fgi = (fg >> (4 * i)) & 15u, fei = (fe >> (4 * i)) & 15u;
-        if (__ballot_sync(0xffffffffu, (fgi | fei) != 0u) == 0u) continue;  // warp-uniform
-        uint32_t gbefore = gb, ebefore = eb, tg = 0, te = 0;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          // lanes hold 4 consecutive elements each: everything in lower lanes precedes this lane
-          const uint32_t bg = __ballot_sync(0xffffffffu, (fgi >> j) & 1u);
-          gbefore += __popc(bg & lt);
-          tg += __popc(bg);
-          if (TOPK) {
-            const uint32_t be = __ballot_sync(0xffffffffu, (fei >> j) & 1u);
-            ebefore += __popc(be & lt);
-            te += __popc(be);
-          }
-        }
-        if (fgi | fei) {
-          const int i0 = wbeg + (i * 32 + lane) * 4;
-          const float e[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+        for (int u = 0; u < 4; ++u) {
+          if (rr[u] < 0) continue;                           // warp-uniform
+          const int i0 = rr[u] * GK_ROW + lane * 4;
+          const int nv = B.len - i0;
+          const float ev[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+          uint32_t fgi = 0, fei = 0;                         // bit j: element j of this lane's quad is gt / eq
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const bool isg = (fgi >> j) & 1u, ise = (fei >> j) & 1u;
-            if (isg || (ise && ebefore < ties)) {
-              const uint32_t pos = base_gt + gbefore + (ebefore < ties ? ebefore : ties);
-              if (pos < cap) {
-                const uint32_t idx = (uint32_t)(B.start + i0 + j);
-                const uint64_t pair = (uint64_t)idx | ((uint64_t)__float_as_uint(e[j]) << 32);
-                for (int q = 0; q < d.ndst; ++q) d.slot[q][poff + GK_SLOT_HDR + pos] = pair;
-                a[i0 + j] = 0.f;  // sent => leaves the residual
-              }
+            if (TOPK) {
+              const uint32_t key = sel_key<MINK>(ev[j]);
+              if (j < nv && key > tb) fgi |= 1u << j;
+              if (j < nv && key == tb) fei |= 1u << j;
+            } else {
+              if (fabsf(ev[j]) > thr) fgi |= 1u << j;        // padding reads as NaN: never selected
             }
-            gbefore += isg ? 1u : 0u;
-            ebefore += ise ? 1u : 0u;
           }
+          if (__ballot_sync(0xffffffffu, (fgi | fei) != 0u) == 0u) continue;  // warp-uniform
+          uint32_t gbefore = gb, ebefore = eb, tg = 0, te = 0;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            // lanes hold 4 consecutive elements each: everything in lower lanes precedes this lane
+            const uint32_t bg = __ballot_sync(0xffffffffu, (fgi >> j) & 1u);
+            gbefore += __popc(bg & lt);
+            tg += __popc(bg);
+            if (TOPK) {
+              const uint32_t be = __ballot_sync(0xffffffffu, (fei >> j) & 1u);
+              ebefore += __popc(be & lt);
+              te += __popc(be);
+            }
+          }
+          if (fgi | fei) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const bool isg = (fgi >> j) & 1u, ise = (fei >> j) & 1u;
+              if (isg || (ise && ebefore < ties)) {
+                const uint32_t pos = base_gt + gbefore + (ebefore < ties ? ebefore : ties);
+                if (pos < cap) {
+                  const uint32_t idx = (uint32_t)(B.start + i0 + j);
+                  const uint64_t pair = (uint64_t)idx | ((uint64_t)__float_as_uint(ev[j]) << 32);
+                  for (int q = 0; q < d.ndst; ++q) d.slot[q][poff + GK_SLOT_HDR + pos] = pair;
+                  a[i0 + j] = 0.f;  // sent => leaves the residual
+                }
+              }
+              gbefore += isg ? 1u : 0u;
+              ebefore += ise ? 1u : 0u;
+            }
+          }
+          gb += tg;
+          eb += te;
         }
-        gb += tg;
-        eb += te;
       }
     }
-    run_gt += total & 0xffffu;
-    run_eq += total >> 16;
   }
-  }  // entries
   // Every block: bar.sync + one gpu-scope fence by thread 0 + ticket.  The last block then issues ONE
   // system-scope fence before the release store of the header: fences are cumulative, so the pairs the
   // other blocks stored to peer memory (ordered before their tickets at gpu scope) are ordered before
@@ -926,9 +1050,9 @@ __global__ void __launch_bounds__(GK_THREADS) k_scatter(GkSrc s, GkCtrl* ctrl, f
       const uint64_t p = __ldcg(pairs + j);
       const uint32_t idx = (uint32_t)p;
       if (idx < (uint32_t)nelem) {
-        const float v = __uint_as_float((uint32_t)(p >> 32)) * scale;
+        const float v = __fmul_rn(__uint_as_float((uint32_t)(p >> 32)), scale);   // never fused with the add
         if (UNSCATTER) grad[idx] = 0.f;
-        else if (ORDERED) grad[idx] += v;
+        else if (ORDERED) grad[idx] = __fadd_rn(grad[idx], v);
         else atomicAdd(grad + idx, v);
       }
     }
@@ -936,6 +1060,19 @@ __global__ void __launch_bounds__(GK_THREADS) k_scatter(GkSrc s, GkCtrl* ctrl, f
 }
 
 // ------------------------------------------------------------------------- K6 fused SGD
+// torch.optim.SGD arithmetic for one element (FMA placement included); shared by the materialising kernel
+// (gradient read from the arena) and the folded one (gradient == 0 in the dense pass).
+__device__ __forceinline__ float sgd_upd(const GkHyper& h, bool has_m, float gs, float pv, float gv, float& mv) {
+  if (gs != 1.f) gv = __fmul_rn(gv, gs);
+  if (h.weight_decay != 0.f) gv = __fmaf_rn(h.weight_decay, pv, gv);
+  float u = gv;
+  if (has_m) {
+    mv = h.first_step ? gv : __fmaf_rn(1.f - h.dampening, gv, __fmul_rn(h.momentum, mv));
+    u = h.nesterov ? __fmaf_rn(h.momentum, mv, gv) : mv;
+  }
+  return __fmaf_rn(-h.lr, u, pv);
+}
+
 __global__ void __launch_bounds__(GK_THREADS) k_sgd(float* __restrict__ p, const float* __restrict__ g,
                                                      float* __restrict__ m, const GkBlk* __restrict__ blk,
                                                      const GkHyper* __restrict__ hy,
@@ -944,17 +1081,7 @@ __global__ void __launch_bounds__(GK_THREADS) k_sgd(float* __restrict__ p, const
   const GkHyper h = hy[B.seg];
   const float gs = gscale ? *gscale : 1.f;
   const bool has_m = (h.momentum != 0.f) && (m != nullptr);
-  const float nlr = -h.lr, omd = 1.f - h.dampening;
-  auto upd = [&](float pv, float gv, float& mv) -> float {
-    if (gs != 1.f) gv = __fmul_rn(gv, gs);
-    if (h.weight_decay != 0.f) gv = __fmaf_rn(h.weight_decay, pv, gv);
-    float u = gv;
-    if (has_m) {
-      mv = h.first_step ? gv : __fmaf_rn(omd, gv, __fmul_rn(h.momentum, mv));
-      u = h.nesterov ? __fmaf_rn(h.momentum, mv, gv) : mv;
-    }
-    return __fmaf_rn(nlr, u, pv);
-  };
+  auto upd = [&](float pv, float gv, float& mv) -> float { return sgd_upd(h, has_m, gs, pv, gv, mv); };
   float* pp = p + B.start; const float* gg = g + B.start; float* mm = has_m ? m + B.start : nullptr;
   const int n4 = B.len >> 2;
 #pragma unroll 2
@@ -971,6 +1098,154 @@ __global__ void __launch_bounds__(GK_THREADS) k_sgd(float* __restrict__ p, const
     float mv = has_m ? mm[i] : 0.f;
     pp[i] = upd(pp[i], gg[i], mv);
     if (has_m) mm[i] = mv;
+  }
+}
+
+// ------------------------------------------------- K6 folded: receive + momentum-SGD, no dense gradient
+// The reference zeroes the group buffer, scatter-adds P lists, divides, and then runs SGD over dense
+// tensors (distributed_optimizer.py:468-482, :543-546).  Only <= P*k coordinates of that gradient are
+// non-zero, so the update splits into
+//   phase A  the dense part with g == 0:  m = mu*m + (1-d)*wd*p ;  p -= lr*m     (16 B/element, and —
+//            the point — independent of the peers: it runs while their pairs are still in flight);
+//   wait     bounded acquire-spin on the P slot headers;
+//   pass 1   every pair ORs its source rank into mask[idx] (the gradient arena, all zero by invariant);
+//   barrier  grid-wide (cooperative launch);
+//   pass 2   the pair of the LOWEST rank that holds a coordinate owns it: it sums the contributions in
+//            rank order (binary search in the other ranks' index-sorted lists), applies the correction
+//            m += (1-d)*g ; p -= lr*(1-d)*g (Nesterov / first step / no momentum accordingly) and clears
+//            mask[idx] — so the arena is all zero again and zero_grad() has nothing to do.
+// Every replica forms the same sums in the same order => bit-identical parameters on all ranks.  The
+// result differs from the materialising path (k_scatter + k_sgd) only by the rounding of the split FMA
+// on the <= P*k touched coordinates.
+struct GkRecvUpdDev {
+  float* p; float* m; uint32_t* mask; const GkBlk* blk; const GkHyper* hy; const uint8_t* gmap;
+  GkCtrl* ctrl; uint32_t* bar; float scale; int nblk; int nelem; int skip_dense;
+};
+
+// Grid-wide barrier for a cooperative launch: bar[0] = arrival count, bar[1] = generation.  `gen` is the
+// generation read by thread 0 before the block's first arrival.  Bounded like every wait of this library.
+__device__ __forceinline__ void gk_grid_barrier(uint32_t* bar, uint32_t gen, uint32_t* err) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(bar, 1u) == gridDim.x - 1u) {
+      bar[0] = 0;
+      st_release_gpu_u32(bar + 1, gen + 1u);
+    } else {
+      const uint64_t t0 = globaltimer_ns();
+      while (ld_relaxed_gpu_u32(bar + 1) == gen) {
+        if (globaltimer_ns() - t0 > 2000000000ull) { atomicExch(err, 3u); break; }
+      }
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(GK_THREADS) k_sgd_recv(GkRecvUpdDev u, GkSrc s) {
+  __shared__ uint32_t scnt[GK_MAXP];
+  __shared__ uint32_t s_gen;
+  __shared__ int s_bad;
+  const int tid = threadIdx.x;
+  if (tid == 0) { s_gen = ld_relaxed_gpu_u32(u.bar + 1); s_bad = 0; }
+  // ---- phase A: dense update with a zero gradient (same arithmetic as k_sgd given g == 0)
+  if (!u.skip_dense) {
+    for (int e = blockIdx.x; e < u.nblk; e += gridDim.x) {
+      const GkBlk B = u.blk[e];
+      const GkHyper h = u.hy[B.seg];
+      const bool has_m = (h.momentum != 0.f) && (u.m != nullptr);
+      if (!has_m && h.weight_decay == 0.f) continue;     // p -= lr*0: nothing to do for this entry
+      float* pp = u.p + B.start; float* mm = has_m ? u.m + B.start : nullptr;
+      const int n4 = B.len >> 2;
+#pragma unroll 4
+      for (int i = tid; i < n4; i += T) {
+        float4 pv = ld4(pp + 4 * i);
+        float4 mv = has_m ? ld4(mm + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        pv.x = sgd_upd(h, has_m, 1.f, pv.x, 0.f, mv.x); pv.y = sgd_upd(h, has_m, 1.f, pv.y, 0.f, mv.y);
+        pv.z = sgd_upd(h, has_m, 1.f, pv.z, 0.f, mv.z); pv.w = sgd_upd(h, has_m, 1.f, pv.w, 0.f, mv.w);
+        st4(pp + 4 * i, pv);
+        if (has_m) st4(mm + 4 * i, mv);
+      }
+      for (int i = 4 * n4 + tid; i < B.len; i += T) {
+        float mv = has_m ? mm[i] : 0.f;
+        pp[i] = sgd_upd(h, has_m, 1.f, pp[i], 0.f, mv);
+        if (has_m) mm[i] = mv;
+      }
+    }
+  }
+  // ---- wait for the peers' headers (their pairs were stored before the release of the header)
+  const uint32_t seq = u.ctrl->seq;
+  const uint64_t* base = s.arena + (uint64_t)(seq & 1u) * s.parity_stride;
+  const uint32_t cap = (uint32_t)(s.slot_stride - GK_SLOT_HDR);
+  __syncthreads();
+  if (tid < s.nsrc) {
+    const uint64_t* hp = base + (uint64_t)tid * s.slot_stride;
+    uint64_t v = ld_acquire_sys_u64(hp);
+    if (s.wait) {
+      const uint64_t t0 = globaltimer_ns();
+      while ((uint32_t)(v >> 32) != seq) {
+        if (globaltimer_ns() - t0 > s.timeout_ns) { s_bad = 1; break; }
+        __nanosleep(100);
+        v = ld_acquire_sys_u64(hp);
+      }
+    }
+    const uint32_t n = (uint32_t)v;
+    scnt[tid] = n < cap ? n : cap;
+  }
+  __syncthreads();
+  const bool bad = s_bad != 0;
+  if (bad && tid == 0) atomicExch(&u.ctrl->err, 1u);
+  const uint32_t gstride = gridDim.x * T, g0 = blockIdx.x * T + tid;
+  // ---- pass 1: which ranks hold which coordinate
+  if (!bad) {
+    for (int r = 0; r < s.nsrc; ++r) {
+      const uint64_t* pairs = base + (uint64_t)r * s.slot_stride + GK_SLOT_HDR;
+      const uint32_t n = scnt[r];
+      for (uint32_t j = g0; j < n; j += gstride) {
+        const uint32_t idx = (uint32_t)__ldcg(pairs + j);
+        if (idx < (uint32_t)u.nelem) atomicOr(u.mask + idx, 1u << r);
+      }
+    }
+  }
+  gk_grid_barrier(u.bar, s_gen, &u.ctrl->err);
+  if (bad) return;
+  // ---- pass 2: the lowest rank's pair owns the coordinate
+  for (int r = 0; r < s.nsrc; ++r) {
+    const uint64_t* pairs = base + (uint64_t)r * s.slot_stride + GK_SLOT_HDR;
+    const uint32_t n = scnt[r];
+    for (uint32_t j = g0; j < n; j += gstride) {
+      const uint64_t pr = __ldcg(pairs + j);
+      const uint32_t idx = (uint32_t)pr;
+      if (idx >= (uint32_t)u.nelem) continue;
+      uint32_t w = __ldcg(u.mask + idx);
+      if (w == 0u || (int)(__ffs(w) - 1) != r) continue;
+      float g = __fadd_rn(0.f, __fmul_rn(__uint_as_float((uint32_t)(pr >> 32)), u.scale));
+      w &= w - 1u;
+      while (w) {                                  // contributions of higher ranks, ascending
+        const int q = __ffs(w) - 1;
+        w &= w - 1u;
+        const uint64_t* pq = base + (uint64_t)q * s.slot_stride + GK_SLOT_HDR;
+        uint32_t lo = 0, hi = scnt[q];
+        while (lo < hi) {
+          const uint32_t mid = (lo + hi) >> 1;
+          if ((uint32_t)__ldcg(pq + mid) < idx) lo = mid + 1; else hi = mid;
+        }
+        const uint64_t hit = (lo < scnt[q]) ? __ldcg(pq + lo) : ~0ull;
+        if ((uint32_t)hit != idx) { atomicExch(&u.ctrl->err, 2u); continue; }   // list not index-sorted
+        g = __fadd_rn(g, __fmul_rn(__uint_as_float((uint32_t)(hit >> 32)), u.scale));
+      }
+      // p and m of this coordinate were written in phase A, possibly by another block: read them at L2
+      const GkHyper h = u.hy[u.gmap ? u.gmap[idx >> 6] : 0];
+      const bool has_m = (h.momentum != 0.f) && (u.m != nullptr);
+      float du = g;
+      if (has_m) {
+        const float dm = h.first_step ? g : __fmul_rn(1.f - h.dampening, g);
+        u.m[idx] = __fadd_rn(__ldcg(u.m + idx), dm);
+        du = h.nesterov ? __fmaf_rn(h.momentum, dm, g) : dm;
+      }
+      u.p[idx] = __fmaf_rn(-h.lr, du, __ldcg(u.p + idx));
+      u.mask[idx] = 0u;
+    }
   }
 }
 
@@ -1151,6 +1426,68 @@ __global__ void __launch_bounds__(GK_THREADS) k_randomk(GkChain c, GkDst d, uint
   }
 }
 
+// ------------------------------------------------------------------- K9 DGC sampling threshold
+// compression.py:576-606: draw int(0.01*n) coordinates, take the k-th largest |acc| among them as the
+// threshold, select everything above it; if more than 4k/3 pass, fall back to the exact top-k.  The sample
+// is drawn with the keyed bijection of the random-k kernel (distinct coordinates, no n-element permutation);
+// its k-th largest is found with the same 11+11+9-bit radix select as the exact top-k, on the sample only.
+// With fewer than k sampled coordinates (density > 0.01, where the reference's torch.topk raises) the
+// threshold is 0 and the exact top-k takes over.
+__device__ __forceinline__ int dgc_sample_size(int n) { return (int)((double)n * 0.01); }
+
+template <int PASS>
+__global__ void __launch_bounds__(GK_THREADS) k_dgc_pass(GkChain c, uint64_t seed) {
+  constexpr int NB = (PASS == 3) ? 512 : 2048;
+  constexpr int SHIFT_MATCH = (PASS == 2) ? 20 : 9;        // PASS 1 matches everything
+  constexpr int SHIFT_DIGIT = (PASS == 1) ? 20 : (PASS == 2 ? 9 : 0);
+  __shared__ uint32_t shist[NB];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t seqn = c.ctrl->seq + 1u;
+  for (int s = 0; s < c.nseg; ++s) {                       // block-uniform
+    const GkSeg sg = c.seg[s];
+    const int fk = dgc_sample_size(sg.n);
+    if (fk < sg.k || fk < 1) continue;
+    for (int i = tid; i < NB; i += T) shist[i] = 0;
+    __syncthreads();
+    const uint32_t prefix = (PASS == 1) ? 0u : c.stat[s].sprefix;
+    const uint64_t sd = seed + 0x632be59bd9b4e019ull * (uint64_t)(s + 1) + 0x9e3779b97f4a7c15ull * (uint64_t)seqn;
+    for (uint32_t j = blockIdx.x * T + tid; j < (uint32_t)fk; j += gridDim.x * T) {
+      const uint32_t li = feistel_perm(j, (uint32_t)sg.n, sd);
+      int lo = sg.blk_begin, hi = sg.blk_end - 1;          // segment-local index -> arena index
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if ((uint32_t)c.blk[mid].soff <= li) lo = mid; else hi = mid - 1;
+      }
+      const GkBlk B = c.blk[lo];
+      const uint32_t key = absbits(c.resid[(uint32_t)B.start + (li - (uint32_t)B.soff)]);
+      if (PASS == 1 || (key >> SHIFT_MATCH) == prefix) atomicAdd(&shist[(key >> SHIFT_DIGIT) & (NB - 1)], 1u);
+    }
+    __syncthreads();
+    uint32_t* h = c.hist + (size_t)s * GK_HIST_BINS;
+    for (int i = tid; i < NB; i += T) {
+      const uint32_t v = shist[i];
+      if (v) atomicAdd(h + i, v);
+    }
+    __syncthreads();
+  }
+  if (last_block_done(&c.ctrl->done[1])) {
+    for (int s = warp; s < c.nseg; s += NWARP) {
+      GkSegStat* st = c.stat + s;
+      const GkSeg sg = c.seg[s];
+      const int fk = dgc_sample_size(sg.n);
+      if (fk < sg.k || fk < 1) {
+        if (lane == 0) { st->tbits = 0; st->ties = 0; }
+        continue;
+      }
+      if (PASS == 1 && lane == 0) { st->sprefix = 0; st->skrem = (uint32_t)sg.k; }
+      __syncwarp();
+      radix_pick_warp_at(c.hist + (size_t)s * GK_HIST_BINS, &st->sprefix, &st->skrem, NB, lane);
+      __syncwarp();
+      if (PASS == 3 && lane == 0) { st->tbits = st->sprefix; st->ties = 0; }
+    }
+  }
+}
+
 // ------------------------------------------------------------------- K10 bucket compressor
 __global__ void __launch_bounds__(GK_THREADS) k_bucket_means(GkChain c, float* means) {
   __shared__ double sred[4][NWARP];
@@ -1298,13 +1635,24 @@ static int gk_persistent_grid(K kernel, int* cache, int nblk) {
   } while (0)
 #define GK_RET() return (int)cudaGetLastError()
 
+static int gk_sm_count() {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0, n = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    sms = n > 0 ? n : 148;
+  }
+  return sms;
+}
+
 extern "C" {
 
 const char* gk_version(void) { return "gk_b200 cuda sm_100a 0.1"; }
 
 int gk_accumulate(const GkChain* c, void* stream) {
   if (c->nblk <= 0) return 0;
-  if (c->mode == GK_MODE_TOPK) GK_LAUNCH_PERSISTENT((k_accumulate<true, false>), c->nblk, stream, *c);
+  if (c->rowmax != nullptr && (c->rpb <= 0 || c->rpb > 4096)) return (int)cudaErrorInvalidValue;
+  if (c->mode == GK_MODE_TOPK || c->mode == GK_MODE_DGC) GK_LAUNCH_PERSISTENT((k_accumulate<true, false>), c->nblk, stream, *c);
   else if (c->mode == GK_MODE_MINK) GK_LAUNCH_PERSISTENT((k_accumulate<true, true>), c->nblk, stream, *c);
   else GK_LAUNCH_PERSISTENT((k_accumulate<false, false>), c->nblk, stream, *c);
   GK_RET();
@@ -1312,45 +1660,71 @@ int gk_accumulate(const GkChain* c, void* stream) {
 
 int gk_count_pick(const GkChain* c, void* stream) {
   if (c->nblk <= 0) return 0;
-  int nc = 1;
-  if (c->mode == GK_MODE_GAUSSIAN) nc = c->nloops * (c->nloops + 1) / 2;
-  else if (c->mode == GK_MODE_REDSYNC) nc = 7;
-  else if (c->mode == GK_MODE_REDSYNCTRIM) nc = GK_NC;
-  if (nc <= 1) GK_LAUNCH_PERSISTENT(k_count<1>, c->nblk, stream, *c);
-  else if (nc <= 6) GK_LAUNCH_PERSISTENT(k_count<6>, c->nblk, stream, *c);
-  else if (nc <= 7) GK_LAUNCH_PERSISTENT(k_count<7>, c->nblk, stream, *c);
-  else GK_LAUNCH_PERSISTENT(k_count<GK_NC>, c->nblk, stream, *c);
-  GK_RET();
+  // the blocks meet at a grid barrier between counting rounds: one resident wave, cooperative launch
+  static int cache = 0;
+  const int noct = (c->nblk + NWARP - 1) / NWARP;
+  const int grid = gk_persistent_grid(k_count_rounds, &cache, noct);
+  GkChain cc = *c;
+  void* args[] = {&cc};
+  const cudaError_t e = cudaLaunchCooperativeKernel((const void*)k_count_rounds, dim3(grid), dim3(T), args, 0, S(stream));
+  if (e != cudaSuccess) (void)cudaGetLastError();
+  return (int)e;
 }
 
 int gk_topk_select(const GkChain* c, void* stream) {
   if (c->nblk <= 0) return 0;
+  const int noct = (c->nblk + NWARP - 1) / NWARP;
   if (c->mode == GK_MODE_MINK) {
     k_radix_pass<2, true><<<c->nblk, T, 0, S(stream)>>>(*c);
     k_radix_pass<3, true><<<c->nblk, T, 0, S(stream)>>>(*c);
-    GK_LAUNCH_PERSISTENT(k_count_topk<true>, c->nblk, stream, *c);
+    k_count_topk<true, false><<<noct, T, 0, S(stream)>>>(*c);
   } else {
     k_radix_pass<2, false><<<c->nblk, T, 0, S(stream)>>>(*c);
     k_radix_pass<3, false><<<c->nblk, T, 0, S(stream)>>>(*c);
-    GK_LAUNCH_PERSISTENT(k_count_topk<false>, c->nblk, stream, *c);
+    k_count_topk<false, false><<<noct, T, 0, S(stream)>>>(*c);
   }
+  GK_RET();
+}
+
+int gk_dgc_select(const GkChain* c, uint64_t seed, void* stream) {
+  if (c->nblk <= 0) return 0;
+  if (c->mode != GK_MODE_DGC) return (int)cudaErrorInvalidValue;
+  const int noct = (c->nblk + NWARP - 1) / NWARP;
+  const int grid = 4 * gk_sm_count();
+  k_dgc_pass<1><<<grid, T, 0, S(stream)>>>(*c, seed);
+  k_dgc_pass<2><<<grid, T, 0, S(stream)>>>(*c, seed);
+  k_dgc_pass<3><<<grid, T, 0, S(stream)>>>(*c, seed);
+  k_count_topk<false, true><<<noct, T, 0, S(stream)>>>(*c);      // accept the sampled threshold or not
+  k_radix_pass<2, false><<<c->nblk, T, 0, S(stream)>>>(*c);        // no-ops for the segments that accepted it
+  k_radix_pass<3, false><<<c->nblk, T, 0, S(stream)>>>(*c);
+  k_count_topk<false, false><<<noct, T, 0, S(stream)>>>(*c);
   GK_RET();
 }
 
 int gk_compact_send(const GkChain* c, const GkDst* dst, void* stream) {
   if (c->nblk <= 0) return 0;
   if (dst->ndst < 1 || dst->ndst > GK_MAXP) return (int)cudaErrorInvalidValue;
-  if (c->mode == GK_MODE_TOPK) GK_LAUNCH_PERSISTENT((k_compact_send<true, false>), c->nblk, stream, *c, *dst);
-  else if (c->mode == GK_MODE_MINK) GK_LAUNCH_PERSISTENT((k_compact_send<true, true>), c->nblk, stream, *c, *dst);
-  else GK_LAUNCH_PERSISTENT((k_compact_send<false, false>), c->nblk, stream, *c, *dst);
+  const int noct = (c->nblk + NWARP - 1) / NWARP;
+  if (c->mode == GK_MODE_TOPK || c->mode == GK_MODE_DGC) k_compact_send<true, false><<<noct, T, 0, S(stream)>>>(*c, *dst);
+  else if (c->mode == GK_MODE_MINK) k_compact_send<true, true><<<noct, T, 0, S(stream)>>>(*c, *dst);
+  else k_compact_send<false, false><<<noct, T, 0, S(stream)>>>(*c, *dst);
   GK_RET();
 }
 
 int gk_compress(const GkChain* c, const GkDst* dst, void* stream) {
+  if (c->mode == GK_MODE_DGC) return (int)cudaErrorInvalidValue;   // needs a seed: gk_dgc_compress
   int e = gk_accumulate(c, stream);
   if (e) return e;
   if (c->mode == GK_MODE_TOPK || c->mode == GK_MODE_MINK) e = gk_topk_select(c, stream);
   else e = gk_count_pick(c, stream);
+  if (e) return e;
+  return gk_compact_send(c, dst, stream);
+}
+
+int gk_dgc_compress(const GkChain* c, const GkDst* dst, uint64_t seed, void* stream) {
+  int e = gk_accumulate(c, stream);
+  if (e) return e;
+  e = gk_dgc_select(c, seed, stream);
   if (e) return e;
   return gk_compact_send(c, dst, stream);
 }
@@ -1388,6 +1762,21 @@ int gk_sgd(float* param, const float* grad, float* mom, const GkBlk* blk, int32_
   if (nblk <= 0) return 0;
   k_sgd<<<nblk, T, 0, S(stream)>>>(param, grad, mom, blk, hyper, grad_scale);
   GK_RET();
+}
+
+int gk_sgd_recv(const GkRecvUpd* u, const GkSrc* src, void* stream) {
+  if (u->nblk <= 0) return 0;
+  if (src->nsrc < 1 || src->nsrc > GK_MAXP) return (int)cudaErrorInvalidValue;
+  // one resident wave: the blocks wait on one another at the grid barrier, so the launch is cooperative
+  static int cache = 0;
+  const int grid = gk_persistent_grid(k_sgd_recv, &cache, u->nblk);
+  GkRecvUpdDev d{u->param, u->mom, u->mask, u->blk, u->hyper, u->gmap, u->ctrl, u->bar, u->scale,
+                 u->nblk, u->nelem, u->skip_dense};
+  GkSrc s = *src;
+  void* args[] = {&d, &s};
+  const cudaError_t e = cudaLaunchCooperativeKernel((const void*)k_sgd_recv, dim3(grid), dim3(T), args, 0, S(stream));
+  if (e != cudaSuccess) (void)cudaGetLastError();
+  return (int)e;
 }
 
 int gk_lars(float* param, const float* grad, float* mom, const GkBlk* blk, int32_t nblk, const GkSeg* tens,
@@ -1431,7 +1820,7 @@ int gk_scale(float* grad, const GkBlk* blk, int32_t nblk, const float* scale, vo
 
 int gk_randomk_send(const GkChain* c, const GkDst* dst, uint64_t seed, void* stream) {
   if (dst->ndst < 1 || dst->ndst > GK_MAXP) return (int)cudaErrorInvalidValue;
-  k_randomk<<<148, T, 0, S(stream)>>>(*c, *dst, seed);
+  k_randomk<<<gk_sm_count(), T, 0, S(stream)>>>(*c, *dst, seed);
   GK_RET();
 }
 
@@ -1490,3 +1879,4 @@ int gk_ipc_close(void* ptr) { return (int)cudaIpcCloseMemHandle(ptr); }
 int gk_ipc_free(void* ptr) { return (int)cudaFree(ptr); }
 
 }  // extern "C"
+

@@ -24,14 +24,15 @@ SEG_DTYPE = np.dtype([("n", "<i4"), ("k", "<i4"), ("blk_begin", "<i4"), ("blk_en
 STAT_DTYPE = np.dtype([("mean", "<f4"), ("std", "<f4"), ("meanabs", "<f4"), ("maxabs", "<f4"),
                        ("cand", "<f4", (N.GK_NC,)), ("thr", "<f4"), ("tbits", "<u4"), ("ties", "<u4"),
                        ("chosen", "<i4"), ("count", "<u4"), ("out_base", "<u4"), ("prefix", "<u4"),
-                       ("krem", "<u4"), ("order", "u1", (N.GK_NC,)), ("nlow", "<i4"),
-                       ("tot", "<u4", (N.GK_NC,))])
+                       ("krem", "<u4"), ("rcand", "u1", (N.GK_NC,)), ("nrc", "<i4"),
+                       ("tot", "<u4", (N.GK_NC,)), ("known", "<u4"), ("gate", "<i4"), ("done", "<i4"),
+                       ("sprefix", "<u4"), ("skrem", "<u4")])
 CTRL_DTYPE = np.dtype([("done", "<u4", (8,)), ("total", "<u4"), ("sent", "<u4"), ("seq", "<u4"),
                        ("err", "<u4"), ("overflow", "<u4"), ("rsv", "<u4", (3,)), ("sent_total", "<u8"),
                        ("ring", "<u4", (64,))])
 HYPER_DTYPE = np.dtype([("lr", "<f4"), ("momentum", "<f4"), ("dampening", "<f4"), ("weight_decay", "<f4"),
                         ("nesterov", "<i4"), ("first_step", "<i4"), ("lars_eeta", "<f4"), ("lars_eps", "<f4")])
-assert SEG_DTYPE.itemsize == 32 and STAT_DTYPE.itemsize == 196 and CTRL_DTYPE.itemsize == 328
+assert SEG_DTYPE.itemsize == 32 and STAT_DTYPE.itemsize == 216 and CTRL_DTYPE.itemsize == 328
 assert HYPER_DTYPE.itemsize == 32
 
 DEFAULT_CHUNK = 8192
@@ -44,8 +45,9 @@ MODES = {
     "gaussian": (N.MODE_GAUSSIAN, 3), "gaussiank": (N.MODE_GAUSSIAN, 3), "gaussian2": (N.MODE_GAUSSIAN, 5),
     "topk": (N.MODE_TOPK, 0), "topk2": (N.MODE_TOPK, 0), "mink": (N.MODE_MINK, 0),
     "redsync": (N.MODE_REDSYNC, 0), "redsynctrim": (N.MODE_REDSYNCTRIM, 0),
-    "threshold": (N.MODE_THRESHOLD, 0), "dgcsampling": (N.MODE_TOPK, 0),
+    "threshold": (N.MODE_THRESHOLD, 0), "dgcsampling": (N.MODE_DGC, 0),
 }
+ROW = 128   # elements per row of the row-maximum table (csrc/gk_cuda.cu: GK_ROW)
 
 
 def compute_k(n: int, density: float) -> int:
@@ -65,7 +67,7 @@ def build_tables(segments: Sequence[Sequence[Tuple[int, int]]], chunk: int = DEF
     """segments[s] = [(arena_start, numel), ...] extents (tensors) of selection segment s.
     Returns (blk int32[nblk,4], seg structured[nseg]).  Every block is a contiguous extent of at most
     ``chunk`` elements starting on a multiple of 4 (tensors start on aligned arena offsets)."""
-    assert chunk % 4 == 0 and chunk > 0
+    assert chunk % ROW == 0 and chunk > 0
     blks: List[Tuple[int, int, int, int]] = []
     segs = np.zeros(len(segments), dtype=SEG_DTYPE)
     for s, extents in enumerate(segments):
@@ -176,7 +178,11 @@ class CompressChain:
         self.stat = torch.zeros(self.nseg * STAT_DTYPE.itemsize, dtype=torch.uint8, device=dev)
         self.bcnt = torch.zeros(max(self.nblk, 1) * N.GK_NC, dtype=torch.int32, device=dev)
         self.boff = torch.zeros(max(self.nblk, 1) * 2, dtype=torch.int32, device=dev)
-        need_hist = self.mode in (N.MODE_TOPK, N.MODE_MINK)
+        # largest |acc| bit pattern of every 128-element row of every table entry (written by K1, read by the
+        # later passes to skip rows that cannot hold a selected element)
+        self.rpb = (chunk + ROW - 1) // ROW
+        self.rowmax = torch.zeros(max(self.nblk, 1) * self.rpb, dtype=torch.int32, device=dev)
+        need_hist = self.mode in (N.MODE_TOPK, N.MODE_MINK, N.MODE_DGC)
         self.hist = torch.zeros(self.nseg * N.GK_HIST_BINS if need_hist else 1, dtype=torch.int32, device=dev)
         self.ctrl = torch.zeros(CTRL_DTYPE.itemsize, dtype=torch.uint8, device=dev)
         self._seg_pinned = None
@@ -279,11 +285,22 @@ class CompressChain:
         return N.GkChain(self.grad.data_ptr(), self.resid.data_ptr(), self.blk.data_ptr(), self.seg.data_ptr(),
                          self.part.data_ptr(), self.stat.data_ptr(), self.bcnt.data_ptr(), self.boff.data_ptr(),
                          self.hist.data_ptr(), self.ctrl.data_ptr(), self.nblk, self.nseg, self.mode,
-                         self.nloops, 1 if self.use_residual else 0, 1 if self.zero_grad else 0, self.cap, 0)
+                         self.nloops, 1 if self.use_residual else 0, 1 if self.zero_grad else 0, self.cap, 0,
+                         None, self.rowmax.data_ptr() if self.is_cuda else None, self.rpb, 0)
 
     # ------------------------------------------------------------------------ launches
-    def compress(self, dst: N.GkDst) -> None:
-        """Enqueue the whole send-side chain on the current stream (no host sync)."""
+    def compress(self, dst: N.GkDst, seed: int = 0) -> None:
+        """Enqueue the whole send-side chain on the current stream (no host sync).  ``seed`` keys the
+        coordinate sample of the DGC mode (compression.py:588-591 draws a fresh permutation every call)."""
+        if self.mode == N.MODE_DGC:
+            LAUNCHES["n"] += 9
+            if self.is_cuda:
+                N.check(self._lib.gk_dgc_compress(C.byref(self._desc), C.byref(dst), C.c_uint64(seed),
+                                                  _stream_ptr(self.device)), "gk_dgc_compress")
+            else:
+                N.check(self._lib.gkcpu_dgc_compress(C.byref(self._desc), C.byref(dst), C.c_uint64(seed)),
+                        "gkcpu_dgc_compress")
+            return
         LAUNCHES["n"] += 5 if self.mode in (N.MODE_TOPK, N.MODE_MINK) else 3
         if self.is_cuda:
             N.check(self._lib.gk_compress(C.byref(self._desc), C.byref(dst), _stream_ptr(self.device)),
@@ -410,6 +427,16 @@ class FlatTables:
         self.norm_out = torch.ones(2, dtype=torch.float32, device=device)
         self.ctrl = torch.zeros(CTRL_DTYPE.itemsize, dtype=torch.uint8, device=device)
         self.device = torch.device(device)
+        # folded receive+update (gk_sgd_recv): param group of every 64-element granule of the arena (tensors
+        # start on 64-element boundaries, parallel/arena.py) and the grid-barrier words
+        total = max((s + n + 63) // 64 for s, n in extents) if len(extents) else 1
+        gmap = np.zeros(total, dtype=np.uint8)
+        self.foldable = max(group_of, default=0) < 256 and all(s % 64 == 0 for s, _ in extents)
+        if self.foldable:
+            for (s, n), g in zip(extents, group_of):
+                gmap[s // 64:(s + n + 63) // 64] = g
+        self.gmap = torch.from_numpy(gmap).to(device)
+        self.bar = torch.zeros(4, dtype=torch.int32, device=device)
 
 
 def sgd_step(param: torch.Tensor, grad: torch.Tensor, mom: Optional[torch.Tensor], tables: FlatTables,
@@ -423,6 +450,24 @@ def sgd_step(param: torch.Tensor, grad: torch.Tensor, mom: Optional[torch.Tensor
     else:
         N.check(N.cpu_lib().gkcpu_sgd(param.data_ptr(), grad.data_ptr(), _ptr(mom), tables.group_blk_t.data_ptr(),
                                       tables.nblk, hyper.data_ptr(), _ptr(grad_scale)), "gkcpu_sgd")
+
+
+def sgd_recv_step(param: torch.Tensor, mask: torch.Tensor, mom: Optional[torch.Tensor], tables: FlatTables,
+                  hyper: torch.Tensor, src: N.GkSrc, ctrl: torch.Tensor, scale: float,
+                  skip_dense: bool = False) -> None:
+    """Folded receive + momentum-SGD (include/gk_b200.h: gk_sgd_recv): the dense weight-decay / momentum pass
+    runs while the peers' pairs are in flight, then the received pairs are folded in per coordinate in rank
+    order; no dense gradient is formed.  ``mask`` is the all-zero gradient arena (scratch, zero again
+    afterwards).  Replaces distributed_optimizer.py:461-482 + :543-546 for the common path."""
+    assert tables.foldable
+    LAUNCHES["n"] += 1
+    u = N.GkRecvUpd(param.data_ptr(), _ptr(mom), mask.data_ptr(), tables.group_blk_t.data_ptr(),
+                    hyper.data_ptr(), tables.gmap.data_ptr(), ctrl.data_ptr(), tables.bar.data_ptr(),
+                    float(scale), tables.nblk, mask.numel(), 1 if skip_dense else 0)
+    if param.device.type == "cuda":
+        N.check(N.cuda_lib().gk_sgd_recv(C.byref(u), C.byref(src), _stream_ptr(param.device)), "gk_sgd_recv")
+    else:
+        N.check(N.cpu_lib().gkcpu_sgd_recv(C.byref(u), C.byref(src)), "gkcpu_sgd_recv")
 
 
 def lars_step(param: torch.Tensor, grad: torch.Tensor, acc: torch.Tensor, tables: FlatTables,

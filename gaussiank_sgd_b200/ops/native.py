@@ -28,7 +28,7 @@ GK_HIST_BINS = 2048
 GK_THREADS = 256
 GK_SLOT_HDR = 2
 
-MODE_GAUSSIAN, MODE_TOPK, MODE_REDSYNC, MODE_REDSYNCTRIM, MODE_THRESHOLD, MODE_MINK = range(6)
+MODE_GAUSSIAN, MODE_TOPK, MODE_REDSYNC, MODE_REDSYNCTRIM, MODE_THRESHOLD, MODE_MINK, MODE_DGC = range(7)
 
 
 class GkBlk(C.Structure):
@@ -44,8 +44,9 @@ class GkSegStat(C.Structure):
     _fields_ = [("mean", C.c_float), ("std", C.c_float), ("meanabs", C.c_float), ("maxabs", C.c_float),
                 ("cand", C.c_float * GK_NC), ("thr", C.c_float), ("tbits", C.c_uint32), ("ties", C.c_uint32),
                 ("chosen", C.c_int32), ("count", C.c_uint32), ("out_base", C.c_uint32),
-                ("prefix", C.c_uint32), ("krem", C.c_uint32), ("order", C.c_uint8 * GK_NC), ("nlow", C.c_int32),
-                ("tot", C.c_uint32 * GK_NC)]
+                ("prefix", C.c_uint32), ("krem", C.c_uint32), ("rcand", C.c_uint8 * GK_NC), ("nrc", C.c_int32),
+                ("tot", C.c_uint32 * GK_NC), ("known", C.c_uint32), ("gate", C.c_int32), ("done", C.c_int32),
+                ("sprefix", C.c_uint32), ("skrem", C.c_uint32)]
 
 
 class GkCtrl(C.Structure):
@@ -60,7 +61,7 @@ class GkChain(C.Structure):
                 ("hist", C.c_void_p), ("ctrl", C.c_void_p),
                 ("nblk", C.c_int32), ("nseg", C.c_int32), ("mode", C.c_int32), ("nloops", C.c_int32),
                 ("use_residual", C.c_int32), ("zero_grad", C.c_int32), ("cap", C.c_uint32), ("rsv", C.c_int32),
-                ("gsrc", C.c_void_p)]
+                ("gsrc", C.c_void_p), ("rowmax", C.c_void_p), ("rpb", C.c_int32), ("rsv2", C.c_int32)]
 
 
 class GkDst(C.Structure):
@@ -79,7 +80,13 @@ class GkHyper(C.Structure):
                 ("lars_eeta", C.c_float), ("lars_eps", C.c_float)]
 
 
-assert C.sizeof(GkBlk) == 16 and C.sizeof(GkSeg) == 32 and C.sizeof(GkSegStat) == 196
+class GkRecvUpd(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("mom", C.c_void_p), ("mask", C.c_void_p), ("blk", C.c_void_p),
+                ("hyper", C.c_void_p), ("gmap", C.c_void_p), ("ctrl", C.c_void_p), ("bar", C.c_void_p),
+                ("scale", C.c_float), ("nblk", C.c_int32), ("nelem", C.c_int32), ("skip_dense", C.c_int32)]
+
+
+assert C.sizeof(GkBlk) == 16 and C.sizeof(GkSeg) == 32 and C.sizeof(GkSegStat) == 216
 assert C.sizeof(GkCtrl) == 328 and C.sizeof(GkHyper) == 32
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
@@ -161,9 +168,12 @@ def cuda_lib():
                 _proto(lib, n, [ch, _P])
             _proto(lib, "gk_compact_send", [ch, ds, _P])
             _proto(lib, "gk_compress", [ch, ds, _P])
+            _proto(lib, "gk_dgc_select", [ch, C.c_uint64, _P])
+            _proto(lib, "gk_dgc_compress", [ch, ds, C.c_uint64, _P])
             _proto(lib, "gk_scatter", [sr, _P, _P, C.c_float, C.c_int32, _P])
             _proto(lib, "gk_unscatter", [sr, _P, _P, C.c_int32, _P])
             _proto(lib, "gk_sgd", [_P, _P, _P, _P, C.c_int32, _P, _P, _P])
+            _proto(lib, "gk_sgd_recv", [C.POINTER(GkRecvUpd), sr, _P])
             _proto(lib, "gk_lars", [_P, _P, _P, _P, C.c_int32, _P, C.c_int32, _P, _P, _P, _P, _P])
             _proto(lib, "gk_grad_norm", [_P, _P, C.c_int32, _P, C.c_float, _P, _P, _P])
             _proto(lib, "gk_grad_norm_static", [_P, _P, C.c_int32, C.c_float, _P, _P])
@@ -207,9 +217,11 @@ def cpu_lib():
             ch, ds, sr = C.POINTER(GkChain), C.POINTER(GkDst), C.POINTER(GkSrc)
             _proto(lib, "gkcpu_version", [], C.c_char_p)
             _proto(lib, "gkcpu_compress", [ch, ds])
+            _proto(lib, "gkcpu_dgc_compress", [ch, ds, C.c_uint64])
             _proto(lib, "gkcpu_scatter", [sr, _P, _P, C.c_float, C.c_int32])
             _proto(lib, "gkcpu_unscatter", [sr, _P, _P, C.c_int32])
             _proto(lib, "gkcpu_sgd", [_P, _P, _P, _P, C.c_int32, _P, _P])
+            _proto(lib, "gkcpu_sgd_recv", [C.POINTER(GkRecvUpd), sr])
             _proto(lib, "gkcpu_lars", [_P, _P, _P, _P, C.c_int32, _P, C.c_int32, _P, _P, _P])
             _proto(lib, "gkcpu_grad_norm", [_P, _P, C.c_int32, C.c_float, _P])
             _proto(lib, "gkcpu_randomk_send", [ch, ds, C.c_uint64])

@@ -35,7 +35,8 @@ enum {
   GK_MODE_REDSYNC = 2,     /* compression.py:644-677 */
   GK_MODE_REDSYNCTRIM = 3, /* compression.py:707-738 */
   GK_MODE_THRESHOLD = 4,   /* fixed threshold supplied in GkSeg.param (select |x| > param) */
-  GK_MODE_MINK = 5         /* compression.py:52-56 k smallest |x| */
+  GK_MODE_MINK = 5,        /* compression.py:52-56 k smallest |x| */
+  GK_MODE_DGC = 6          /* compression.py:576-606 threshold from a 1 % sample, exact top-k if > 4k/3 pass */
 };
 
 /* One block of work: a contiguous extent of the arena that belongs to one segment. */
@@ -70,9 +71,13 @@ typedef struct GkSegStat {
   uint32_t out_base;                /* first output position of this segment       */
   uint32_t prefix;                  /* radix-select: matched high bits so far      */
   uint32_t krem;                    /* radix-select: rank still to find            */
-  uint8_t order[GK_NC];             /* candidate indices sorted by ascending threshold */
-  int32_t nlow;                     /* number of sorted candidates below the "far tail" gate (diagnostic) */
-  uint32_t tot[GK_NC];              /* per-candidate totals of the counting pass (zeroed by K1's epilogue) */
+  uint8_t rcand[GK_NC];             /* candidates counted by the current round (first nrc entries)  */
+  int32_t nrc;                      /* how many; 0 = no round planned                               */
+  uint32_t tot[GK_NC];              /* per-candidate totals of the counting rounds (zeroed by K1's epilogue) */
+  uint32_t known;                   /* bit j: tot[j] is final                                       */
+  int32_t gate;                     /* rows whose maximum bit pattern is <= gate cannot contribute to the round */
+  int32_t done;                     /* threshold search complete / DGC: sampled threshold accepted  */
+  uint32_t sprefix, skrem;          /* DGC: radix-select state of the sample                        */
 } GkSegStat;
 
 /* Chain-wide control block (device memory, zero-initialised once by the caller). */
@@ -83,7 +88,7 @@ typedef struct GkCtrl {
   uint32_t seq;      /* sequence number of the last completed send              */
   uint32_t err;      /* !=0: receive timed out / protocol error (sticky)        */
   uint32_t overflow; /* cumulative pairs withheld because of the cap            */
-  uint32_t rsv[3];
+  uint32_t rsv[3];   /* grid barrier of the counting rounds: arrivals, generation, "another round" */
   uint64_t sent_total; /* cumulative pairs emitted (for logging)                */
   uint32_t ring[64];   /* ring[seq & 63] = pairs selected by send number seq (the reference keeps
                           this list on the host, distributed_optimizer.py:420)   */
@@ -113,6 +118,11 @@ typedef struct GkChain {
                                from.  NULL = grad + start.  Lets K1 consume the tensors autograd
                                produced (p.grad stolen, no accumulate-into-arena kernels); those
                                sources are read only — zero_grad does not apply to them            */
+  uint32_t* rowmax;   /* optional [nblk*rpb] scratch: K1 leaves the largest |acc| bit pattern of every
+                         128-element row of every table entry here; the later passes read only the rows
+                         that can hold an element above their threshold.  NULL = every row is read      */
+  int32_t rpb;        /* rows reserved per table entry: ceil(chunk/128)                                 */
+  int32_t rsv2;
 } GkChain;
 
 /* Where the compaction kernel stores this rank's pairs: one slot per destination.
@@ -152,9 +162,10 @@ typedef struct GkHyper {
  * thresholds.  Replaces compression.py:365-370 and distributed_optimizer.py:375. */
 int gk_accumulate(const GkChain* c, void* stream);
 
-/* K2  count |acc| > cand[j] for every candidate in one pass, replay the reference's
- * refinement loop on the device, pick the threshold, prefix-sum the per-block counts.
- * Replaces compression.py:372-381 (and :653-672, :719-732).  No host sync. */
+/* K2  threshold search on the device: counting rounds over the rows that can exceed the round's smallest
+ * candidate, the reference's refinement loop replayed between rounds (grid barrier, cooperative launch),
+ * then the prefix sums of the per-entry counts for K3.  Replaces compression.py:372-381 (and :653-672,
+ * :719-732).  No host sync.  Uses ctrl->rsv as barrier state. */
 int gk_count_pick(const GkChain* c, void* stream);
 
 /* K4  exact top-k radix select (3 digit passes; the first is fused into gk_accumulate)
@@ -170,6 +181,12 @@ int gk_compact_send(const GkChain* c, const GkDst* dst, void* stream);
 /* Convenience: the whole send-side chain for c->mode. */
 int gk_compress(const GkChain* c, const GkDst* dst, void* stream);
 
+/* K9  DGC sampling (compression.py:576-606), GK_MODE_DGC: k-th largest of a 1 % sample drawn with the keyed
+ * bijection of gk_randomk_send -> threshold -> count -> (exact radix select if more than 4k/3 pass) ->
+ * (gt, eq) counts + prefix sums.  gk_dgc_compress = gk_accumulate + gk_dgc_select + gk_compact_send. */
+int gk_dgc_select(const GkChain* c, uint64_t seed, void* stream);
+int gk_dgc_compress(const GkChain* c, const GkDst* dst, uint64_t seed, void* stream);
+
 /* K5  receive: (optionally wait for all slots,) scatter-add value*scale into the dense
  * gradient arena.  Replaces distributed_optimizer.py:461-482. */
 int gk_scatter(const GkSrc* src, GkCtrl* ctrl, float* grad, float scale, int32_t nelem_arena,
@@ -182,6 +199,32 @@ int gk_unscatter(const GkSrc* src, GkCtrl* ctrl, float* grad, int32_t nelem_aren
  * (torch.optim.SGD arithmetic, dl_trainer.py:848-872).  grad_scale may be NULL. */
 int gk_sgd(float* param, const float* grad, float* mom, const GkBlk* blk, int32_t nblk,
            const GkHyper* hyper, const float* grad_scale, void* stream);
+
+/* K6 (folded)  receive + momentum-SGD in ONE cooperative launch; no dense gradient is ever formed
+ * (replaces distributed_optimizer.py:461-482 + :543-546 / dl_trainer.py:848-872 together).
+ *   phase A: p, m updated as if the gradient were zero (weight decay + momentum; 16 B/element) — this does not
+ *            depend on the peers and runs while their pairs are still arriving;
+ *   then the bounded wait on the slot headers, and the <= P*k received pairs are folded in per coordinate,
+ *   contributions summed in rank order (=> bit-identical replicas).
+ * Requirements: every source list sorted by ascending index (the compaction kernels emit them that way when the
+ * table entries are in arena order; random-k lists are not — use gk_scatter + gk_sgd there; a violation sets
+ * ctrl->err = 2); `mask` is an all-zero uint32 view of nelem words (the gradient arena) and is all zero again
+ * afterwards; `gmap[i >> 6]` = index into `hyper` of arena element i (NULL: group 0 everywhere); `bar` = 2
+ * zero-initialised uint32 (grid barrier state, never reset); `blk[].seg` indexes `hyper` as in gk_sgd.
+ * skip_dense != 0 leaves phase A out (momentum == 0 and weight_decay == 0 in every group). */
+typedef struct GkRecvUpd {
+  float* param;
+  float* mom;           /* may be NULL (no momentum) */
+  uint32_t* mask;
+  const GkBlk* blk;
+  const GkHyper* hyper;
+  const uint8_t* gmap;
+  GkCtrl* ctrl;         /* the chain's control block: seq of the exchange, err */
+  uint32_t* bar;
+  float scale;          /* 1 / world size */
+  int32_t nblk, nelem, skip_dense;
+} GkRecvUpd;
+int gk_sgd_recv(const GkRecvUpd* u, const GkSrc* src, void* stream);
 
 /* K7  LARS (lars.py:67-134): segmented ||w||, ||g|| then the trust-ratio update. */
 int gk_lars(float* param, const float* grad, float* mom, const GkBlk* blk, int32_t nblk,
@@ -338,10 +381,12 @@ const char* gk_version(void);
 
 /* ------------------------------------------------------------------- CPU twins (host) */
 int gkcpu_compress(const GkChain* c, const GkDst* dst);
+int gkcpu_dgc_compress(const GkChain* c, const GkDst* dst, uint64_t seed);
 int gkcpu_scatter(const GkSrc* src, GkCtrl* ctrl, float* grad, float scale, int32_t nelem_arena);
 int gkcpu_unscatter(const GkSrc* src, GkCtrl* ctrl, float* grad, int32_t nelem_arena);
 int gkcpu_sgd(float* param, const float* grad, float* mom, const GkBlk* blk, int32_t nblk,
               const GkHyper* hyper, const float* grad_scale);
+int gkcpu_sgd_recv(const GkRecvUpd* u, const GkSrc* src);
 int gkcpu_lars(float* param, const float* grad, float* mom, const GkBlk* blk, int32_t nblk,
                const GkSeg* tens, int32_t ntens, const GkHyper* hyper, double* part, float* ratio);
 int gkcpu_grad_norm(const float* grad, const GkBlk* blk, int32_t nblk, float max_norm, float* out);
