@@ -72,6 +72,7 @@ def ssgd(dnn, dataset, data_dir, nworkers, lr, batch_size, nsteps_update, max_ep
     hvd.broadcast_parameters(trainer.net.state_dict(), root_rank=0)
     trainer.update_optimizer(optimizer)
     trainer.restore_optimizer_state()
+    optimizer.sync_resume_state(root_rank=0)      # rank 0 alone has read the checkpoint
     for _ in range(trainer.get_train_epoch()):      # resume: put the density schedule where it was
         if optimizer.train_epoch < trainer.get_train_epoch():
             optimizer.train_epoch += 1

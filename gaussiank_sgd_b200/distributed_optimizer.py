@@ -39,9 +39,10 @@ from .parallel.transport import Transport, make_transport
 from .settings import logger
 
 DEFAULT_DYNAMIC_DENSITIES = [0.015625, 0.004, 0.001]  # distributed_optimizer.py:60
-_SPARSE_KERNEL_COMPRESSORS = {"gaussian", "gaussiank", "gaussian2", "topk", "topk2", "mink", "redsync",
-                              "redsynctrim", "dgcsampling", "randomk", "randomkec", "randomksame",
-                              "randomksameec"}
+# compressors whose selection runs in the sm_100a / C++ kernels; every other registered key (the fork's
+# ordering selectors: bucketized_topk, uniform_topk, uniform_abs_topk, bellk, median_topk) runs on the
+# torch-op path of _launch_group_torch — same algorithm as compression.py, library sort, never a substitute
+_KERNEL_COMPRESSORS = set(ch.MODES) | {"randomk", "randomkec", "randomksame", "randomksameec"}
 
 
 def synchronize(handle=None):
@@ -77,6 +78,40 @@ class _Group:
         self.ready_event = None
 
 
+class _Phase:
+    """NVTX range + optional CUDA-event pair around one phase (see _DistributedOptimizer._phase)."""
+
+    def __init__(self, opt, name):
+        self.opt, self.name = opt, name
+        self.cuda = opt.device.type == "cuda"
+        self.timed = opt._profiling and not (self.cuda and torch.cuda.is_current_stream_capturing())
+
+    def __enter__(self):
+        if self.cuda and settings.NVTX:
+            torch.cuda.nvtx.range_push("gk:" + self.name)
+        if self.timed:
+            if self.cuda:
+                self.e0 = torch.cuda.Event(enable_timing=True)
+                self.e0.record()
+            else:
+                import time
+                self.t0 = time.perf_counter()
+        return self
+
+    def __exit__(self, *exc):
+        if self.timed:
+            if self.cuda:
+                e1 = torch.cuda.Event(enable_timing=True)
+                e1.record()
+                self.opt._phase_events.append((self.name, self.e0, e1))
+            else:
+                import time
+                self.opt._phase_events.append((self.name, None, time.perf_counter() - self.t0))
+        if self.cuda and settings.NVTX:
+            torch.cuda.nvtx.range_pop()
+        return False
+
+
 class _DistributedOptimizer(torch.optim.Optimizer):
     def __init__(self, params, named_parameters, compression, is_sparse=False, density=0.001,
                  seq_layernames=None, layerwise_times=None, norm_clip=None, threshold=0, writer=None,
@@ -95,6 +130,9 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         self._gradient_path = gradient_path
         self._profiling = settings.PROFILE_PHASES
         self._timers = {"compress": [], "comm": [], "update": []}
+        self._phase_events = []
+        self._verify_every = settings.VERIFY_EVERY
+        self._verify = None
         self.train_epoch = 0
         self.train_iter = 0
         if dynamic_densities == "default":
@@ -107,6 +145,7 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         self._chunk = chunk
         self._transport_kind = transport
         self._random_seed = 0
+        self._torch_select = False
         self._steal_req = settings.STEAL_GRADS if steal_grads is None else bool(steal_grads)
 
         named_parameters = list(named_parameters) if named_parameters is not None else []
@@ -127,7 +166,8 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         self.device = self._arena.device
         self._resid = self._arena.new_arena() if self._sparse or self._compressor == "bucket" else None
         self._active = size() > 1 or self._force_compress   # distributed_optimizer.py:97: 1 worker => plain optimizer
-        self._steal = self._steal_req and self._active and self._sparse
+        self._steal = (self._steal_req and self._active and self._sparse
+                       and self._compressor in ch.MODES)       # random-k / torch-op selectors read the arena
         group_of_tensor = self._param_group_index()
         self._tables = ch.FlatTables(self._arena.extents(), group_of_tensor, self.device, chunk)
         self._fused_kind = self._detect_fused(fused)
@@ -225,14 +265,17 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         if self._per_tensor:
             # threshold=0: every tensor is its own selection segment, but all of them go through ONE
             # segmented launch instead of 161 chains.
-            g = _Group([n for grp in groups for n in grp], 0)
+            # Inside a group the tensors are taken in ARENA order (the planners work in backward order): the
+            # compaction kernel emits pairs in table order, so every rank's list comes out sorted by index,
+            # which the folded receive relies on.  Selection does not depend on the order.
+            g = _Group(sorted((n for grp in groups for n in grp), key=arena.index.__getitem__), 0)
             g.segments = [[arena.extent(arena.index[n])] for n in g.names]
             self._groups = [g]
         else:
             self._groups = []
             for gi, names in enumerate(groups):
-                g = _Group(list(names), gi)
-                g.segments = [[arena.extent(arena.index[n]) for n in names]]
+                g = _Group(sorted(names, key=arena.index.__getitem__), gi)
+                g.segments = [[arena.extent(arena.index[n]) for n in g.names]]
                 self._groups.append(g)
         self._group_of_param = {}
         for g in self._groups:
@@ -249,11 +292,25 @@ class _DistributedOptimizer(torch.optim.Optimizer):
             if self._sparse:
                 comp = self._compressor
                 use_res = comp not in ("topk2", "gaussian2", "randomk", "randomksame")
-                kcomp = comp if comp in ch.MODES else "topk"
+                if comp in ch.MODES:
+                    kcomp = comp
+                elif comp.startswith("randomk"):
+                    kcomp = "threshold"        # random-k only uses K1 of the chain (gk_randomk_send selects)
+                else:
+                    # The fork's ordering selectors need a sort; they run with torch ops (library sort) on the
+                    # tensors of the group and hand their (index, value) pairs to the same transports.  The
+                    # chain object only provides tables, slots and the control block here.
+                    if self._compression is None or not hasattr(self._compression, "compress"):
+                        raise ValueError(f"compressor {comp!r} has no kernel and no compress() implementation")
+                    kcomp = "threshold"
+                    self._torch_select = True
+                    logger.warning("compressor %r runs on the torch-op path (library sort, eager, NCCL all_gather); "
+                                   "the fused kernels cover %s", comp, sorted(_KERNEL_COMPRESSORS))
                 g.chain = ch.CompressChain(arena.grad, self._resid, g.segments, compressor=kcomp,
                                            density=min(self.get_current_density(), 0.999), use_residual=use_res,
                                            zero_grad=True, chunk=self._chunk, max_density=min(dmax, 0.999))
-                g.transport = make_transport(g.chain.cap, self.device, self._transport_kind)
+                g.transport = make_transport(g.chain.cap, self.device,
+                                             "allgather" if self._torch_select and size() > 1 else self._transport_kind)
                 if rank() == 0:
                     logger.info('group %d: %d tensors, %d elements, cap %d pairs, transport %s', g.idx,
                                 len(g.names), g.chain.n_total, g.chain.cap, g.transport.name)
@@ -304,16 +361,47 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         g.chain.set_grad_sources(ptrs)
         g._dirty_views = dirty
 
-    def _release_grad_sources(self, g: _Group) -> None:
+    def _release_grad_sources(self, g: _Group, keep_alive: bool = False) -> None:
         """After the chain is enqueued: the arena views become the visible gradients again (they will hold
-        the averaged sparse gradient); arena regions that served as a dense source are cleared."""
+        the averaged sparse gradient); arena regions that served as a dense source are cleared.  When the chain
+        runs on the side stream (``keep_alive``) the tensors autograd produced stay referenced until
+        ``synchronize()`` has joined the streams: they were allocated on the compute stream, and dropping the
+        last reference here would let the caching allocator hand their memory to backward kernels that run
+        while K1 is still reading them."""
         arena = self._arena
         for v in getattr(g, "_dirty_views", ()):
             v.zero_()
         g._dirty_views = []
+        if keep_alive:
+            g._stolen = [arena.params[arena.index[n]].grad for n in g.names]
         for n in g.names:
             i = arena.index[n]
             arena.params[i].grad = arena.grad_views[i]
+
+    def _launch_group_torch(self, g: _Group) -> None:
+        """Send side for the selectors that have no kernel (the fork's ordering selectors,
+        compression.py:60-177): the registry object's own ``compress()`` — torch ops, library sort — selects on
+        the dense group vector and keeps its residual under the group's name, exactly as it would under the
+        reference's optimizer (distributed_optimizer.py:416-427); the pairs are packed into the send slot in
+        the wire format of the kernels and travel through the all-gather transport."""
+        arena, chain = self._arena, g.chain
+        if not hasattr(g, "_dense_map"):
+            g._dense_map = arena.dense_index_map(g.names).to(self.device)
+            g._torch_seq = 0
+        acc = arena.grad.index_select(0, g._dense_map)
+        arena.grad[g.lo:g.hi].zero_()
+        _t, idx, vals = self._compression.compress(acc, "gk_group%d" % g.idx, ratio=min(self.get_current_density(), 0.999))
+        idx = idx.reshape(-1)[:chain.cap].to(torch.int64)
+        vals = vals.reshape(-1)[:chain.cap].to(torch.float32).contiguous()
+        aidx = g._dense_map[idx]
+        g._torch_seq += 1
+        words = aidx | ((vals.view(torch.int32).to(torch.int64) & 0xFFFFFFFF) << 32)
+        send = g.transport.send_tensor()
+        send[0] = int(idx.numel()) | (g._torch_seq << 32)
+        send[ch.N.GK_SLOT_HDR: ch.N.GK_SLOT_HDR + idx.numel()] = words
+        chain.ctrl.view(torch.int32)[10] = g._torch_seq          # GkCtrl.seq: what the receive kernel keys on
+        chain.ctrl.view(torch.int32)[8] = int(idx.numel())       # GkCtrl.total
+        self._selected_num_gradients.append(int(idx.numel()))
 
     def _make_hook(self, p):
         group = self._group_of_param[p]
@@ -388,8 +476,10 @@ class _DistributedOptimizer(torch.optim.Optimizer):
                 comp = self._compressor
                 dump = (settings.LOGGING_GRADIENTS and self._gradient_path and rank() == 0
                         and self.train_iter % max(settings.GRADIENT_DUMP_EVERY, 1) == 0)
-                if comp.startswith("randomk"):
-                    seed = self._random_seed if comp.startswith("randomksame") else self._random_seed * 1000003 + rank() + 1
+                seed = self._random_seed if comp.startswith("randomksame") else self._random_seed * 1000003 + rank() + 1
+                if self._torch_select:
+                    self._launch_group_torch(g)
+                elif comp.startswith("randomk"):
                     g.chain.randomk_send(g.transport.dst(), seed)
                 else:
                     if self._steal:
@@ -398,9 +488,12 @@ class _DistributedOptimizer(torch.optim.Optimizer):
                         # opt-in gradient-distribution study (the reference does this every iteration by
                         # default, distributed_optimizer.py:422-424)
                         self._dump_gradients(g)
-                    g.chain.compress(g.transport.dst())
+                    if self._verify_every and self.train_iter % self._verify_every == 0:
+                        self._verify_snapshot(g)
+                    with self._phase("compress"):
+                        g.chain.compress(g.transport.dst(), seed)     # the seed only matters to dgcsampling
                     if self._steal:
-                        self._release_grad_sources(g)
+                        self._release_grad_sources(g, keep_alive=stream_ctx is not None)
                 g.transport.exchange()
             elif self._compressor == "bucket":
                 g.chain.bucket_means(g.means)
@@ -445,6 +538,149 @@ class _DistributedOptimizer(torch.optim.Optimizer):
                                                 torch.cuda.current_stream(self.device).cuda_stream), "gk_histogram")
         return out
 
+    # ------------------------------------------------------------------ phase timers / NVTX
+    def _phase(self, name: str):
+        """Context manager around one phase of the step: an NVTX range when ``GK_NVTX=1`` and, when
+        ``GK_PROFILE_PHASES=1``, a CUDA-event pair on the current stream (the reference wraps the same three
+        phases in host timers, distributed_optimizer.py:428-429, :465-466, :484-485)."""
+        return _Phase(self, name)
+
+    def _print_profiling(self):
+        """Every 40 samples: mean device time of the phases, in the reference's line format (:522-540)."""
+        if not self._profiling or len(self._phase_events) < 40 * 2:
+            return
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        acc: Dict[str, List[float]] = {}
+        for name, e0, e1 in self._phase_events:
+            acc.setdefault(name, []).append(e0.elapsed_time(e1) * 1e-3 if e0 is not None else e1)
+        self._phase_events = []
+        for k, v in acc.items():
+            self._timers.setdefault(k, []).extend(v)
+        tcp = float(np.mean(acc.get("compress", [0.0])))
+        tar = float(np.mean(acc.get("comm", [0.0])))
+        tup = float(np.mean(acc.get("update", [0.0])))
+        tcu = float(np.mean(acc.get("comm+update", [0.0])))
+        if rank() == 0:
+            logger.info('[%d]: Total compress: %f, allreduce: %f, update: %f, total: %f', rank(), tcp, tar + tcu, tup,
+                        tcp + tar + tup + tcu)
+        self.last_phase_means = {"compress": tcp, "comm": tar, "update": tup, "comm+update": tcu}
+
+    # ------------------------------------------------------------------ oracle cross-check (GK_VERIFY_EVERY)
+    def _verify_snapshot(self, g: _Group) -> None:
+        """Before the chain of a verify step runs: keep a copy of acc = gradient (+ residual) in arena
+        layout.  compute-sanitizer is not available on every pool; this is the in-situ check that the fused
+        path still agrees with the oracle."""
+        arena = self._arena
+        flat = torch.zeros_like(arena.grad)
+        for n in g.names:
+            i = arena.index[n]
+            gr = arena.params[i].grad
+            if gr is not None:
+                arena.view(flat, i).copy_(gr)
+        if g.chain.use_residual:
+            flat += self._resid
+        self._verify = (g, flat, self.train_iter)
+
+    def _verify_check(self) -> None:
+        """After the materialised receive of a verify step: (1) this rank's pairs are exactly the oracle's
+        selection on the snapshot, (2) the dense gradient is exactly the rank-ordered mean of all ranks' pairs
+        (distributed_optimizer.py:468-482 with the exact mean), (3) the replicas hold identical parameters."""
+        from .ops import oracle
+        g, acc, it = self._verify
+        self._verify = None
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        chain, P, me = g.chain, size(), rank()
+        ctrl = chain.read_ctrl()
+        if ctrl["err"]:
+            raise RuntimeError(f"verify step {it}: chain error flag {ctrl['err']} on rank {me}")
+        src = g.transport.src()
+        nslots, stride = src.nsrc, int(src.slot_stride)
+        parity = (ctrl["seq"] & 1) if src.parity_stride else 0
+        words = self._recv_words(g)
+        lists = []
+        for r in range(nslots):
+            base = (parity * nslots + r) * stride
+            hdr = int(words[base])
+            cnt = min(hdr & 0xFFFFFFFF, chain.cap)
+            w = words[base + ch.N.GK_SLOT_HDR: base + ch.N.GK_SLOT_HDR + cnt]
+            lists.append(((w & 0xFFFFFFFF).to(torch.int64), (w >> 32).to(torch.int32).view(torch.float32)))
+        mine = lists[me if nslots > 1 else 0]
+        comp = self._compressor
+        acc_c = acc.cpu()
+        if comp in ("gaussian", "gaussiank", "gaussian2", "topk", "topk2", "mink", "redsync", "redsynctrim"):
+            stats = chain.read_stats()
+            exp = []
+            for sidx, extents in enumerate(g.segments):
+                amap = torch.cat([torch.arange(o, o + m) for o, m in extents])
+                seg = acc_c[amap]
+                if comp.startswith("gaussian"):
+                    oi, _ = oracle.gaussian_select(seg, chain.density, chain.nloops, mean=float(stats[sidx]["mean"]),
+                                                   std=float(stats[sidx]["std"]))
+                else:
+                    oi = oracle.select(comp, seg, chain.density)
+                exp.append(amap[oi])
+            exp = torch.cat(exp)[:chain.cap]
+            if not torch.equal(mine[0].cpu(), exp):
+                raise RuntimeError(f"verify step {it} rank {me}: selection differs from the oracle "
+                                   f"({mine[0].numel()} vs {exp.numel()} indices)")
+            if not torch.equal(mine[1].cpu(), acc_c[exp]):
+                raise RuntimeError(f"verify step {it} rank {me}: sent values differ from acc[idx]")
+        dense = torch.zeros_like(acc_c)
+        scale = torch.tensor(1.0 / P, dtype=torch.float32)
+        for idx, val in lists:
+            dense[idx.cpu()] += val.cpu() * scale
+        if not torch.equal(dense, self._arena.grad.cpu()):
+            bad = int((dense != self._arena.grad.cpu()).sum())
+            raise RuntimeError(f"verify step {it} rank {me}: received gradient differs from the rank-ordered mean "
+                               f"of the pairs at {bad} coordinates")
+        if P > 1:
+            cs = self.param_checksum()
+            allcs = [None] * P
+            dist.all_gather_object(allcs, cs)
+            if any(c != allcs[0] for c in allcs):
+                raise RuntimeError(f"verify step {it}: replicas differ: {allcs}")
+        self.verified_steps = getattr(self, "verified_steps", 0) + 1
+        if me == 0:
+            logger.info('verify step %d ok: %d pairs sent, %d received, replicas identical', it, mine[0].numel(),
+                        sum(l[0].numel() for l in lists))
+
+    def _recv_words(self, g: _Group) -> torch.Tensor:
+        """The local receive arena of group ``g`` as an int64 CPU tensor (debug / verification only)."""
+        t = g.transport
+        for attr in ("recv", "buf"):
+            if hasattr(t, attr):
+                return getattr(t, attr).t.cpu()
+        return t.local_words().cpu()
+
+    def param_checksum(self):
+        """(fp64 sum, xor of the bit patterns) of the parameter arena: equal on every rank iff the replicas are
+        bit-identical."""
+        p = self._arena.param
+        bits = p.view(torch.int32)
+        x = bits[: bits.numel() // 2 * 2].view(torch.int64)
+        xor = 0
+        # xor-reduce on the device: fold halves until small, finish on the host
+        while x.numel() > 1024:
+            half = x.numel() // 2
+            rest = x[2 * half:]
+            x = torch.bitwise_xor(x[:half], x[half:2 * half])
+            if rest.numel():
+                x = torch.cat([x, rest])
+        for v in x.cpu().tolist():
+            xor ^= v & 0xFFFFFFFFFFFFFFFF
+        return (float(p.double().sum().item()), xor)
+
+    def status_tensor(self) -> Optional[torch.Tensor]:
+        """Device tensor [total, sent, seq, err, overflow] of the first chain's control block as float32 (one
+        tiny conversion kernel, no host sync): the trainer reads it back together with the loss and fails
+        within one step of a receive time-out instead of at the end of training."""
+        for g in self._groups:
+            if g.chain is not None and self._sparse and self._active:
+                return g.chain.ctrl.view(torch.int32)[8:13].to(torch.float32)
+        return None
+
     # ------------------------------------------------------------------ receive side
     def synchronize(self):
         """Finish the exchange: afterwards every ``p.grad`` holds the averaged (sparse) gradient
@@ -461,8 +697,12 @@ class _DistributedOptimizer(torch.optim.Optimizer):
             any_launched = True
             if self._overlap and self._comm_stream is not None:
                 torch.cuda.current_stream(self.device).wait_stream(self._comm_stream)
+            g._stolen = None               # the side stream has been joined: autograd's tensors may go
             if self._sparse:
-                ch.scatter(g.transport.src(), g.chain.ctrl, self._arena.grad, 1.0 / P)
+                with self._phase("comm"):
+                    ch.scatter(g.transport.src(), g.chain.ctrl, self._arena.grad, 1.0 / P)
+                if self._verify is not None and self._verify[0] is g:
+                    self._verify_check()
             elif self._compressor == "bucket":
                 g.chain.bucket_reconstruct(g.means, g.gmeans)
             else:
@@ -474,7 +714,9 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         if any_launched:
             self._random_seed += 1
             self.train_iter += 1
-            self._grad_state = "sparse" if self._sparse else "dense"
+            # "synced": the dense / bucket exchange has run; a second synchronize() (the reference-style
+            # synchronize(); clip; step() sequence calls it again from step()) must not communicate again
+            self._grad_state = "sparse" if self._sparse else "synced"
             if self._norm_clip is not None:
                 # honour norm_clip (the reference's factory discards it); same scaling
                 # as its dense path (:498-505)
@@ -499,6 +741,8 @@ class _DistributedOptimizer(torch.optim.Optimizer):
             return True
         if not self._sparse:
             return size() == 1
+        if self._torch_select or self._verify_every:
+            return False
         return all(g.transport is not None and g.transport.name in ("p2p", "local") for g in self._groups)
 
     def check_errors(self) -> None:
@@ -531,11 +775,52 @@ class _DistributedOptimizer(torch.optim.Optimizer):
     def fused_update(self):
         """The fused optimizer kernel alone (graph-capturable: reads lr & co from device memory)."""
         a = self._arena
-        if self._fused_kind == "sgd":
-            ch.sgd_step(a.param, a.grad, self._mom, self._tables, self._hyper_dev, self._clip_coef)
-        else:
-            ch.lars_step(a.param, a.grad, self._mom, self._tables, self._hyper_dev)
+        with self._phase("update"):
+            if self._fused_kind == "sgd":
+                ch.sgd_step(a.param, a.grad, self._mom, self._tables, self._hyper_dev, self._clip_coef)
+            else:
+                ch.lars_step(a.param, a.grad, self._mom, self._tables, self._hyper_dev)
         self._clip_coef = None
+
+    def can_fold(self) -> bool:
+        """True when the pending exchange can be finished by the folded receive+update kernel: sparse path,
+        fused SGD, ONE group whose send side is (or is about to be) launched, index-sorted pair lists (every
+        kernel compressor except random-k), no clipping pending.  Otherwise ``step()`` materialises the
+        averaged gradient first (``synchronize()``), as it does when the user calls ``synchronize()`` to look
+        at or clip the gradients (LSTM models, dist_trainer.py:80-85)."""
+        if not (settings.FOLDED_UPDATE and self._active and self._sparse and self._fused_kind == "sgd"):
+            return False
+        if len(self._groups) != 1 or self._norm_clip is not None or self._clip_coef is not None:
+            return False
+        if self._compressor.startswith("randomk") or self._torch_select or not self._tables.foldable:
+            return False
+        if size() > ch.N.GK_MAXP:
+            return False
+        if self._verify_every and (self._verify is not None or self.train_iter % self._verify_every == 0):
+            return False                   # verify steps materialise the gradient so that it can be checked
+        g = self._groups[0]
+        return g.launched or self._grad_state == "dense"
+
+    def folded_update(self):
+        """Finish the exchange and update in one kernel (ops.chain.sgd_recv_step).  ``p.grad`` is NOT filled
+        with the averaged gradient on this path (the arena stays zero) — call ``synchronize()`` before
+        ``step()`` if you need to see it."""
+        g = self._groups[0]
+        if not g.launched:
+            self._launch_group(g)
+        if self._overlap and self._comm_stream is not None:
+            torch.cuda.current_stream(self.device).wait_stream(self._comm_stream)
+        a = self._arena
+        skip = all(pg.get("momentum", 0.0) == 0 and pg.get("weight_decay", 0.0) == 0 for pg in self.param_groups)
+        with self._phase("comm+update"):
+            ch.sgd_recv_step(a.param, a.grad.view(torch.int32), self._mom, self._tables, self._hyper_dev,
+                             g.transport.src(), g.chain.ctrl, 1.0 / size(), skip_dense=skip)
+        g.launched = False
+        g.pending = len(g.names)
+        g._stolen = None
+        self._random_seed += 1
+        self.train_iter += 1
+        self._grad_state = "zero"          # the kernel leaves the gradient arena all zero
 
     def step(self, closure=None):
         """Synchronise the exchange, then update (distributed_optimizer.py:543-546)."""
@@ -543,13 +828,19 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
-        if not self.local:
-            self.synchronize()
         if self._fused_kind is not None:
             self._refresh_hyper()
-            self.fused_update()
+            if not self.local and self.can_fold():
+                self.folded_update()
+            else:
+                if not self.local:
+                    self.synchronize()
+                self.fused_update()
             self._steps_done += 1
+            self._print_profiling()
             return loss
+        if not self.local:
+            self.synchronize()
         return super(self.__class__, self).step()
 
     def zero_grad(self, set_to_none: bool = False):
@@ -585,6 +876,31 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         self.train_iter = int(sd.get("train_iter", 0))
         self._steps_done = int(sd.get("steps_done", 0))
         self._random_seed = int(sd.get("random_seed", 0))
+        self._hyper_key = None
+        self._apply_density()
+
+    def sync_resume_state(self, root_rank: int = 0) -> None:
+        """After a resume: only ``root_rank`` has read the checkpoint (dist_trainer.py:26-27 loads it on rank 0
+        only), so its momentum (or LARS acceleration) arena and its step / schedule counters are broadcast —
+        otherwise the other ranks would run their next step as a *first* step (momentum buffer := gradient)
+        and the replicas would drift apart for good.  Residuals are per-rank error feedback: ``root_rank``
+        keeps the one it saved, the others start from zero.  (The reference restores none of this,
+        SURVEY.md Q12, and stays consistent only because every rank then has zero momentum.)"""
+        if not comm.is_distributed():
+            return
+        meta = None
+        if rank() == root_rank:
+            meta = {"steps_done": self._steps_done, "random_seed": self._random_seed, "train_iter": self.train_iter,
+                    "train_epoch": self.train_epoch}
+        meta = comm.bcast_object(meta, root_rank)
+        self._steps_done = int(meta["steps_done"])
+        self._random_seed = int(meta["random_seed"])
+        self.train_iter = int(meta["train_iter"])
+        self.train_epoch = int(meta["train_epoch"])
+        if self._mom is not None:
+            comm.broadcast_(self._mom, root_rank)
+        elif self._fused_kind is None:
+            broadcast_optimizer_state(self, root_rank)
         self._hyper_key = None
         self._apply_density()
 
@@ -658,6 +974,4 @@ def broadcast_optimizer_state(optimizer, root_rank=0):
                     tensors.append(v)
     if tensors:
         broadcast_parameters([(None, t) for t in tensors], root_rank)
-    extra = getattr(optimizer, "residual_state", None)
-    if callable(extra) and extra() is not None:
-        comm.broadcast_(extra(), root_rank)
+    # the compressor residuals are deliberately NOT broadcast: they are each rank's own error-feedback memory

@@ -42,6 +42,23 @@ _support_dnns = ['resnet50', 'googlenet', 'inceptionv4', 'inceptionv3', 'vgg16i'
 
 NUM_CPU_THREADS = int(os.environ.get("GK_NUM_CPU_THREADS", "0"))
 
+
+class _nvtx:
+    """NVTX range (``GK_NVTX=1``) around a phase of the step; a no-op otherwise and on CPUs."""
+
+    def __init__(self, name):
+        self.on = settings.NVTX and torch.cuda.is_available()
+        self.name = name
+
+    def __enter__(self):
+        if self.on:
+            torch.cuda.nvtx.range_push(self.name)
+
+    def __exit__(self, *exc):
+        if self.on:
+            torch.cuda.nvtx.range_pop()
+        return False
+
 MnistNet = models.MnistNet
 
 
@@ -569,18 +586,26 @@ class DLTrainer:
             return [correct[:, :k].any(dim=1).float().mean().mul_(100.0) for k in topk]
 
     # ------------------------------------------------------------------ metric read-back
-    def _enqueue_metrics(self, loss_t, acc_t=None):
+    def _enqueue_metrics(self, loss_t, acc_t=None, status_t=None):
+        """Asynchronous read-back of the step's loss / accuracy and of the exchange's status words
+        [pairs selected, sent, seq, err, withheld]; consumed one step later, so a receive time-out raises within
+        one step instead of going unnoticed until the end of training (the reference has no such check at all)."""
+        if status_t is None:
+            st = getattr(self.optimizer, 'status_tensor', None)
+            status_t = st() if callable(st) else None
         vals = torch.stack([loss_t.detach().float().reshape(()),
                             (acc_t if acc_t is not None else loss_t.new_zeros(())).detach().float().reshape(())])
+        if status_t is not None and status_t.numel():
+            vals = torch.cat([vals, status_t.to(vals.device)])
         if self.is_cuda:
-            host = torch.empty(2, dtype=torch.float32, pin_memory=True)
+            host = torch.empty(vals.numel(), dtype=torch.float32, pin_memory=True)
             host.copy_(vals, non_blocking=True)
             ev = torch.cuda.Event()
             ev.record()
             self._pending.append((ev, host, acc_t is not None))
         else:
             self._pending.append((None, vals.clone(), acc_t is not None))
-        self.d2h_bytes = 8
+        self.d2h_bytes = 4 * vals.numel()
         while len(self._pending) > 1:
             self._consume_metric(self._pending.pop(0))
 
@@ -588,6 +613,12 @@ class DLTrainer:
         ev, host, has_acc = item
         if ev is not None:
             ev.synchronize()
+        if host.numel() >= 7 and float(host[5]) != 0.0:      # [loss, acc, total, sent, seq, err, overflow]
+            code = int(host[5])
+            why = {1: "a peer's pairs did not arrive within GK_P2P_TIMEOUT_S (dead or stalled rank)",
+                   2: "a received pair list was not index-sorted", 3: "a grid barrier of the chain timed out"}
+            raise RuntimeError("sparse gradient exchange failed on rank %d at iteration %d: %s (device error word %d)"
+                               % (self.rank, self.train_iter, why.get(code, "unknown"), code))
         loss_value = float(host[0])
         self.loss = loss_value
         self.avg_loss_per_epoch += loss_value
@@ -691,10 +722,12 @@ class DLTrainer:
             data = None
             self.iotime += (time.time() - ss)
             sforward = time.time()
-            loss, outputs, labels, hidden = self._forward_loss(staged, hidden)
+            with _nvtx('gk:forward'):
+                loss, outputs, labels, hidden = self._forward_loss(staged, hidden)
             self.forwardtime += (time.time() - sforward)
             sbackward = time.time()
-            loss.backward()
+            with _nvtx('gk:backward'):
+                loss.backward()
             acc1 = self.cal_accuracy(outputs, labels, topk=(1,))[0] if outputs is not None else None
             self._enqueue_metrics(loss, acc1)
             self._release_inputs()
@@ -756,8 +789,10 @@ class DLTrainer:
             hidden = self._graph.run(staged, hidden)
         else:
             self.optimizer.zero_grad()
-            loss, outputs, labels, hidden = self._forward_loss(staged, hidden)
-            loss.backward()
+            with _nvtx('gk:forward'):
+                loss, outputs, labels, hidden = self._forward_loss(staged, hidden)
+            with _nvtx('gk:backward'):
+                loss.backward()
             acc1 = self.cal_accuracy(outputs, labels, topk=(1,))[0] if outputs is not None else None
             if clip_norm is not None and hasattr(self.optimizer, 'clip_grad_norm'):
                 self.optimizer.synchronize()
@@ -859,18 +894,26 @@ class GraphedStep:
         self.static_hidden = None
         self.out_hidden = None
         self.metrics = None
+        self.folded = False
+        self.has_status = False
 
     def _eager(self, staged, hidden):
         t = self.t
         opt = t.optimizer
         opt.zero_grad()
-        loss, outputs, labels, hidden = t._forward_loss(staged, hidden)
-        loss.backward()
+        with _nvtx('gk:forward'):
+            loss, outputs, labels, hidden = t._forward_loss(staged, hidden)
+        with _nvtx('gk:backward'):
+            loss.backward()
         acc1 = t.cal_accuracy(outputs, labels, topk=(1,))[0] if outputs is not None else loss.new_zeros(())
-        opt.synchronize()
-        if self.clip_norm is not None:
-            opt.clip_grad_norm(self.clip_norm)
-        opt.fused_update()
+        self.folded = self.clip_norm is None and opt.can_fold()
+        if self.folded:
+            opt.folded_update()            # receive folded into the update: no dense gradient
+        else:
+            opt.synchronize()
+            if self.clip_norm is not None:
+                opt.clip_grad_norm(self.clip_norm)
+            opt.fused_update()
         return loss, acc1, hidden
 
     def run(self, staged, hidden=None):
@@ -889,13 +932,17 @@ class GraphedStep:
                 d.copy_(s_)
             if hidden is not None:
                 self.static_hidden = tuple(h.detach().clone() for h in hidden)
-            self.metrics = torch.zeros(2, dtype=torch.float32, device=t.device)
+            st = getattr(opt, 'status_tensor', None)
+            self.has_status = callable(st) and st() is not None
+            self.metrics = torch.zeros(7 if self.has_status else 2, dtype=torch.float32, device=t.device)
             torch.cuda.synchronize(t.device)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
                 loss, acc1, h_out = self._eager(self.static, self.static_hidden)
                 self.metrics[0].copy_(loss.detach())
                 self.metrics[1].copy_(acc1.detach())
+                if self.has_status:
+                    self.metrics[2:7].copy_(opt.status_tensor())
                 if h_out is not None:
                     self.out_hidden = tuple(h.detach() for h in h_out)
             self.graph = g
@@ -910,8 +957,12 @@ class GraphedStep:
         opt._steps_done += 1
         opt.train_iter += 1
         opt._random_seed += 1
-        opt._grad_state = "sparse" if opt._sparse and opt._active else "dense"
-        t._enqueue_metrics(self.metrics[0], self.metrics[1] if t.dnn != 'lstm' else None)
+        if self.folded:
+            opt._grad_state = "zero"           # the folded kernel leaves the gradient arena all zero
+        else:
+            opt._grad_state = "sparse" if opt._sparse and opt._active else "synced"
+        t._enqueue_metrics(self.metrics[0], self.metrics[1] if t.dnn != 'lstm' else None,
+                           status_t=self.metrics[2:7] if self.has_status else self.metrics[2:2])
         self.calls += 1
         if self.out_hidden is not None:
             return tuple(h.clone() for h in self.out_hidden)

@@ -41,6 +41,10 @@ class Transport:
     def exchange(self) -> None:
         """Host-issued part of the exchange, enqueued after the send kernel (no-op for P2P)."""
 
+    def send_tensor(self) -> torch.Tensor:
+        """The local send slot as an int64 tensor (header words + pairs) for senders that are not kernels."""
+        raise NotImplementedError(f"{self.name} transport is written by the compaction kernel only")
+
     def close(self) -> None:
         pass
 
@@ -58,6 +62,9 @@ class LocalTransport(Transport):
 
     def src(self):
         return self._src
+
+    def send_tensor(self):
+        return self.buf.t
 
 
 class AllGatherTransport(Transport):
@@ -79,6 +86,9 @@ class AllGatherTransport(Transport):
 
     def src(self):
         return self._src
+
+    def send_tensor(self):
+        return self.send.t
 
     def exchange(self):
         if self.P == 1:
@@ -172,6 +182,17 @@ class P2PTransport(Transport):
 
     def src(self):
         return self._src
+
+    def local_words(self) -> torch.Tensor:
+        """Copy of this rank's receive arena as an int64 tensor (verification / debugging; synchronises)."""
+        words = 2 * self.P * self.slot_stride
+        if self._symm_t is not None:
+            return self._symm_t[:words].clone()
+        out = torch.empty(words, dtype=torch.int64, device=self.device)
+        N.check(N.cuda_lib().gk_copy(out.data_ptr(), self._own_raw, 2 * words,
+                                     torch.cuda.current_stream(self.device).cuda_stream), "gk_copy")
+        torch.cuda.synchronize(self.device)
+        return out
 
     def close(self):
         if self.backend == "ipc":

@@ -61,7 +61,10 @@ DYNAMIC_DENSITIES = _floats("DYNAMIC_DENSITIES", [0.015625, 0.004, 0.001])  # di
 COMPRESS_SINGLE = _flag("COMPRESS_SINGLE", False)   # run the chain with one worker too
 STEAL_GRADS = _flag("STEAL_GRADS", True)            # K1 reads autograd's gradient tensors in place (no arena accumulate)
 SPARSE_ZERO = _flag("SPARSE_ZERO", True)            # zero_grad clears only the received coordinates
+FOLDED_UPDATE = _flag("FOLDED_UPDATE", True)        # step(): receive folded into the SGD kernel (no dense gradient)
 PROFILE_PHASES = _flag("PROFILE_PHASES", False)     # CUDA-event timers for compress / comm / update
+NVTX = _flag("NVTX", False)                          # NVTX ranges around forward / backward / compress / comm / update
+VERIFY_EVERY = int(os.environ.get("GK_VERIFY_EVERY", "0"))   # >0: cross-check the fused path against the oracle every N steps
 CUDA_GRAPH = _flag("CUDA_GRAPH", True)              # capture the training step in a CUDA graph on GPUs
 CHANNELS_LAST = _flag("CHANNELS_LAST", True)        # NHWC convolutions on GPUs
 SYNTHETIC_POOL = _flag("SYNTHETIC_POOL", True)      # pre-collated pinned batches for synthetic image data
