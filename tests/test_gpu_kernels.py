@@ -27,6 +27,11 @@ def _data(n, seed, kind="normal"):
     if kind == "laplace":
         u = (torch.rand(n, generator=g) - 0.5) * 0.9999
         return -0.01 * torch.sign(u) * torch.log1p(-2 * u.abs())
+    if kind == "sparse":          # fewer non-zeros than k at density 0.001: the DGC sample threshold (0) is accepted
+        x = torch.zeros(n)
+        m = max(n // 2000, 1)
+        x[torch.randperm(n, generator=g)[:m]] = torch.randn(m, generator=g)
+        return x
     raise KeyError(kind)
 
 
@@ -296,3 +301,155 @@ def test_lars_grad_norm_bucket_histogram():
                                       torch.cuda.current_stream().cuda_stream))
     ref_h = torch.histc(x.clamp(-3.9999, 3.9999), bins=64, min=-4, max=4)
     assert int(out_h.sum()) == 100000 and (out_h.cpu().float() - ref_h.cpu()).abs().max() <= 2
+
+
+# --------------------------------------------------------------------------- round-2 kernels
+def test_row_maxima_written_by_k1():
+    n = 100003
+    g, r = _data(n, 7, "laplace"), _data(n, 8) * 0.2
+    G, R = g.to(DEV).clone(), r.to(DEV).clone()
+    c = ch.CompressChain(G, R, [[(0, n)]], compressor="gaussian", density=0.001, chunk=4096)
+    c.accumulate()
+    torch.cuda.synchronize()
+    acc = (g + r).abs()
+    rows_per = c.rpb
+    rm = c.rowmax.cpu().view(torch.int32)
+    for e, (start, ln, _s, _o) in enumerate(c.blk_np):
+        seg = acc[start:start + ln]
+        nrow = (ln + 127) // 128
+        pad = torch.zeros(nrow * 128)
+        pad[:ln] = seg
+        exp = pad.view(nrow, 128).max(dim=1).values.view(torch.int32)
+        assert torch.equal(rm[e * rows_per: e * rows_per + nrow], exp), e
+
+
+@pytest.mark.parametrize("kind", ["normal", "laplace", "sparse"])
+@pytest.mark.parametrize("n,density", [(269722, 0.001), (3000001, 0.004), (50001, 0.009)])
+def test_dgc_sampling_gpu_matches_cpu_twin(kind, n, density):
+    g, r = _data(n, 11, kind), _data(n, 11, kind) * 0.3
+    out = {}
+    for dev in ("cpu", DEV):
+        G, R = g.to(dev).clone(), r.to(dev).clone()
+        c = ch.CompressChain(G, R, [[(0, n)]], compressor="dgcsampling", density=density)
+        sb = ch.SlotBuffer(1, c.cap, dev)
+        c.compress(ch.make_dst([sb.slot_ptr(0)], 0), seed=1234)
+        if dev != "cpu":
+            torch.cuda.synchronize()
+            assert int(c.hist.abs().sum()) == 0
+        i, v, _ = sb.read_slot(0)
+        st = c.read_stats()[0]
+        out[dev] = (i, v, R.cpu(), int(st["tbits"]), int(st["ties"]))
+    assert out["cpu"][3:] == out[DEV][3:]                       # same threshold / tie budget
+    assert torch.equal(out["cpu"][0], out[DEV][0]) and torch.equal(out["cpu"][1], out[DEV][1])
+    assert torch.equal(out["cpu"][2], out[DEV][2])
+    k = ch.compute_k(n, density)
+    acc = g + r
+    i = out[DEV][0]
+    assert 0 < i.numel() <= 4 * k / 3 + 1
+    if kind == "sparse":
+        assert out[DEV][3] == 0 and i.numel() == int((acc != 0).sum())     # sampled threshold accepted
+    # everything sent is at least as large as everything kept (threshold or exact top-k semantics)
+    keep = torch.ones(n, dtype=torch.bool)
+    keep[i] = False
+    assert acc[i].abs().min() >= acc[keep].abs().max()
+
+
+def _emulated_lists(n, P, k, seed, overlap=200):
+    g = torch.Generator().manual_seed(seed)
+    first = torch.randperm(n, generator=g)[:k].sort().values
+    lists = []
+    for r in range(P):
+        sel = torch.randperm(n, generator=g)[:k]
+        if r > 0:
+            sel = torch.cat([sel, first[:overlap]])      # coordinates held by several ranks
+        sel = sel.unique()                               # sorted ascending
+        lists.append((sel, torch.randn(sel.numel(), generator=g)))
+    return lists
+
+
+def _fill_arena(arena, lists, seq):
+    P = len(lists)
+    for r, (sel, v) in enumerate(lists):
+        words = sel.numpy().astype(np.uint64) | (v.numpy().view(np.uint32).astype(np.uint64) << np.uint64(32))
+        base = ((seq & 1) * P + r) * arena.slot_stride
+        arena.t[base] = int(sel.numel()) | (seq << 32)
+        arena.t[base + N.GK_SLOT_HDR: base + N.GK_SLOT_HDR + sel.numel()] = torch.from_numpy(words.view(np.int64)).to(DEV)
+
+
+@pytest.mark.parametrize("P", [1, 2, 8])
+@pytest.mark.parametrize("momentum,nesterov", [(0.9, False), (0.9, True), (0.0, False)])
+def test_folded_receive_update_matches_materialised_path(P, momentum, nesterov):
+    """gk_sgd_recv (no dense gradient) against gk_scatter + gk_sgd on the same pair lists: identical on the
+    untouched coordinates, within the rounding of the split FMA on the received ones; the arena used as the
+    rank bitmask comes back all zero; two runs give the same bits (rank-ordered sums)."""
+    torch.manual_seed(5)
+    sizes = [300, 410000, 17, 50000, 1000003]
+    offs, total = [], 0
+    for s in sizes:
+        offs.append(total)
+        total += (s + 63) // 64 * 64
+    tables = ch.FlatTables(list(zip(offs, sizes)), [0, 1, 0, 1, 1], DEV)
+    hyp = [{"lr": 0.05, "momentum": momentum, "weight_decay": 0.0, "nesterov": nesterov},
+           {"lr": 0.1, "momentum": momentum, "weight_decay": 1e-3, "nesterov": nesterov}]
+    valid = torch.cat([torch.arange(o, o + s) for o, s in zip(offs, sizes)])
+    P0, M0 = torch.randn(total, device=DEV), torch.randn(total, device=DEV) * 0.1
+    ctrl = torch.zeros(ch.CTRL_DTYPE.itemsize, dtype=torch.uint8, device=DEV)
+    for step, first in enumerate((True, False)):
+        lists = [(valid[s], v) for s, v in _emulated_lists(valid.numel(), P, 3000, 40 + step)]
+        cap = max(l[0].numel() for l in lists) + 8
+        arena = ch.SlotBuffer(P, cap, DEV, parities=2)
+        seq = 7 + step
+        ctrl.view(torch.int32)[10] = seq
+        _fill_arena(arena, lists, seq)
+        hy = ch.make_hyper(hyp, DEV, first).to(DEV)
+        mom = lambda M: M if momentum else None   # noqa: E731
+        P1, M1, G = P0.clone(), M0.clone(), torch.zeros(total, device=DEV)
+        ch.scatter(arena.src(wait=True, timeout_s=2.0), ctrl, G, 1.0 / P)
+        ch.sgd_step(P1, G, mom(M1), tables, hy)
+        res = []
+        for _ in range(2):
+            P2, M2, mask = P0.clone(), M0.clone(), torch.zeros(total, device=DEV)
+            ch.sgd_recv_step(P2, mask.view(torch.int32), mom(M2), tables, hy, arena.src(wait=True, timeout_s=2.0),
+                             ctrl, 1.0 / P)
+            torch.cuda.synchronize()
+            assert torch.count_nonzero(mask) == 0
+            res.append((P2, M2))
+        assert int(ctrl.view(torch.int32)[11]) == 0
+        assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+        P2, M2 = res[0]
+        touched = torch.zeros(total, dtype=torch.bool, device=DEV)
+        for sel, _ in lists:
+            touched[sel.to(DEV)] = True
+        assert torch.equal(P1[~touched], P2[~touched]) and torch.equal(M1[~touched], M2[~touched])
+        assert (P1 - P2).abs().max() <= 4 * torch.finfo(torch.float32).eps * max(1.0, float(P1.abs().max()))
+        assert (M1 - M2).abs().max() <= 4 * torch.finfo(torch.float32).eps * max(1.0, float(M1.abs().max()))
+        P0, M0 = P1, M1
+
+
+def test_folded_update_flags_unsorted_lists():
+    n = 4096 * 4
+    tables = ch.FlatTables([(0, n)], [0], DEV)
+    hy = ch.make_hyper([{"lr": 0.1, "momentum": 0.9, "weight_decay": 0.0}], DEV, False).to(DEV)
+    ctrl = torch.zeros(ch.CTRL_DTYPE.itemsize, dtype=torch.uint8, device=DEV)
+    ctrl.view(torch.int32)[10] = 2
+    arena = ch.SlotBuffer(2, 64, DEV, parities=2)
+    a = (torch.tensor([5, 9, 100]), torch.ones(3))
+    b = (torch.tensor([100, 9, 5]), torch.ones(3))           # descending: the owner's binary search must fail loudly
+    _fill_arena(arena, [a, b], 2)
+    Pm, Mm, mask = torch.zeros(n, device=DEV), torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+    ch.sgd_recv_step(Pm, mask.view(torch.int32), Mm, tables, hy, arena.src(wait=True, timeout_s=1.0), ctrl, 0.5)
+    torch.cuda.synchronize()
+    assert int(ctrl.view(torch.int32)[11]) == 2
+
+
+def test_gaussian_heavy_tail_needs_several_rounds_and_matches_oracle():
+    """A few huge entries inflate sigma, the first threshold selects far fewer than 2k/3 and the search
+    descends (compression.py:375-376): the lazy rounds must follow it exactly."""
+    n = 2000000
+    g = _data(n, 21) * 0.1
+    g[torch.randperm(n, generator=torch.Generator().manual_seed(3))[:40]] = 50.0
+    c, G, R, idx, val, seq = _run("gaussian", g, torch.zeros(n), 0.001)
+    st = c.read_stats()[0]
+    oi, thr = oracle.gaussian_select(g, 0.001, 3, mean=float(st["mean"]), std=float(st["std"]))
+    assert int(st["chosen"]) != 0                    # not settled by the first candidate
+    assert np.float32(thr) == st["thr"] and torch.equal(idx, oi) and torch.equal(val, g[oi])

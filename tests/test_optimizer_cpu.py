@@ -180,3 +180,179 @@ def test_two_gloo_workers_stay_in_sync(comp):
     else:
         nz = int((g0 != 0).sum())
         assert 0 < nz <= 2 * max(int(g0.numel() * 0.05 * 4 / 3) + 1, 1) * 2
+
+
+# ------------------------------------------------------------------ round 2
+def test_folded_step_equals_materialised_step_cpu():
+    """step() folds the receive into the update (no dense gradient); synchronize()+step() materialises it.
+    Same parameters up to the rounding of the split FMA, and p.grad stays zero on the folded path."""
+    res = {}
+    for fold in (True, False):
+        m = _mlp()
+        o = torch.optim.SGD(_param_groups(m, 1e-3), lr=0.1, momentum=0.9, nesterov=True)
+        opt = hvd.DistributedOptimizer(o, named_parameters=m.named_parameters(), compression=compressors["topk"],
+                                       is_sparse=True, density=0.05, threshold=524288000, dynamic_densities=None,
+                                       force_compress=True)
+        torch.manual_seed(1)
+        x, y = torch.randn(16, 20), torch.randint(0, 5, (16,))
+        for _ in range(4):
+            opt.zero_grad()
+            nn.functional.cross_entropy(m(x), y).backward()
+            if fold:
+                assert opt.can_fold()
+            else:
+                opt.synchronize()
+                assert not opt.can_fold()
+            opt.step()
+            if fold:
+                assert all(int(torch.count_nonzero(p.grad)) == 0 for p in m.parameters())
+        res[fold] = torch.cat([p.detach().reshape(-1) for p in m.parameters()])
+        opt.close()
+    assert torch.allclose(res[True], res[False], rtol=0, atol=1e-6)
+    assert not torch.equal(res[True], torch.cat([p.detach().reshape(-1) for p in _mlp().parameters()]))
+
+
+@pytest.mark.parametrize("comp", ["uniform_abs_topk", "bucketized_topk"])
+def test_ordering_selectors_run_their_own_algorithm(comp):
+    """No registered key may silently run another algorithm: the fork's ordering selectors go through the
+    registry object's compress() (torch ops) inside the optimizer and select what that function selects."""
+    if comp not in compressors:
+        pytest.skip("selector not registered")
+    m = _mlp()
+    o = torch.optim.SGD(m.parameters(), lr=0.1)
+    opt = hvd.DistributedOptimizer(o, named_parameters=m.named_parameters(), compression=compressors[comp],
+                                   is_sparse=True, density=0.05, threshold=524288000, dynamic_densities=None,
+                                   force_compress=True)
+    assert opt._torch_select and not opt.graph_safe
+    x, y = torch.randn(16, 20), torch.randint(0, 5, (16,))
+    compressors[comp].clear()
+    opt.zero_grad()
+    nn.functional.cross_entropy(m(x), y).backward()
+    names = opt._groups[0].names
+    raw = torch.cat([dict(m.named_parameters())[n].grad.reshape(-1).clone() for n in names])
+    opt.synchronize()
+    got = torch.cat([dict(m.named_parameters())[n].grad.reshape(-1) for n in names])
+    compressors[comp].clear()
+    _t, idx, vals = compressors[comp].compress(raw.clone(), "check", ratio=0.05)
+    exp = torch.zeros_like(raw)
+    exp[idx.reshape(-1)] = vals.reshape(-1)
+    assert torch.equal(got, exp)
+    exact = oracle.topk_select(raw, max(int(raw.numel() * 0.05), 1))
+    assert not torch.equal(torch.sort(idx.reshape(-1)).values, exact)      # really not exact top-k
+    compressors[comp].clear()
+    opt.close()
+
+
+def test_unknown_compressor_is_refused():
+    m = _mlp()
+
+    class Fake:
+        key = "does_not_exist"
+
+    with pytest.raises(ValueError):
+        hvd.DistributedOptimizer(torch.optim.SGD(m.parameters(), lr=0.1), named_parameters=m.named_parameters(),
+                                 compression=Fake(), is_sparse=True, density=0.05, force_compress=True)
+
+
+def _resume_worker(rank, world, port, ckpt, q):
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port), GK_FORCE_CPU="1")
+    torch.set_num_threads(1)
+    hvd.init()
+
+    def make():
+        model = _mlp(seed=3)
+        base = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9)
+        opt = hvd.DistributedOptimizer(base, named_parameters=model.named_parameters(),
+                                       compression=compressors["topk"], is_sparse=True, density=0.05,
+                                       threshold=524288000, dynamic_densities=None)
+        return model, opt
+
+    def steps(model, opt, n, seed):
+        g = torch.Generator().manual_seed(seed + rank)
+        for _ in range(n):
+            x, y = torch.randn(8, 20, generator=g), torch.randint(0, 5, (8,), generator=g)
+            opt.zero_grad()
+            nn.functional.cross_entropy(model(x), y).backward()
+            opt.step()
+
+    model, opt = make()
+    hvd.broadcast_parameters(model.state_dict(), root_rank=0)
+    steps(model, opt, 3, 10)
+    if rank == 0:
+        torch.save({"state": model.state_dict(), "optimizer": opt.state_dict(), "gk_extra": opt.extra_state_dict()}, ckpt)
+    hvd.barrier()
+    opt.close()
+    # ---- resume the way ssgd() does: rank 0 alone reads the file
+    model, opt = make()
+    if rank == 0:
+        ck = torch.load(ckpt, weights_only=False)
+        model.load_state_dict(ck["state"])
+        opt.load_state_dict(ck["optimizer"])
+        opt._init_fused_state_from_loaded()
+        opt.load_extra_state_dict(ck["gk_extra"])
+    hvd.broadcast_parameters(model.state_dict(), root_rank=0)
+    opt.sync_resume_state(root_rank=0)
+    assert opt._steps_done == 3
+    steps(model, opt, 3, 20)
+    flat = torch.cat([p.detach().reshape(-1) for p in model.parameters()])
+    mom = opt._mom.clone()
+    q.put((rank, flat.numpy().copy(), mom.numpy().copy()))
+    hvd.barrier()
+    opt.close()
+    hvd.shutdown()
+
+
+def test_resume_with_two_workers_keeps_replicas_identical(tmp_path):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    ckpt = str(tmp_path / "resume.pth")
+    procs = [ctx.Process(target=_resume_worker, args=(r, 2, port, ckpt, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in procs], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert (res[0][1] == res[1][1]).all() and (res[0][2] == res[1][2]).all()
+    assert abs(res[0][2]).sum() > 0
+
+
+def test_dense_synchronize_is_idempotent():
+    """synchronize(); clip; step() calls synchronize() twice per iteration (dist_trainer.py:80-86): the second
+    call must not exchange again (bucket: subtract/add the means twice; none: a second all-reduce)."""
+    m = _mlp()
+    opt = hvd.DistributedOptimizer(torch.optim.SGD(m.parameters(), lr=0.1), named_parameters=m.named_parameters(),
+                                   compression=compressors["bucket"], is_sparse=False, density=1,
+                                   dynamic_densities=None, force_compress=True)
+    x, y = torch.randn(8, 20), torch.randint(0, 5, (8,))
+    opt.zero_grad()
+    nn.functional.cross_entropy(m(x), y).backward()
+    opt.synchronize()
+    g1 = torch.cat([p.grad.reshape(-1).clone() for p in m.parameters()])
+    it = opt.train_iter
+    opt.synchronize()
+    g2 = torch.cat([p.grad.reshape(-1).clone() for p in m.parameters()])
+    assert torch.equal(g1, g2) and opt.train_iter == it
+    opt.step()
+    opt.close()
+
+
+def test_verify_mode_cross_checks_against_the_oracle(monkeypatch):
+    """GK_VERIFY_EVERY: every N-th step materialises the gradient and compares selection, received gradient
+    and (with >1 rank) replica checksums with the oracle."""
+    from gaussiank_sgd_b200 import settings
+    monkeypatch.setattr(settings, "VERIFY_EVERY", 2)
+    m = _mlp()
+    opt = hvd.DistributedOptimizer(torch.optim.SGD(m.parameters(), lr=0.1, momentum=0.9),
+                                   named_parameters=m.named_parameters(), compression=compressors["gaussian"],
+                                   is_sparse=True, density=0.05, threshold=524288000, dynamic_densities=None,
+                                   force_compress=True)
+    x, y = torch.randn(16, 20), torch.randint(0, 5, (16,))
+    for _ in range(5):
+        opt.zero_grad()
+        nn.functional.cross_entropy(m(x), y).backward()
+        opt.step()
+    assert opt.verified_steps == 3          # iterations 0, 2, 4
+    opt.close()

@@ -5,6 +5,7 @@ flushed between iterations).  Prints achieved GB/s against MEASURED_PEAKS.json.
     python tools/bench_chain.py [--n 25557032] [--comp gaussian] [--density 0.001] [--chunk 8192]
 """
 import argparse
+import ctypes as C
 import json
 import os
 import sys
@@ -13,6 +14,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from gaussiank_sgd_b200.ops import chain as ch  # noqa: E402
+from gaussiank_sgd_b200.ops import native as N  # noqa: E402
 from gaussiank_sgd_b200.utils.perf_model import measured_peaks  # noqa: E402
 
 
@@ -83,36 +85,37 @@ def main():
             name, med, best, bytes_per_elem, gbs, gbs / hbm, peaks["source"]))
 
     topk = a.comp in ("topk", "mink")
+    dgc = a.comp == "dgcsampling"
     def prep_k2():
         restore(); c.accumulate()
 
     def prep_k3():
         restore(); c.accumulate()
-        c.topk_select() if topk else c.count_pick()
+        if dgc:
+            N.check(c._lib.gk_dgc_select(C.byref(c._desc), C.c_uint64(1), torch.cuda.current_stream().cuda_stream))
+        elif topk:
+            c.topk_select()
+        else:
+            c.count_pick()
 
     report("K1 accumulate+moments", c.accumulate, 16.0, prep=restore)
-    if topk:
+    if dgc:
+        report("K9 dgc sample + select", lambda: N.check(c._lib.gk_dgc_select(
+            C.byref(c._desc), C.c_uint64(1), torch.cuda.current_stream().cuda_stream)), 12.0, prep=prep_k2)
+    elif topk:
         report("K4 radix x2 + count(gt,eq)", c.topk_select, 12.0, prep=prep_k2)
     else:
         report("K2 count+pick", c.count_pick, 4.0, prep=prep_k2)
-    if os.environ.get("GK_EXPERIMENT"):
-        for flag, name in ((1, "K2 without epilogue"),):
-            c._desc.rsv = flag
-            report(name, c.count_pick, 4.0, prep=prep_k2)
-        c._desc.rsv = 4
-        prep_k2(); c.ctrl.view(torch.int32)[18 + 45] = 0; torch.cuda.synchronize()
-        c.count_pick(); torch.cuda.synchronize()
-        ring = c.read_ctrl()["ring"]
-        t = [ring[i] for i in range(40, 46)]
-        print("K2 timeline (ns, rel. to block 0 start): last block end %d, epilogue start %d, after phase1 %d, after phase2 %d, after phase3 %d" % (
-            (t[5] - t[4]) & 0xffffffff, (t[0] - t[4]) & 0xffffffff, (t[1] - t[4]) & 0xffffffff, (t[2] - t[4]) & 0xffffffff, (t[3] - t[4]) & 0xffffffff))
-        c._desc.rsv = 0
     report("K3 compact+send", lambda: c.compact_send(dst), 4.0, prep=prep_k3)
-    report("chain (K1..K3)", lambda: c.compress(dst), 32.0 if topk else 24.0, prep=restore)
+    report("chain (K1..K3)", lambda: c.compress(dst, 1), 32.0 if (topk or dgc) else 24.0, prep=restore)
     dense = torch.zeros(total, device=dev)
     report("K5 scatter (recv)", lambda: ch.scatter(sb.src(), c.ctrl, dense, 1.0), 0.0)
     report("unscatter (zero_grad)", lambda: ch.unscatter(sb.src(), c.ctrl, dense), 0.0)
     report("K6 fused SGD", lambda: ch.sgd_step(P, G, M, tables, hyper), 20.0)
+    dense.zero_()
+    report("K6 folded recv+SGD", lambda: ch.sgd_recv_step(P, dense.view(torch.int32), M, tables, hyper, sb.src(), c.ctrl,
+                                                          1.0), 16.0)
+    assert int(torch.count_nonzero(dense)) == 0
     report("K8 grad norm", lambda: ch.grad_norm(G, tables, 1.0), 4.0)
     report("memset (torch zero_)", lambda: G.zero_(), 4.0)
     report("copy (torch, ref)", lambda: M.copy_(P), 8.0)
