@@ -111,6 +111,52 @@ def _host_batches(n, batch, rank, seed=0):
     return out
 
 
+def _common_config(world, compressor_key):
+    """The config keys both arms print (the driver compares them)."""
+    return {"model": "resnet50", "global_batch": BATCH_PER_GPU * world, "seq_len": None, "image": "3x224x224",
+            "parallelism": f"dp{world}", "compressor": "gaussiank", "density": DENSITY, "lr": LR,
+            "optimizer": "sgd momentum 0.875 wd 6.1e-5", "batch_per_gpu": BATCH_PER_GPU,
+            "l2": "no explicit flush: every step streams ~0.4 GB of arenas plus GBs of activations, far larger "
+                  "than the 126 MB L2", "registry_key": compressor_key}
+
+
+def _transport_selfcheck(hvd, compressors, device, world, steps=12):
+    """Same seed, same data, two transports: the in-kernel P2P exchange and the NCCL all-gather must leave
+    bit-identical parameters on every rank (rank-ordered sums on both paths).  A small MLP (cuBLAS only, no
+    atomics in the model) so that any difference can only come from the exchange."""
+    import torch
+    import torch.nn as nn
+    out = {}
+    for kind in ("p2p", "allgather"):
+        torch.manual_seed(1234)
+        model = nn.Sequential(nn.Linear(256, 1024), nn.ReLU(), nn.Linear(1024, 1024), nn.ReLU(),
+                              nn.Linear(1024, 100)).to(device)
+        base = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
+        opt = hvd.DistributedOptimizer(base, named_parameters=model.named_parameters(),
+                                       compression=compressors["gaussiank"], is_sparse=True, density=0.01,
+                                       threshold=524288000, dynamic_densities=None, transport=kind)
+        hvd.broadcast_parameters(model.state_dict(), root_rank=0)
+        g = torch.Generator().manual_seed(77 + hvd.rank())
+        for _ in range(steps):
+            x = torch.randn(64, 256, generator=g).to(device)
+            y = torch.randint(0, 100, (64,), generator=g).to(device)
+            opt.zero_grad()
+            nn.functional.cross_entropy(model(x), y).backward()
+            opt.step()
+        torch.cuda.synchronize(device)
+        opt.check_errors()
+        cs = opt.param_checksum()
+        allcs = [None] * world
+        torch.distributed.all_gather_object(allcs, cs)
+        out[kind] = (allcs, opt._groups[0].transport.name)
+        hvd.barrier()
+        opt.close()
+    same_ranks = all(c == out["p2p"][0][0] for c in out["p2p"][0]) and all(c == out["allgather"][0][0] for c in out["allgather"][0])
+    return {"p2p_equals_allgather": bool(same_ranks and out["p2p"][0][0] == out["allgather"][0][0]),
+            "selfcheck_replicas_identical": bool(same_ranks), "selfcheck_transports": [out["p2p"][1], out["allgather"][1]],
+            "selfcheck_steps": steps}
+
+
 # --------------------------------------------------------------------------- this framework
 def run_ours(args):
     import torch
@@ -175,6 +221,28 @@ def run_ours(args):
     clocks = sampler.stop() if rank == 0 else None
     opt.check_errors()
 
+    # ---- replica consistency of the run that was just timed: every rank checksums its parameter arena
+    cs = opt.param_checksum()
+    if world > 1:
+        allcs = [None] * world
+        torch.distributed.all_gather_object(allcs, cs)
+    else:
+        allcs = [cs]
+    replicas_identical = all(c == allcs[0] for c in allcs)
+    phase_means = None
+    if args.phases:
+        # in-step phase times: eager steps with CUDA events around compress / exchange+update
+        settings.CUDA_GRAPH = False
+        opt._profiling = True
+        opt._phase_events = []
+        for _ in range(44):
+            trainer.train_and_update()
+        trainer.flush_metrics()
+        opt._print_profiling()
+        phase_means = getattr(opt, "last_phase_means", None)
+        opt._profiling = False
+        settings.CUDA_GRAPH = not args.no_graph
+
     # ---- sparse path alone (compress + exchange + receive + zero), eager, CUDA events
     g0 = opt._groups[0]
     sel = opt.selected_num_gradients()
@@ -204,6 +272,9 @@ def run_ours(args):
     n_elem = g0.chain.n_total
     peaks = measured_peaks()
     chain_bytes = 24.0 * n_elem            # K1 16 B/elem (grad+resid read, acc+zero write), K2 4, K3 4
+    check = {}
+    if world > 1 and not args.no_selfcheck:
+        check = _transport_selfcheck(hvd, compressors, device, world)
     result = None
     if rank == 0:
         imgs = BATCH_PER_GPU * world * args.steps
@@ -211,20 +282,21 @@ def run_ours(args):
         e2e = imgs / (ms_b * 1e-3)
         result = {
             "metric": METRIC, "value": round(value, 2), "unit": "images/s", "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3) + 7, "ms_per_step": round(ms_a / args.steps, 4), "higher_is_better": True,
+            "warmup": args.warmup, "ms_per_step": round(ms_a / args.steps, 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic", "impl": "gaussiank_sgd_b200",
-            "config": {"model": "resnet50", "global_batch": BATCH_PER_GPU * world, "seq_len": None,
-                       "image": "3x224x224", "parallelism": f"dp{world}", "compressor": "gaussiank",
-                       "density": DENSITY, "optimizer": "sgd momentum 0.875 wd 6.1e-5", "lr": LR,
-                       "transport": transport.name + (":" + getattr(transport, "backend", "") if hasattr(transport, "backend") else ""),
-                       "cuda_graph": graphed, "channels_last": trainer.channels_last,
-                       "fused_bn_sites": getattr(trainer, "fused_bn_sites", 0),
-                       "model_rewrites": "own BN(+residual)(+ReLU)(+maxpool) kernels at every BatchNorm2d, stem 7x7/2 "
-                                         "convolution computed as 4x4 on the space-to-depth image (exact); same "
-                                         "parameters, same arithmetic as torchvision resnet50",
-                       "conv_math": "fp32 storage, cuDNN TF32 convolutions allowed (torch default), fp32 matmul",
-                       "l2": "no explicit flush: every step streams ~0.4 GB of arenas plus GBs of activations, "
-                             "far larger than the 126 MB L2"},
+            "config": _common_config(world, "gaussiank"),
+            "details": {"warmup_steps_run": max(args.warmup, 3) + 7,
+                        "transport": transport.name + (":" + getattr(transport, "backend", "") if hasattr(transport, "backend") else ""),
+                        "cuda_graph": graphed, "channels_last": trainer.channels_last,
+                        "folded_update": bool(getattr(trainer._graph, "folded", False)) if graphed else opt.can_fold(),
+                        "fused_bn_sites": getattr(trainer, "fused_bn_sites", 0),
+                        "model_rewrites": "own BN(+residual)(+ReLU)(+maxpool) kernels at every BatchNorm2d, stem 7x7/2 "
+                                          "convolution computed as 4x4 on the space-to-depth image (exact); same "
+                                          "parameters, same arithmetic as torchvision resnet50",
+                        "conv_math": "fp32 storage, cuDNN TF32 convolutions allowed (torch default), fp32 matmul",
+                        "phase_means_s": phase_means},
+            "replicas_identical": bool(replicas_identical),
+            **check,
             "clocks": clocks,
             "e2e": {"value": round(e2e, 2), "unit": "images/s", "ms_per_step": round(ms_b / args.steps, 4),
                     "h2d_bytes_per_step": trainer._prefetch.bytes,
@@ -304,16 +376,15 @@ def run_reference(args):
         imgs = BATCH_PER_GPU * world * args.steps
         result = {
             "metric": METRIC, "value": round(imgs / (ms_a * 1e-3), 2), "unit": "images/s", "n_gpus": world,
-            "steps": args.steps, "warmup": max(args.warmup, 3) + 7, "ms_per_step": round(ms_a / args.steps, 4),
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_a / args.steps, 4),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
             "impl": "reference",
-            "config": {"model": "resnet50", "global_batch": BATCH_PER_GPU * world, "seq_len": None,
-                       "image": "3x224x224", "parallelism": f"dp{world}", "compressor": "gaussian",
-                       "density": DENSITY, "lr": LR,
-                       "note": "unmodified reference from baseline/_ref driven like ssgd() with train(1, data=batch); "
-                               "horovod/mpi4py replaced by torch.distributed stand-ins (baseline/shims); "
-                               "settings.LOGGING_GRADIENTS=False; with one worker the reference does not compress "
-                               "(distributed_optimizer.py:97)"},
+            "config": _common_config(world, "gaussian"),
+            "details": {"warmup_steps_run": max(args.warmup, 3) + 7,
+                        "note": "unmodified reference from baseline/_ref driven like ssgd() with train(1, data=batch); "
+                                "horovod/mpi4py replaced by torch.distributed stand-ins (baseline/shims); "
+                                "settings.LOGGING_GRADIENTS=False; with one worker the reference does not compress "
+                                "(distributed_optimizer.py:97)"},
             "clocks": clocks,
             "e2e": {"value": round(imgs / (ms_b * 1e-3), 2), "unit": "images/s", "ms_per_step": round(ms_b / args.steps, 4),
                     "h2d_bytes_per_step": host[0][0].numel() * 4 + host[0][1].numel() * 8, "d2h_bytes_per_step": 4},
@@ -333,6 +404,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--transport", default=None)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-selfcheck", action="store_true", help="skip the P2P == all-gather transport self-check (N > 1)")
+    ap.add_argument("--phases", action="store_true", help="also report in-step phase times (44 extra eager steps)")
     args = ap.parse_args()
     if args.gpus > 1 and "RANK" not in os.environ:
         # convenience: re-launch ourselves under torchrun

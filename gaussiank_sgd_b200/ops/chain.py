@@ -376,26 +376,38 @@ class CompressChain:
 
 
 # ------------------------------------------------------------------- receive side / optimizer
+def _src_chunks(src: N.GkSrc):
+    """The receive kernels take at most GK_MAXP slots per launch: split a wider arena into rank-ordered views."""
+    if src.nsrc <= N.GK_MAXP:
+        yield src
+        return
+    for r0 in range(0, src.nsrc, N.GK_MAXP):
+        yield N.GkSrc(src.arena + 8 * r0 * src.slot_stride, src.slot_stride, src.parity_stride,
+                      min(N.GK_MAXP, src.nsrc - r0), src.wait, src.timeout_ns)
+
+
 def scatter(src: N.GkSrc, ctrl: torch.Tensor, grad: torch.Tensor, scale: float) -> None:
     """grad[idx] += val*scale over every slot, in rank order (distributed_optimizer.py:468-482): one launch
     for up to two sources, one launch per source rank beyond that (bit-identical sums on every replica)."""
     LAUNCHES["n"] += src.nsrc if (src.nsrc > 2 and grad.device.type == "cuda") else 1
-    if grad.device.type == "cuda":
-        N.check(N.cuda_lib().gk_scatter(C.byref(src), ctrl.data_ptr(), grad.data_ptr(), C.c_float(scale),
-                                        grad.numel(), _stream_ptr(grad.device)), "gk_scatter")
-    else:
-        N.check(N.cpu_lib().gkcpu_scatter(C.byref(src), ctrl.data_ptr(), grad.data_ptr(), C.c_float(scale),
-                                          grad.numel()), "gkcpu_scatter")
+    for part in _src_chunks(src):
+        if grad.device.type == "cuda":
+            N.check(N.cuda_lib().gk_scatter(C.byref(part), ctrl.data_ptr(), grad.data_ptr(), C.c_float(scale),
+                                            grad.numel(), _stream_ptr(grad.device)), "gk_scatter")
+        else:
+            N.check(N.cpu_lib().gkcpu_scatter(C.byref(part), ctrl.data_ptr(), grad.data_ptr(), C.c_float(scale),
+                                              grad.numel()), "gkcpu_scatter")
 
 
 def unscatter(src: N.GkSrc, ctrl: torch.Tensor, grad: torch.Tensor) -> None:
     LAUNCHES["n"] += 1
-    if grad.device.type == "cuda":
-        N.check(N.cuda_lib().gk_unscatter(C.byref(src), ctrl.data_ptr(), grad.data_ptr(), grad.numel(),
-                                          _stream_ptr(grad.device)), "gk_unscatter")
-    else:
-        N.check(N.cpu_lib().gkcpu_unscatter(C.byref(src), ctrl.data_ptr(), grad.data_ptr(), grad.numel()),
-                "gkcpu_unscatter")
+    for part in _src_chunks(src):
+        if grad.device.type == "cuda":
+            N.check(N.cuda_lib().gk_unscatter(C.byref(part), ctrl.data_ptr(), grad.data_ptr(), grad.numel(),
+                                              _stream_ptr(grad.device)), "gk_unscatter")
+        else:
+            N.check(N.cpu_lib().gkcpu_unscatter(C.byref(part), ctrl.data_ptr(), grad.data_ptr(), grad.numel()),
+                    "gkcpu_unscatter")
 
 
 class FlatTables:

@@ -120,17 +120,33 @@ class P2PTransport(Transport):
         self._symm_t = None
         self.backend = None
         errs = []
+        # Every attempt ends with a collective vote: a backend is used only if it came up on EVERY rank, so the
+        # ranks can never end up on different transports (or in different collectives) after a partial failure.
         if backend in ("auto", "symm"):
             try:
                 self._init_symm(words)
-                self.backend = "symm"
+                ok = True
             except Exception as e:  # noqa: BLE001 - any failure falls through to CUDA IPC
                 errs.append(f"symmetric memory: {type(e).__name__}: {e}")
+                ok = False
+            if _all_ranks_ok(ok, device):
+                self.backend = "symm"
+            else:
+                self._symm_t = None
                 if backend == "symm":
-                    raise
+                    raise RuntimeError("symmetric-memory transport did not come up on every rank: " + "; ".join(errs))
         if self.backend is None:
-            self._init_ipc(words)
-            self.backend = "ipc"
+            try:
+                self._init_ipc(words)
+                ok = True
+            except Exception as e:  # noqa: BLE001
+                errs.append(f"cuda ipc: {type(e).__name__}: {e}")
+                ok = False
+            if _all_ranks_ok(ok, device):
+                self.backend = "ipc"
+            else:
+                self._release_ipc()
+                raise RuntimeError("P2P transport did not come up on every rank: " + "; ".join(errs))
         self.errors = errs
         self.slot_stride = slot_stride
         parity_stride = self.P * slot_stride
@@ -194,21 +210,38 @@ class P2PTransport(Transport):
         torch.cuda.synchronize(self.device)
         return out
 
+    def _release_ipc(self):
+        lib = N.cuda_lib()
+        for p in self._ipc_ptrs:
+            lib.gk_ipc_close(p)
+        self._ipc_ptrs = []
+        if self._own_raw:
+            lib.gk_ipc_free(self._own_raw)
+            self._own_raw = None
+
     def close(self):
         if self.backend == "ipc":
-            lib = N.cuda_lib()
             torch.cuda.synchronize(self.device)
             comm.barrier()
-            for p in self._ipc_ptrs:
-                lib.gk_ipc_close(p)
-            self._ipc_ptrs = []
-            if self._own_raw:
-                lib.gk_ipc_free(self._own_raw)
-                self._own_raw = None
+            self._release_ipc()
+
+
+def _all_ranks_ok(ok: bool, device) -> bool:
+    """Collective AND of a per-rank success flag (one tiny all-reduce)."""
+    if not comm.is_distributed():
+        return ok
+    dev = device if dist.get_backend() == "nccl" else torch.device("cpu")
+    t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return bool(int(t.item()))
 
 
 def make_transport(cap: int, device, kind: Optional[str] = None) -> Transport:
-    """Pick the transport: ``GK_TRANSPORT`` = auto | p2p | symm | ipc | allgather."""
+    """Pick the transport: ``GK_TRANSPORT`` = auto | p2p | symm | ipc | allgather.
+
+    The P2P transport stores into at most ``GK_MAXP`` = 16 peers from one kernel (one NVSwitch domain of a
+    B200 node has 8 GPUs); larger worlds, worlds that span several nodes (no NVLink between them) and CPU runs
+    use the all-gather transport, whose receive side handles any number of ranks in chunks of 16."""
     kind = (kind or os.environ.get("GK_TRANSPORT", "auto")).lower()
     P = comm.size()
     if P == 1 and kind in ("auto", "local"):
@@ -216,10 +249,16 @@ def make_transport(cap: int, device, kind: Optional[str] = None) -> Transport:
     if device.type != "cuda" or kind == "allgather":
         return AllGatherTransport(cap, device)
     if kind in ("auto", "p2p", "symm", "ipc"):
+        multi_node = comm.local_size() < P
+        if P > N.GK_MAXP or multi_node:
+            if kind != "auto":
+                raise ValueError(f"transport {kind!r} needs all {P} ranks on one NVLink domain of at most "
+                                 f"{N.GK_MAXP} GPUs (local size {comm.local_size()}); use 'allgather' or 'auto'")
+            return AllGatherTransport(cap, device)
         try:
             return P2PTransport(cap, device, backend={"p2p": "auto"}.get(kind, kind),
                                 timeout_s=float(os.environ.get("GK_P2P_TIMEOUT_S", "20")))
-        except Exception as e:  # noqa: BLE001
+        except Exception as e:  # noqa: BLE001 - raised on every rank alike (collective vote inside)
             if kind != "auto":
                 raise
             import warnings
