@@ -524,7 +524,8 @@ __global__ void __launch_bounds__(GK_THREADS) k_radix_pass(GkChain c) {
 // reference's refinement loop replayed on the device, then the prefix sums K3 needs.
 // Leader work of the K2 epilogue for one segment: replay the reference's refinement loop on the
 // per-candidate totals and record the decision.
-__device__ void k2_decide_segment(const GkChain& c, int s, const GkSeg& sg, const uint32_t* tot, bool topk) {
+__device__ uint32_t k2_decide_segment(const GkChain& c, int s, const GkSeg& sg, const uint32_t* tot, bool topk,
+                                      int* chosen_out = nullptr) {
   GkSegStat* st = c.stat + s;
   const double k = (double)sg.k;
   int chosen = 0;
@@ -569,6 +570,8 @@ __device__ void k2_decide_segment(const GkChain& c, int s, const GkSeg& sg, cons
   }
   st->chosen = chosen;
   st->count = count;
+  if (chosen_out) *chosen_out = chosen;
+  return count;
 }
 
 // Epilogue shared by the threshold-count pass and the (gt,eq) pass: per-segment totals, the
@@ -695,75 +698,214 @@ __device__ void k2_epilogue(const GkChain& c, bool topk) {
 }
 
 
-// Counting rounds.  One warp per table entry: it reads the entry's row maxima, then only the rows that can
-// hold an element above the smallest candidate of the round, four rows in flight at a time, and leaves the
-// entry's count for every candidate of the round in its row of bcnt (plain stores: one writer per cell).
-// Totals go to stat.tot with integer atomics (commutative => deterministic).  Between rounds the blocks
-// meet at a grid-wide barrier (cooperative launch) whose last arrival replays the searches (k2_advance);
-// after the last round the last block to finish runs the prefix-sum epilogue for K3.
-template <int NR>
-__device__ __forceinline__ void count_rows(const float* __restrict__ a, const uint32_t* __restrict__ rmx, int len,
-                                           int gate, const float (&cs)[GK_RC], uint32_t (&cnt)[GK_RC], int lane) {
-  const int nrow = (len + GK_ROW - 1) / GK_ROW;
-  for (int rb = 0; rb < nrow; rb += 32) {
-    const int row = rb + lane;
-    const bool flag = row < nrow && (rmx == nullptr || (int)rmx[row] > gate);
-    uint32_t m = __ballot_sync(0xffffffffu, flag);
-    while (m) {                                     // warp-uniform: m is a ballot
-      int rr[4];
+// Counting rounds.  One warp per table entry.  With ~13 MB read at density 0.001 the kernel is pure latency, so
+// (a) the dependent memory round trips are kept to two before the rows arrive — the table entry, the entry's
+// row maxima and (one segment) the search state in the first, the rows that can hold an element above the
+// smallest candidate of the round in the second, up to GK_RB rows in flight through cp.async — and (b) the
+// executed code path is kept short (rows are consumed from shared memory in a rolled loop: these kernels run
+// once per step with a cold instruction cache, an unrolled body costs more in instruction fetches than in
+// issue slots).  The entry's count for every candidate of the round goes to its row of bcnt (plain stores:
+// one writer per cell), totals to stat.tot with integer atomics (commutative => deterministic).  Between
+// rounds the blocks meet at a grid-wide barrier (cooperative launch) whose last arrival replays the searches
+// (k2_advance) and, after the last round, computes the prefix sums K3 needs before it releases the others.
+#define GK_RB 8   /* rows in flight per warp */
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  const uint32_t sa = (uint32_t)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+
+// flags of up to 64 rows starting at row0: bit i set <=> row row0+i exists and may hold a selected element
+__device__ __forceinline__ uint64_t row_flags(uint32_t r0, uint32_t r1, int row0, int nrow, int lane, bool gated, int gate) {
+  const bool f0 = (row0 + lane < nrow) && (!gated || (int)r0 > gate);
+  const bool f1 = (row0 + 32 + lane < nrow) && (!gated || (int)r1 > gate);
+  return (uint64_t)__ballot_sync(0xffffffffu, f0) | ((uint64_t)__ballot_sync(0xffffffffu, f1) << 32);
+}
+
+// Bring the next (up to GK_RB) flagged rows into the warp's staging buffer; returns how many.  `m` loses the
+// rows taken.  Rows that end inside a float4 are loaded with guarded scalar loads (NaN padding).
+__device__ __forceinline__ int stage_rows(float4 (*buf)[32], const float* __restrict__ a, uint64_t& m, int row0,
+                                          int len, int lane) {
+  int nr = 0;
+#pragma unroll 1
+  for (; nr < GK_RB && m; ++nr) {
+    const int rr = row0 + __ffsll((long long)m) - 1;
+    m &= m - 1ull;
+    const int i0 = rr * GK_ROW + lane * 4;
+    if (i0 + 3 < len) cp_async16(&buf[nr][lane], a + i0);
+    else buf[nr][lane] = ld_row(a, rr, lane, len);
+  }
+  cp_async_wait_all();
+  __syncwarp();
+  return nr;
+}
+
+// Prefix sums of one segment's per-entry counts for candidate column `col` (merged-buffer mode, thresholds):
+// the short form of k2_epilogue — one decision, one column, no segment scan.
+__device__ void k2_epilogue_one(const GkChain& c) {
+  __shared__ uint32_t sscan1[T];
+  __shared__ int s_col;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int per = (c.nblk + T - 1) / T;
+  const int b0 = tid * per, b1 = min(c.nblk, b0 + per);
+  if (tid == 0) {
+    const GkSeg sg = c.seg[0];
+    uint32_t tot[GK_NC];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        rr[u] = m ? rb + __ffs(m) - 1 : -1;
-        m &= m - 1u;                                // 0 stays 0
-      }
-      float4 v[4];
-      const float qn = __int_as_float(0x7fc00000);
+    for (int j = 0; j < GK_NC; ++j) tot[j] = __ldcg(&c.stat[0].tot[j]);
+    int chosen;
+    const uint32_t count = k2_decide_segment(c, 0, sg, tot, false, &chosen);
+    c.stat[0].out_base = 0;
+    c.ctrl->total = count;
+    s_col = chosen;
+  }
+  __syncthreads();
+  const int col = s_col;
+  // all loads of a thread's run are issued unconditionally on clamped indices: one round trip instead of `per`
+  // serialised ones (a bounds check in front of each load stops the compiler from batching them)
+  constexpr int KEEP = 16;
+  uint32_t vg[KEEP];
+  uint32_t loc = 0;
+  if (per <= KEEP) {
 #pragma unroll
-      for (int u = 0; u < 4; ++u) v[u] = (rr[u] >= 0) ? ld_row(a, rr[u], lane, len) : make_float4(qn, qn, qn, qn);
+    for (int i = 0; i < KEEP; ++i) vg[i] = __ldcg(c.bcnt + (size_t)min(b0 + i, c.nblk - 1) * GK_NC + col);
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const float e0 = fabsf(v[u].x), e1 = fabsf(v[u].y), e2 = fabsf(v[u].z), e3 = fabsf(v[u].w);
+    for (int i = 0; i < KEEP; ++i) {
+      vg[i] = (i < per && b0 + i < b1) ? vg[i] : 0u;
+      loc += vg[i];
+    }
+  } else {
+    for (int b = b0; b < b1; ++b) loc += __ldcg(c.bcnt + (size_t)b * GK_NC + col);
+  }
+  sscan1[tid] = loc;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t carry = 0;
+    for (int base = 0; base < T; base += 32) {
+      const uint32_t v = sscan1[base + lane];
+      const uint32_t inc = warp_incl_scan_u(v, lane);
+      sscan1[base + lane] = carry + inc - v;
+      carry += __shfl_sync(0xffffffffu, inc, 31);
+    }
+  }
+  __syncthreads();
+  uint32_t run = sscan1[tid];
+  if (per <= KEEP) {
 #pragma unroll
-        for (int j = 0; j < NR; ++j)
-          cnt[j] += (uint32_t)(e0 > cs[j]) + (uint32_t)(e1 > cs[j]) + (uint32_t)(e2 > cs[j]) + (uint32_t)(e3 > cs[j]);
+    for (int i = 0; i < KEEP; ++i) {
+      if (i < per && b0 + i < b1) {
+        *reinterpret_cast<uint2*>(c.boff + 2 * (size_t)(b0 + i)) = make_uint2(run, 0u);
+        run += vg[i];
       }
     }
+  } else {
+    for (int b = b0; b < b1; ++b) {
+      *reinterpret_cast<uint2*>(c.boff + 2 * (size_t)b) = make_uint2(run, 0u);
+      run += __ldcg(c.bcnt + (size_t)b * GK_NC + col);
+    }
+  }
+  __syncthreads();
+}
+
+template <int NR>
+__device__ __forceinline__ void count_staged(const float4 (*buf)[32], int nr, const float (&cs)[GK_RC],
+                                             uint32_t (&cnt)[GK_RC], int lane) {
+#pragma unroll 1
+  for (int u = 0; u < nr; ++u) {
+    const float4 v = buf[u][lane];
+    const float e0 = fabsf(v.x), e1 = fabsf(v.y), e2 = fabsf(v.z), e3 = fabsf(v.w);
+#pragma unroll
+    for (int j = 0; j < NR; ++j)
+      cnt[j] += (uint32_t)(e0 > cs[j]) + (uint32_t)(e1 > cs[j]) + (uint32_t)(e2 > cs[j]) + (uint32_t)(e3 > cs[j]);
   }
 }
 
-__global__ void __launch_bounds__(GK_THREADS) k_count_rounds(GkChain c) {
-  __shared__ uint32_t s_tot[GK_RC];
-  __shared__ uint32_t s_gen, s_more;
-  __shared__ int s_last;
+__global__ void __launch_bounds__(GK_THREADS, 3) k_count_rounds(GkChain c) {
+  __shared__ float4 s_rows[NWARP][GK_RB][32];
+  __shared__ uint32_t s_tot[GK_RC], s_ci[GK_RC];
+  __shared__ float s_cand[GK_NC];
+  __shared__ int s_state[5];
+  __shared__ uint32_t s_gen, s_word;
+  __shared__ int s_last, s_nrc;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int noct = (c.nblk + NWARP - 1) / NWARP;
-  uint32_t* bar = c.ctrl->rsv;      // [0] arrivals, [1] generation, [2] "another round is needed"
-  if (tid == 0) s_gen = ld_relaxed_gpu_u32(bar + 1);
+  // ctrl->rsv[0] = arrivals, rsv[1] = generation word: advances by 2 per barrier, bit 0 = "another round follows"
+  uint32_t* bar = c.ctrl->rsv;
+  if (tid == 0) s_gen = ld_relaxed_gpu_u32(bar + 1) & ~1u;
   const bool one_seg = c.nseg == 1;
+  const bool dbg = (c.rsv & 4) != 0;               // tools/bench_chain.py --timeline: globaltimer stamps in ctrl->ring
+  if (dbg && tid == 0 && blockIdx.x == 0) c.ctrl->ring[44] = (uint32_t)globaltimer_ns();
   for (int round = 0; round < GK_NC + 1; ++round) {
     if (tid < GK_RC) s_tot[tid] = 0;
+    if (tid == 0) s_nrc = 0;
+    if (one_seg) {
+      // one segment: its search state is the same for every warp of the grid — one load per block, not one per
+      // warp (thousands of warps asking one L2 sector for the same words serialise there)
+      if (tid < GK_NC) s_cand[tid] = __ldcg(&c.stat->cand[tid]);
+      if (tid == 32) {
+        s_state[0] = __ldcg(&c.stat->done); s_state[1] = __ldcg(&c.stat->nrc); s_state[2] = __ldcg(&c.stat->gate);
+        const uint2 w = __ldcg(reinterpret_cast<const uint2*>(c.stat->rcand));
+        s_state[3] = (int)w.x; s_state[4] = (int)w.y;
+      }
+    }
     __syncthreads();
     for (int oct = blockIdx.x; oct < noct; oct += gridDim.x) {
       const int e = oct * NWARP + warp;
       if (e >= c.nblk) continue;                    // warp-uniform
+      // round trip 1: the entry, its first 64 row maxima and — when there is only one segment, so that its
+      // address is known — the search state; lane j holds candidate j
+      const uint32_t* __restrict__ rmx = c.rowmax ? c.rowmax + (size_t)e * c.rpb : nullptr;
+      uint32_t r0 = 0, r1 = 0;
+      if (rmx) {
+        if (lane < c.rpb) r0 = __ldcg(rmx + lane);
+        if (32 + lane < c.rpb) r1 = __ldcg(rmx + 32 + lane);
+      }
+      const GkSegStat* st = c.stat;
+      int done = 0, nrc = 0, gate = 0;
+      uint2 rcw = make_uint2(0u, 0u);
+      float cand_l = 0.f;
+      if (one_seg) {
+        done = s_state[0]; nrc = s_state[1]; gate = s_state[2];
+        rcw = make_uint2((uint32_t)s_state[3], (uint32_t)s_state[4]);         // rcand[0..7]
+        cand_l = s_cand[lane & (GK_NC - 1)];
+      }
       const GkBlk B = c.blk[e];
-      const GkSegStat* st = c.stat + B.seg;
-      if (__ldcg(&st->done)) continue;              // this segment's search is complete
-      const int nrc = __ldcg(&st->nrc), gate = __ldcg(&st->gate);
-      const uint2 rcw = __ldcg(reinterpret_cast<const uint2*>(st->rcand));   // rcand[0..7], 8-byte aligned
+      if (!one_seg) {                               // round trip 2 (several segments): this entry's segment
+        st = c.stat + B.seg;
+        done = __ldcg(&st->done); nrc = __ldcg(&st->nrc); gate = __ldcg(&st->gate);
+        rcw = __ldcg(reinterpret_cast<const uint2*>(st->rcand));
+        cand_l = __ldcg(&st->cand[lane & (GK_NC - 1)]);
+      }
+      if (done) continue;                           // this segment's search is complete (warp-uniform)
       float cs[GK_RC];
       uint32_t ci[GK_RC], cnt[GK_RC];
 #pragma unroll
       for (int j = 0; j < GK_RC; ++j) {
-        ci[j] = ((j < 4 ? rcw.x >> (8 * j) : rcw.y >> (8 * (j - 4))) & 0xffu);
-        cs[j] = (j < nrc) ? __ldcg(&st->cand[ci[j] & (GK_NC - 1)]) : __int_as_float(0x7f800000);   // +inf: never exceeded
+        ci[j] = ((j < 4 ? rcw.x >> (8 * j) : rcw.y >> (8 * (j - 4))) & 0xffu) & (GK_NC - 1);
+        const float cv = __shfl_sync(0xffffffffu, cand_l, (int)ci[j]);
+        cs[j] = (j < nrc) ? cv : __int_as_float(0x7f800000);   // +inf: never exceeded
         cnt[j] = 0;
       }
       const float* __restrict__ a = c.resid + B.start;
-      const uint32_t* __restrict__ rmx = c.rowmax ? c.rowmax + (size_t)e * c.rpb : nullptr;
-      if (nrc <= 1) count_rows<1>(a, rmx, B.len, gate, cs, cnt, lane);
-      else if (nrc <= 3) count_rows<3>(a, rmx, B.len, gate, cs, cnt, lane);
-      else count_rows<GK_RC>(a, rmx, B.len, gate, cs, cnt, lane);
+      const int nrow = (B.len + GK_ROW - 1) / GK_ROW;
+      // last round trip: the rows
+      for (int row0 = 0; row0 < nrow; row0 += 64) {
+        if (row0 && rmx) {                           // chunks above 8192 elements: further groups of 64 rows
+          r0 = (row0 + lane < nrow) ? __ldcg(rmx + row0 + lane) : 0u;
+          r1 = (row0 + 32 + lane < nrow) ? __ldcg(rmx + row0 + 32 + lane) : 0u;
+        }
+        uint64_t m = row_flags(r0, r1, row0, nrow, lane, rmx != nullptr, gate);
+        while (m) {                                  // warp-uniform: m comes from ballots
+          const int nr = stage_rows(s_rows[warp], a, m, row0, B.len, lane);
+          if (nrc <= 1) count_staged<1>(s_rows[warp], nr, cs, cnt, lane);
+          else if (nrc <= 3) count_staged<3>(s_rows[warp], nr, cs, cnt, lane);
+          else count_staged<GK_RC>(s_rows[warp], nr, cs, cnt, lane);
+          __syncwarp();                              // the buffer is refilled by the next batch
+        }
+      }
       uint32_t* brow = c.bcnt + (size_t)e * GK_NC;
 #pragma unroll
       for (int j = 0; j < GK_RC; ++j) {
@@ -771,28 +913,27 @@ __global__ void __launch_bounds__(GK_THREADS) k_count_rounds(GkChain c) {
           const uint32_t w = warp_sum_u(cnt[j]);
           if (lane == 0) {
             brow[ci[j]] = w;
-            if (w) {
-              if (one_seg) atomicAdd(&s_tot[j], w);
-              else atomicAdd(&c.stat[B.seg].tot[ci[j]], w);
-            }
+            if (one_seg) { if (w) atomicAdd(&s_tot[j], w); s_ci[j] = ci[j]; }
+            else if (w) atomicAdd(&c.stat[B.seg].tot[ci[j]], w);
           }
         }
       }
+      if (one_seg && lane == 0) s_nrc = nrc;
     }
     __syncthreads();
-    if (one_seg && tid < GK_RC && s_tot[tid]) {
-      const GkSegStat* st = c.stat;
-      if (tid < __ldcg(&st->nrc)) atomicAdd(&c.stat[0].tot[__ldcg(&st->rcand[tid])], s_tot[tid]);
-    }
+    if (one_seg && tid < s_nrc && s_tot[tid]) atomicAdd(&c.stat[0].tot[s_ci[tid]], s_tot[tid]);
     // ---- grid barrier; the last block to arrive advances every segment's search before releasing it
     __syncthreads();
     if (tid == 0) {
       __threadfence();
+      if (dbg) atomicMax(&c.ctrl->ring[45], (uint32_t)globaltimer_ns());
       s_last = (atomicAdd(bar, 1u) == gridDim.x - 1u);
     }
     __syncthreads();
+    const uint32_t gen_now = s_gen + 2u * (uint32_t)round;
     if (s_last) {
       __threadfence();
+      if (dbg && tid == 0) c.ctrl->ring[46] = (uint32_t)globaltimer_ns();
       int more = 0;
       for (int s = tid; s < c.nseg; s += T) {
         GkSegStat* st = c.stat + s;
@@ -803,59 +944,85 @@ __global__ void __launch_bounds__(GK_THREADS) k_count_rounds(GkChain c) {
         if (k2_advance(c, c.seg[s], st)) st->done = 1; else more = 1;
       }
       more = __syncthreads_or(more);
+      if (dbg && tid == 0) c.ctrl->ring[47] = (uint32_t)globaltimer_ns();
+      if (!more) {                                  // search complete everywhere: prefix sums for K3, then release
+        __threadfence();
+        if (one_seg) k2_epilogue_one(c); else k2_epilogue(c, false);
+        __syncthreads();
+      }
+      if (dbg && tid == 0) c.ctrl->ring[48] = (uint32_t)globaltimer_ns();
       if (tid == 0) {
         bar[0] = 0;
-        bar[2] = (uint32_t)more;
+        s_word = (gen_now + 2u) | (more ? 1u : 0u);
         __threadfence();
-        st_release_gpu_u32(bar + 1, s_gen + (uint32_t)round + 1u);
+        st_release_gpu_u32(bar + 1, s_word);
       }
     } else if (tid == 0) {
       const uint64_t t0 = globaltimer_ns();
-      while (ld_relaxed_gpu_u32(bar + 1) == s_gen + (uint32_t)round) {
-        if (globaltimer_ns() - t0 > 2000000000ull) { atomicExch(&c.ctrl->err, 3u); break; }
+      uint32_t w;
+      while (((w = ld_relaxed_gpu_u32(bar + 1)) & ~1u) == gen_now) {
+        if (globaltimer_ns() - t0 > 2000000000ull) { atomicExch(&c.ctrl->err, 3u); w = gen_now + 2u; break; }
+        __nanosleep(200);                           // hundreds of pollers on one L2 line: back off
       }
-    }
-    __syncthreads();
-    if (tid == 0) {
       __threadfence();
-      s_more = ld_relaxed_gpu_u32(bar + 2);
+      s_word = w;
     }
     __syncthreads();
-    if (!s_more) break;
+    if (!(s_word & 1u)) break;
   }
-  if (last_block_done(&c.ctrl->done[2])) k2_epilogue(c, false);
+  if (dbg && tid == 0) atomicMax(&c.ctrl->ring[49], (uint32_t)globaltimer_ns());
 }
 
 // top-k / DGC: per-entry counts of key > T (column 0) and key == T (column 1), one warp per entry, rows below
 // T skipped.  FIRST (DGC only) is the pass with the sampled threshold: its epilogue accepts the threshold when
 // at most 4k/3 elements pass it (compression.py:598), otherwise the exact radix select runs.
 template <bool MINK, bool FIRST>
-__global__ void __launch_bounds__(GK_THREADS) k_count_topk(GkChain c) {
+__global__ void __launch_bounds__(GK_THREADS, 3) k_count_topk(GkChain c) {
+  __shared__ float4 s_rows[NWARP][GK_RB][32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int e = (int)blockIdx.x * NWARP + warp;
-  if (e < c.nblk) {
-    const GkBlk B = c.blk[e];
+  // round trip 1: entry + row maxima (+ the threshold key when there is one segment: one load per block);
+  // last: the rows
+  const bool one_seg = c.nseg == 1, active = e < c.nblk;
+  __shared__ uint32_t s_tb;
+  const uint32_t* __restrict__ rmx = (active && c.rowmax && !MINK) ? c.rowmax + (size_t)e * c.rpb : nullptr;
+  uint32_t r0 = 0, r1 = 0;
+  GkBlk B = {0, 0, 0, 0};
+  if (active) {
+    if (rmx) {
+      if (lane < c.rpb) r0 = __ldcg(rmx + lane);
+      if (32 + lane < c.rpb) r1 = __ldcg(rmx + 32 + lane);
+    }
+    B = c.blk[e];
+  }
+  if (one_seg) {
+    if (tid == 0) s_tb = c.stat[0].tbits;
+    __syncthreads();
+  }
+  if (active) {
     GkSegStat* st = c.stat + B.seg;
-    const uint32_t tb = st->tbits;
+    const uint32_t tb = one_seg ? s_tb : st->tbits;
     uint32_t gt = 0, eq = 0;
     const float* __restrict__ a = c.resid + B.start;
-    const uint32_t* __restrict__ rmx = (c.rowmax && !MINK) ? c.rowmax + (size_t)e * c.rpb : nullptr;
     const int nrow = (B.len + GK_ROW - 1) / GK_ROW;
-    for (int rb = 0; rb < nrow; rb += 32) {
-      const int row = rb + lane;
-      const bool flag = row < nrow && (rmx == nullptr || rmx[row] >= tb);
-      uint32_t m = __ballot_sync(0xffffffffu, flag);
+    for (int row0 = 0; row0 < nrow; row0 += 64) {
+      if (row0 && rmx) {
+        r0 = (row0 + lane < nrow) ? __ldcg(rmx + row0 + lane) : 0u;
+        r1 = (row0 + 32 + lane < nrow) ? __ldcg(rmx + row0 + 32 + lane) : 0u;
+      }
+      // rows whose maximum key is >= tb: as a signed gate that is "> tb - 1" (tb <= 0x7fffffff)
+      uint64_t m = row_flags(r0, r1, row0, nrow, lane, rmx != nullptr, (int)tb - 1);
       while (m) {
-        int rr[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) { rr[u] = m ? rb + __ffs(m) - 1 : -1; m &= m - 1u; }
-        float4 v[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = (rr[u] >= 0) ? ld_row(a, rr[u], lane, B.len) : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const float ev[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
-          const int nv = (rr[u] >= 0) ? B.len - (rr[u] * GK_ROW + lane * 4) : 0;
+        const uint64_t mc = m;
+        const int nr = stage_rows(s_rows[warp], a, m, row0, B.len, lane);
+        uint64_t walk = mc;
+#pragma unroll 1
+        for (int u = 0; u < nr; ++u) {
+          const int rr = row0 + __ffsll((long long)walk) - 1;
+          walk &= walk - 1ull;
+          const float4 v = s_rows[warp][u][lane];
+          const float ev[4] = {v.x, v.y, v.z, v.w};
+          const int nv = B.len - (rr * GK_ROW + lane * 4);
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const uint32_t key = sel_key<MINK>(ev[j]);
@@ -863,6 +1030,7 @@ __global__ void __launch_bounds__(GK_THREADS) k_count_topk(GkChain c) {
             eq += (uint32_t)(j < nv && key == tb);
           }
         }
+        __syncwarp();
       }
     }
     gt = warp_sum_u(gt); eq = warp_sum_u(eq);
@@ -898,47 +1066,78 @@ __global__ void __launch_bounds__(GK_THREADS) k_count_topk(GkChain c) {
 // output position comes from K2's prefix sums; inside the entry the single warp walks the rows in order and
 // ranks the selected elements of a row with ballots, so the pairs leave in ascending index order.
 template <bool TOPK, bool MINK>
-__global__ void __launch_bounds__(GK_THREADS) k_compact_send(GkChain c, GkDst d) {
+__global__ void __launch_bounds__(GK_THREADS, 3) k_compact_send(GkChain c, GkDst d) {
+  __shared__ float4 s_rows[NWARP][GK_RB][32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t seqn = c.ctrl->seq + 1u;  // every block reads it before the last block bumps it
   const uint64_t poff = (uint64_t)(seqn & 1u) * d.parity_stride;
   const uint32_t cap = c.cap;
   const uint32_t lt = (1u << lane) - 1u;
   const int e = (int)blockIdx.x * NWARP + warp;
-  if (e < c.nblk) {
-    const GkBlk B = c.blk[e];
-    const GkSegStat* st = c.stat + B.seg;
-    const float thr = st->thr;
-    const uint32_t tb = st->tbits, ties = st->ties;
-    const uint32_t seg_first = (uint32_t)c.seg[B.seg].blk_begin;
-    const uint2 off_b = *reinterpret_cast<const uint2*>(c.boff + 2 * (size_t)e);
-    const uint2 off_s = *reinterpret_cast<const uint2*>(c.boff + 2 * (size_t)seg_first);
-    const uint32_t base_gt = st->out_base + (off_b.x - off_s.x);
+  const bool dbg = (c.rsv & 4) != 0;
+  if (dbg && tid == 0 && blockIdx.x == 0) c.ctrl->ring[50] = (uint32_t)globaltimer_ns();
+  // round trip 1: entry, its output offsets, its row maxima and (one segment: loaded once per block, every
+  // warp of the grid would otherwise ask one L2 sector for the same words) the decision; with several
+  // segments the decision is a second trip; the rows come last
+  const bool one_seg = c.nseg == 1, active = e < c.nblk;
+  __shared__ uint32_t s_dec[6];
+  const uint32_t* __restrict__ rmx = (active && c.rowmax && !(TOPK && MINK)) ? c.rowmax + (size_t)e * c.rpb : nullptr;
+  uint32_t r0 = 0, r1 = 0;
+  uint2 off_b = make_uint2(0u, 0u);
+  GkBlk B = {0, 0, 0, 0};
+  if (active) {
+    if (rmx) {
+      if (lane < c.rpb) r0 = __ldcg(rmx + lane);
+      if (32 + lane < c.rpb) r1 = __ldcg(rmx + 32 + lane);
+    }
+    off_b = __ldcg(reinterpret_cast<const uint2*>(c.boff + 2 * (size_t)e));
+    B = c.blk[e];
+  }
+  if (one_seg) {
+    if (tid == 0) {
+      const GkSegStat* st0 = c.stat;
+      s_dec[0] = __float_as_uint(st0->thr); s_dec[1] = st0->tbits; s_dec[2] = st0->ties; s_dec[3] = st0->out_base;
+      const uint2 o = __ldcg(reinterpret_cast<const uint2*>(c.boff));
+      s_dec[4] = o.x; s_dec[5] = o.y;
+    }
+    __syncthreads();
+  }
+  if (active) {
+    float thr;
+    uint32_t tb, ties, out_base;
+    uint2 off_s;
+    if (one_seg) {
+      thr = __uint_as_float(s_dec[0]); tb = s_dec[1]; ties = s_dec[2]; out_base = s_dec[3];
+      off_s = make_uint2(s_dec[4], s_dec[5]);
+    } else {
+      const GkSegStat* st = c.stat + B.seg;
+      thr = st->thr; tb = st->tbits; ties = st->ties; out_base = st->out_base;
+      off_s = __ldcg(reinterpret_cast<const uint2*>(c.boff + 2 * (size_t)c.seg[B.seg].blk_begin));
+    }
+    const uint32_t base_gt = out_base + (off_b.x - off_s.x);
     uint32_t gb = 0;                                         // gt elements of this entry before the current row
     uint32_t eb = TOPK ? (off_b.y - off_s.y) : 0u;           // eq elements of the segment before the current row
     float* __restrict__ a = c.resid + B.start;
-    const uint32_t* __restrict__ rmx = (c.rowmax && !(TOPK && MINK)) ? c.rowmax + (size_t)e * c.rpb : nullptr;
-    const int gate = gate_of(thr);
+    // rows that can hold a selected element: max > thr, or max key >= tb (> tb when no tie is taken)
+    const int gate = TOPK ? (ties ? (int)tb - 1 : (int)tb) : gate_of(thr);
     const int nrow = (B.len + GK_ROW - 1) / GK_ROW;
-    for (int rb = 0; rb < nrow; rb += 32) {
-      const int row = rb + lane;
-      bool flag = row < nrow;
-      if (flag && rmx) flag = TOPK ? (ties ? rmx[row] >= tb : rmx[row] > tb) : ((int)rmx[row] > gate);
-      uint32_t m = __ballot_sync(0xffffffffu, flag);
+    for (int row0 = 0; row0 < nrow; row0 += 64) {
+      if (row0 && rmx) {
+        r0 = (row0 + lane < nrow) ? __ldcg(rmx + row0 + lane) : 0u;
+        r1 = (row0 + 32 + lane < nrow) ? __ldcg(rmx + row0 + 32 + lane) : 0u;
+      }
+      uint64_t m = row_flags(r0, r1, row0, nrow, lane, rmx != nullptr, gate);
       while (m) {
-        int rr[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) { rr[u] = m ? rb + __ffs(m) - 1 : -1; m &= m - 1u; }
-        float4 v[4];
-        const float qn = __int_as_float(0x7fc00000);
-#pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = (rr[u] >= 0) ? ld_row(a, rr[u], lane, B.len) : make_float4(qn, qn, qn, qn);
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          if (rr[u] < 0) continue;                           // warp-uniform
-          const int i0 = rr[u] * GK_ROW + lane * 4;
+        uint64_t walk = m;
+        const int nr = stage_rows(s_rows[warp], a, m, row0, B.len, lane);
+#pragma unroll 1
+        for (int u = 0; u < nr; ++u) {
+          const int rr = row0 + __ffsll((long long)walk) - 1;
+          walk &= walk - 1ull;
+          const float4 v = s_rows[warp][u][lane];
+          const int i0 = rr * GK_ROW + lane * 4;
           const int nv = B.len - i0;
-          const float ev[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+          const float ev[4] = {v.x, v.y, v.z, v.w};
           uint32_t fgi = 0, fei = 0;                         // bit j: element j of this lane's quad is gt / eq
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -984,9 +1183,11 @@ __global__ void __launch_bounds__(GK_THREADS) k_compact_send(GkChain c, GkDst d)
           gb += tg;
           eb += te;
         }
+        __syncwarp();                                        // the staging buffer is refilled next
       }
     }
   }
+  if (dbg && lane == 0) atomicMax(&c.ctrl->ring[51], (uint32_t)globaltimer_ns());
   // Every block: bar.sync + one gpu-scope fence by thread 0 + ticket.  The last block then issues ONE
   // system-scope fence before the release store of the header: fences are cumulative, so the pairs the
   // other blocks stored to peer memory (ordered before their tickets at gpu scope) are ordered before
@@ -1003,6 +1204,7 @@ __global__ void __launch_bounds__(GK_THREADS) k_compact_send(GkChain c, GkDst d)
       c.ctrl->sent_total += sent;
       c.ctrl->ring[seqn & 63u] = total;
       c.ctrl->seq = seqn;
+      if (dbg) c.ctrl->ring[52] = (uint32_t)globaltimer_ns();
     }
   }
 }
@@ -1135,6 +1337,7 @@ __device__ __forceinline__ void gk_grid_barrier(uint32_t* bar, uint32_t gen, uin
       const uint64_t t0 = globaltimer_ns();
       while (ld_relaxed_gpu_u32(bar + 1) == gen) {
         if (globaltimer_ns() - t0 > 2000000000ull) { atomicExch(err, 3u); break; }
+        __nanosleep(400);
       }
     }
     __threadfence();
@@ -1148,8 +1351,10 @@ __global__ void __launch_bounds__(GK_THREADS) k_sgd_recv(GkRecvUpdDev u, GkSrc s
   __shared__ int s_bad;
   const int tid = threadIdx.x;
   if (tid == 0) { s_gen = ld_relaxed_gpu_u32(u.bar + 1); s_bad = 0; }
+  const bool dbg = (u.skip_dense & 4) != 0;        // tools/bench_chain.py --timeline
+  if (dbg && tid == 0 && blockIdx.x == 0) u.ctrl->ring[53] = (uint32_t)globaltimer_ns();
   // ---- phase A: dense update with a zero gradient (same arithmetic as k_sgd given g == 0)
-  if (!u.skip_dense) {
+  if (!(u.skip_dense & 1)) {
     for (int e = blockIdx.x; e < u.nblk; e += gridDim.x) {
       const GkBlk B = u.blk[e];
       const GkHyper h = u.hy[B.seg];
@@ -1173,6 +1378,7 @@ __global__ void __launch_bounds__(GK_THREADS) k_sgd_recv(GkRecvUpdDev u, GkSrc s
       }
     }
   }
+  if (dbg && tid == 0) atomicMax(&u.ctrl->ring[54], (uint32_t)globaltimer_ns());
   // ---- wait for the peers' headers (their pairs were stored before the release of the header)
   const uint32_t seq = u.ctrl->seq;
   const uint64_t* base = s.arena + (uint64_t)(seq & 1u) * s.parity_stride;
@@ -1207,7 +1413,9 @@ __global__ void __launch_bounds__(GK_THREADS) k_sgd_recv(GkRecvUpdDev u, GkSrc s
       }
     }
   }
+  if (dbg && tid == 0) atomicMax(&u.ctrl->ring[55], (uint32_t)globaltimer_ns());
   gk_grid_barrier(u.bar, s_gen, &u.ctrl->err);
+  if (dbg && tid == 0) atomicMax(&u.ctrl->ring[56], (uint32_t)globaltimer_ns());
   if (bad) return;
   // ---- pass 2: the lowest rank's pair owns the coordinate
   for (int r = 0; r < s.nsrc; ++r) {
@@ -1217,7 +1425,12 @@ __global__ void __launch_bounds__(GK_THREADS) k_sgd_recv(GkRecvUpdDev u, GkSrc s
       const uint64_t pr = __ldcg(pairs + j);
       const uint32_t idx = (uint32_t)pr;
       if (idx >= (uint32_t)u.nelem) continue;
+      // everything this coordinate may need is requested at once (p and m were written in phase A, possibly
+      // by another block: read them at L2); most coordinates have one owner and use all of it
       uint32_t w = __ldcg(u.mask + idx);
+      const float p_old = __ldcg(u.p + idx);
+      const float m_old = u.m ? __ldcg(u.m + idx) : 0.f;
+      const int gi = u.gmap ? (int)__ldg(u.gmap + (idx >> 6)) : 0;
       if (w == 0u || (int)(__ffs(w) - 1) != r) continue;
       float g = __fadd_rn(0.f, __fmul_rn(__uint_as_float((uint32_t)(pr >> 32)), u.scale));
       w &= w - 1u;
@@ -1234,19 +1447,19 @@ __global__ void __launch_bounds__(GK_THREADS) k_sgd_recv(GkRecvUpdDev u, GkSrc s
         if ((uint32_t)hit != idx) { atomicExch(&u.ctrl->err, 2u); continue; }   // list not index-sorted
         g = __fadd_rn(g, __fmul_rn(__uint_as_float((uint32_t)(hit >> 32)), u.scale));
       }
-      // p and m of this coordinate were written in phase A, possibly by another block: read them at L2
-      const GkHyper h = u.hy[u.gmap ? u.gmap[idx >> 6] : 0];
+      const GkHyper h = u.hy[gi];
       const bool has_m = (h.momentum != 0.f) && (u.m != nullptr);
       float du = g;
       if (has_m) {
         const float dm = h.first_step ? g : __fmul_rn(1.f - h.dampening, g);
-        u.m[idx] = __fadd_rn(__ldcg(u.m + idx), dm);
+        u.m[idx] = __fadd_rn(m_old, dm);
         du = h.nesterov ? __fmaf_rn(h.momentum, dm, g) : dm;
       }
-      u.p[idx] = __fmaf_rn(-h.lr, du, __ldcg(u.p + idx));
+      u.p[idx] = __fmaf_rn(-h.lr, du, p_old);
       u.mask[idx] = 0u;
     }
   }
+  if (dbg && tid == 0) atomicMax(&u.ctrl->ring[57], (uint32_t)globaltimer_ns());
 }
 
 // ------------------------------------------------------------------------------ K7 LARS

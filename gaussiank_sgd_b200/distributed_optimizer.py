@@ -145,6 +145,7 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         self._chunk = chunk
         self._transport_kind = transport
         self._random_seed = 0
+        self.graph_version = 0        # bumped whenever device pointers a captured step depends on change
         self._torch_select = False
         self._steal_req = settings.STEAL_GRADS if steal_grads is None else bool(steal_grads)
 
@@ -287,7 +288,6 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         self._layerwise_compressors = {':'.join(g.names): self._density for g in self._groups}
         if not self._active:
             return
-        dmax = max([self._density] + (self._dynamic_densities or []))
         for g in self._groups:
             if self._sparse:
                 comp = self._compressor
@@ -308,7 +308,7 @@ class _DistributedOptimizer(torch.optim.Optimizer):
                                    "the fused kernels cover %s", comp, sorted(_KERNEL_COMPRESSORS))
                 g.chain = ch.CompressChain(arena.grad, self._resid, g.segments, compressor=kcomp,
                                            density=min(self.get_current_density(), 0.999), use_residual=use_res,
-                                           zero_grad=True, chunk=self._chunk, max_density=min(dmax, 0.999))
+                                           zero_grad=True, chunk=self._chunk)
                 g.transport = make_transport(g.chain.cap, self.device,
                                              "allgather" if self._torch_select and size() > 1 else self._transport_kind)
                 if rank() == 0:
@@ -439,12 +439,30 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         return density
 
     def _apply_density(self):
+        """Push the current density into the chains.  The receive arenas follow it: their slots hold 8x k pairs
+        of the CURRENT density, so after the two warm-up epochs of the reference's schedule (:60) the
+        peer-mapped arena of ResNet-50 shrinks from 409 MB to 26 MB per rank.  Re-creating a transport is a
+        collective (every rank changes density at the same step) and invalidates captured CUDA graphs
+        (``graph_version``)."""
         if not (self._active and self._sparse):
             return
         d = min(self.get_current_density(), 0.999)
         for g in self._groups:
-            if g.chain is not None:
-                g.chain.set_density(d)
+            if g.chain is None:
+                continue
+            g.chain.set_density(d)
+            if g.chain.auto_cap and g.transport is not None and g.chain.cap_for(d) != g.chain.cap:
+                if self.device.type == "cuda":
+                    torch.cuda.synchronize(self.device)
+                g.transport.close()
+                g.transport = None
+                g.chain.set_cap(g.chain.cap_for(d))
+                g.transport = make_transport(g.chain.cap, self.device,
+                                             "allgather" if self._torch_select and size() > 1 else self._transport_kind)
+                self.graph_version += 1
+                if rank() == 0:
+                    logger.info('group %d: density %g -> slot capacity %d pairs (%.1f MB receive arena)', g.idx, d,
+                                g.chain.cap, 16e-6 * size() * (g.chain.cap + 2))
 
     def selected_num_gradients(self) -> List[int]:
         """Pairs selected by the most recent sends (<= 64, oldest first), read from the device-side ring
@@ -744,6 +762,10 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         if self._torch_select or self._verify_every:
             return False
         return all(g.transport is not None and g.transport.name in ("p2p", "local") for g in self._groups)
+
+    def read_overflow(self) -> int:
+        """Pairs withheld so far because a send exceeded the slot capacity (they stay in the residual)."""
+        return sum(int(g.chain.read_ctrl()["overflow"]) for g in self._groups if g.chain is not None and self._sparse)
 
     def check_errors(self) -> None:
         """Host-side check of the device error flags (receive timeouts).  Synchronises."""

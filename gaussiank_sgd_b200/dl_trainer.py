@@ -784,6 +784,8 @@ class DLTrainer:
                      and getattr(self.optimizer, 'graph_safe', False))
         n0 = LAUNCHES["n"]
         if use_graph:
+            if self._graph is not None and self._graph.version != getattr(self.optimizer, 'graph_version', 0):
+                self._graph = None             # the optimizer re-created buffers the captured step points at
             if self._graph is None:
                 self._graph = GraphedStep(self, clip_norm)
             hidden = self._graph.run(staged, hidden)
@@ -896,6 +898,7 @@ class GraphedStep:
         self.metrics = None
         self.folded = False
         self.has_status = False
+        self.version = getattr(trainer.optimizer, 'graph_version', 0)
 
     def _eager(self, staged, hidden):
         t = self.t

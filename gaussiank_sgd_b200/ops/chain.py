@@ -172,35 +172,53 @@ class CompressChain:
         self.nblk, self.nseg = blk.shape[0], segs.shape[0]
         self.n_total = int(segs["n"].sum())
         dev = self.device
-        self.blk = _to_dev(blk, dev)
-        self.seg = torch.zeros(self.nseg * SEG_DTYPE.itemsize, dtype=torch.uint8, device=dev)
-        self.part = torch.zeros(max(self.nblk, 1) * 4, dtype=torch.float64, device=dev)
-        self.stat = torch.zeros(self.nseg * STAT_DTYPE.itemsize, dtype=torch.uint8, device=dev)
-        self.bcnt = torch.zeros(max(self.nblk, 1) * N.GK_NC, dtype=torch.int32, device=dev)
-        self.boff = torch.zeros(max(self.nblk, 1) * 2, dtype=torch.int32, device=dev)
-        # largest |acc| bit pattern of every 128-element row of every table entry (written by K1, read by the
-        # later passes to skip rows that cannot hold a selected element)
-        self.rpb = (chunk + ROW - 1) // ROW
-        self.rowmax = torch.zeros(max(self.nblk, 1) * self.rpb, dtype=torch.int32, device=dev)
+        # Every table and scratch array of the chain lives in ONE allocation (views carved on 256-byte
+        # boundaries): the kernels of a step run with cold TLBs, and each separate allocation would cost the
+        # first warp that touches it a page walk in the middle of a latency-bound kernel.
         need_hist = self.mode in (N.MODE_TOPK, N.MODE_MINK, N.MODE_DGC)
-        self.hist = torch.zeros(self.nseg * N.GK_HIST_BINS if need_hist else 1, dtype=torch.int32, device=dev)
-        self.ctrl = torch.zeros(CTRL_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+        self.rpb = (chunk + ROW - 1) // ROW   # rows of the row-maximum table reserved per table entry
+        nb = max(self.nblk, 1)
+        layout = [("blk", nb * 16, torch.int32), ("seg", self.nseg * SEG_DTYPE.itemsize, torch.uint8),
+                  ("part", nb * 4 * 8, torch.float64), ("stat", self.nseg * STAT_DTYPE.itemsize, torch.uint8),
+                  ("bcnt", nb * N.GK_NC * 4, torch.int32), ("boff", nb * 2 * 4, torch.int32),
+                  ("rowmax", nb * self.rpb * 4, torch.int32),
+                  ("hist", (self.nseg * N.GK_HIST_BINS if need_hist else 1) * 4, torch.int32),
+                  ("ctrl", CTRL_DTYPE.itemsize, torch.uint8)]
+        off, offs = 0, {}
+        for name, nbytes, _dt in layout:
+            offs[name] = off
+            off += (nbytes + 255) // 256 * 256
+        self._scratch = torch.zeros(off + 256, dtype=torch.uint8, device=dev)
+        shift = (-self._scratch.data_ptr()) % 256
+        for name, nbytes, dt in layout:
+            view = self._scratch[shift + offs[name]: shift + offs[name] + nbytes]
+            setattr(self, name, view if dt == torch.uint8 else view.view(dt))
+        # largest |acc| bit pattern of every 128-element row of every table entry: self.rowmax (written by K1,
+        # read by the later passes to skip rows that cannot hold a selected element)
+        self.blk.copy_(torch.from_numpy(np.ascontiguousarray(blk).reshape(-1)))
         self._seg_pinned = None
         self.density = None
         dmax = max(density, max_density or density)
+        self.auto_cap = cap is None      # capacity follows the density (cap_for); an explicit cap is kept
         if cap is None:
-            # receive-slot capacity: 8x the largest k this run can ask for (the
-            # gaussian estimate selects up to ~10x k on skewed residuals); pairs beyond it stay in
-            # the residual (error feedback keeps them)
-            kmax = sum(compute_k(int(n), dmax) for n in segs["n"])
-            cap = max(8 * kmax, 1024)
-            cap = min(cap, max(self.n_total, 1024))
+            cap = self.cap_for(dmax)
         self.cap = int(cap)
         self.set_density(density)
         self._lib = N.cuda_lib() if self.is_cuda else N.cpu_lib()
         self._desc = self._make_desc()
 
     # ------------------------------------------------------------------ configuration
+    def cap_for(self, density: float) -> int:
+        """Receive-slot capacity for a density: 8x k (the gaussian estimate selects up to
+        ~10x k on skewed residuals); pairs beyond it stay in the residual (error feedback keeps them)."""
+        k = sum(compute_k(int(n), density) for n in self.seg_np["n"])
+        return int(min(max(8 * k, 1024), max(self.n_total, 1024)))
+
+    def set_cap(self, cap: int) -> None:
+        """New slot capacity (the caller re-creates the transport to match)."""
+        self.cap = int(cap)
+        self._desc.cap = self.cap
+
     def set_density(self, density: float, threshold_param: Optional[float] = None) -> None:
         """Rewrite k / zabs of every segment (only when the density changes, i.e. per epoch:
         distributed_optimizer.py:146-160)."""

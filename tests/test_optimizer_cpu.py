@@ -356,3 +356,30 @@ def test_verify_mode_cross_checks_against_the_oracle(monkeypatch):
         opt.step()
     assert opt.verified_steps == 3          # iterations 0, 2, 4
     opt.close()
+
+
+def test_receive_arena_follows_the_density_schedule():
+    """Slot capacity is 8x k of the CURRENT density: after the warm-up epochs the arena shrinks with it, the
+    graph version is bumped (captured steps must be re-captured) and training simply continues."""
+    torch.manual_seed(0)
+    m = nn.Sequential(nn.Linear(64, 512), nn.ReLU(), nn.Linear(512, 512), nn.ReLU(), nn.Linear(512, 10))
+    opt = hvd.DistributedOptimizer(torch.optim.SGD(m.parameters(), lr=0.05, momentum=0.9),
+                                   named_parameters=m.named_parameters(), compression=compressors["topk"],
+                                   is_sparse=True, density=0.001, threshold=524288000, force_compress=True)
+    n = sum(p.numel() for p in m.parameters())
+    x, y = torch.randn(8, 64), torch.randint(0, 10, (8,))
+    caps, versions = [], []
+    for epoch in range(3):
+        for _ in range(2):
+            opt.zero_grad()
+            nn.functional.cross_entropy(m(x), y).backward()
+            opt.step()
+        caps.append(opt._groups[0].chain.cap)
+        versions.append(opt.graph_version)
+        assert opt._groups[0].transport.src().slot_stride == caps[-1] + 2
+        opt.increase_one_epoch()
+    assert caps == [max(8 * int(n * d), 1024) for d in (0.015625, 0.004, 0.001)]
+    assert versions == [0, 1, 2]
+    assert opt.selected_num_gradients()[-1] == max(int(n * 0.001), 1)
+    assert opt.read_overflow() == 0
+    opt.close()

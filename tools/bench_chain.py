@@ -44,6 +44,7 @@ def main():
     ap.add_argument("--segments", type=int, default=1)
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--json", default=None)
+    ap.add_argument("--timeline", action="store_true")
     a = ap.parse_args()
     dev = "cuda"
     n = a.n
@@ -106,6 +107,22 @@ def main():
         report("K4 radix x2 + count(gt,eq)", c.topk_select, 12.0, prep=prep_k2)
     else:
         report("K2 count+pick", c.count_pick, 4.0, prep=prep_k2)
+    if a.timeline:
+        # globaltimer stamps written by the kernels when GkChain.rsv has bit 2 set (debug builds of the numbers only)
+        c._desc.rsv = 4
+        for name, fn, prep, idx in (("K2", c.count_pick, prep_k2, (44, 58, 61, 62, 63, 59, 60, 45, 46, 47, 48, 49)),
+                                    ("K3", lambda: c.compact_send(dst), prep_k3, (50, 51, 52))):
+            prep()
+            for i in idx:
+                c.ctrl.view(torch.int32)[18 + i] = 0
+            flush.add_(1.0) if flush is not None else None
+            torch.cuda.synchronize()
+            fn()
+            torch.cuda.synchronize()
+            ring = c.read_ctrl()["ring"]
+            t0 = ring[idx[0]]
+            print(name, "timeline ns since first block start:", [(ring[i] - t0) & 0xffffffff for i in idx[1:]])
+        c._desc.rsv = 0
     report("K3 compact+send", lambda: c.compact_send(dst), 4.0, prep=prep_k3)
     report("chain (K1..K3)", lambda: c.compress(dst, 1), 32.0 if (topk or dgc) else 24.0, prep=restore)
     dense = torch.zeros(total, device=dev)
@@ -116,6 +133,19 @@ def main():
     report("K6 folded recv+SGD", lambda: ch.sgd_recv_step(P, dense.view(torch.int32), M, tables, hyper, sb.src(), c.ctrl,
                                                           1.0), 16.0)
     assert int(torch.count_nonzero(dense)) == 0
+    if a.timeline:
+        for i in range(53, 58):
+            c.ctrl.view(torch.int32)[18 + i] = 0
+        flush.add_(1.0) if flush is not None else None
+        torch.cuda.synchronize()
+        u = N.GkRecvUpd(P.data_ptr(), M.data_ptr(), dense.data_ptr(), tables.group_blk_t.data_ptr(), hyper.data_ptr(),
+                        tables.gmap.data_ptr(), c.ctrl.data_ptr(), tables.bar.data_ptr(), 1.0, tables.nblk, dense.numel(), 4)
+        src = sb.src()
+        N.check(N.cuda_lib().gk_sgd_recv(C.byref(u), C.byref(src), torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+        ring = c.read_ctrl()["ring"]
+        print("K6 folded timeline ns since first block start (phase A end, pass 1 end, barrier exit, end):",
+              [(ring[i] - ring[53]) & 0xffffffff for i in range(54, 58)])
     report("K8 grad norm", lambda: ch.grad_norm(G, tables, 1.0), 4.0)
     report("memset (torch zero_)", lambda: G.zero_(), 4.0)
     report("copy (torch, ref)", lambda: M.copy_(P), 8.0)
