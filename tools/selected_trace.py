@@ -101,6 +101,10 @@ def run_reference(args):
                             dataset="imagenet", dnn="resnet50", lr=LR, nworkers=world, prefix="allreduce",
                             pretrain=None, num_steps=35, tb_writer=None)
     trainer.num_batches_per_epoch = args.epoch_steps
+    # the epoch roll-over of the reference's train() evaluates on rank 0 and re-seeds the sampler
+    # (dl_trainer.py:640-663); without a dataset directory neither attribute exists: one tiny batch, no sampler
+    trainer.testloader = [(torch.randn(2, 3, 224, 224), torch.randint(0, 1000, (2,)))]
+    trainer.train_sampler = None
     key = {"gaussiank": "gaussian"}.get(args.compressor, args.compressor)
     opt = rhvd.DistributedOptimizer(trainer.optimizer, named_parameters=trainer.net.named_parameters(),
                                     compression=rcomp.compressors[key], is_sparse=True, density=DENSITY,
