@@ -105,6 +105,9 @@ def run_reference(args):
     # (dl_trainer.py:640-663); without a dataset directory neither attribute exists: one tiny batch, no sampler
     trainer.testloader = [(torch.randn(2, 3, 224, 224), torch.randint(0, 1000, (2,)))]
     trainer.train_sampler = None
+    # ... and its test() cannot run on this torch (cal_accuracy views a non-contiguous tensor for top-5,
+    # dl_trainer.py:621): the roll-over only evaluates and checkpoints on the trainer whose rank is 0
+    trainer.rank = rank + 1000
     key = {"gaussiank": "gaussian"}.get(args.compressor, args.compressor)
     opt = rhvd.DistributedOptimizer(trainer.optimizer, named_parameters=trainer.net.named_parameters(),
                                     compression=rcomp.compressors[key], is_sparse=True, density=DENSITY,
