@@ -25,6 +25,56 @@ from .settings import formatter, logger
 writer = None
 
 
+NORM_CLIP = {'lstm': 0.25, 'lstman4': 400}      # gradient-norm clipping of the recurrent models (dist_trainer.py:50-54)
+
+
+def _merge_plan_inputs(trainer, rank):
+    """Layer-wise backward profile for the adaptive merge planners (dist_trainer.py:38-46): measured on every
+    rank, rank 0's timings are the ones everybody plans with.  (None, None) when the planners are off."""
+    if not (settings.ADAPTIVE_MERGE or settings.ADAPTIVE_SPARSE):
+        return None, None
+    names, times, sizes = benchmark(trainer)
+    times = hvd.comm.bcast_object(times, root=0)      # mpi4py comm.bcast in the reference
+    if rank == 0:
+        logger.info('layerwise backward times: %s', list(times))
+        logger.info('layerwise backward sizes: %s', list(sizes))
+    logger.info('Benchmarked backward time: %f', np.sum(times))
+    logger.info('Model size: %d', np.sum(sizes))
+    return names, times
+
+
+def _resume(trainer, optimizer):
+    """Second half of a resume (the first is DLTrainer loading ``--pretrain`` on rank 0): every rank adopts rank
+    0's position, optimizer state and schedule stage.  The reference restores the weights only."""
+    position = torch.tensor([float(trainer.get_train_epoch()), float(trainer.get_train_iter())])
+    position = hvd.broadcast(position, root_rank=0)
+    trainer.set_train_epoch(int(position[0]))
+    trainer.set_train_iter(int(position[1]))
+    hvd.broadcast_parameters(trainer.net.state_dict(), root_rank=0)
+    trainer.update_optimizer(optimizer)
+    trainer.restore_optimizer_state()
+    optimizer.sync_resume_state(root_rank=0)          # rank 0 alone has read the checkpoint
+    optimizer.train_epoch = max(optimizer.train_epoch, trainer.get_train_epoch())
+    optimizer._apply_density()
+
+
+def _step_reference_style(trainer, optimizer, dnn, nsteps_update, norm_clip, hidden):
+    """zero_grad / nsteps_update x train(1) / (clip) / update_model — the loop body of dist_trainer.py:70-86, used
+    when gradients are accumulated over several mini-batches."""
+    optimizer.zero_grad()
+    for j in range(nsteps_update):
+        optimizer.local = j < nsteps_update - 1       # only the last mini-batch communicates
+        if dnn == 'lstm':
+            _, hidden = trainer.train(1, hidden=hidden)
+        else:
+            trainer.train(1)
+    if norm_clip is not None:
+        optimizer.synchronize()
+        optimizer.clip_grad_norm(norm_clip)
+    trainer.update_model()
+    return hidden
+
+
 def ssgd(dnn, dataset, data_dir, nworkers, lr, batch_size, nsteps_update, max_epochs, nwpernode, pretrain,
          num_steps, compressor, density, threshold, gradient_path=None, max_iters=None, optimizer_name='sgd',
          synthetic_samples=None, transport=None, dynamic_densities="default", force_compress=False):
@@ -33,76 +83,33 @@ def ssgd(dnn, dataset, data_dir, nworkers, lr, batch_size, nsteps_update, max_ep
     use_cuda = torch.cuda.is_available() and os.environ.get("GK_FORCE_CPU", "0") != "1"
     if use_cuda:
         torch.cuda.set_device(hvd.local_rank() % max(torch.cuda.device_count(), 1))
-    if rank != 0:
-        pretrain = None
     trainer = DLTrainer(rank, nworkers, dist=False, batch_size=batch_size, is_weak_scaling=True,
                         ngpus=1 if use_cuda else 0, data_dir=data_dir, dataset=dataset, dnn=dnn, lr=lr,
-                        nworkers=nworkers, prefix='allreduce', pretrain=pretrain, num_steps=num_steps,
-                        tb_writer=writer, optimizer_name=optimizer_name, synthetic_samples=synthetic_samples)
-
-    init_epoch = torch.ones(1) * trainer.get_train_epoch()
-    init_iter = torch.ones(1) * trainer.get_train_iter()
-    trainer.set_train_epoch(int(hvd.broadcast(init_epoch, root_rank=0)[0]))
-    trainer.set_train_iter(int(hvd.broadcast(init_iter, root_rank=0)[0]))
-    is_sparse = density < 1
-
-    if settings.ADAPTIVE_MERGE or settings.ADAPTIVE_SPARSE:
-        seq_layernames, layerwise_times, layerwise_sizes = benchmark(trainer)
-        layerwise_times = hvd.comm.bcast_object(layerwise_times, root=0)   # mpi4py comm.bcast in the reference
-        if rank == 0:
-            logger.info('layerwise backward times: %s', list(layerwise_times))
-            logger.info('layerwise backward sizes: %s', list(layerwise_sizes))
-        logger.info('Bencharmked backward time: %f', np.sum(layerwise_times))
-        logger.info('Model size: %d', np.sum(layerwise_sizes))
-    else:
-        seq_layernames, layerwise_times, layerwise_sizes = None, None, None
-
-    norm_clip = None
-    if dnn == 'lstm':
-        norm_clip = 0.25
-    elif dnn == 'lstman4':
-        norm_clip = 400
-
+                        nworkers=nworkers, prefix='allreduce', pretrain=pretrain if rank == 0 else None,
+                        num_steps=num_steps, tb_writer=writer, optimizer_name=optimizer_name,
+                        synthetic_samples=synthetic_samples)
+    seq_layernames, layerwise_times = _merge_plan_inputs(trainer, rank)
+    norm_clip = NORM_CLIP.get(dnn)
     optimizer = hvd.DistributedOptimizer(trainer.optimizer, named_parameters=trainer.net.named_parameters(),
-                                         compression=compressors[compressor], is_sparse=is_sparse, density=density,
+                                         compression=compressors[compressor], is_sparse=density < 1, density=density,
                                          seq_layernames=seq_layernames, layerwise_times=layerwise_times,
                                          norm_clip=None, threshold=threshold, writer=writer,
                                          gradient_path=gradient_path, transport=transport,
                                          dynamic_densities=dynamic_densities, force_compress=force_compress)
-    hvd.broadcast_parameters(trainer.net.state_dict(), root_rank=0)
-    trainer.update_optimizer(optimizer)
-    trainer.restore_optimizer_state()
-    optimizer.sync_resume_state(root_rank=0)      # rank 0 alone has read the checkpoint
-    for _ in range(trainer.get_train_epoch()):      # resume: put the density schedule where it was
-        if optimizer.train_epoch < trainer.get_train_epoch():
-            optimizer.train_epoch += 1
-    optimizer._apply_density()
+    _resume(trainer, optimizer)
     iters_per_epoch = max(trainer.get_num_of_training_samples() // (nworkers * batch_size * nsteps_update), 1)
-
-    times = []
     logger.info('max_epochs: %d', max_epochs)
     display = 40 if iters_per_epoch > 40 else max(iters_per_epoch - 1, 1)
-    fused_loop = nsteps_update == 1
-    done = 0
+    times, done = [], 0
     for epoch in range(max_epochs):
         hidden = trainer.net.init_hidden() if dnn == 'lstm' else None
         for i in range(iters_per_epoch):
             s = time.time()
-            if fused_loop:
+            if nsteps_update == 1:
                 # zero_grad + forward/backward + exchange + (clip) + update as one (graph-captured) step
                 hidden = trainer.train_and_update(hidden=hidden, clip_norm=norm_clip)
             else:
-                optimizer.zero_grad()
-                for j in range(nsteps_update):
-                    optimizer.local = j < nsteps_update - 1
-                    if dnn == 'lstm':
-                        _, hidden = trainer.train(1, hidden=hidden)
-                    else:
-                        trainer.train(1)
-                if norm_clip is not None:
-                    optimizer.synchronize()
-                    optimizer.clip_grad_norm(norm_clip)
-                trainer.update_model()
+                hidden = _step_reference_style(trainer, optimizer, dnn, nsteps_update, norm_clip, hidden)
             times.append(time.time() - s)
             done += 1
             if i % display == 0 and i > 0:
