@@ -145,6 +145,7 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         self._chunk = chunk
         self._transport_kind = transport
         self._random_seed = 0
+        self.loss_scale = 1.0         # gradients arrive multiplied by this (fp16 training); divided out on receipt
         self.graph_version = 0        # bumped whenever device pointers a captured step depends on change
         self._torch_select = False
         self._steal_req = settings.STEAL_GRADS if steal_grads is None else bool(steal_grads)
@@ -646,7 +647,7 @@ class _DistributedOptimizer(torch.optim.Optimizer):
             if not torch.equal(mine[1].cpu(), acc_c[exp]):
                 raise RuntimeError(f"verify step {it} rank {me}: sent values differ from acc[idx]")
         dense = torch.zeros_like(acc_c)
-        scale = torch.tensor(1.0 / P, dtype=torch.float32)
+        scale = torch.tensor(1.0 / (P * self.loss_scale), dtype=torch.float32)
         for idx, val in lists:
             dense[idx.cpu()] += val.cpu() * scale
         if not torch.equal(dense, self._arena.grad.cpu()):
@@ -718,7 +719,7 @@ class _DistributedOptimizer(torch.optim.Optimizer):
             g._stolen = None               # the side stream has been joined: autograd's tensors may go
             if self._sparse:
                 with self._phase("comm"):
-                    ch.scatter(g.transport.src(), g.chain.ctrl, self._arena.grad, 1.0 / P)
+                    ch.scatter(g.transport.src(), g.chain.ctrl, self._arena.grad, 1.0 / (P * self.loss_scale))
                 if self._verify is not None and self._verify[0] is g:
                     self._verify_check()
             elif self._compressor == "bucket":
@@ -727,6 +728,8 @@ class _DistributedOptimizer(torch.optim.Optimizer):
                 if g.work is not None:
                     g.work.wait()
                     g.work = None
+                if self.loss_scale != 1.0:
+                    self._arena.grad[g.lo:g.hi].mul_(1.0 / self.loss_scale)
             g.launched = False
             g.pending = len(g.names)
         if any_launched:
@@ -804,6 +807,16 @@ class _DistributedOptimizer(torch.optim.Optimizer):
                 ch.lars_step(a.param, a.grad, self._mom, self._tables, self._hyper_dev)
         self._clip_coef = None
 
+    def set_loss_scale(self, scale: float) -> None:
+        """Static loss scale of fp16 training (dl_trainer.py:41-45 uses 128): the gradients, the residuals and the
+        pairs on the wire live in the scaled domain (selection is scale-invariant), the receive side divides by
+        it.  Supported on the sparse path and the dense all-reduce path with more than one worker (or
+        ``force_compress``); clipping thresholds refer to the unscaled gradient, so LSTM recipes use bf16."""
+        if scale != 1.0 and (not self._active or self._compressor == "bucket"):
+            raise ValueError("fp16 loss scaling needs the exchange path (several workers or force_compress)")
+        self.loss_scale = float(scale)
+        self.graph_version += 1
+
     def can_fold(self) -> bool:
         """True when the pending exchange can be finished by the folded receive+update kernel: sparse path,
         fused SGD, ONE group whose send side is (or is about to be) launched, index-sorted pair lists (every
@@ -836,7 +849,7 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         skip = all(pg.get("momentum", 0.0) == 0 and pg.get("weight_decay", 0.0) == 0 for pg in self.param_groups)
         with self._phase("comm+update"):
             ch.sgd_recv_step(a.param, a.grad.view(torch.int32), self._mom, self._tables, self._hyper_dev,
-                             g.transport.src(), g.chain.ctrl, 1.0 / size(), skip_dense=skip)
+                             g.transport.src(), g.chain.ctrl, 1.0 / (size() * self.loss_scale), skip_dense=skip)
         g.launched = False
         g.pending = len(g.names)
         g._stolen = None

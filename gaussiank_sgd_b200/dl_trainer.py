@@ -167,7 +167,15 @@ class DLTrainer:
         self.num_steps = num_steps
         self.ngpus = ngpus
         self.writer = tb_writer
+        # Mixed precision (dl_trainer.py:39-45, 256-259, 707-710: apex O2 with a static loss scale of 128, switched
+        # by settings.USE_FP16 or an ``amp_handle``): forward and backward run under torch.autocast; parameters,
+        # gradients, residuals and the sparse exchange stay fp32 in the arenas (apex O2 keeps fp32 master weights as
+        # well).  With fp16 the loss is multiplied by the static scale before backward and the optimizer divides
+        # the received gradient by it (DistributedOptimizer.loss_scale); bf16 needs no scaling.
         self.amp_handle = amp_handle
+        self.amp = bool(settings.USE_FP16 or amp_handle is not None)
+        self.amp_dtype = torch.bfloat16 if settings.AMP_DTYPE.lower() in ("bf16", "bfloat16") else torch.float16
+        self.loss_scale = settings.AMP_LOSS_SCALE if (self.amp and self.amp_dtype == torch.float16) else 1.0
         self.synthetic_samples = synthetic_samples
         self.batch_size = batch_size * self.ngpus if (self.ngpus > 0 and is_weak_scaling) else batch_size
         self.num_batches_per_epoch = -1
@@ -303,8 +311,18 @@ class DLTrainer:
     def get_num_of_training_samples(self):
         return len(self.trainset)
 
+    def _autocast(self):
+        return torch.autocast(self.device.type, dtype=self.amp_dtype, enabled=self.amp)
+
+    def _backward(self, loss):
+        (loss * self.loss_scale if self.loss_scale != 1.0 else loss).backward()
+
     def update_optimizer(self, optimizer):
         self.optimizer = optimizer
+        if self.loss_scale != 1.0:
+            if not hasattr(optimizer, 'set_loss_scale'):
+                raise ValueError('fp16 loss scaling needs the DistributedOptimizer wrapper (GK_AMP_DTYPE=bf16 does not)')
+            optimizer.set_loss_scale(self.loss_scale)
         self._graph = None
 
     def finish(self):
@@ -691,7 +709,12 @@ class DLTrainer:
         self._prefetch.release(getattr(self, '_cur_slot', None))
 
     def _forward_loss(self, staged, hidden=None):
-        """Forward + loss; returns (loss, outputs-or-None, labels-or-None, hidden)."""
+        """Forward + loss (under autocast when mixed precision is on); returns (loss, outputs-or-None,
+        labels-or-None, hidden)."""
+        with self._autocast():
+            return self._forward_loss_impl(staged, hidden)
+
+    def _forward_loss_impl(self, staged, hidden=None):
         if self.dnn == 'lstman4':
             inputs, labels_cpu, input_sizes, target_sizes = staged
             out, output_sizes = self.net(inputs, input_sizes)
@@ -727,7 +750,7 @@ class DLTrainer:
             self.forwardtime += (time.time() - sforward)
             sbackward = time.time()
             with _nvtx('gk:backward'):
-                loss.backward()
+                self._backward(loss)
             acc1 = self.cal_accuracy(outputs, labels, topk=(1,))[0] if outputs is not None else None
             self._enqueue_metrics(loss, acc1)
             self._release_inputs()
@@ -794,7 +817,7 @@ class DLTrainer:
             with _nvtx('gk:forward'):
                 loss, outputs, labels, hidden = self._forward_loss(staged, hidden)
             with _nvtx('gk:backward'):
-                loss.backward()
+                self._backward(loss)
             acc1 = self.cal_accuracy(outputs, labels, topk=(1,))[0] if outputs is not None else None
             if clip_norm is not None and hasattr(self.optimizer, 'clip_grad_norm'):
                 self.optimizer.synchronize()
@@ -907,7 +930,7 @@ class GraphedStep:
         with _nvtx('gk:forward'):
             loss, outputs, labels, hidden = t._forward_loss(staged, hidden)
         with _nvtx('gk:backward'):
-            loss.backward()
+            t._backward(loss)
         acc1 = t.cal_accuracy(outputs, labels, topk=(1,))[0] if outputs is not None else loss.new_zeros(())
         self.folded = self.clip_norm is None and opt.can_fold()
         if self.folded:

@@ -52,7 +52,10 @@ if ADAPTIVE_MERGE:
     PREFIX = PREFIX + '-ada'
 
 TENSORBOARD = _flag("TENSORBOARD", False)
-USE_FP16 = _flag("USE_FP16", False)
+USE_FP16 = _flag("USE_FP16", False)                  # mixed precision (settings.py:28): autocast forward/backward,
+#   fp32 master weights / gradients / residuals / exchange in the arenas (what apex O2 keeps in fp32 too)
+AMP_DTYPE = os.environ.get("GK_AMP_DTYPE", "fp16")   # fp16 (the reference's apex O2, static loss scale 128) | bf16
+AMP_LOSS_SCALE = float(os.environ.get("GK_AMP_LOSS_SCALE", "128"))   # dl_trainer.py:41-45
 
 MAX_EPOCHS = int(os.environ.get("GK_MAX_EPOCHS", "10"))
 

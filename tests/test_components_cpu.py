@@ -326,3 +326,42 @@ def test_log_parsing_plots_and_rank_flags(tmp_path):
     np.save(str(tmp_path / 'g.npy'), np.random.randn(1000))
     assert os.path.getsize(plotting.plot_gradient_distribution([str(tmp_path / 'g.npy')], ['g'], str(tmp_path / 'c.png'))) > 100
     assert rank_flags.selection_overlap([[1, 2, 3], [3, 4], [3]], 6).tolist() == [2, 3, 0, 1]
+
+
+def test_mixed_precision_bf16_and_fp16_loss_scale(monkeypatch):
+    """settings.USE_FP16 (dl_trainer.py:39-45, 256-259): autocast forward/backward over fp32 arenas; fp16 adds the
+    reference's static loss scale, which the optimizer divides out on receipt — the update must match an
+    unscaled fp32 run of the same (scale-invariant) top-k selection closely."""
+    import torch
+    import gaussiank_sgd_b200.distributed_optimizer as hvd
+    from gaussiank_sgd_b200 import settings
+    from gaussiank_sgd_b200.compression import compressors
+    from gaussiank_sgd_b200.dl_trainer import DLTrainer
+
+    def run(amp, dtype):
+        monkeypatch.setattr(settings, "USE_FP16", amp)
+        monkeypatch.setattr(settings, "AMP_DTYPE", dtype)
+        torch.manual_seed(0)
+        t = DLTrainer(0, 1, dist=False, batch_size=8, ngpus=0, data_dir="synthetic", dataset="mnist", dnn="mnistnet",
+                      lr=0.05, nworkers=1, synthetic_samples=64)
+        opt = hvd.DistributedOptimizer(t.optimizer, named_parameters=t.net.named_parameters(),
+                                       compression=compressors["topk"], is_sparse=True, density=0.05,
+                                       threshold=524288000, dynamic_densities=None, force_compress=True)
+        t.update_optimizer(opt)
+        g = torch.Generator().manual_seed(5)
+        x, y = torch.randn(8, 1, 28, 28, generator=g), torch.randint(0, 10, (8,), generator=g)
+        for _ in range(3):
+            t.train_and_update(data=(x, y))
+        t.flush_metrics()
+        w = torch.cat([p.detach().reshape(-1) for p in t.net.parameters()]).clone()
+        scale = opt.loss_scale
+        opt.close()
+        return w, scale, t.loss
+
+    w32, s32, l32 = run(False, "fp16")
+    wbf, sbf, lbf = run(True, "bf16")
+    assert s32 == 1.0 and sbf == 1.0
+    assert torch.isfinite(wbf).all() and (wbf - w32).abs().max() < 0.05 and abs(lbf - l32) < 0.2
+    w16, s16, l16 = run(True, "fp16")
+    assert s16 == 128.0
+    assert torch.isfinite(w16).all() and (w16 - w32).abs().max() < 0.05      # scaled in, divided out
