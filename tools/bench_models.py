@@ -42,8 +42,8 @@ def run_one(cfg, args):
     name, dnn, dataset, batch, lr, comp, density, clip, num_steps = cfg
     rank, world = hvd.rank(), hvd.size()
     device = hvd.comm.device()
-    trainer = DLTrainer(rank, world, dist=False, batch_size=batch, is_weak_scaling=True, ngpus=1,
-                        data_dir="synthetic", dataset=dataset, dnn=dnn, lr=lr, nworkers=world, prefix="bench",
+    trainer = DLTrainer(rank, world, dist=False, batch_size=batch, is_weak_scaling=True,
+                        ngpus=1 if device.type == "cuda" else 0, data_dir="synthetic", dataset=dataset, dnn=dnn, lr=lr, nworkers=world, prefix="bench",
                         num_steps=num_steps, synthetic_samples=batch * world * 64)
     opt = hvd.DistributedOptimizer(trainer.optimizer, named_parameters=trainer.net.named_parameters(),
                                    compression=compressors[comp], is_sparse=density < 1, density=density,
@@ -56,18 +56,26 @@ def run_one(cfg, args):
     for _ in range(max(args.warmup, 3) + 4):
         hidden = trainer.train_and_update(hidden=hidden, clip_norm=clip)
     trainer.flush_metrics()
-    torch.cuda.synchronize()
+    cuda = device.type == "cuda"
+    import time
+    if cuda:
+        torch.cuda.synchronize()
     hvd.barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
-    e0.record()
+    if cuda:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+    t0 = time.perf_counter()
     for _ in range(args.steps):
         hidden = trainer.train_and_update(hidden=hidden, clip_norm=clip)
     trainer.flush_metrics()
-    e1.record()
-    torch.cuda.synchronize()
+    if cuda:
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+    else:
+        ms = (time.perf_counter() - t0) * 1e3            # CPU / gloo run (BASELINE.json config 1)
     hvd.barrier()
-    ms = e0.elapsed_time(e1)
     if world > 1:
         t = torch.tensor([ms], dtype=torch.float64, device=device)
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
@@ -86,8 +94,120 @@ def run_one(cfg, args):
     if hasattr(opt, "close"):
         opt.close()
     del trainer, opt
-    torch.cuda.empty_cache()
+    if torch.cuda.is_available():
+        torch.cuda.empty_cache()
     return res
+
+
+def _ref_batches(dnn, batch, num_steps, rank, n=4):
+    """Synthetic host batches in the formats the reference's train() unpacks (dl_trainer.py:665-680)."""
+    import torch
+    g = torch.Generator().manual_seed(99 + rank)
+    out = []
+    for _ in range(n):
+        if dnn == "lstm":
+            x = torch.randint(0, 10000, (batch, num_steps), generator=g)
+            out.append((x, torch.roll(x, -1, 1)))
+        elif dnn == "lstman4":
+            T = int(torch.randint(100, 400, (1,), generator=g))
+            x = torch.randn(batch, 1, 161, T, generator=g)
+            sizes = torch.randint(5, 20, (batch,), generator=g).int()
+            out.append((x, torch.randint(1, 29, (int(sizes.sum()),), generator=g).int(), torch.ones(batch), sizes))
+        else:
+            out.append((torch.randn(batch, 3, 32, 32, generator=g), torch.randint(0, 10, (batch,), generator=g)))
+    return out
+
+
+def run_reference_one(cfg, args, mods):
+    """The UNMODIFIED reference (baseline/_ref over baseline/shims, as in bench.py --impl reference) on the same
+    configuration, driven like the body of its ssgd() loop (dist_trainer.py:70-86).  Its registry key for the
+    configured compressor is used as is — at the reference's HEAD ``topk`` runs ``uniform_abs_topk``
+    (compression.py:191)."""
+    import time
+    import torch
+    rhvd, rcomp, rdl = mods
+    name, dnn, dataset, batch, lr, comp, density, clip, num_steps = cfg
+    rank, world = rhvd.rank(), rhvd.size()
+    cuda = torch.cuda.is_available() and os.environ.get("GK_FORCE_CPU", "0") != "1"
+    if comp == "none" and world > 1:
+        return {"config": name, "impl": "reference", "unavailable": "the reference's dense path unpacks three values "
+                "from NoneCompressor.compress, which returns two (distributed_optimizer.py:407): it raises with >1 worker"}
+    rdl.DLTrainer.vocab_size = 10000          # set by ptb_prepare() only when a data directory exists
+    datadir = os.path.join(ROOT, "baseline", "_ref", "audio_data") if dnn == "lstman4" else None
+    trainer = rdl.DLTrainer(rank, world, dist=False, batch_size=batch, is_weak_scaling=True, ngpus=1 if cuda else 0,
+                            data_dir=None, dataset=dataset, dnn=dnn, lr=lr, nworkers=world, prefix="allreduce",
+                            pretrain=None, num_steps=num_steps, tb_writer=None) if dnn != "lstman4" else None
+    if trainer is None:
+        return {"config": name, "impl": "reference", "unavailable": "DLTrainer('lstman4') needs audio_data/data_loader.py "
+                "and decoder.py, which the reference imports and does not ship (dl_trainer.py:456-457)"}
+    trainer.num_batches_per_epoch = 10 ** 6
+    key = {"gaussiank": "gaussian"}.get(comp, comp)
+    opt = rhvd.DistributedOptimizer(trainer.optimizer, named_parameters=trainer.net.named_parameters(),
+                                    compression=rcomp.compressors[key], is_sparse=density < 1, density=density,
+                                    seq_layernames=None, layerwise_times=None, norm_clip=None, threshold=524288000,
+                                    writer=None, gradient_path=None)
+    rhvd.broadcast_parameters(trainer.net.state_dict(), root_rank=0)
+    trainer.update_optimizer(opt)
+    opt.train_epoch = 2                        # density schedule -> the configured value
+    data = _ref_batches(dnn, batch, num_steps, rank)
+    hidden = [trainer.net.init_hidden()] if dnn == "lstm" else [None]
+
+    def step(i):
+        opt.zero_grad()
+        opt.local = False
+        if dnn == "lstm":
+            _, hidden[0] = trainer.train(1, data=data[i % len(data)], hidden=hidden[0])
+        else:
+            trainer.train(1, data=data[i % len(data)])
+        if clip is not None:
+            opt.synchronize()
+            torch.nn.utils.clip_grad_norm_(trainer.net.parameters(), clip)
+        trainer.update_model()
+
+    for i in range(max(args.warmup, 3) + 4):
+        step(i)
+    if cuda:
+        torch.cuda.synchronize()
+    if world > 1:
+        torch.distributed.barrier()
+    t0 = time.perf_counter()
+    if cuda:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+    for i in range(args.steps):
+        step(i)
+    if cuda:
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+    else:
+        ms = (time.perf_counter() - t0) * 1e3
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda" if cuda else "cpu")
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        ms = float(t.item())
+    res = {"config": name, "impl": "reference", "model": dnn, "n_gpus": world if cuda else 0, "n_workers": world,
+           "batch_per_gpu": batch, "compressor": key, "density": density, "clip_norm": clip, "steps": args.steps,
+           "ms_per_step": round(ms / args.steps, 4), "samples_per_s": round(batch * world * args.steps / (ms * 1e-3), 1),
+           "data": "synthetic", "dtype": "fp32",
+           "note": "one worker: the reference does not compress (distributed_optimizer.py:97)" if world == 1 else ""}
+    del trainer, opt
+    if cuda:
+        torch.cuda.empty_cache()
+    return res
+
+
+def _reference_modules():
+    sys.path[:0] = [os.path.join(ROOT, "baseline", "shims"), os.path.join(ROOT, "baseline", "_ref")]
+    import logging
+    import settings as rsettings
+    rsettings.LOGGING_GRADIENTS = False
+    rsettings.logger.setLevel(logging.WARNING)
+    import compression as rcomp
+    import distributed_optimizer as rhvd
+    import dl_trainer as rdl
+    rhvd.init()
+    return rhvd, rcomp, rdl
 
 
 def main():
@@ -97,21 +217,31 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--only", default=None)
     ap.add_argument("--out", default=None)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     args = ap.parse_args()
     if args.gpus > 1 and "RANK" not in os.environ:
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 400),
                os.path.abspath(__file__)] + sys.argv[1:]
         sys.exit(subprocess.call(cmd))
-    import gaussiank_sgd_b200.distributed_optimizer as hvd
-    hvd.init()
+    if args.impl == "reference":
+        if not os.path.isfile(os.path.join(ROOT, "baseline", "_ref", "distributed_optimizer.py")):
+            print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref missing: run tools/install_reference.sh"}))
+            return
+        mods = _reference_modules()
+        hvd = mods[0]
+        hvd.barrier = lambda: None
+        hvd.shutdown = lambda: None
+    else:
+        import gaussiank_sgd_b200.distributed_optimizer as hvd
+        hvd.init()
     only = set(args.only.split(",")) if args.only else None
     out = []
     for cfg in CONFIGS:
         if only and cfg[0] not in only and cfg[1] not in only:
             continue
         try:
-            res = run_one(cfg, args)
+            res = run_reference_one(cfg, args, mods) if args.impl == "reference" else run_one(cfg, args)
         except Exception as e:  # noqa: BLE001 — one failing configuration must not hide the others
             import traceback
             traceback.print_exc()
