@@ -1062,38 +1062,127 @@ __global__ void __launch_bounds__(GK_THREADS, 3) k_count_topk(GkChain c) {
 }
 
 // ------------------------------------------------------- K3 select + compact + residual + send
-// One warp per table entry, rows without a selected element skipped via the row maxima.  The entry's first
-// output position comes from K2's prefix sums; inside the entry the single warp walks the rows in order and
-// ranks the selected elements of a row with ballots, so the pairs leave in ascending index order.
+// Rows are skipped via the row maxima, the flagged ones staged through cp.async and consumed in rolled loops;
+// the entry's first output position comes from K2's prefix sums and the elements' ranks from ballots, so the
+// pairs leave in ascending index order.  Work is split two ways, because both shapes occur:
+//   * the usual entry has a handful of flagged rows: ONE warp walks them in order (no block-level exchange;
+//     all ~3 000 entries of ResNet-50 are in flight at once, the kernel is a few memory round trips long);
+//   * in training the selected coordinates cluster in a few tensors whose entries have every row flagged: a
+//     single warp walking 64 rows was the long tail of the first gated version (69 us in the step against 23
+//     on uniformly spread data).  Entries with more than GK_K3_SOLO flagged rows are therefore left to the
+//     whole block afterwards: warp w takes rows 8w .. 8w+7 of every 64-row group and one shared-memory
+//     exchange of the per-warp counts gives the warps their bases.
+// Entries are dealt to the warps of a block with a stride of the grid size, so that the entries of one tensor
+// land in different blocks.
+#define GK_K3_SOLO 16
+
+struct K3Dec { float thr; uint32_t tb, ties; };
+
+// which elements of the staged rows are selected: 4 bits per row in fg (above the threshold / key) and fe (ties)
+template <bool TOPK, bool MINK>
+__device__ __forceinline__ void k3_classify(const float4 (*buf)[32], int nr, uint64_t walk, int row0, int len, int lane,
+                                            const K3Dec& dec, uint32_t& fg, uint32_t& fe) {
+  fg = 0; fe = 0;
+#pragma unroll 1
+  for (int u = 0; u < nr; ++u) {
+    const int rr = row0 + __ffsll((long long)walk) - 1;
+    walk &= walk - 1ull;
+    const float4 v = buf[u][lane];
+    const int nv = len - (rr * GK_ROW + lane * 4);
+    const float ev[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (TOPK) {
+        const uint32_t key = sel_key<MINK>(ev[j]);
+        if (j < nv && key > dec.tb) fg |= 1u << (4 * u + j);
+        if (j < nv && key == dec.tb) fe |= 1u << (4 * u + j);
+      } else {
+        if (fabsf(ev[j]) > dec.thr) fg |= 1u << (4 * u + j);  // padding reads as NaN: never selected
+      }
+    }
+  }
+}
+
+// store the selected elements of the staged rows; gb / eb = selected before the first of these rows
+template <bool TOPK>
+__device__ __forceinline__ void k3_emit(const float4 (*buf)[32], int nr, uint64_t walk, int row0, int lane, uint32_t fg,
+                                        uint32_t fe, uint32_t& gb, uint32_t& eb, uint32_t base_gt, uint32_t ties,
+                                        uint32_t cap, const GkDst& d, uint64_t poff, float* __restrict__ a, int start) {
+  const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll 1
+  for (int u = 0; u < nr; ++u) {
+    const int rr = row0 + __ffsll((long long)walk) - 1;
+    walk &= walk - 1ull;
+    const uint32_t fgi = (fg >> (4 * u)) & 15u, fei = (fe >> (4 * u)) & 15u;
+    if (__ballot_sync(0xffffffffu, (fgi | fei) != 0u) == 0u) continue;  // warp-uniform
+    uint32_t gbefore = gb, ebefore = eb, tg = 0, te = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      // lanes hold 4 consecutive elements each: everything in lower lanes precedes this lane
+      const uint32_t bg = __ballot_sync(0xffffffffu, (fgi >> j) & 1u);
+      gbefore += __popc(bg & lt);
+      tg += __popc(bg);
+      if (TOPK) {
+        const uint32_t be = __ballot_sync(0xffffffffu, (fei >> j) & 1u);
+        ebefore += __popc(be & lt);
+        te += __popc(be);
+      }
+    }
+    if (fgi | fei) {
+      const float4 v = buf[u][lane];
+      const float ev[4] = {v.x, v.y, v.z, v.w};
+      const int i0 = rr * GK_ROW + lane * 4;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const bool isg = (fgi >> j) & 1u, ise = (fei >> j) & 1u;
+        if (isg || (ise && ebefore < ties)) {
+          const uint32_t pos = base_gt + gbefore + (ebefore < ties ? ebefore : ties);
+          if (pos < cap) {
+            const uint32_t idx = (uint32_t)(start + i0 + j);
+            const uint64_t pair = (uint64_t)idx | ((uint64_t)__float_as_uint(ev[j]) << 32);
+            for (int q = 0; q < d.ndst; ++q) d.slot[q][poff + GK_SLOT_HDR + pos] = pair;
+            a[i0 + j] = 0.f;  // sent => leaves the residual
+          }
+        }
+        gbefore += isg ? 1u : 0u;
+        ebefore += ise ? 1u : 0u;
+      }
+    }
+    gb += tg;
+    eb += te;
+  }
+}
+
 template <bool TOPK, bool MINK>
 __global__ void __launch_bounds__(GK_THREADS, 3) k_compact_send(GkChain c, GkDst d) {
   __shared__ float4 s_rows[NWARP][GK_RB][32];
+  __shared__ uint32_t s_wcnt[2][NWARP];
+  __shared__ uint32_t s_dec[6];
+  __shared__ int s_dense[NWARP];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t seqn = c.ctrl->seq + 1u;  // every block reads it before the last block bumps it
   const uint64_t poff = (uint64_t)(seqn & 1u) * d.parity_stride;
   const uint32_t cap = c.cap;
-  const uint32_t lt = (1u << lane) - 1u;
-  const int e = (int)blockIdx.x * NWARP + warp;
+  const bool one_seg = c.nseg == 1;
+  const bool use_rmx = c.rowmax != nullptr && !(TOPK && MINK);
   const bool dbg = (c.rsv & 4) != 0;
   if (dbg && tid == 0 && blockIdx.x == 0) c.ctrl->ring[50] = (uint32_t)globaltimer_ns();
-  // round trip 1: entry, its output offsets, its row maxima and (one segment: loaded once per block, every
-  // warp of the grid would otherwise ask one L2 sector for the same words) the decision; with several
-  // segments the decision is a second trip; the rows come last
-  const bool one_seg = c.nseg == 1, active = e < c.nblk;
-  __shared__ uint32_t s_dec[6];
-  const uint32_t* __restrict__ rmx = (active && c.rowmax && !(TOPK && MINK)) ? c.rowmax + (size_t)e * c.rpb : nullptr;
+  // entry of warp w: w * gridDim.x + blockIdx.x — issue its loads before the block-level state is exchanged
+  const int e = warp * (int)gridDim.x + (int)blockIdx.x;
+  const bool active = e < c.nblk;
   uint32_t r0 = 0, r1 = 0;
   uint2 off_b = make_uint2(0u, 0u);
   GkBlk B = {0, 0, 0, 0};
   if (active) {
-    if (rmx) {
-      if (lane < c.rpb) r0 = __ldcg(rmx + lane);
-      if (32 + lane < c.rpb) r1 = __ldcg(rmx + 32 + lane);
+    if (use_rmx) {
+      const uint32_t* q = c.rowmax + (size_t)e * c.rpb;
+      if (lane < c.rpb) r0 = __ldcg(q + lane);
+      if (32 + lane < c.rpb) r1 = __ldcg(q + 32 + lane);
     }
     off_b = __ldcg(reinterpret_cast<const uint2*>(c.boff + 2 * (size_t)e));
     B = c.blk[e];
   }
-  if (one_seg) {
+  if (one_seg) {                           // the single segment's decision: one load per block
     if (tid == 0) {
       const GkSegStat* st0 = c.stat;
       s_dec[0] = __float_as_uint(st0->thr); s_dec[1] = st0->tbits; s_dec[2] = st0->ties; s_dec[3] = st0->out_base;
@@ -1102,89 +1191,91 @@ __global__ void __launch_bounds__(GK_THREADS, 3) k_compact_send(GkChain c, GkDst
     }
     __syncthreads();
   }
-  if (active) {
-    float thr;
-    uint32_t tb, ties, out_base;
-    uint2 off_s;
+  // decision of the segment an entry belongs to
+  auto decision = [&](const GkBlk& Bx, K3Dec& dec, uint32_t& out_base, uint2& off_s) {
     if (one_seg) {
-      thr = __uint_as_float(s_dec[0]); tb = s_dec[1]; ties = s_dec[2]; out_base = s_dec[3];
+      dec.thr = __uint_as_float(s_dec[0]); dec.tb = s_dec[1]; dec.ties = s_dec[2]; out_base = s_dec[3];
       off_s = make_uint2(s_dec[4], s_dec[5]);
     } else {
-      const GkSegStat* st = c.stat + B.seg;
-      thr = st->thr; tb = st->tbits; ties = st->ties; out_base = st->out_base;
-      off_s = __ldcg(reinterpret_cast<const uint2*>(c.boff + 2 * (size_t)c.seg[B.seg].blk_begin));
+      const GkSegStat* st = c.stat + Bx.seg;
+      dec.thr = st->thr; dec.tb = st->tbits; dec.ties = st->ties; out_base = st->out_base;
+      off_s = __ldcg(reinterpret_cast<const uint2*>(c.boff + 2 * (size_t)c.seg[Bx.seg].blk_begin));
     }
-    const uint32_t base_gt = out_base + (off_b.x - off_s.x);
-    uint32_t gb = 0;                                         // gt elements of this entry before the current row
-    uint32_t eb = TOPK ? (off_b.y - off_s.y) : 0u;           // eq elements of the segment before the current row
-    float* __restrict__ a = c.resid + B.start;
+  };
+  // ---- solo pass: every warp its own entry, unless the entry has too many flagged rows
+  bool dense = false;
+  if (active) {
+    K3Dec dec; uint32_t out_base; uint2 off_s;
+    decision(B, dec, out_base, off_s);
     // rows that can hold a selected element: max > thr, or max key >= tb (> tb when no tie is taken)
-    const int gate = TOPK ? (ties ? (int)tb - 1 : (int)tb) : gate_of(thr);
+    const int gate = TOPK ? (dec.ties ? (int)dec.tb - 1 : (int)dec.tb) : gate_of(dec.thr);
     const int nrow = (B.len + GK_ROW - 1) / GK_ROW;
-    for (int row0 = 0; row0 < nrow; row0 += 64) {
-      if (row0 && rmx) {
-        r0 = (row0 + lane < nrow) ? __ldcg(rmx + row0 + lane) : 0u;
-        r1 = (row0 + 32 + lane < nrow) ? __ldcg(rmx + row0 + 32 + lane) : 0u;
-      }
-      uint64_t m = row_flags(r0, r1, row0, nrow, lane, rmx != nullptr, gate);
-      while (m) {
-        uint64_t walk = m;
-        const int nr = stage_rows(s_rows[warp], a, m, row0, B.len, lane);
-#pragma unroll 1
-        for (int u = 0; u < nr; ++u) {
-          const int rr = row0 + __ffsll((long long)walk) - 1;
-          walk &= walk - 1ull;
-          const float4 v = s_rows[warp][u][lane];
-          const int i0 = rr * GK_ROW + lane * 4;
-          const int nv = B.len - i0;
-          const float ev[4] = {v.x, v.y, v.z, v.w};
-          uint32_t fgi = 0, fei = 0;                         // bit j: element j of this lane's quad is gt / eq
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            if (TOPK) {
-              const uint32_t key = sel_key<MINK>(ev[j]);
-              if (j < nv && key > tb) fgi |= 1u << j;
-              if (j < nv && key == tb) fei |= 1u << j;
-            } else {
-              if (fabsf(ev[j]) > thr) fgi |= 1u << j;        // padding reads as NaN: never selected
-            }
-          }
-          if (__ballot_sync(0xffffffffu, (fgi | fei) != 0u) == 0u) continue;  // warp-uniform
-          uint32_t gbefore = gb, ebefore = eb, tg = 0, te = 0;
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            // lanes hold 4 consecutive elements each: everything in lower lanes precedes this lane
-            const uint32_t bg = __ballot_sync(0xffffffffu, (fgi >> j) & 1u);
-            gbefore += __popc(bg & lt);
-            tg += __popc(bg);
-            if (TOPK) {
-              const uint32_t be = __ballot_sync(0xffffffffu, (fei >> j) & 1u);
-              ebefore += __popc(be & lt);
-              te += __popc(be);
-            }
-          }
-          if (fgi | fei) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const bool isg = (fgi >> j) & 1u, ise = (fei >> j) & 1u;
-              if (isg || (ise && ebefore < ties)) {
-                const uint32_t pos = base_gt + gbefore + (ebefore < ties ? ebefore : ties);
-                if (pos < cap) {
-                  const uint32_t idx = (uint32_t)(B.start + i0 + j);
-                  const uint64_t pair = (uint64_t)idx | ((uint64_t)__float_as_uint(ev[j]) << 32);
-                  for (int q = 0; q < d.ndst; ++q) d.slot[q][poff + GK_SLOT_HDR + pos] = pair;
-                  a[i0 + j] = 0.f;  // sent => leaves the residual
-                }
-              }
-              gbefore += isg ? 1u : 0u;
-              ebefore += ise ? 1u : 0u;
-            }
-          }
-          gb += tg;
-          eb += te;
-        }
+    uint64_t m = row_flags(r0, r1, 0, nrow, lane, use_rmx, gate);
+    dense = nrow > 64 || __popcll(m) > GK_K3_SOLO;
+    if (!dense) {
+      const uint32_t base_gt = out_base + (off_b.x - off_s.x);
+      uint32_t gb = 0, eb = TOPK ? (off_b.y - off_s.y) : 0u;
+      float* __restrict__ a = c.resid + B.start;
+      while (m) {                                            // at most GK_K3_SOLO / GK_RB batches
+        const uint64_t walk = m;
+        const int nr = stage_rows(s_rows[warp], a, m, 0, B.len, lane);
+        uint32_t fg, fe;
+        k3_classify<TOPK, MINK>(s_rows[warp], nr, walk, 0, B.len, lane, dec, fg, fe);
+        k3_emit<TOPK>(s_rows[warp], nr, walk, 0, lane, fg, fe, gb, eb, base_gt, dec.ties, cap, d, poff, a, B.start);
         __syncwarp();                                        // the staging buffer is refilled next
       }
+    }
+  }
+  if (lane == 0) s_dense[warp] = dense ? 1 : 0;
+  __syncthreads();
+  // ---- cooperative pass: the whole block on every entry that was left over (block-uniform loop)
+  int par = 0;
+  for (int w2 = 0; w2 < NWARP; ++w2) {
+    if (!s_dense[w2]) continue;
+    const int e2 = w2 * (int)gridDim.x + (int)blockIdx.x;
+    const GkBlk B2 = c.blk[e2];
+    const uint2 ob = __ldcg(reinterpret_cast<const uint2*>(c.boff + 2 * (size_t)e2));
+    K3Dec dec; uint32_t out_base; uint2 off_s;
+    decision(B2, dec, out_base, off_s);
+    const int gate = TOPK ? (dec.ties ? (int)dec.tb - 1 : (int)dec.tb) : gate_of(dec.thr);
+    const uint32_t base_gt = out_base + (ob.x - off_s.x);
+    const uint32_t base_eq = TOPK ? (ob.y - off_s.y) : 0u;
+    float* __restrict__ a = c.resid + B2.start;
+    const uint32_t* __restrict__ rmx = use_rmx ? c.rowmax + (size_t)e2 * c.rpb : nullptr;
+    const int nrow = (B2.len + GK_ROW - 1) / GK_ROW;
+    uint32_t run_gt = 0, run_eq = 0;       // selected in earlier 64-row groups of this entry
+    for (int row0 = 0; row0 < nrow; row0 += 64) {
+      uint32_t q0 = 0, q1 = 0;
+      if (rmx) {
+        q0 = (row0 + lane < nrow) ? __ldcg(rmx + row0 + lane) : 0u;
+        q1 = (row0 + 32 + lane < nrow) ? __ldcg(rmx + row0 + 32 + lane) : 0u;
+      }
+      const uint64_t mall = row_flags(q0, q1, row0, nrow, lane, rmx != nullptr, gate);
+      if (mall == 0ull) continue;                            // block-uniform: every warp sees all 64 flags
+      uint64_t m = mall & (0xffull << (8 * warp));           // this warp's eight rows
+      const uint64_t walk = m;
+      const int nr = stage_rows(s_rows[warp], a, m, row0, B2.len, lane);
+      uint32_t fg, fe;
+      k3_classify<TOPK, MINK>(s_rows[warp], nr, walk, row0, B2.len, lane, dec, fg, fe);
+      const uint32_t wsum = warp_sum_u((uint32_t)__popc(fg) | ((uint32_t)__popc(fe) << 16));
+      if (lane == 0) s_wcnt[par][warp] = wsum;
+      __syncthreads();
+      uint32_t wbase = 0, total = 0;
+#pragma unroll
+      for (int w = 0; w < NWARP; ++w) {
+        const uint32_t x = s_wcnt[par][w];
+        if (w < warp) wbase += x;
+        total += x;
+      }
+      par ^= 1;
+      if (wsum != 0) {                                       // warp-uniform
+        uint32_t gb = run_gt + (wbase & 0xffffu);            // gt elements of the entry before this warp's rows
+        uint32_t eb = base_eq + run_eq + (wbase >> 16);      // eq elements of the segment before them
+        k3_emit<TOPK>(s_rows[warp], nr, walk, row0, lane, fg, fe, gb, eb, base_gt, dec.ties, cap, d, poff, a, B2.start);
+      }
+      __syncwarp();                                          // the staging buffer is refilled next
+      run_gt += total & 0xffffu;
+      run_eq += total >> 16;
     }
   }
   if (dbg && lane == 0) atomicMax(&c.ctrl->ring[51], (uint32_t)globaltimer_ns());
@@ -1917,10 +2008,10 @@ int gk_dgc_select(const GkChain* c, uint64_t seed, void* stream) {
 int gk_compact_send(const GkChain* c, const GkDst* dst, void* stream) {
   if (c->nblk <= 0) return 0;
   if (dst->ndst < 1 || dst->ndst > GK_MAXP) return (int)cudaErrorInvalidValue;
-  const int noct = (c->nblk + NWARP - 1) / NWARP;
-  if (c->mode == GK_MODE_TOPK || c->mode == GK_MODE_DGC) k_compact_send<true, false><<<noct, T, 0, S(stream)>>>(*c, *dst);
-  else if (c->mode == GK_MODE_MINK) k_compact_send<true, true><<<noct, T, 0, S(stream)>>>(*c, *dst);
-  else k_compact_send<false, false><<<noct, T, 0, S(stream)>>>(*c, *dst);
+  const int grid = (c->nblk + NWARP - 1) / NWARP;
+  if (c->mode == GK_MODE_TOPK || c->mode == GK_MODE_DGC) k_compact_send<true, false><<<grid, T, 0, S(stream)>>>(*c, *dst);
+  else if (c->mode == GK_MODE_MINK) k_compact_send<true, true><<<grid, T, 0, S(stream)>>>(*c, *dst);
+  else k_compact_send<false, false><<<grid, T, 0, S(stream)>>>(*c, *dst);
   GK_RET();
 }
 
