@@ -84,3 +84,32 @@ def test_static_scratch_rejects_tables_beyond_its_capacity():
     torch.cuda.synchronize(dev)
     assert rc == GK_ERR_NOALLOC_TOO_LARGE
     assert out.cpu().tolist() == [-7.0, -7.0]      # nothing was launched
+
+
+@pytest.mark.multigpu
+def test_static_scratch_on_a_second_device():
+    """The array exists once per GPU and its address is looked up per device, with that device current: a call
+    on device 1 (after device 0 has cached its own address) must use device 1's copy."""
+    lib = N.cuda_lib()
+    results = []
+    for d in (0, 1, 0):
+        dev = torch.device("cuda", d)
+        torch.cuda.set_device(dev)
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        sizes = [70_001, 4_099]
+        extents, total, blk = _table(sizes, chunk=4096)
+        blk_t = torch.from_numpy(blk.copy()).to(dev)
+        grad = torch.zeros(total, dtype=torch.float32)
+        g = torch.Generator().manual_seed(7 + d)
+        for (o, s) in extents:
+            grad[o:o + s] = torch.randn(s, generator=g)
+        grad = grad.to(dev)
+        out = torch.zeros(2, dtype=torch.float32, device=dev)
+        N.check(lib.gk_grad_norm_static(grad.data_ptr(), blk_t.data_ptr(), blk.shape[0], C.c_float(1.0),
+                                        out.data_ptr(), stream), "gk_grad_norm_static")
+        torch.cuda.synchronize(dev)
+        exact = torch.cat([grad[o:o + s] for o, s in extents]).double().norm().item()
+        results.append((out[0].item(), exact))
+    torch.cuda.set_device(0)
+    for got, exact in results:
+        assert abs(got - exact) <= 1e-5 * exact
