@@ -760,10 +760,14 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         CUDA graph: the P2P / local transports communicate from inside the kernels."""
         if not self._active:
             return True
+        nccl_ok = (settings.NCCL_GRAPH and comm.is_distributed() and dist.get_backend() == "nccl"
+                   and self.device.type == "cuda")      # replays of captured NCCL collectives work on this stack
         if not self._sparse:
-            return size() == 1
+            return size() == 1 or (nccl_ok and self._compressor == "none")
         if self._torch_select or self._verify_every:
             return False
+        if nccl_ok and all(g.transport is not None and g.transport.name == "allgather" for g in self._groups):
+            return True
         return all(g.transport is not None and g.transport.name in ("p2p", "local") for g in self._groups)
 
     def read_overflow(self) -> int:

@@ -327,6 +327,10 @@ class DLTrainer:
 
     def finish(self):
         self.flush_metrics()
+        if self._graph is not None:          # captured collectives must be gone before the process group is
+            if self.is_cuda:
+                torch.cuda.synchronize(self.device)
+            self._graph = None
         if self.writer is not None:
             self.writer.close()
 

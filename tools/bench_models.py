@@ -91,9 +91,12 @@ def run_one(cfg, args):
            "cuda_graph": bool(getattr(trainer, "_graph", None) is not None and trainer._graph.graph is not None),
            "own_kernels_per_step": trainer.launches_per_step(), "data": "synthetic", "dtype": "fp32",
            "timing": "CUDA events around K x train_and_update() incl. H2D of inputs, max over ranks"}
+    trainer.finish()
     if hasattr(opt, "close"):
         opt.close()
     del trainer, opt
+    import gc
+    gc.collect()
     if torch.cuda.is_available():
         torch.cuda.empty_cache()
     return res
