@@ -279,6 +279,10 @@ class DLTrainer:
         self._next_slot = None
         self._pending = []          # lagged device->host reads: (event, pinned tensor)
         self._graph: Optional[GraphedStep] = None
+        import weakref
+        from .parallel import comm as _comm
+        _ref = weakref.ref(self)
+        _comm.on_shutdown(lambda: _ref() is not None and _ref().finish())
         self._hidden = None
         self.d2h_bytes = 0
         logger.info('num_batches_per_epoch: %d' % self.num_batches_per_epoch)

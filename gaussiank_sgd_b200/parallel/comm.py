@@ -52,7 +52,21 @@ def init(backend: Optional[str] = None, device: Optional[torch.device] = None, t
     _state["initialized"] = True
 
 
+_shutdown_hooks = []
+
+
+def on_shutdown(fn) -> None:
+    """Run ``fn()`` before the process group is destroyed (e.g. drop CUDA graphs that captured collectives:
+    destroying a communicator that a live graph still references blocks)."""
+    _shutdown_hooks.append(fn)
+
+
 def shutdown() -> None:
+    while _shutdown_hooks:
+        try:
+            _shutdown_hooks.pop()()
+        except Exception:  # noqa: BLE001 - shutting down anyway
+            pass
     if _state["owns_pg"] and dist.is_initialized():
         dist.destroy_process_group()
     _state.update(initialized=False, owns_pg=False)

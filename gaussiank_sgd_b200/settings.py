@@ -69,7 +69,7 @@ PROFILE_PHASES = _flag("PROFILE_PHASES", False)     # CUDA-event timers for comp
 NVTX = _flag("NVTX", False)                          # NVTX ranges around forward / backward / compress / comm / update
 VERIFY_EVERY = int(os.environ.get("GK_VERIFY_EVERY", "0"))   # >0: cross-check the fused path against the oracle every N steps
 CUDA_GRAPH = _flag("CUDA_GRAPH", True)              # capture the training step in a CUDA graph on GPUs
-NCCL_GRAPH = _flag("NCCL_GRAPH", False)             # also capture steps that contain NCCL collectives (dense / all-gather paths)
+NCCL_GRAPH = _flag("NCCL_GRAPH", True)              # also capture steps that contain NCCL collectives (dense / all-gather paths)
 CHANNELS_LAST = _flag("CHANNELS_LAST", True)        # NHWC convolutions on GPUs
 SYNTHETIC_POOL = _flag("SYNTHETIC_POOL", True)      # pre-collated pinned batches for synthetic image data
 FUSED_BN = _flag("FUSED_BN", True)                  # BN(+residual)+ReLU through csrc/gk_bn.cu on GPUs (ops/bn.py)
