@@ -169,7 +169,6 @@ class P2PTransport(Transport):
         self.peer_ptrs = [int(p) for p in hdl.buffer_ptrs]
         assert len(self.peer_ptrs) == self.P
         self._symm_t, self._symm_h = t, hdl
-        self.multicast_ptr = int(getattr(hdl, "multicast_ptr", 0) or 0)
         torch.cuda.synchronize(self.device)
         hdl.barrier()
 
@@ -191,7 +190,6 @@ class P2PTransport(Transport):
                 ptrs.append(p.value)
                 self._ipc_ptrs.append(p.value)
         self.peer_ptrs = ptrs
-        self.multicast_ptr = 0
 
     def dst(self):
         return self._dst
