@@ -270,13 +270,13 @@ class _DistributedOptimizer(torch.optim.Optimizer):
             # Inside a group the tensors are taken in ARENA order (the planners work in backward order): the
             # compaction kernel emits pairs in table order, so every rank's list comes out sorted by index,
             # which the folded receive relies on.  Selection does not depend on the order.
-            g = _Group(sorted((n for grp in groups for n in grp), key=arena.index.__getitem__), 0)
+            g = _Group(sorted((n for grp in groups for n in grp), key=lambda n: arena.offsets[arena.index[n]]), 0)
             g.segments = [[arena.extent(arena.index[n])] for n in g.names]
             self._groups = [g]
         else:
             self._groups = []
             for gi, names in enumerate(groups):
-                g = _Group(sorted(names, key=arena.index.__getitem__), gi)
+                g = _Group(sorted(names, key=lambda n: arena.offsets[arena.index[n]]), gi)
                 g.segments = [[arena.extent(arena.index[n]) for n in g.names]]
                 self._groups.append(g)
         self._group_of_param = {}

@@ -810,7 +810,8 @@ class DLTrainer:
         # the recurrent models stay eager: cuDNN's RNN backward re-packs the weights (they live in the flat
         # parameter arena, not in one cuDNN blob) through the legacy stream, which a capture cannot contain,
         # and lstman4's batches change shape from step to step
-        use_graph = (self.is_cuda and settings.CUDA_GRAPH and self.dnn not in ('lstm', 'lstman4')
+        use_graph = (self.is_cuda and settings.CUDA_GRAPH and self.dnn != 'lstman4'
+                     and (self.dnn != 'lstm' or settings.LSTM_GRAPH)
                      and getattr(self.optimizer, '_fused_kind', None) is not None
                      and getattr(self.optimizer, 'graph_safe', False))
         n0 = LAUNCHES["n"]

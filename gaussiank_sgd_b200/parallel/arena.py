@@ -23,6 +23,13 @@ def _is_channels_last(t: torch.Tensor) -> bool:
     return t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last) and not t.is_contiguous()
 
 
+class _DeviceSpan:
+    """``__cuda_array_interface__`` over a span of device memory owned by somebody else (the arena)."""
+
+    def __init__(self, ptr: int, numel: int):
+        self.__cuda_array_interface__ = {"shape": (numel,), "typestr": "<f4", "data": (ptr, False), "version": 2}
+
+
 class ParamArena:
     def __init__(self, named_params: Sequence[Tuple[str, torch.nn.Parameter]], with_grad: bool = True):
         named_params = [(n, p) for n, p in named_params if p.requires_grad]
@@ -37,11 +44,33 @@ class ParamArena:
                 raise ValueError("all parameters must live on one device (one process per GPU)")
         self.device = dev
         self.numels = [p.numel() for p in self.params]
-        self.offsets: List[int] = []
+        # Parameters that are views of ONE flat buffer (cuDNN's RNN weight blob, created by
+        # nn.LSTM.flatten_parameters() when the module moves to the GPU) keep their relative offsets: the blob
+        # becomes one extent of the arena.  cuDNN then finds its weights where it expects them and neither the
+        # forward nor the backward re-packs them (which also makes the step capturable in a CUDA graph).
+        groups: Dict[int, List[int]] = {}
+        if dev.type == "cuda":
+            for i, p in enumerate(self.params):
+                groups.setdefault(p.data.untyped_storage().data_ptr(), []).append(i)
+        groups = {k: v for k, v in groups.items() if len(v) > 1 and all(
+            self.params[i].data.is_contiguous() and self.params[i].data.storage_offset() % 4 == 0 for i in v)}
+        group_of = {i: k for k, v in groups.items() for i in v}
+        self.offsets: List[int] = [0] * len(self.params)
+        self._blobs = []                 # (arena offset, numel, member indices) of every adopted flat buffer
+        placed = {}
         off = 0
-        for n in self.numels:
-            self.offsets.append(off)
-            off += (n + ALIGN - 1) // ALIGN * ALIGN
+        for i, n in enumerate(self.numels):
+            k = group_of.get(i)
+            if k is None:
+                self.offsets[i] = off
+                off += (n + ALIGN - 1) // ALIGN * ALIGN
+                continue
+            if k not in placed:
+                blob = self.params[i].data.untyped_storage().nbytes() // 4
+                placed[k] = off
+                self._blobs.append((off, blob, groups[k]))
+                off += (blob + ALIGN - 1) // ALIGN * ALIGN
+            self.offsets[i] = placed[k] + self.params[i].data.storage_offset()
         self.total = max(off, ALIGN)
         assert self.total < 2 ** 31
         self.index: Dict[str, int] = {n: i for i, n in enumerate(self.names)}
@@ -49,7 +78,14 @@ class ParamArena:
         self.param = torch.zeros(self.total, dtype=torch.float32, device=dev)
         self.grad = torch.zeros(self.total, dtype=torch.float32, device=dev) if with_grad else None
         self.grad_views = []
+        self._aliases = {}
         with torch.no_grad():
+            for (boff, blob, members) in self._blobs:
+                # a tensor over the arena's memory with a storage of its own that STARTS at the blob: cuDNN looks
+                # for the weights at the beginning of the storage of the first parameter
+                alias = torch.as_tensor(_DeviceSpan(self.param.data_ptr() + 4 * boff, blob), device=dev)
+                for i in members:
+                    self._aliases[i] = (alias, self.offsets[i] - boff)
             for i, p in enumerate(self.params):
                 v = self.view(self.param, i)
                 v.copy_(p.data)
@@ -60,6 +96,9 @@ class ParamArena:
 
     def view(self, arena: torch.Tensor, i: int) -> torch.Tensor:
         """Tensor i's window of ``arena`` with the parameter's shape and memory format."""
+        if arena is self.param and i in getattr(self, "_aliases", {}):
+            alias, rel = self._aliases[i]
+            return alias[rel: rel + self.numels[i]].view(self.params[i].shape)
         flat = arena[self.offsets[i]: self.offsets[i] + self.numels[i]]
         shape = self.params[i].shape
         if self._cl[i]:
