@@ -807,11 +807,11 @@ class DLTrainer:
 
     def _run_step(self, staged, hidden, clip_norm):
         from .ops.chain import LAUNCHES
-        # the recurrent models stay eager: cuDNN's RNN backward re-packs the weights (they live in the flat
-        # parameter arena, not in one cuDNN blob) through the legacy stream, which a capture cannot contain,
-        # and lstman4's batches change shape from step to step
-        use_graph = (self.is_cuda and settings.CUDA_GRAPH and self.dnn != 'lstman4'
-                     and (self.dnn != 'lstm' or settings.LSTM_GRAPH)
+        # the recurrent models stay eager: the weights sit in cuDNN's flat layout inside the arena (no re-pack),
+        # but cuDNN's RNN with inter-layer dropout still touches the legacy stream, which a capture cannot
+        # contain ("operation would make the legacy stream depend on a capturing blocking stream"), and
+        # lstman4's batches change shape from step to step
+        use_graph = (self.is_cuda and settings.CUDA_GRAPH and self.dnn not in ('lstm', 'lstman4')
                      and getattr(self.optimizer, '_fused_kind', None) is not None
                      and getattr(self.optimizer, 'graph_safe', False))
         n0 = LAUNCHES["n"]

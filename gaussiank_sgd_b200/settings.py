@@ -69,7 +69,6 @@ PROFILE_PHASES = _flag("PROFILE_PHASES", False)     # CUDA-event timers for comp
 NVTX = _flag("NVTX", False)                          # NVTX ranges around forward / backward / compress / comm / update
 VERIFY_EVERY = int(os.environ.get("GK_VERIFY_EVERY", "0"))   # >0: cross-check the fused path against the oracle every N steps
 CUDA_GRAPH = _flag("CUDA_GRAPH", True)              # capture the training step in a CUDA graph on GPUs
-LSTM_GRAPH = _flag("LSTM_GRAPH", False)             # capture the PTB LSTM step too (its weights sit in cuDNN's flat layout inside the arena)
 NCCL_GRAPH = _flag("NCCL_GRAPH", True)              # also capture steps that contain NCCL collectives (dense / all-gather paths)
 CHANNELS_LAST = _flag("CHANNELS_LAST", True)        # NHWC convolutions on GPUs
 SYNTHETIC_POOL = _flag("SYNTHETIC_POOL", True)      # pre-collated pinned batches for synthetic image data
