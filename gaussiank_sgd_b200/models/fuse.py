@@ -18,6 +18,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from .. import settings
+from ..ops import stem
 from ..ops.bn import bn2_act, bn_act, bn_relu_maxpool
 
 
@@ -79,6 +80,10 @@ def _stem_conv_s2d(conv, x):
     X = F.pad(xs, (0, 0, 2, 1, 2, 1)).permute(0, 3, 1, 2)          # logical NCHW over NHWC memory
     O = conv.out_channels
     w4 = F.pad(conv.weight, (1, 0, 1, 0)).reshape(O, 3, 4, 2, 4, 2).permute(0, 3, 5, 1, 2, 4).reshape(O, 12, 4, 4)
+    if settings.STEM_TC and not x.requires_grad:
+        Xn = X.permute(0, 2, 3, 1)                                  # the padded NHWC memory itself
+        if stem.supported(Xn, w4):
+            return stem.stem_conv_tc(Xn, w4)                        # TMA + tcgen05 implicit GEMM
     return F.conv2d(X, w4.contiguous(memory_format=torch.channels_last), None, 1, 0)
 
 

@@ -108,7 +108,7 @@ def _nvcc() -> str:
     return "nvcc"
 
 
-CUDA_SOURCES = ("gk_cuda.cu", "gk_bn.cu")
+CUDA_SOURCES = ("gk_cuda.cu", "gk_bn.cu", "gk_stem.cu")
 
 
 def _cuda_deps():
@@ -116,7 +116,7 @@ def _cuda_deps():
 
 
 def build_cuda(force: bool = False, verbose: bool = False) -> str:
-    """Cross-compile csrc/gk_cuda.cu + csrc/gk_bn.cu for sm_100a into one library (works without a GPU)."""
+    """Cross-compile csrc/gk_cuda.cu + csrc/gk_bn.cu + csrc/gk_stem.cu for sm_100a into one library (works without a GPU)."""
     srcs = [os.path.join(CSRC, f) for f in CUDA_SOURCES]
     if force or _stale(CUDA_SO, _cuda_deps()):
         cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", CUDA_SO + ".tmp"] + srcs
@@ -176,6 +176,7 @@ def cuda_lib():
             _proto(lib, "gk_sgd_recv", [C.POINTER(GkRecvUpd), sr, _P])
             _proto(lib, "gk_lars", [_P, _P, _P, _P, C.c_int32, _P, C.c_int32, _P, _P, _P, _P, _P])
             _proto(lib, "gk_grad_norm", [_P, _P, C.c_int32, _P, C.c_float, _P, _P, _P])
+            _proto(lib, "gk_stem_fwd", [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P])
             _proto(lib, "gk_grad_norm_static", [_P, _P, C.c_int32, C.c_float, _P, _P])
             _proto(lib, "gk_scale", [_P, _P, C.c_int32, _P, _P])
             _proto(lib, "gk_randomk_send", [ch, ds, C.c_uint64, _P])

@@ -310,6 +310,39 @@ def test_stem_space_to_depth_rewrite_is_exact():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(2, 32, 32), (3, 40, 56), (32, 224, 224), (5, 224, 224)])
+def test_stem_tensor_core_kernel_matches_fp32_convolution(shape):
+    """csrc/gk_stem.cu (TMA + tcgen05.mma kind::tf32, accumulator in TMEM) against an fp32 PyTorch convolution of the
+    original 7x7 / stride 2 form, within TF32 tolerance; the weight gradient against the same reference."""
+    from gaussiank_sgd_b200 import settings
+    from gaussiank_sgd_b200.models.fuse import _stem_conv
+    from gaussiank_sgd_b200.ops import stem
+    N, H, W = shape
+    dev = torch.device("cuda:0")
+    torch.manual_seed(N + H)
+    conv = nn.Conv2d(3, 64, 7, 2, 3, bias=False).to(dev)
+    ref = copy.deepcopy(conv).double()
+    x = torch.randn(N, 3, H, W, device=dev).contiguous(memory_format=torch.channels_last)
+    assert settings.STEM_TC and settings.STEM_S2D
+    before = dict(stem.calls)
+    y = _stem_conv(conv, x)
+    assert stem.calls["fwd"] == before["fwd"] + 1, "the tensor-core path was not taken"
+    want = ref(x.double())
+    assert y.shape == want.shape and y.is_contiguous(memory_format=torch.channels_last)
+    # TF32 keeps 10 mantissa bits of each operand: |error| <~ 2^-10 * sum |x w| over the 147 taps
+    scale = F.conv2d(x.double().abs(), ref.weight.abs(), None, 2, 3)
+    err = (y.double() - want).abs()
+    assert float((err / scale).max()) < 2.0 ** -9, float((err / scale).max())
+    assert float(err.max()) > 0 or H < 8
+    d = torch.randn_like(y)
+    y.backward(d)
+    want.backward(d.double())
+    torch.testing.assert_close(conv.weight.grad.double(), ref.weight.grad, rtol=2e-2, atol=2e-2 * float(ref.weight.grad.abs().max()))
+    torch.cuda.synchronize()
+    assert all(v == 0 for v in stem.error_codes().values())
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("shape", [(32, 256, 28, 28), (8, 2048, 7, 7), (4, 96, 9, 9), (16, 512, 14, 14)])
 @pytest.mark.parametrize("twice", [False, True])
 def test_two_bns_into_one_activation(shape, twice):
