@@ -2,26 +2,35 @@
 //
 // The reference runs torchvision's resnet50 (dl_trainer.py:187-196 picks the model, the stem is its conv1) through
 // cuDNN.  Here the stem is computed on the 2x2 space-to-depth image X [N, Hp, Wp, 12] (Hp = H/2 + 3, Wp = W/2 + 3,
-// two zero rows / columns in front and one behind; see models/fuse.py), where it is a 4x4 / stride 1 convolution:
+// two zero rows / columns in front and one behind; k_stem_s2d below writes it), where it is a 4x4 / stride 1
+// convolution.  With q = (n*Hp + i)*Wp + j the flat position in the padded grid,
 //
-//     y[n, oh, ow, o] = sum_{a<4} sum_{k<48} X_flat[(p + a*Wp) * 12 + k] * Wk[o][a*48 + k],   p = (n*Hp + oh)*Wp + ow
+//     y[q, o] = sum_{a<4} sum_{b<4} sum_{c<12} X[q + a*Wp + b, c] * W4[o, c, a, b]
 //
-// i.e. for every kernel row a the operand rows are 48 consecutive floats starting 12 floats apart: a matrix with
-// OVERLAPPING rows (row pitch 48 B, row length 192 B).  A TMA tensor map describes exactly that (dims {48, P, 4},
-// strides {4, 48, 48*Wp} bytes), so the im2col expansion happens in the copy engine: no gather kernel, no expanded
-// copy in HBM.  The flat index p runs over the padded grid, so a 128-row tile is 128 consecutive p; the 3 of every
-// Wp positions (and 3 of every Hp rows) that are not output pixels are computed and dropped by the epilogue.
+// for every q that is an output pixel (i < OH, j < OW); the other 3 of every Wp positions and 3 of every Hp rows
+// are computed and dropped.  A tile is 128 consecutive q.
 //
-// One persistent CTA per SM, warp-specialised:
-//   warp 0   TMA producer: per kernel row two 128 x 32-float boxes (128-byte swizzle; the second box's upper half is
-//            out of bounds in k and arrives as zeros) into a 4-deep ring; the 64 x 192 weight matrix once.
-//   warp 1   one lane issues tcgen05.mma kind::tf32, M = 128, N = 64, K = 8, six per kernel row, accumulating the
-//            four kernel rows in TMEM; tcgen05.commit releases ring slots and publishes the accumulator.
-//   warp 2   allocates / frees 128 TMEM columns (two accumulators: the MMAs of tile t+1 overlap the epilogue of t).
-//   warps 4-7  epilogue: tcgen05.ld the 128 x 64 fp32 tile (warp w owns lanes 32(w%4)..), transpose through padded
-//            shared memory, store whole 128-byte lines of the NHWC output.
-// Every mbarrier wait is bounded (2 s on %globaltimer): on expiry the kernel records a code and traps rather than
-// spinning forever.
+// No im2col, not even in shared memory.  X is kept in shared memory ONCE, as three planes of 16-byte quarters
+// (plane t holds channels 4t..4t+3 of every position, 16 B apart).  In the un-swizzled K-major operand layout of
+// tcgen05.mma a "core matrix" is 8 rows x 16 B stored contiguously, 8-row groups SBO apart, the two 16-byte halves
+// of a K = 8 tf32 step LBO apart.  With SBO = 128 B and LBO = 16 B a descriptor that starts at position q + a*Wp + b
+// of plane t therefore reads, for row r, channels 4t..4t+3 of positions q+r+a*Wp+b and q+r+a*Wp+b+1: the operand
+// rows of consecutive output pixels overlap in shared memory exactly as the convolution windows overlap in the
+// image.  One tile is 4 (a) x 3 (t) x 2 (b pairs) = 24 MMAs of M = 128, N = 64, K = 8; the weights are packed on the
+// host side in that order.  (The first version staged each kernel row through 128-byte-swizzled TMA boxes over an
+// overlapping-row tensor map: correct, 59 us, bound by the 4x-expanded L2 -> shared memory traffic; this one reads
+// X from L2 1.7 times.)
+//
+// One persistent CTA per SM owns a contiguous range of tiles and walks it in chunks of 4 tiles (512 + 3*Wp + 3
+// positions of X per chunk, double-buffered).  Warp-specialised:
+//   warp 0   producer: 12 TMA boxes {4 floats, boxP positions} per chunk (tensor map dims {4, P, 3}, strides
+//            {4, 48, 16} B: the plane split happens in the copy engine); one bulk copy of the packed weights.
+//   warp 1   one lane issues the tcgen05.mma kind::tf32 instructions into one of two TMEM accumulators;
+//            tcgen05.commit publishes the accumulator and releases the chunk buffer.
+//   warp 2   allocates / frees 128 TMEM columns.
+//   warps 4-7  epilogue: tcgen05.ld the 128 x 64 fp32 tile, transpose through padded shared memory, store whole
+//            128-byte lines of the NHWC output (the valid rows of a tile are contiguous in y).
+// Every mbarrier wait is bounded (2 s on %globaltimer): on expiry the kernel records a code and traps.
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -32,18 +41,16 @@ namespace {
 
 constexpr int ST_M = 128;                          // flat padded positions per tile
 constexpr int ST_N = 64;                           // output channels
-constexpr int ST_TAPS = 4;                         // kernel rows of the 4x4 form
-constexpr int ST_KROW = 48;                        // 4 positions x 12 channels per kernel row
-constexpr int ST_STAGES = 4;
-constexpr int ST_SLAB_A = ST_M * 128;              // 128 rows x 128 B
-constexpr int ST_STAGE_A = 2 * ST_SLAB_A;          // k 0..31 and k 32..63 (48..63 zero)
-constexpr int ST_SLAB_B = ST_N * 128;
-constexpr int ST_B_BYTES = ST_TAPS * 2 * ST_SLAB_B;
+constexpr int ST_TAPS = 4;                         // kernel rows (and columns) of the 4x4 form
+constexpr int ST_CHUNK = 4;                        // tiles per chunk of X
+constexpr int ST_NMMA = ST_TAPS * 3 * 2;           // K = 8 steps per tile
+constexpr int ST_B_MMA = 2 * ST_N * 16;            // weight bytes per step: 2 halves x 64 rows x 16 B
+constexpr int ST_B_BYTES = ST_NMMA * ST_B_MMA;     // 48 KB
 constexpr int ST_EPI_PITCH = 36;                   // floats; 32 + 4 keeps the float4 phases conflict-free
 constexpr int ST_EPI_BYTES = 4 * 32 * ST_EPI_PITCH * 4;
 constexpr int ST_THREADS = 256;
 constexpr int ST_TMEM_COLS = 128;
-constexpr int ST_SMEM = ST_STAGES * ST_STAGE_A + ST_B_BYTES + ST_EPI_BYTES + 256 + 1024;
+constexpr int ST_FIXED = ST_B_BYTES + ST_EPI_BYTES + 256;   // + 2 chunk buffers of 3 planes
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -96,20 +103,9 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* m, 
       ::"r"(dst), "l"(m), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(dst), "l"(m), "r"(bar), "r"(c0), "r"(c1)
-      : "memory");
-}
-
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
-// K-major operand, 128-byte swizzle: rows 128 B apart, 8-row groups 1024 B apart (SBO), LBO unused (1), version 1.
-__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
-  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
-}
 // D fp32 (1 << 4), A and B tf32 (2 << 7, 2 << 10), both K-major, N >> 3 at bit 17, M >> 4 at bit 24.
 constexpr uint32_t ST_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(ST_N >> 3) << 17) | ((uint32_t)(ST_M >> 4) << 24);
 
@@ -139,45 +135,61 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
 }
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+__device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+
+// K-major operand without swizzle: 8 x 16 B core matrices, `lbo` bytes between the two K halves, `sbo` bytes between
+// 8-row groups; descriptor version 1.
+__device__ __forceinline__ uint64_t smem_desc_plain(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) | (1ull << 46);
+}
+
 struct StemGeom {
   int nimg, Hp, Wp, OH, OW, ntiles;
+  int boxP;                                          // positions per TMA box; a chunk buffer plane holds 4 boxes
 };
 
 __global__ void __launch_bounds__(ST_THREADS, 1)
-k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
-              float* __restrict__ out, const StemGeom g, unsigned int* __restrict__ err) {
+k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict__ wpk, float* __restrict__ out,
+              const StemGeom g, unsigned int* __restrict__ err) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
-  const uint32_t base = (raw + 1023u) & ~1023u;     // the swizzle atoms repeat every 1024 B
-  const uint32_t sA = base;
-  const uint32_t sB = sA + ST_STAGES * ST_STAGE_A;
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t plane = (uint32_t)g.boxP * 4u * 16u;            // bytes per plane (boxP is a multiple of 8)
+  const uint32_t sB = base;
   const uint32_t sE = sB + ST_B_BYTES;
   const uint32_t sBar = sE + ST_EPI_BYTES;
+  const uint32_t sX = sBar + 256u;                               // 2 buffers x 3 planes
   auto full = [&](uint32_t s) { return sBar + 8u * s; };
-  auto empty = [&](uint32_t s) { return sBar + 8u * (ST_STAGES + s); };
-  const uint32_t bfull = sBar + 8u * (2 * ST_STAGES);
-  auto tfull = [&](uint32_t s) { return bfull + 8u + 8u * s; };
-  auto tempty = [&](uint32_t s) { return bfull + 24u + 8u * s; };
-  const uint32_t tslot = bfull + 40u;
+  auto empty = [&](uint32_t s) { return sBar + 16u + 8u * s; };
+  const uint32_t bfull = sBar + 32u;
+  auto tfull = [&](uint32_t s) { return sBar + 40u + 8u * s; };
+  auto tempty = [&](uint32_t s) { return sBar + 56u + 8u * s; };
+  const uint32_t tslot = sBar + 72u;
   float* const epi = reinterpret_cast<float*>(smem_raw + (sE - raw));
   volatile uint32_t* const tslot_p = reinterpret_cast<volatile uint32_t*>(smem_raw + (tslot - raw));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&mapA);
-    tma_prefetch_desc(&mapB);
-  }
+  // this CTA's contiguous range of tiles
+  const int per = g.ntiles / (int)gridDim.x, extra = g.ntiles % (int)gridDim.x;
+  const int bid = (int)blockIdx.x;
+  const int t0 = bid * per + (bid < extra ? bid : extra);
+  const int nt = per + (bid < extra ? 1 : 0);
+  const int nchunk = (nt + ST_CHUNK - 1) / ST_CHUNK;
+
+  if (warp == 0 && lane == 0) tma_prefetch_desc(&mapX);
   if (warp == 1 && lane == 0) {
-    for (uint32_t s = 0; s < ST_STAGES; ++s) {
+    for (uint32_t s = 0; s < 2; ++s) {
       mbar_init(full(s), 1);
       mbar_init(empty(s), 1);
-    }
-    mbar_init(bfull, 1);
-    for (uint32_t s = 0; s < 2; ++s) {
       mbar_init(tfull(s), 1);
       mbar_init(tempty(s), 4);                      // one arrival per epilogue warp
     }
+    mbar_init(bfull, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -190,61 +202,64 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ 
   const uint32_t tmem = *tslot_p;
 
   if (warp == 0) {
-    if (lane == 0) {                                // ---- TMA producer
+    if (lane == 0) {                                // ---- producer
       mbar_expect_tx(bfull, ST_B_BYTES);
-      for (int a = 0; a < ST_TAPS; ++a)
-        for (int h = 0; h < 2; ++h)
-          tma_load_2d(sB + (a * 2 + h) * ST_SLAB_B, &mapB, bfull, a * ST_KROW + h * 32, 0);
-      uint32_t stage = 0, phase = 0;
-      for (int tile = blockIdx.x; tile < g.ntiles; tile += gridDim.x) {
-        const int p0 = tile * ST_M;
-        for (int a = 0; a < ST_TAPS; ++a) {
-          mbar_wait(empty(stage), phase ^ 1u, err, 1);
-          mbar_expect_tx(full(stage), ST_STAGE_A);
-          const uint32_t dst = sA + stage * ST_STAGE_A;
-          tma_load_3d(dst, &mapA, full(stage), 0, p0, a);
-          tma_load_3d(dst + ST_SLAB_A, &mapA, full(stage), 32, p0, a);
-          if (++stage == ST_STAGES) { stage = 0; phase ^= 1u; }
-        }
+      bulk_load_1d(sB, wpk, ST_B_BYTES, bfull);
+      for (int c = 0; c < nchunk; ++c) {
+        const uint32_t buf = c & 1, ph = (c >> 1) & 1;
+        mbar_wait(empty(buf), ph ^ 1u, err, 1);
+        mbar_expect_tx(full(buf), 3u * plane);
+        const int q0 = (t0 + c * ST_CHUNK) * ST_M;
+        const uint32_t dst = sX + buf * 3u * plane;
+        for (int t = 0; t < 3; ++t)
+          for (int k = 0; k < 4; ++k)
+            tma_load_3d(dst + t * plane + (uint32_t)(k * g.boxP) * 16u, &mapX, full(buf), 0, q0 + k * g.boxP, t);
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {                                // ---- MMA issuer
       mbar_wait(bfull, 0, err, 2);
-      uint32_t stage = 0, phase = 0;
       int it = 0;
-      for (int tile = blockIdx.x; tile < g.ntiles; tile += gridDim.x, ++it) {
-        const uint32_t as = it & 1, aph = (it >> 1) & 1;
-        mbar_wait(tempty(as), aph ^ 1u, err, 3);    // the epilogue has drained this accumulator
+      for (int c = 0; c < nchunk; ++c) {
+        const uint32_t buf = c & 1, ph = (c >> 1) & 1;
+        mbar_wait(full(buf), ph, err, 4);
         tc_fence_after();
-        const uint32_t d = tmem + as * ST_N;
-        for (int a = 0; a < ST_TAPS; ++a) {
-          mbar_wait(full(stage), phase, err, 4);
+        const uint32_t xb = sX + buf * 3u * plane;
+        const int ntc = nt - c * ST_CHUNK < ST_CHUNK ? nt - c * ST_CHUNK : ST_CHUNK;
+        for (int tl = 0; tl < ntc; ++tl, ++it) {
+          const uint32_t as = it & 1, aph = (it >> 1) & 1;
+          mbar_wait(tempty(as), aph ^ 1u, err, 3);  // the epilogue has drained this accumulator
           tc_fence_after();
-          const uint32_t a0 = sA + stage * ST_STAGE_A, b0 = sB + a * 2 * ST_SLAB_B;
+          const uint32_t d = tmem + as * ST_N;
+          uint32_t bw = sB;
+#pragma unroll 1
+          for (int a = 0; a < ST_TAPS; ++a) {
+            const uint32_t row = xb + (uint32_t)(tl * ST_M + a * g.Wp) * 16u;
 #pragma unroll
-          for (int kk = 0; kk < ST_KROW / 8; ++kk) {  // k 0..31 from the first slab, 32..47 from the second
-            const uint32_t h = kk >> 2, ko = (kk & 3) * 32;
-            mma_tf32(d, smem_desc_sw128(a0 + h * ST_SLAB_A + ko), smem_desc_sw128(b0 + h * ST_SLAB_B + ko),
-                     (a | kk) != 0 ? 1u : 0u);
+            for (int t = 0; t < 3; ++t) {
+#pragma unroll
+              for (int bp = 0; bp < 2; ++bp) {
+                mma_tf32(d, smem_desc_plain(row + t * plane + bp * 32u, 16u, 128u),
+                         smem_desc_plain(bw, ST_N * 16u, 128u), (a | t | bp) != 0 ? 1u : 0u);
+                bw += ST_B_MMA;
+              }
+            }
           }
-          mma_commit(empty(stage));                 // slot free once these MMAs have read it
-          if (++stage == ST_STAGES) { stage = 0; phase ^= 1u; }
+          mma_commit(tfull(as));
         }
-        mma_commit(tfull(as));
+        mma_commit(empty(buf));                     // the chunk buffer is free once these MMAs have read it
       }
     }
   } else if (warp >= 4) {                           // ---- epilogue
     const int q = warp & 3;                         // TMEM lanes 32q .. 32q+31
     float* const stg = epi + q * 32 * ST_EPI_PITCH;
-    const long long plane = (long long)g.Hp * g.Wp;
-    int it = 0;
-    for (int tile = blockIdx.x; tile < g.ntiles; tile += gridDim.x, ++it) {
+    const long long pl = (long long)g.Hp * g.Wp;
+    for (int it = 0; it < nt; ++it) {
       const uint32_t as = it & 1, aph = (it >> 1) & 1;
-      // where this lane's row goes: p -> (n, oh, ow); -1 for the padded positions
-      const long long p = (long long)tile * ST_M + q * 32 + lane;
-      const int n = (int)(p / plane);
-      const int rem = (int)(p - (long long)n * plane);
+      // where this lane's row goes: position -> (n, i, j); -1 for the positions that are not output pixels
+      const long long p = (long long)(t0 + it) * ST_M + q * 32 + lane;
+      const int n = (int)(p / pl);
+      const int rem = (int)(p - (long long)n * pl);
       const int oh = rem / g.Wp, ow = rem - oh * g.Wp;
       const long long off = (n < g.nimg && oh < g.OH && ow < g.OW)
                                 ? (((long long)n * g.OH + oh) * g.OW + ow) * ST_N : -1ll;
@@ -284,6 +299,49 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ 
   }
 }
 
+__device__ __forceinline__ float to_tf32(float v) {   // round to nearest: the MMA itself would truncate
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+  return __uint_as_float(r);
+}
+
+// x [N, H, W, 3] (NHWC) -> X [N, Hp, Wp, 12], X[n, i, j, (dy*2+dx)*3 + c] = x[n, 2(i-2)+dy, 2(j-2)+dx, c], zero in the
+// two leading and one trailing rows / columns.  One thread per 16-byte quarter of a position.
+__global__ void k_stem_s2d(const float* __restrict__ x, float4* __restrict__ X, int nimg, int H, int W, long long nquart) {
+  const int Hp = H / 2 + 3, Wp = W / 2 + 3;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < nquart; g += (long long)gridDim.x * blockDim.x) {
+    const int t = (int)(g % 3);
+    const long long pos = g / 3;
+    const int j = (int)(pos % Wp);
+    const long long ni = pos / Wp;
+    const int i = (int)(ni % Hp), n = (int)(ni / Hp);
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    if (i >= 2 && i < Hp - 1 && j >= 2 && j < Wp - 1) {
+      const float* r0 = x + (((long long)n * H + 2 * (i - 2)) * W + 2 * (j - 2)) * 3;   // 6 floats: dy = 0
+      const float* r1 = r0 + (long long)W * 3;                                           // 6 floats: dy = 1
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int k = 4 * t + e;
+        v[e] = to_tf32(__ldg(k < 6 ? r0 + k : r1 + (k - 6)));
+      }
+    }
+    X[g] = make_float4(v[0], v[1], v[2], v[3]);
+  }
+}
+
+// weight [64, 3, 7, 7] -> the 24 K = 8 steps of the kernel above, each [half 2][row group 8][row 8][4 floats]:
+// step (a, t, bp), half kc, row o = 8*og + r, float e  <-  W4[o, 4t + e, a, 2bp + kc], where W4 is the 4x4 form
+// W4[o, (dy*2+dx)*3 + ch, a, b] = w[o, ch, 2a+dy-1, 2b+dx-1] (zero where an index is -1).
+__global__ void k_stem_pack_w(const float* __restrict__ w, float* __restrict__ wpk) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= ST_NMMA * 2 * ST_N * 4) return;
+  const int e = g & 3, r = (g >> 2) & 7, og = (g >> 5) & 7, kc = (g >> 8) & 1, m = g >> 9;
+  const int bp = m & 1, t = (m >> 1) % 3, a = m / 6;
+  const int o = og * 8 + r, c12 = 4 * t + e, s = c12 / 3, ch = c12 % 3, dy = s >> 1, dx = s & 1;
+  const int u = 2 * a + dy - 1, v = 2 * (2 * bp + kc) + dx - 1;
+  wpk[g] = (u >= 0 && v >= 0) ? to_tf32(w[((o * 3 + ch) * 7 + u) * 7 + v]) : 0.f;
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -310,57 +368,72 @@ int stem_sm_count() {
   return sms;
 }
 
+int stem_box(int Wp) { return ((ST_CHUNK * ST_M + 3 * Wp + 3 + 3) / 4 + 7) & ~7; }
+
 }  // namespace
 
 extern "C" {
 
-// x: the padded space-to-depth image [nimg, Hp, Wp, 12] fp32 (Hp = OH + 3, Wp = OW + 3), wk: [64, 192] fp32 with
-// wk[o][a*48 + b*12 + c] the weight of kernel row a, column b, channel c; y: [nimg, OH, OW, 64] fp32 (NHWC).
-// err (optional, device uint32) receives the code of a wait that timed out.  Returns a cudaError_t, or -2 when the
-// shape is not covered, -3 when the driver cannot encode the tensor maps.
-int gk_stem_fwd(const void* x, const void* wk, void* y, int nimg, int OH, int OW, void* err, void* stream) {
+// 1 when gk_stem_fwd covers an H x W image (even sizes; the chunk of X must fit four 256-position TMA boxes).
+int gk_stem_supported(int H, int W) {
+  return H >= 2 && W >= 2 && H % 2 == 0 && W % 2 == 0 && stem_box(W / 2 + 3) <= 256;
+}
+
+// x [nimg, H, W, 3] fp32 NHWC  ->  X [nimg, H/2+3, W/2+3, 12] fp32 (values rounded to tf32).
+int gk_stem_s2d(const void* x, void* X, int nimg, int H, int W, void* stream) {
+  if (nimg <= 0 || H % 2 || W % 2) return -2;
+  const long long nquart = (long long)nimg * (H / 2 + 3) * (W / 2 + 3) * 3;
+  const int threads = 256;
+  long long blocks = (nquart + threads - 1) / threads;
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  k_stem_s2d<<<(int)blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const float*>(x), static_cast<float4*>(X), nimg, H, W, nquart);
+  return (int)cudaGetLastError();
+}
+
+// w [64, 3, 7, 7] fp32  ->  wpk [12288] fp32 in the kernel's operand order (values rounded to tf32).
+int gk_stem_pack_w(const void* w, void* wpk, void* stream) {
+  k_stem_pack_w<<<(ST_NMMA * 2 * ST_N * 4 + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const float*>(w), static_cast<float*>(wpk));
+  return (int)cudaGetLastError();
+}
+
+// X: the padded space-to-depth image [nimg, OH+3, OW+3, 12] fp32, wpk: gk_stem_pack_w's output,
+// y: [nimg, OH, OW, 64] fp32 (NHWC).  err (optional, device uint32) receives the code of a wait that timed out.
+// Returns a cudaError_t, or -2 when the shape is not covered, -3 when the driver cannot encode the tensor map.
+int gk_stem_fwd(const void* X, const void* wpk, void* y, int nimg, int OH, int OW, void* err, void* stream) {
   if (nimg <= 0 || OH <= 0 || OW <= 0) return -2;
   const int Hp = OH + 3, Wp = OW + 3;
   const long long P = (long long)nimg * Hp * Wp;
-  const long long rows = P - 3LL * Wp - 3;           // rows whose 4 x 48 floats lie inside x
-  if (rows <= 0 || P > (1LL << 31) - ST_M) return -2;
-  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(wk) | reinterpret_cast<uintptr_t>(y)) & 15) return -2;
+  const long long rows = P - 3LL * Wp - 3;           // one past the last position that is an output pixel
+  const int boxP = stem_box(Wp);
+  if (rows <= 0 || P > (1LL << 31) - 2048 || boxP > 256) return -2;
+  if ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(wpk) | reinterpret_cast<uintptr_t>(y)) & 15) return -2;
   EncodeTiledFn enc = encode_fn();
   if (!enc) return -3;
-  CUtensorMap mapA, mapB;
+  CUtensorMap mapX;
   {
-    const cuuint64_t dims[3] = {(cuuint64_t)ST_KROW, (cuuint64_t)rows, (cuuint64_t)ST_TAPS};
-    const cuuint64_t strides[2] = {12 * sizeof(float), (cuuint64_t)Wp * 12 * sizeof(float)};
-    const cuuint32_t box[3] = {32, ST_M, 1};
+    const cuuint64_t dims[3] = {4, (cuuint64_t)P, 3};                       // {float in quarter, position, quarter}
+    const cuuint64_t strides[2] = {12 * sizeof(float), 4 * sizeof(float)};
+    const cuuint32_t box[3] = {4, (cuuint32_t)boxP, 1};
     const cuuint32_t es[3] = {1, 1, 1};
-    if (enc(&mapA, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(x), dims, strides, box, es,
-            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+    if (enc(&mapX, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(X), dims, strides, box, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return -3;
   }
+  const int smem = ST_FIXED + 2 * 3 * boxP * 4 * 16 + 1024;
   {
-    const cuuint64_t dims[2] = {(cuuint64_t)(ST_TAPS * ST_KROW), (cuuint64_t)ST_N};
-    const cuuint64_t strides[1] = {ST_TAPS * ST_KROW * sizeof(float)};
-    const cuuint32_t box[2] = {32, ST_N};
-    const cuuint32_t es[2] = {1, 1};
-    if (enc(&mapB, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(wk), dims, strides, box, es,
-            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
-      return -3;
-  }
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(k_stem_fwd_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(k_stem_fwd_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return (int)e;
-    attr_set = true;
   }
   StemGeom g;
-  g.nimg = nimg; g.Hp = Hp; g.Wp = Wp; g.OH = OH; g.OW = OW;
+  g.nimg = nimg; g.Hp = Hp; g.Wp = Wp; g.OH = OH; g.OW = OW; g.boxP = boxP;
   g.ntiles = (int)((rows + ST_M - 1) / ST_M);
   const int sms = stem_sm_count();
   const int grid = g.ntiles < sms ? g.ntiles : sms;
-  k_stem_fwd_tc<<<grid, ST_THREADS, ST_SMEM, static_cast<cudaStream_t>(stream)>>>(
-      mapA, mapB, static_cast<float*>(y), g, static_cast<unsigned int*>(err));
+  k_stem_fwd_tc<<<grid, ST_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(
+      mapX, static_cast<const float*>(wpk), static_cast<float*>(y), g, static_cast<unsigned int*>(err));
   return (int)cudaGetLastError();
 }
 

@@ -80,10 +80,6 @@ def _stem_conv_s2d(conv, x):
     X = F.pad(xs, (0, 0, 2, 1, 2, 1)).permute(0, 3, 1, 2)          # logical NCHW over NHWC memory
     O = conv.out_channels
     w4 = F.pad(conv.weight, (1, 0, 1, 0)).reshape(O, 3, 4, 2, 4, 2).permute(0, 3, 5, 1, 2, 4).reshape(O, 12, 4, 4)
-    if settings.STEM_TC and not x.requires_grad:
-        Xn = X.permute(0, 2, 3, 1)                                  # the padded NHWC memory itself
-        if stem.supported(Xn, w4):
-            return stem.stem_conv_tc(Xn, w4)                        # TMA + tcgen05 implicit GEMM
     return F.conv2d(X, w4.contiguous(memory_format=torch.channels_last), None, 1, 0)
 
 
@@ -98,6 +94,8 @@ def _stem_conv(conv, x):
             and tuple(conv.kernel_size) == (7, 7) and tuple(conv.stride) == (2, 2) and tuple(conv.padding) == (3, 3)
             and tuple(conv.dilation) == (1, 1) and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0
             and x.is_contiguous(memory_format=torch.channels_last)):
+        if settings.STEM_TC and conv.out_channels == 64 and stem.supported(x, conv.weight):
+            return stem.stem_conv_tc(x, conv.weight)                # TMA + tcgen05 implicit GEMM (csrc/gk_stem.cu)
         return _stem_conv_s2d(conv, x)
     if not (settings.STEM_PAD4 and x.is_cuda and x.dim() == 4 and x.shape[1] == 3 and conv.in_channels == 3
             and conv.groups == 1 and conv.bias is None and conv.padding_mode == 'zeros'

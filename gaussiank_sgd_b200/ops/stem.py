@@ -2,9 +2,10 @@
 
 The reference trains torchvision's resnet50 (dl_trainer.py:187-196); its first layer, the 7x7 / stride 2 convolution
 on 3 channels, is the one convolution cuDNN has no Blackwell kernel for (it runs a pre-Hopper kernel plus a layout
-conversion).  ``stem_conv_tc`` computes it as a 4x4 convolution on the padded 2x2 space-to-depth image with the
-implicit-GEMM kernel; the weight gradient still comes from cuDNN (``aten.convolution_backward`` on the same 4x4 form),
-the input is the image and needs no gradient.
+conversion).  ``stem_conv_tc`` computes it as a 4x4 convolution on the padded 2x2 space-to-depth image: one kernel
+writes that image, one packs the weight into operand order, the implicit-GEMM kernel does the rest.  The weight
+gradient still comes from cuDNN (``aten.convolution_backward`` on the same 4x4 form); the input is the image and
+needs no gradient.
 """
 from __future__ import annotations
 
@@ -28,40 +29,51 @@ def error_codes():
     return {str(d): int(t.item()) for d, t in _err.items()}
 
 
-def supported(X: torch.Tensor, w4: torch.Tensor) -> bool:
-    return (X.is_cuda and X.dtype == torch.float32 and w4.dtype == torch.float32 and X.dim() == 4 and X.shape[3] == 12
-            and X.is_contiguous() and tuple(w4.shape) == (64, 12, 4, 4) and not torch.is_autocast_enabled()
-            and X.shape[0] * X.shape[1] * X.shape[2] < 2 ** 31 - 128)
+def supported(x: torch.Tensor, weight: torch.Tensor) -> bool:
+    """x: the image batch [N, 3, H, W] in channels_last memory; weight: the stem's [64, 3, 7, 7] parameter."""
+    return (x.is_cuda and x.dtype == torch.float32 and weight.dtype == torch.float32 and x.dim() == 4
+            and x.shape[1] == 3 and tuple(weight.shape) == (64, 3, 7, 7)
+            and x.is_contiguous(memory_format=torch.channels_last) and not x.requires_grad
+            and not torch.is_autocast_enabled()
+            and x.shape[0] * (x.shape[2] // 2 + 3) * (x.shape[3] // 2 + 3) < 2 ** 31 - 2048
+            and bool(native.cuda_lib().gk_stem_supported(int(x.shape[2]), int(x.shape[3]))))
 
 
 class _StemConvTC(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, X, w4):
-        # X [N, Hp, Wp, 12] padded space-to-depth image (NHWC), w4 [64, 12, 4, 4]
-        N, Hp, Wp, _ = X.shape
-        OH, OW = Hp - 3, Wp - 3
-        wk = w4.detach().permute(0, 2, 3, 1).reshape(64, 192).contiguous()      # [o][a*48 + b*12 + c]
-        y = torch.empty((N, OH, OW, 64), dtype=torch.float32, device=X.device)
-        rc = native.cuda_lib().gk_stem_fwd(X.data_ptr(), wk.data_ptr(), y.data_ptr(), N, OH, OW,
-                                           _err_word(X.device).data_ptr(), torch.cuda.current_stream().cuda_stream)
-        native.check(rc, "gk_stem_fwd")
+    def forward(ctx, x, weight):
+        lib = native.cuda_lib()
+        st = torch.cuda.current_stream().cuda_stream
+        N, _, H, W = x.shape
+        OH, OW = H // 2, W // 2
+        X = torch.empty((N, OH + 3, OW + 3, 12), dtype=torch.float32, device=x.device)   # padded space-to-depth image
+        native.check(lib.gk_stem_s2d(x.data_ptr(), X.data_ptr(), N, H, W, st), "gk_stem_s2d")
+        wpk = torch.empty(24 * 512, dtype=torch.float32, device=x.device)
+        wc = weight.detach().contiguous()                                       # channels_last models stride it
+        native.check(lib.gk_stem_pack_w(wc.data_ptr(), wpk.data_ptr(), st), "gk_stem_pack_w")
+        y = torch.empty((N, OH, OW, 64), dtype=torch.float32, device=x.device)
+        native.check(lib.gk_stem_fwd(X.data_ptr(), wpk.data_ptr(), y.data_ptr(), N, OH, OW,
+                                     _err_word(x.device).data_ptr(), st), "gk_stem_fwd")
         calls["fwd"] += 1
-        ctx.save_for_backward(X, w4)
+        ctx.save_for_backward(X)
         return y.permute(0, 3, 1, 2)                                            # NCHW over NHWC memory
 
     @staticmethod
     def backward(ctx, gy):
-        X, w4 = ctx.saved_tensors
         if not ctx.needs_input_grad[1]:
             return None, None
+        X, = ctx.saved_tensors
         gy = gy.contiguous(memory_format=torch.channels_last)
-        _, gw, _ = torch.ops.aten.convolution_backward(
-            gy, X.permute(0, 3, 1, 2), w4.contiguous(memory_format=torch.channels_last), None,
-            [1, 1], [0, 0], [1, 1], False, [0, 0], 1, [False, True, False])
-        return None, gw
+        # weight gradient of the 4x4 form from cuDNN (only the weight's shape matters), folded back to 7x7:
+        # gw[o, ch, 2a+dy-1, 2b+dx-1] = gw4[o, (dy*2+dx)*3 + ch, a, b]
+        w4 = torch.empty((64, 12, 4, 4), dtype=gy.dtype, device=gy.device).contiguous(memory_format=torch.channels_last)
+        _, gw4, _ = torch.ops.aten.convolution_backward(
+            gy, X.permute(0, 3, 1, 2), w4, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1, [False, True, False])
+        gw = gw4.reshape(64, 2, 2, 3, 4, 4).permute(0, 3, 4, 1, 5, 2).reshape(64, 3, 8, 8)[:, :, 1:, 1:]
+        return None, gw.contiguous()
 
 
-def stem_conv_tc(X: torch.Tensor, w4: torch.Tensor) -> torch.Tensor:
-    """``conv2d(X.permute(0, 3, 1, 2), w4)`` for the padded space-to-depth image X [N, Hp, Wp, 12] and the 4x4 form
-    w4 [64, 12, 4, 4] of the stem weight; returns [N, 64, Hp-3, Wp-3] in channels_last memory."""
-    return _StemConvTC.apply(X, w4)
+def stem_conv_tc(x: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+    """``conv2d(x, weight, stride=2, padding=3)`` for a 3-channel channels_last image batch and a [64, 3, 7, 7]
+    weight; returns [N, 64, H/2, W/2] in channels_last memory."""
+    return _StemConvTC.apply(x, weight)

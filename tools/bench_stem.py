@@ -67,16 +67,21 @@ def main():
             want = torch.nn.functional.conv2d(x.double(), conv.weight.double(), None, 2, 3)
         res[name] = {"fwd_us": timed(run(True), args.iters), "fwd_wgrad_us": timed(run(False), args.iters),
                      "max_abs_err_vs_fp64": float((y.double() - want).abs().max())}
-    # the kernel alone (no space-to-depth copy, no weight repack)
+    # the implicit-GEMM kernel alone (no space-to-depth kernel, no weight packing)
     settings.STEM_TC = settings.STEM_S2D = True
+    from gaussiank_sgd_b200.ops import native
+    lib = native.cuda_lib()
     N, H, W = args.batch, args.size, args.size
-    X = torch.zeros(N, H // 2 + 3, W // 2 + 3, 12, device=dev)
-    X[:, 2:-1, 2:-1] = torch.randn(N, H // 2, W // 2, 12, device=dev)
-    w4 = torch.randn(64, 12, 4, 4, device=dev)
-    with torch.no_grad():
-        res["kernel_only_us"] = timed(lambda: stem.stem_conv_tc(X, w4), args.iters)
-    out_bytes = N * (H // 2) * (W // 2) * 64 * 4
-    res["kernel_bytes"] = X.numel() * 4 + out_bytes
+    st = torch.cuda.current_stream().cuda_stream
+    X = torch.empty(N, H // 2 + 3, W // 2 + 3, 12, device=dev)
+    wpk = torch.empty(24 * 512, device=dev)
+    y = torch.empty(N, H // 2, W // 2, 64, device=dev)
+    e = torch.zeros(1, dtype=torch.int32, device=dev)
+    res["s2d_kernel_us"] = timed(lambda: lib.gk_stem_s2d(x.data_ptr(), X.data_ptr(), N, H, W, st), args.iters)
+    lib.gk_stem_pack_w(conv.weight.data_ptr(), wpk.data_ptr(), st)
+    res["kernel_only_us"] = timed(lambda: lib.gk_stem_fwd(X.data_ptr(), wpk.data_ptr(), y.data_ptr(), N, H // 2, W // 2,
+                                                          e.data_ptr(), st), args.iters)
+    res["kernel_bytes"] = X.numel() * 4 + y.numel() * 4
     res["kernel_gbs"] = res["kernel_bytes"] / res["kernel_only_us"] / 1e3
     res["errors"] = stem.error_codes()
     print(json.dumps(res, indent=1))
