@@ -35,6 +35,7 @@ def supported(x: torch.Tensor, weight: torch.Tensor) -> bool:
             and x.shape[1] == 3 and tuple(weight.shape) == (64, 3, 7, 7)
             and x.is_contiguous(memory_format=torch.channels_last) and not x.requires_grad
             and not torch.is_autocast_enabled()
+            and torch.backends.cudnn.allow_tf32        # the kernel is tf32: honour the switch that forbids it
             and x.shape[0] * (x.shape[2] // 2 + 3) * (x.shape[3] // 2 + 3) < 2 ** 31 - 2048
             and bool(native.cuda_lib().gk_stem_supported(int(x.shape[2]), int(x.shape[3]))))
 
