@@ -34,6 +34,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../include/gk_b200.h"
 
@@ -103,20 +104,36 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* m, 
       ::"r"(dst), "l"(m), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(m), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
 // D fp32 (1 << 4), A and B tf32 (2 << 7, 2 << 10), both K-major, N >> 3 at bit 17, M >> 4 at bit 24.
 constexpr uint32_t ST_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(ST_N >> 3) << 17) | ((uint32_t)(ST_M >> 4) << 24);
 
-__device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t da, uint64_t db, uint32_t accumulate) {
+// The same instruction with the descriptors given as (lo, hi) words: lo = start address >> 4 | LBO >> 4 << 16,
+// hi = SBO >> 4 | version | layout type.  Stepping an operand is then one 32-bit add on lo (a single thread issues
+// every MMA of the CTA, so the instructions between two MMAs are on the critical path).
+__device__ __forceinline__ void mma_tf32_w(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                           uint32_t idesc, uint32_t accumulate) {
   asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "l"(da), "l"(db), "r"(ST_IDESC), "r"(accumulate)
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "mov.b64 da, {%1, %2};\n\t"
+      "mov.b64 db, {%3, %4};\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %5, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+__device__ __forceinline__ uint32_t desc_lo(uint32_t saddr, uint32_t lbo) { return ((saddr & 0x3FFFFu) >> 4) | ((lbo >> 4) << 16); }
+__device__ __forceinline__ uint32_t desc_hi(uint32_t sbo, uint32_t layout) { return (sbo >> 4) | (1u << 14) | (layout << 29); }
+
 __device__ __forceinline__ void mma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -139,12 +156,6 @@ __device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
                : "memory");
-}
-
-// K-major operand without swizzle: 8 x 16 B core matrices, `lbo` bytes between the two K halves, `sbo` bytes between
-// 8-row groups; descriptor version 1.
-__device__ __forceinline__ uint64_t smem_desc_plain(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
-  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) | (1ull << 46);
 }
 
 struct StemGeom {
@@ -219,6 +230,7 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
   } else if (warp == 1) {
     if (lane == 0) {                                // ---- MMA issuer
       mbar_wait(bfull, 0, err, 2);
+      const uint32_t hi_plain = desc_hi(128u, 0u);  // both operands: K-major, no swizzle, 8-row groups 128 B apart
       int it = 0;
       for (int c = 0; c < nchunk; ++c) {
         const uint32_t buf = c & 1, ph = (c >> 1) & 1;
@@ -231,17 +243,17 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
           mbar_wait(tempty(as), aph ^ 1u, err, 3);  // the epilogue has drained this accumulator
           tc_fence_after();
           const uint32_t d = tmem + as * ST_N;
-          uint32_t bw = sB;
+          uint32_t b_lo = desc_lo(sB, ST_N * 16u);
 #pragma unroll 1
           for (int a = 0; a < ST_TAPS; ++a) {
-            const uint32_t row = xb + (uint32_t)(tl * ST_M + a * g.Wp) * 16u;
+            const uint32_t a_lo = desc_lo(xb + (uint32_t)(tl * ST_M + a * g.Wp) * 16u, 16u);
 #pragma unroll
             for (int t = 0; t < 3; ++t) {
 #pragma unroll
               for (int bp = 0; bp < 2; ++bp) {
-                mma_tf32(d, smem_desc_plain(row + t * plane + bp * 32u, 16u, 128u),
-                         smem_desc_plain(bw, ST_N * 16u, 128u), (a | t | bp) != 0 ? 1u : 0u);
-                bw += ST_B_MMA;
+                mma_tf32_w(d, a_lo + (uint32_t)t * (plane >> 4) + (uint32_t)bp * 2u, hi_plain, b_lo, hi_plain, ST_IDESC,
+                           (a | t | bp) != 0 ? 1u : 0u);
+                b_lo += ST_B_MMA >> 4;
               }
             }
           }
@@ -342,6 +354,196 @@ __global__ void k_stem_pack_w(const float* __restrict__ w, float* __restrict__ w
   wpk[g] = (u >= 0 && v >= 0) ? to_tf32(w[((o * 3 + ch) * 7 + u) * 7 + v]) : 0.f;
 }
 
+// ------------------------------------------------------------------------------------------------ weight gradient
+// gW4[o, c, a, b] = sum over output pixels q of gY[q, o] * X[q + a*Wp + b, c]: a GEMM whose reduction index is the
+// pixel, so both operands are "MN-major" (the pixel index is the slow one in memory).  Measured on a B200
+// (tools/experiments/umma_probe.cu): with kind::tf32 an MN-major operand is read only under layout type 1, the
+// 128-byte swizzle with 32-byte atoms (every other layout type yields zeros): 4 K rows x 128 B per atom, the 32-byte
+// chunk index XORed with the K row, MN atoms LBO apart, K atoms SBO apart.  TMA's SWIZZLE_128B_ATOM_32B writes that.
+//   A (M = 64 channels o, K = 8 pixels): a row of gY, [OW pixels][64 floats], as two column halves [OW][32 floats];
+//     a K step is 8 rows = 1024 B, LBO = one half, SBO = 512.
+//   B (N = 48 = 4 column shifts b x 12 channels, K = 8 pixels): row j of the operand is the 48 floats of X that start
+//     at position (input row, j) - consecutive rows overlap in memory (48 B apart), which an overlapping-row tensor map
+//     expresses; they land as two boxes [OW][32 floats] (the upper half of the second is out of bounds = zeros).
+// Per K step 4 MMAs (one per kernel row a) of M = 64, N = 48 accumulate into 4 x 48 = 192 TMEM columns; row m of an
+// M = 64 accumulator lives in lane (m % 16) + 32 (m / 16).  Every CTA owns a contiguous range of output rows (n, oh),
+// keeps the expanded input rows it needs in a 5-slot ring (each is loaded once and used by up to four output rows),
+// double-buffers the gY rows, and finally writes its 64 x 192 partial sums; k_stem_wgrad_fold adds the partials and
+// folds the 4x4 form back to [64, 3, 7, 7].
+constexpr int WG_SLOTS = 5;
+constexpr int WG_GST = 2;
+constexpr int WG_COLS = 192;
+constexpr int WG_TMEM_COLS = 256;
+constexpr uint32_t WG_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((48u >> 3) << 17) | ((64u >> 4) << 24);
+
+struct WgGeom {
+  int nimg, Hp, Wp, OH, OW, nrows;
+  int dbg;                                           // 1: dump all 128 TMEM lanes (part has 128 rows per CTA)
+};
+
+__global__ void __launch_bounds__(ST_THREADS, 1)
+k_stem_wgrad_tc(const __grid_constant__ CUtensorMap mapG, const __grid_constant__ CUtensorMap mapX,
+                float* __restrict__ part, const WgGeom g, unsigned int* __restrict__ err) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t half = (uint32_t)g.OW * 128u;                   // one [OW][32 floats] box (OW % 8 == 0: 1024-multiple)
+  const uint32_t sG = base;
+  const uint32_t sX = sG + WG_GST * 2u * half;
+  const uint32_t sBar = sX + WG_SLOTS * 2u * half;
+  auto gfull = [&](uint32_t s) { return sBar + 8u * s; };
+  auto gempty = [&](uint32_t s) { return sBar + 16u + 8u * s; };
+  auto xfull = [&](uint32_t s) { return sBar + 32u + 8u * s; };
+  auto xempty = [&](uint32_t s) { return sBar + 72u + 8u * s; };
+  const uint32_t tfull = sBar + 112u;
+  const uint32_t tslot = sBar + 120u;
+  volatile uint32_t* const tslot_p = reinterpret_cast<volatile uint32_t*>(smem_raw + (tslot - raw));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int per = g.nrows / (int)gridDim.x, extra = g.nrows % (int)gridDim.x;
+  const int bid = (int)blockIdx.x;
+  const int r0 = bid * per + (bid < extra ? bid : extra);
+  const int r1 = r0 + per + (bid < extra ? 1 : 0);
+  const int nks = g.OW >> 3;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&mapG);
+    tma_prefetch_desc(&mapX);
+  }
+  if (warp == 1 && lane == 0) {
+    for (uint32_t s = 0; s < WG_GST; ++s) {
+      mbar_init(gfull(s), 1);
+      mbar_init(gempty(s), 1);
+    }
+    for (uint32_t s = 0; s < WG_SLOTS; ++s) {
+      mbar_init(xfull(s), 1);
+      mbar_init(xempty(s), 1);
+    }
+    mbar_init(tfull, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tslot), "r"(WG_TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tslot_p;
+
+  if (warp == 0) {
+    if (lane == 0) {                                // ---- producer
+      uint32_t seq = 0;
+      long long lastI = -1;
+      int rc = 0;
+      for (int R = r0; R < r1; ++R, ++rc) {
+        const int n = R / g.OH, oh = R - n * g.OH;
+        const long long I0 = (long long)n * g.Hp + oh;
+        for (long long I = (I0 > lastI + 1 ? I0 : lastI + 1); I <= I0 + 3; ++I, ++seq) {
+          const uint32_t s = seq % WG_SLOTS;
+          mbar_wait(xempty(s), ((seq / WG_SLOTS) & 1u) ^ 1u, err, 11);
+          mbar_expect_tx(xfull(s), 2u * half);
+          tma_load_2d(sX + s * 2u * half, &mapX, xfull(s), 0, (int)(I * g.Wp));
+          tma_load_2d(sX + s * 2u * half + half, &mapX, xfull(s), 32, (int)(I * g.Wp));
+        }
+        lastI = I0 + 3;
+        const uint32_t gs = rc % WG_GST;
+        mbar_wait(gempty(gs), ((rc / WG_GST) & 1u) ^ 1u, err, 12);
+        mbar_expect_tx(gfull(gs), 2u * half);
+        tma_load_2d(sG + gs * 2u * half, &mapG, gfull(gs), 0, R * g.OW);
+        tma_load_2d(sG + gs * 2u * half + half, &mapG, gfull(gs), 32, R * g.OW);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {                                // ---- MMA issuer
+      uint32_t seq = 0;
+      long long lastI = -1;
+      int rc = 0;
+      for (int R = r0; R < r1; ++R, ++rc) {
+        const int n = R / g.OH, oh = R - n * g.OH;
+        const long long I0 = (long long)n * g.Hp + oh;
+        const long long first = I0 > lastI + 1 ? I0 : lastI + 1;
+        const uint32_t cnt = (uint32_t)(I0 + 4 - first);
+        for (uint32_t s = seq; s < seq + cnt; ++s) mbar_wait(xfull(s % WG_SLOTS), (s / WG_SLOTS) & 1u, err, 13);
+        seq += cnt;
+        lastI = I0 + 3;
+        const uint32_t gs = rc % WG_GST;
+        mbar_wait(gfull(gs), (rc / WG_GST) & 1u, err, 14);
+        tc_fence_after();
+        const uint32_t ga = sG + gs * 2u * half;
+        uint32_t xs[ST_TAPS];
+#pragma unroll
+        for (int a = 0; a < ST_TAPS; ++a) xs[a] = sX + ((seq - 4u + (uint32_t)a) % WG_SLOTS) * 2u * half;
+        const uint32_t hi = desc_hi(512u, 1u);
+        uint32_t a_lo = desc_lo(ga, half);
+        uint32_t x_lo[ST_TAPS];
+#pragma unroll
+        for (int a = 0; a < ST_TAPS; ++a) x_lo[a] = desc_lo(xs[a], half);
+#pragma unroll 1
+        for (int ks = 0; ks < nks; ++ks) {
+#pragma unroll
+          for (int a = 0; a < ST_TAPS; ++a) {
+            mma_tf32_w(tmem + (uint32_t)a * 48u, a_lo, hi, x_lo[a], hi, WG_IDESC, (rc | ks) != 0 ? 1u : 0u);
+            x_lo[a] += 1024u >> 4;
+          }
+          a_lo += 1024u >> 4;
+        }
+        mma_commit(gempty(gs));
+        const bool slide = R + 1 < r1 && (R + 1) / g.OH == n;   // the next row reuses three of these input rows
+        mma_commit(xempty((seq - 4u) % WG_SLOTS));
+        if (!slide)
+          for (uint32_t a = 1; a < 4; ++a) mma_commit(xempty((seq - 4u + a) % WG_SLOTS));
+      }
+      mma_commit(tfull);
+    }
+  } else if (warp >= 4) {                           // ---- epilogue: the partial sums of this CTA
+    const int q = warp & 3;
+    mbar_wait(tfull, 0, err, 15);
+    tc_fence_after();
+    float* dst = g.dbg ? part + ((size_t)bid * 128 + 32 * q + lane) * WG_COLS
+                       : part + ((size_t)bid * ST_N + 16 * q + (lane & 15)) * WG_COLS;
+#pragma unroll 1
+    for (int c = 0; c < WG_COLS / 32; ++c) {
+      uint32_t v[32];
+      tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)c * 32u, v);
+      tmem_wait_ld();
+      if (lane < 16 || g.dbg) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(dst + c * 32 + j * 4) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      }
+    }
+    tc_fence_before();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(WG_TMEM_COLS) : "memory");
+  }
+}
+
+// gw[o, ch, u, v] = sum over CTAs of part[cta][o][a*48 + b*12 + c], 2a + dy - 1 = u, 2b + dx - 1 = v,
+// c = (dy*2 + dx)*3 + ch.
+__global__ void k_stem_wgrad_fold(const float* __restrict__ part, int nparts, float* __restrict__ gw) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= ST_N * 3 * 49) return;
+  const int v = i % 7, u = (i / 7) % 7, ch = (i / 49) % 3, o = i / 147;
+  const int dy = (u + 1) & 1, a = (u + 1) >> 1, dx = (v + 1) & 1, b = (v + 1) >> 1;
+  const int c12 = (dy * 2 + dx) * 3 + ch;
+  const float* p = part + (size_t)o * WG_COLS + a * 48 + b * 12 + c12;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  int k = 0;
+  for (; k + 4 <= nparts; k += 4) {
+    s0 += p[(size_t)(k + 0) * ST_N * WG_COLS];
+    s1 += p[(size_t)(k + 1) * ST_N * WG_COLS];
+    s2 += p[(size_t)(k + 2) * ST_N * WG_COLS];
+    s3 += p[(size_t)(k + 3) * ST_N * WG_COLS];
+  }
+  for (; k < nparts; ++k) s0 += p[(size_t)k * ST_N * WG_COLS];
+  gw[i] = (s0 + s1) + (s2 + s3);
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -434,6 +636,65 @@ int gk_stem_fwd(const void* X, const void* wpk, void* y, int nimg, int OH, int O
   const int grid = g.ntiles < sms ? g.ntiles : sms;
   k_stem_fwd_tc<<<grid, ST_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(
       mapX, static_cast<const float*>(wpk), static_cast<float*>(y), g, static_cast<unsigned int*>(err));
+  return (int)cudaGetLastError();
+}
+
+static int wgrad_smem(int OW) { return (WG_GST + WG_SLOTS) * 2 * OW * 128 + 256 + 1024; }
+
+// 1 when gk_stem_wgrad covers an output of OH x OW pixels.
+int gk_stem_wgrad_supported(int OH, int OW) {
+  return OH > 0 && OW >= 8 && OW % 8 == 0 && OW <= 256 && wgrad_smem(OW) <= 227 * 1024;
+}
+
+// Floats of workspace gk_stem_wgrad needs (one 64 x 192 partial per CTA).
+long long gk_stem_wgrad_workspace(void) { return (long long)stem_sm_count() * ST_N * WG_COLS; }
+
+// gy [nimg, OH, OW, 64] fp32 (NHWC), X: the padded space-to-depth image of the forward pass  ->  gw [64, 3, 7, 7].
+int gk_stem_wgrad(const void* gy, const void* X, void* gw, void* work, int nimg, int OH, int OW, void* err, void* stream) {
+  if (nimg <= 0 || !gk_stem_wgrad_supported(OH, OW)) return -2;
+  const int Hp = OH + 3, Wp = OW + 3;
+  const long long P = (long long)nimg * Hp * Wp;
+  const long long nrows = (long long)nimg * OH;
+  if (P > (1LL << 31) - 2048 || nrows * OW > (1LL << 31) - 1) return -2;
+  if ((reinterpret_cast<uintptr_t>(gy) | reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(work)) & 15) return -2;
+  EncodeTiledFn enc = encode_fn();
+  if (!enc) return -3;
+  WgGeom g;
+  g.nimg = nimg; g.Hp = Hp; g.Wp = Wp; g.OH = OH; g.OW = OW; g.nrows = (int)nrows;
+  g.dbg = getenv("GK_STEM_WG_DEBUG") != nullptr;
+  CUtensorMap mapG, mapX;
+  {
+    const cuuint64_t dims[2] = {(cuuint64_t)ST_N, (cuuint64_t)(nrows * OW)};
+    const cuuint64_t strides[1] = {ST_N * sizeof(float)};
+    const cuuint32_t box[2] = {32, (cuuint32_t)OW};
+    const cuuint32_t es[2] = {1, 1};
+    if (enc(&mapG, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(gy), dims, strides, box, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return -3;
+  }
+  {
+    // rows = positions, 48 floats each, 48 B apart: consecutive rows overlap (the window of a position is the next
+    // 4 positions' channels); the last rows' windows would run past the image: they are cut off (zeros)
+    const cuuint64_t dims[2] = {48, (cuuint64_t)(P - 3)};
+    const cuuint64_t strides[1] = {12 * sizeof(float)};
+    const cuuint32_t box[2] = {32, (cuuint32_t)OW};
+    const cuuint32_t es[2] = {1, 1};
+    if (enc(&mapX, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(X), dims, strides, box, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return -3;
+  }
+  const int smem = wgrad_smem(OW);
+  {
+    cudaError_t e = cudaFuncSetAttribute(k_stem_wgrad_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+  }
+  const int sms = stem_sm_count();
+  const int grid = nrows < sms ? (int)nrows : sms;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  k_stem_wgrad_tc<<<grid, ST_THREADS, smem, s>>>(mapG, mapX, static_cast<float*>(work), g, static_cast<unsigned int*>(err));
+  k_stem_wgrad_fold<<<(ST_N * 147 + 255) / 256, 256, 0, s>>>(static_cast<const float*>(work), grid, static_cast<float*>(gw));
   return (int)cudaGetLastError();
 }
 

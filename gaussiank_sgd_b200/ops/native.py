@@ -180,6 +180,9 @@ def cuda_lib():
             _proto(lib, "gk_stem_s2d", [_P, _P, C.c_int32, C.c_int32, C.c_int32, _P])
             _proto(lib, "gk_stem_pack_w", [_P, _P, _P])
             _proto(lib, "gk_stem_supported", [C.c_int32, C.c_int32])
+            _proto(lib, "gk_stem_wgrad_supported", [C.c_int32, C.c_int32])
+            _proto(lib, "gk_stem_wgrad_workspace", [], C.c_longlong)
+            _proto(lib, "gk_stem_wgrad", [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P])
             _proto(lib, "gk_grad_norm_static", [_P, _P, C.c_int32, C.c_float, _P, _P])
             _proto(lib, "gk_scale", [_P, _P, C.c_int32, _P, _P])
             _proto(lib, "gk_randomk_send", [ch, ds, C.c_uint64, _P])

@@ -4,17 +4,19 @@ The reference trains torchvision's resnet50 (dl_trainer.py:187-196); its first l
 on 3 channels, is the one convolution cuDNN has no Blackwell kernel for (it runs a pre-Hopper kernel plus a layout
 conversion).  ``stem_conv_tc`` computes it as a 4x4 convolution on the padded 2x2 space-to-depth image: one kernel
 writes that image, one packs the weight into operand order, the implicit-GEMM kernel does the rest.  The weight
-gradient still comes from cuDNN (``aten.convolution_backward`` on the same 4x4 form); the input is the image and
-needs no gradient.
+gradient is a second tcgen05 kernel (reduction over the pixels, both operands MN-major) plus a fold of the per-CTA
+partial sums; shapes it does not cover go to cuDNN (``aten.convolution_backward`` on the same 4x4 form).  The input
+is the image and needs no gradient.
 """
 from __future__ import annotations
 
 import torch
 
+from .. import settings
 from . import native
 
 _err = {}
-calls = {"fwd": 0}                                   # launches of the tensor-core kernel (tests assert on it)
+calls = {"fwd": 0, "wgrad": 0}                                   # launches of the tensor-core kernel (tests assert on it)
 
 
 def _err_word(device):
@@ -65,6 +67,16 @@ class _StemConvTC(torch.autograd.Function):
             return None, None
         X, = ctx.saved_tensors
         gy = gy.contiguous(memory_format=torch.channels_last)
+        N, OH, OW = gy.shape[0], gy.shape[2], gy.shape[3]
+        lib = native.cuda_lib()
+        if settings.STEM_TC_WGRAD and gy.dtype == torch.float32 and lib.gk_stem_wgrad_supported(OH, OW):
+            work = torch.empty(lib.gk_stem_wgrad_workspace(), dtype=torch.float32, device=gy.device)
+            gw = torch.empty((64, 3, 7, 7), dtype=torch.float32, device=gy.device)
+            native.check(lib.gk_stem_wgrad(gy.data_ptr(), X.data_ptr(), gw.data_ptr(), work.data_ptr(), N, OH, OW,
+                                           _err_word(gy.device).data_ptr(), torch.cuda.current_stream().cuda_stream),
+                         "gk_stem_wgrad")
+            calls["wgrad"] += 1
+            return None, gw
         # weight gradient of the 4x4 form from cuDNN (only the weight's shape matters), folded back to 7x7:
         # gw[o, ch, 2a+dy-1, 2b+dx-1] = gw4[o, (dy*2+dx)*3 + ch, a, b]
         w4 = torch.empty((64, 12, 4, 4), dtype=gy.dtype, device=gy.device).contiguous(memory_format=torch.channels_last)

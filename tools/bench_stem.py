@@ -59,8 +59,9 @@ def main():
         return f
 
     want = None
-    for name, tc, s2d in (("cudnn_7x7", False, False), ("cudnn_s2d_4x4", False, True), ("tcgen05_s2d_4x4", True, True)):
-        settings.STEM_TC, settings.STEM_S2D = tc, s2d
+    for name, tc, s2d, wg in (("cudnn_7x7", False, False, False), ("cudnn_s2d_4x4", False, True, False),
+                              ("tcgen05_fwd_cudnn_wgrad", True, True, False), ("tcgen05_s2d_4x4", True, True, True)):
+        settings.STEM_TC, settings.STEM_S2D, settings.STEM_TC_WGRAD = tc, s2d, wg
         with torch.no_grad():
             y = fuse._stem_conv(conv, x).float()
         if want is None:
@@ -68,7 +69,7 @@ def main():
         res[name] = {"fwd_us": timed(run(True), args.iters), "fwd_wgrad_us": timed(run(False), args.iters),
                      "max_abs_err_vs_fp64": float((y.double() - want).abs().max())}
     # the implicit-GEMM kernel alone (no space-to-depth kernel, no weight packing)
-    settings.STEM_TC = settings.STEM_S2D = True
+    settings.STEM_TC = settings.STEM_S2D = settings.STEM_TC_WGRAD = True
     from gaussiank_sgd_b200.ops import native
     lib = native.cuda_lib()
     N, H, W = args.batch, args.size, args.size
@@ -81,6 +82,10 @@ def main():
     lib.gk_stem_pack_w(conv.weight.data_ptr(), wpk.data_ptr(), st)
     res["kernel_only_us"] = timed(lambda: lib.gk_stem_fwd(X.data_ptr(), wpk.data_ptr(), y.data_ptr(), N, H // 2, W // 2,
                                                           e.data_ptr(), st), args.iters)
+    gw = torch.empty(64, 3, 7, 7, device=dev)
+    work = torch.empty(lib.gk_stem_wgrad_workspace(), device=dev)
+    res["wgrad_kernels_us"] = timed(lambda: lib.gk_stem_wgrad(y.data_ptr(), X.data_ptr(), gw.data_ptr(), work.data_ptr(), N,
+                                                            H // 2, W // 2, e.data_ptr(), st), args.iters)
     res["kernel_bytes"] = X.numel() * 4 + y.numel() * 4
     res["kernel_gbs"] = res["kernel_bytes"] / res["kernel_only_us"] / 1e3
     res["errors"] = stem.error_codes()
