@@ -49,8 +49,11 @@ constexpr int ST_B_MMA = 2 * ST_N * 16;            // weight bytes per step: 2 h
 constexpr int ST_B_BYTES = ST_NMMA * ST_B_MMA;     // 48 KB
 constexpr int ST_EPI_PITCH = 36;                   // floats; 32 + 4 keeps the float4 phases conflict-free
 constexpr int ST_EPI_BYTES = 4 * 32 * ST_EPI_PITCH * 4;
-constexpr int ST_THREADS = 256;
-constexpr int ST_TMEM_COLS = 128;
+constexpr int ST_NI = 4;                           // MMA-issuing warps = TMEM accumulators
+constexpr int ST_W_ALLOC = 1 + ST_NI;              // warp 0 producer, 1..ST_NI issuers, then TMEM allocator, then 4 epilogue
+constexpr int ST_W_EPI = 2 + ST_NI;
+constexpr int ST_THREADS = 32 * (ST_W_EPI + 4);
+constexpr int ST_TMEM_COLS = 256;
 constexpr int ST_FIXED = ST_B_BYTES + ST_EPI_BYTES + 256;   // + 2 chunk buffers of 3 planes
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -178,8 +181,8 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
   auto empty = [&](uint32_t s) { return sBar + 16u + 8u * s; };
   const uint32_t bfull = sBar + 32u;
   auto tfull = [&](uint32_t s) { return sBar + 40u + 8u * s; };
-  auto tempty = [&](uint32_t s) { return sBar + 56u + 8u * s; };
-  const uint32_t tslot = sBar + 72u;
+  auto tempty = [&](uint32_t s) { return sBar + 40u + 8u * ST_NI + 8u * s; };
+  const uint32_t tslot = sBar + 40u + 16u * ST_NI;
   float* const epi = reinterpret_cast<float*>(smem_raw + (sE - raw));
   volatile uint32_t* const tslot_p = reinterpret_cast<volatile uint32_t*>(smem_raw + (tslot - raw));
 
@@ -196,14 +199,16 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
   if (warp == 1 && lane == 0) {
     for (uint32_t s = 0; s < 2; ++s) {
       mbar_init(full(s), 1);
-      mbar_init(empty(s), 1);
+      mbar_init(empty(s), ST_NI);                   // every issuer releases the chunk buffer
+    }
+    for (uint32_t s = 0; s < ST_NI; ++s) {
       mbar_init(tfull(s), 1);
       mbar_init(tempty(s), 4);                      // one arrival per epilogue warp
     }
     mbar_init(bfull, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 2) {
+  if (warp == ST_W_ALLOC) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tslot), "r"(ST_TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -227,10 +232,15 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
             tma_load_3d(dst + t * plane + (uint32_t)(k * g.boxP) * 16u, &mapX, full(buf), 0, q0 + k * g.boxP, t);
       }
     }
-  } else if (warp == 1) {
-    if (lane == 0) {                                // ---- MMA issuer
+  } else if (warp <= ST_NI) {
+    if (lane == 0) {                                // ---- MMA issuers: issuer `me` owns accumulator `me` and every ST_NI-th tile
+      // (one thread can issue an MMA of this size only every ~100 cycles - the descriptor arithmetic and the issue
+      // itself are a dependent instruction chain - so several warps, each on its own scheduler, issue in parallel)
+      const uint32_t me = (uint32_t)warp - 1u;
       mbar_wait(bfull, 0, err, 2);
       const uint32_t hi_plain = desc_hi(128u, 0u);  // both operands: K-major, no swizzle, 8-row groups 128 B apart
+      const uint32_t d = tmem + me * ST_N;
+      uint32_t use = 0;
       int it = 0;
       for (int c = 0; c < nchunk; ++c) {
         const uint32_t buf = c & 1, ph = (c >> 1) & 1;
@@ -239,10 +249,10 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
         const uint32_t xb = sX + buf * 3u * plane;
         const int ntc = nt - c * ST_CHUNK < ST_CHUNK ? nt - c * ST_CHUNK : ST_CHUNK;
         for (int tl = 0; tl < ntc; ++tl, ++it) {
-          const uint32_t as = it & 1, aph = (it >> 1) & 1;
-          mbar_wait(tempty(as), aph ^ 1u, err, 3);  // the epilogue has drained this accumulator
+          if ((uint32_t)it % ST_NI != me) continue;
+          mbar_wait(tempty(me), (use & 1u) ^ 1u, err, 3);  // the epilogue has drained this accumulator
+          ++use;
           tc_fence_after();
-          const uint32_t d = tmem + as * ST_N;
           uint32_t b_lo = desc_lo(sB, ST_N * 16u);
 #pragma unroll 1
           for (int a = 0; a < ST_TAPS; ++a) {
@@ -257,17 +267,17 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
               }
             }
           }
-          mma_commit(tfull(as));
+          mma_commit(tfull(me));
         }
-        mma_commit(empty(buf));                     // the chunk buffer is free once these MMAs have read it
+        mma_commit(empty(buf));                     // this issuer's MMAs on the chunk buffer are done (or it had none)
       }
     }
-  } else if (warp >= 4) {                           // ---- epilogue
+  } else if (warp >= ST_W_EPI) {                    // ---- epilogue
     const int q = warp & 3;                         // TMEM lanes 32q .. 32q+31
     float* const stg = epi + q * 32 * ST_EPI_PITCH;
     const long long pl = (long long)g.Hp * g.Wp;
     for (int it = 0; it < nt; ++it) {
-      const uint32_t as = it & 1, aph = (it >> 1) & 1;
+      const uint32_t as = (uint32_t)it % ST_NI, aph = ((uint32_t)it / ST_NI) & 1u;
       // where this lane's row goes: position -> (n, i, j); -1 for the positions that are not output pixels
       const long long p = (long long)(t0 + it) * ST_M + q * 32 + lane;
       const int n = (int)(p / pl);
@@ -305,7 +315,7 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) {
+  if (warp == ST_W_ALLOC) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(ST_TMEM_COLS) : "memory");
   }
@@ -318,26 +328,31 @@ __device__ __forceinline__ float to_tf32(float v) {   // round to nearest: the M
 }
 
 // x [N, H, W, 3] (NHWC) -> X [N, Hp, Wp, 12], X[n, i, j, (dy*2+dx)*3 + c] = x[n, 2(i-2)+dy, 2(j-2)+dx, c], zero in the
-// two leading and one trailing rows / columns.  One thread per 16-byte quarter of a position.
-__global__ void k_stem_s2d(const float* __restrict__ x, float4* __restrict__ X, int nimg, int H, int W, long long nquart) {
+// two leading and one trailing rows / columns.  One thread per (position, dy): six consecutive floats in, six out,
+// both 8-byte aligned.
+__global__ void __launch_bounds__(256) k_stem_s2d(const float* __restrict__ x, float* __restrict__ X, int nimg, int H, int W,
+                                                  long long nhalf) {
   const int Hp = H / 2 + 3, Wp = W / 2 + 3;
-  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < nquart; g += (long long)gridDim.x * blockDim.x) {
-    const int t = (int)(g % 3);
-    const long long pos = g / 3;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < nhalf; g += (long long)gridDim.x * blockDim.x) {
+    const int dy = (int)(g & 1);
+    const long long pos = g >> 1;
     const int j = (int)(pos % Wp);
     const long long ni = pos / Wp;
     const int i = (int)(ni % Hp), n = (int)(ni / Hp);
-    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    float2 v0 = make_float2(0.f, 0.f), v1 = v0, v2 = v0;
     if (i >= 2 && i < Hp - 1 && j >= 2 && j < Wp - 1) {
-      const float* r0 = x + (((long long)n * H + 2 * (i - 2)) * W + 2 * (j - 2)) * 3;   // 6 floats: dy = 0
-      const float* r1 = r0 + (long long)W * 3;                                           // 6 floats: dy = 1
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const int k = 4 * t + e;
-        v[e] = to_tf32(__ldg(k < 6 ? r0 + k : r1 + (k - 6)));
-      }
+      const float2* r = reinterpret_cast<const float2*>(x + (((long long)n * H + 2 * (i - 2) + dy) * W + 2 * (j - 2)) * 3);
+      v0 = __ldg(r);
+      v1 = __ldg(r + 1);
+      v2 = __ldg(r + 2);
+      v0.x = to_tf32(v0.x); v0.y = to_tf32(v0.y);
+      v1.x = to_tf32(v1.x); v1.y = to_tf32(v1.y);
+      v2.x = to_tf32(v2.x); v2.y = to_tf32(v2.y);
     }
-    X[g] = make_float4(v[0], v[1], v[2], v[3]);
+    float2* o = reinterpret_cast<float2*>(X + g * 6);
+    o[0] = v0;
+    o[1] = v1;
+    o[2] = v2;
   }
 }
 
@@ -413,16 +428,16 @@ k_stem_wgrad_tc(const __grid_constant__ CUtensorMap mapG, const __grid_constant_
   if (warp == 1 && lane == 0) {
     for (uint32_t s = 0; s < WG_GST; ++s) {
       mbar_init(gfull(s), 1);
-      mbar_init(gempty(s), 1);
+      mbar_init(gempty(s), ST_TAPS);                // every issuer releases the gY row
     }
     for (uint32_t s = 0; s < WG_SLOTS; ++s) {
       mbar_init(xfull(s), 1);
       mbar_init(xempty(s), 1);
     }
-    mbar_init(tfull, 1);
+    mbar_init(tfull, ST_TAPS);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 2) {
+  if (warp == ST_W_ALLOC) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tslot), "r"(WG_TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -439,6 +454,11 @@ k_stem_wgrad_tc(const __grid_constant__ CUtensorMap mapG, const __grid_constant_
       for (int R = r0; R < r1; ++R, ++rc) {
         const int n = R / g.OH, oh = R - n * g.OH;
         const long long I0 = (long long)n * g.Hp + oh;
+        const uint32_t gs = rc % WG_GST;            // gY first: the issuers release X slots only after they see it
+        mbar_wait(gempty(gs), ((rc / WG_GST) & 1u) ^ 1u, err, 12);
+        mbar_expect_tx(gfull(gs), 2u * half);
+        tma_load_2d(sG + gs * 2u * half, &mapG, gfull(gs), 0, R * g.OW);
+        tma_load_2d(sG + gs * 2u * half + half, &mapG, gfull(gs), 32, R * g.OW);
         for (long long I = (I0 > lastI + 1 ? I0 : lastI + 1); I <= I0 + 3; ++I, ++seq) {
           const uint32_t s = seq % WG_SLOTS;
           mbar_wait(xempty(s), ((seq / WG_SLOTS) & 1u) ^ 1u, err, 11);
@@ -447,16 +467,14 @@ k_stem_wgrad_tc(const __grid_constant__ CUtensorMap mapG, const __grid_constant_
           tma_load_2d(sX + s * 2u * half + half, &mapX, xfull(s), 32, (int)(I * g.Wp));
         }
         lastI = I0 + 3;
-        const uint32_t gs = rc % WG_GST;
-        mbar_wait(gempty(gs), ((rc / WG_GST) & 1u) ^ 1u, err, 12);
-        mbar_expect_tx(gfull(gs), 2u * half);
-        tma_load_2d(sG + gs * 2u * half, &mapG, gfull(gs), 0, R * g.OW);
-        tma_load_2d(sG + gs * 2u * half + half, &mapG, gfull(gs), 32, R * g.OW);
       }
     }
-  } else if (warp == 1) {
-    if (lane == 0) {                                // ---- MMA issuer
-      uint32_t seq = 0;
+  } else if (warp <= ST_TAPS) {
+    if (lane == 0) {                                // ---- MMA issuers: issuer a owns kernel row a and its 48 TMEM columns
+      const uint32_t a = (uint32_t)warp - 1u;
+      const uint32_t hi = desc_hi(512u, 1u);
+      const uint32_t d = tmem + a * 48u;
+      uint32_t seq = 0, pending = 0xffffffffu;
       long long lastI = -1;
       int rc = 0;
       for (int R = r0; R < r1; ++R, ++rc) {
@@ -464,39 +482,34 @@ k_stem_wgrad_tc(const __grid_constant__ CUtensorMap mapG, const __grid_constant_
         const long long I0 = (long long)n * g.Hp + oh;
         const long long first = I0 > lastI + 1 ? I0 : lastI + 1;
         const uint32_t cnt = (uint32_t)(I0 + 4 - first);
-        for (uint32_t s = seq; s < seq + cnt; ++s) mbar_wait(xfull(s % WG_SLOTS), (s / WG_SLOTS) & 1u, err, 13);
+        const uint32_t mine = seq + cnt - 4u + a;             // the load that brought input row I0 + a
         seq += cnt;
         lastI = I0 + 3;
         const uint32_t gs = rc % WG_GST;
         mbar_wait(gfull(gs), (rc / WG_GST) & 1u, err, 14);
+        // gY row R is only loaded once every issuer has finished output row R - 2, and the other users of the slot
+        // freed here read it at output rows <= R - 2: now it is safe to hand it back (after this thread's own MMAs).
+        // This must precede the wait for this row's X data: at an image boundary the producer needs these slots.
+        if (pending != 0xffffffffu) mma_commit(xempty(pending));
+        mbar_wait(xfull(mine % WG_SLOTS), (mine / WG_SLOTS) & 1u, err, 13);
         tc_fence_after();
-        const uint32_t ga = sG + gs * 2u * half;
-        uint32_t xs[ST_TAPS];
-#pragma unroll
-        for (int a = 0; a < ST_TAPS; ++a) xs[a] = sX + ((seq - 4u + (uint32_t)a) % WG_SLOTS) * 2u * half;
-        const uint32_t hi = desc_hi(512u, 1u);
-        uint32_t a_lo = desc_lo(ga, half);
-        uint32_t x_lo[ST_TAPS];
-#pragma unroll
-        for (int a = 0; a < ST_TAPS; ++a) x_lo[a] = desc_lo(xs[a], half);
-#pragma unroll 1
+        uint32_t a_lo = desc_lo(sG + gs * 2u * half, half);
+        uint32_t x_lo = desc_lo(sX + (mine % WG_SLOTS) * 2u * half, half);
+#pragma unroll 2
         for (int ks = 0; ks < nks; ++ks) {
-#pragma unroll
-          for (int a = 0; a < ST_TAPS; ++a) {
-            mma_tf32_w(tmem + (uint32_t)a * 48u, a_lo, hi, x_lo[a], hi, WG_IDESC, (rc | ks) != 0 ? 1u : 0u);
-            x_lo[a] += 1024u >> 4;
-          }
+          mma_tf32_w(d, a_lo, hi, x_lo, hi, WG_IDESC, (rc | ks) != 0 ? 1u : 0u);
           a_lo += 1024u >> 4;
+          x_lo += 1024u >> 4;
         }
         mma_commit(gempty(gs));
-        const bool slide = R + 1 < r1 && (R + 1) / g.OH == n;   // the next row reuses three of these input rows
-        mma_commit(xempty((seq - 4u) % WG_SLOTS));
-        if (!slide)
-          for (uint32_t a = 1; a < 4; ++a) mma_commit(xempty((seq - 4u + a) % WG_SLOTS));
+        // input row I0 is not needed after this output row; at the end of an image neither are the other three.  The
+        // slot is handed back at the start of the next output row (see above); after the last row nothing is reloaded.
+        const bool slide = R + 1 < r1 && (R + 1) / g.OH == n;
+        pending = (a == 0 || !slide) ? mine % WG_SLOTS : 0xffffffffu;
       }
       mma_commit(tfull);
     }
-  } else if (warp >= 4) {                           // ---- epilogue: the partial sums of this CTA
+  } else if (warp >= ST_W_EPI) {                    // ---- epilogue: the partial sums of this CTA
     const int q = warp & 3;
     mbar_wait(tfull, 0, err, 15);
     tc_fence_after();
@@ -517,7 +530,7 @@ k_stem_wgrad_tc(const __grid_constant__ CUtensorMap mapG, const __grid_constant_
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) {
+  if (warp == ST_W_ALLOC) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(WG_TMEM_COLS) : "memory");
   }
@@ -584,12 +597,13 @@ int gk_stem_supported(int H, int W) {
 // x [nimg, H, W, 3] fp32 NHWC  ->  X [nimg, H/2+3, W/2+3, 12] fp32 (values rounded to tf32).
 int gk_stem_s2d(const void* x, void* X, int nimg, int H, int W, void* stream) {
   if (nimg <= 0 || H % 2 || W % 2) return -2;
-  const long long nquart = (long long)nimg * (H / 2 + 3) * (W / 2 + 3) * 3;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(X)) & 7) return -2;
+  const long long nhalf = (long long)nimg * (H / 2 + 3) * (W / 2 + 3) * 2;
   const int threads = 256;
-  long long blocks = (nquart + threads - 1) / threads;
+  long long blocks = (nhalf + threads - 1) / threads;
   if (blocks > 148 * 32) blocks = 148 * 32;
   k_stem_s2d<<<(int)blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const float*>(x), static_cast<float4*>(X), nimg, H, W, nquart);
+      static_cast<const float*>(x), static_cast<float*>(X), nimg, H, W, nhalf);
   return (int)cudaGetLastError();
 }
 

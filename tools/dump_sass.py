@@ -14,7 +14,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SO = os.path.join(ROOT, "gaussiank_sgd_b200", "ops", "libgk_cuda.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
 WATCH = ["LDG", "STG", "LDGSTS", "LDS", "STS", "ATOMG", "RED", "ATOMS", "BAR", "MEMBAR", "FENCE", "ERRBAR", "CCTL",
-         "SHFL", "VOTE", "MATCH", "NANOSLEEP", "MUFU", "DFMA", "DMUL", "DADD", "FFMA", "IMAD", "BRA"]
+         "SHFL", "VOTE", "MATCH", "NANOSLEEP", "MUFU", "DFMA", "DMUL", "DADD", "FFMA", "IMAD", "BRA",
+         "UTCHMMA", "UTCBAR", "UTCATOMSWS", "UTMALDG", "UTMACCTL", "UBLKCP", "LDTM", "SYNCS", "ELECT"]
 
 
 def demangle(name):
@@ -25,7 +26,7 @@ def demangle(name):
 
 
 def short(dem):
-    base = dem.split("(")[0].replace("void ", "")
+    base = dem.replace("(anonymous namespace)::", "").split("(")[0].replace("void ", "")
     return re.sub(r"[^A-Za-z0-9_]+", "_", base).strip("_")
 
 

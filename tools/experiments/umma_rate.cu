@@ -8,7 +8,7 @@
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-__global__ void rate(int M, int N, int nacc, int a_major, int mode, long long* out) {
+__global__ void rate(int M, int N, int nacc, int a_major, int mode, int step, int kind, long long* out) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ uint64_t bar;
   __shared__ uint32_t tslot;
@@ -29,9 +29,16 @@ __global__ void rate(int M, int N, int nacc, int a_major, int mode, long long* o
   const uint32_t tmem = tslot;
   if (mode == 0 ? threadIdx.x == 0 : threadIdx.x < 32) {
     const uint32_t layout = a_major ? 1u : 0u;
-    const uint32_t a_lo = ((base & 0x3FFFFu) >> 4) | ((a_major ? 4096u >> 4 : 128u >> 4) << 16);
+    // kind 0: K-major no swizzle, canonical (LBO 128, SBO 256); kind 1: the stem forward's overlapping form (LBO 16, SBO 128,
+    // start 48 B off alignment); kind 2: K-major 128-byte swizzle (SBO 1024)
+    const uint32_t lbo = a_major ? 4096u : (kind == 1 ? 16u : 128u);
+    const uint32_t sbo = a_major ? 512u : (kind == 1 ? 128u : (kind == 2 ? 1024u : 256u));
+    const uint32_t lay = a_major ? 1u : (kind == 2 ? 2u : 0u);
+    const uint32_t a_lo0 = (((base + (kind == 1 ? 48u : 0u)) & 0x3FFFFu) >> 4) | ((lbo >> 4) << 16);
     const uint32_t b_lo = (((base + 65536u) & 0x3FFFFu) >> 4) | ((a_major ? 4096u >> 4 : 128u >> 4) << 16);
-    const uint32_t hi = ((a_major ? 512u : 256u) >> 4) | (1u << 14) | (layout << 29);
+    const uint32_t hi = (sbo >> 4) | (1u << 14) | (lay << 29);
+    const uint32_t hib = ((a_major ? 512u : 256u) >> 4) | (1u << 14) | (layout << 29);
+    uint32_t a_lo = a_lo0;
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)a_major << 15) | ((uint32_t)a_major << 16) |
                            ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
     const long long t0 = clock64();
@@ -41,8 +48,9 @@ __global__ void rate(int M, int N, int nacc, int a_major, int mode, long long* o
     for (int i = 0; i < 512; ++i) {
       const uint32_t d = tmem + (uint32_t)(i & (nacc - 1)) * (uint32_t)N;
       if (elected) asm volatile(
-          "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tmov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %2};\n\tsetp.ne.b32 p, %5, 0;\n\t"
-          "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, p;\n\t}" ::"r"(d), "r"(a_lo), "r"(hi), "r"(b_lo), "r"(idesc), "r"(1u));
+          "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tmov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %6};\n\tsetp.ne.b32 p, %5, 0;\n\t"
+          "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, p;\n\t}" ::"r"(d), "r"(a_lo), "r"(hi), "r"(b_lo), "r"(idesc), "r"(1u), "r"(hib));
+      a_lo = a_lo0 + ((uint32_t)((i + 1) * step) & 1023u);
     }
     const long long t1 = clock64();
     if (elected) asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar)));
@@ -64,19 +72,20 @@ int main() {
   cudaFuncSetAttribute(rate, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   printf("M N nacc major : issue cyc/MMA, complete cyc/MMA\n");
   const int Ns[] = {8, 16, 48, 64, 128, 256};
-  for (int mode = 0; mode < 2; ++mode)
-  for (int major = 0; major < 1; ++major)
-    for (int M = 128; M <= 128; M += 64)
-      for (int ni = 0; ni < 6; ++ni)
-        for (int nacc = 1; nacc <= 4; nacc *= 2) {
+  const int mode = 0;
+  for (int cfg = 0; cfg < 5; ++cfg)
+    for (int M = 64; M <= 128; M += 64)
+      for (int ni = 2; ni < 6; ++ni)
+        for (int nacc = 1; nacc <= 2; nacc *= 2) {
+          const int major = cfg == 4, kind = cfg < 3 ? cfg : (cfg == 3 ? 1 : 0), step = cfg == 0 ? 0 : (cfg == 3 ? 3 : 64);
           const int N = Ns[ni];
           if (N * nacc > 512) continue;
           for (int rep = 0; rep < 2; ++rep) {
-            rate<<<1, 128, 200 * 1024>>>(M, N, nacc, major, mode, d);
+            rate<<<1, 128, 200 * 1024>>>(M, N, nacc, major, mode, step, kind, d);
             if (cudaDeviceSynchronize() != cudaSuccess) { printf("error\n"); return 1; }
           }
           cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost);
-          printf("mode %d %3d %3d %d %s : %6.1f %6.1f\n", mode, M, N, nacc, major ? "MN" : "K ", h[0] / 512.0, h[1] / 512.0);
+          printf("cfg %d (major %s kind %d step %d) M %3d N %3d nacc %d : %6.1f %6.1f\n", cfg, major ? "MN" : "K", kind, step * 16, M, N, nacc, h[0] / 512.0, h[1] / 512.0);
         }
   return 0;
 }
