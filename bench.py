@@ -290,9 +290,11 @@ def run_ours(args):
                         "cuda_graph": graphed, "channels_last": trainer.channels_last,
                         "folded_update": bool(getattr(trainer._graph, "folded", False)) if graphed else opt.can_fold(),
                         "fused_bn_sites": getattr(trainer, "fused_bn_sites", 0),
-                        "model_rewrites": "own BN(+residual)(+ReLU)(+maxpool) kernels at every BatchNorm2d, stem 7x7/2 "
-                                          "convolution computed as 4x4 on the space-to-depth image (exact); same "
-                                          "parameters, same arithmetic as torchvision resnet50",
+                        "model_rewrites": "own BN(+residual)(+ReLU)(+maxpool) kernels at every BatchNorm2d; stem 7x7/2 "
+                                          "convolution and its weight gradient by own tcgen05 tf32 kernels on the "
+                                          "space-to-depth image (csrc/gk_stem.cu); same parameters, same arithmetic "
+                                          "as torchvision resnet50",
+                        "stem_tensor_core_calls": dict(__import__("gaussiank_sgd_b200.ops.stem", fromlist=["calls"]).calls),
                         "conv_math": "fp32 storage, cuDNN TF32 convolutions allowed (torch default), fp32 matmul",
                         "phase_means_s": phase_means},
             "replicas_identical": bool(replicas_identical),

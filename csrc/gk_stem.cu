@@ -332,13 +332,14 @@ __device__ __forceinline__ float to_tf32(float v) {   // round to nearest: the M
 // both 8-byte aligned.
 __global__ void __launch_bounds__(256) k_stem_s2d(const float* __restrict__ x, float* __restrict__ X, int nimg, int H, int W,
                                                   long long nhalf) {
-  const int Hp = H / 2 + 3, Wp = W / 2 + 3;
-  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < nhalf; g += (long long)gridDim.x * blockDim.x) {
-    const int dy = (int)(g & 1);
-    const long long pos = g >> 1;
-    const int j = (int)(pos % Wp);
-    const long long ni = pos / Wp;
-    const int i = (int)(ni % Hp), n = (int)(ni / Hp);
+  const uint32_t Hp = H / 2 + 3, Wp = W / 2 + 3;   // positions < 2^31 (host check): 32-bit index arithmetic
+  for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < (uint32_t)nhalf; g += gridDim.x * blockDim.x) {
+    const int dy = (int)(g & 1u);
+    const uint32_t pos = g >> 1;
+    const uint32_t ni = pos / Wp;
+    const int j = (int)(pos - ni * Wp);
+    const uint32_t nn = ni / Hp;
+    const int i = (int)(ni - nn * Hp), n = (int)nn;
     float2 v0 = make_float2(0.f, 0.f), v1 = v0, v2 = v0;
     if (i >= 2 && i < Hp - 1 && j >= 2 && j < Wp - 1) {
       const float2* r = reinterpret_cast<const float2*>(x + (((long long)n * H + 2 * (i - 2) + dy) * W + 2 * (j - 2)) * 3);
@@ -349,7 +350,7 @@ __global__ void __launch_bounds__(256) k_stem_s2d(const float* __restrict__ x, f
       v1.x = to_tf32(v1.x); v1.y = to_tf32(v1.y);
       v2.x = to_tf32(v2.x); v2.y = to_tf32(v2.y);
     }
-    float2* o = reinterpret_cast<float2*>(X + g * 6);
+    float2* o = reinterpret_cast<float2*>(X + (size_t)g * 6);
     o[0] = v0;
     o[1] = v1;
     o[2] = v2;
@@ -599,6 +600,7 @@ int gk_stem_s2d(const void* x, void* X, int nimg, int H, int W, void* stream) {
   if (nimg <= 0 || H % 2 || W % 2) return -2;
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(X)) & 7) return -2;
   const long long nhalf = (long long)nimg * (H / 2 + 3) * (W / 2 + 3) * 2;
+  if (nhalf >= (1LL << 32) - (1LL << 24)) return -2;
   const int threads = 256;
   long long blocks = (nhalf + threads - 1) / threads;
   if (blocks > 148 * 32) blocks = 148 * 32;

@@ -13,6 +13,7 @@ from __future__ import annotations
 import torch
 
 from .. import settings
+from . import chain as _chain
 from . import native
 
 _err = {}
@@ -58,6 +59,7 @@ class _StemConvTC(torch.autograd.Function):
         native.check(lib.gk_stem_fwd(X.data_ptr(), wpk.data_ptr(), y.data_ptr(), N, OH, OW,
                                      _err_word(x.device).data_ptr(), st), "gk_stem_fwd")
         calls["fwd"] += 1
+        _chain.LAUNCHES["n"] += 3                                                # s2d, weight pack, implicit GEMM
         ctx.save_for_backward(X)
         return y.permute(0, 3, 1, 2)                                            # NCHW over NHWC memory
 
@@ -76,6 +78,7 @@ class _StemConvTC(torch.autograd.Function):
                                            _err_word(gy.device).data_ptr(), torch.cuda.current_stream().cuda_stream),
                          "gk_stem_wgrad")
             calls["wgrad"] += 1
+            _chain.LAUNCHES["n"] += 2                                            # pixel-reduction GEMM, fold
             return None, gw
         # weight gradient of the 4x4 form from cuDNN (only the weight's shape matters), folded back to 7x7:
         # gw[o, ch, 2a+dy-1, 2b+dx-1] = gw4[o, (dy*2+dx)*3 + ch, a, b]

@@ -379,6 +379,21 @@ int gk_ipc_free(void* ptr);
 
 const char* gk_version(void);
 
+/* ---- ResNet stem convolution on the tensor cores (csrc/gk_stem.cu: TMA + tcgen05.mma kind::tf32 + TMEM).
+ * The reference runs this layer (torchvision resnet50 conv1, dl_trainer.py:187-196) through cuDNN.
+ * Layouts: x [N, H, W, 3] fp32 NHWC; X the padded 2x2 space-to-depth image [N, H/2+3, W/2+3, 12]; w [64, 3, 7, 7];
+ * wpk 12288 floats (operand order); y / gy [N, H/2, W/2, 64] NHWC; `err` an optional device uint32 that receives
+ * the code of a pipeline wait that timed out (the kernels trap instead of hanging).  All pointers 16-byte aligned.
+ * Return: 0, a cudaError_t, -2 (shape not covered) or -3 (the driver cannot encode the tensor map). */
+int gk_stem_supported(int H, int W);                 /* forward: even sizes, W <= 332 */
+int gk_stem_s2d(const void* x, void* X, int nimg, int H, int W, void* stream);
+int gk_stem_pack_w(const void* w, void* wpk, void* stream);
+int gk_stem_fwd(const void* X, const void* wpk, void* y, int nimg, int OH, int OW, void* err, void* stream);
+int gk_stem_wgrad_supported(int OH, int OW);         /* OW % 8 == 0, OW <= 128 */
+long long gk_stem_wgrad_workspace(void);             /* floats of scratch for gk_stem_wgrad */
+int gk_stem_wgrad(const void* gy, const void* X, void* gw, void* work, int nimg, int OH, int OW, void* err,
+                  void* stream);
+
 /* ------------------------------------------------------------------- CPU twins (host) */
 int gkcpu_compress(const GkChain* c, const GkDst* dst);
 int gkcpu_dgc_compress(const GkChain* c, const GkDst* dst, uint64_t seed);

@@ -23,6 +23,8 @@ DATASET = {'resnet50': 'imagenet', 'resnet20': 'cifar10', 'vgg16': 'cifar10', 'l
 
 def category(name: str) -> str:
     n = name.lower()
+    if 'k_stem' in n:
+        return 'ours (stem conv, tcgen05)'
     if 'k_bn' in n or 'k_pool_gather' in n:
         return 'ours (fused bn+relu)'
     if n.startswith('k_') or 'gkchain' in n:
@@ -50,6 +52,7 @@ def main():
     ap.add_argument('--no-graph', action='store_true')
     ap.add_argument('--compressor', default='gaussiank')
     ap.add_argument('--out', default=None)
+    ap.add_argument('--launches', default=None, help='substring: also list every launch of the matching kernels (us, step 0)')
     a = ap.parse_args()
     settings.CUDA_GRAPH = not a.no_graph
     torch.cuda.set_device(0)
@@ -83,6 +86,16 @@ def main():
     lines.append('top kernels (us per step, launches per step):')
     for name, (us, cnt) in sorted(per.items(), key=lambda kv: -kv[1][0])[:45]:
         lines.append('  %9.1f  %4d  %s' % (us, cnt // a.steps, name[:150]))
+    if a.launches:
+        seen = collections.defaultdict(list)
+        for e in ev:
+            if a.launches in e.name:
+                seen[e.name].append(e.device_time)
+        lines.append('launches of kernels matching %r (us, all %d profiled steps, in launch order):' % (a.launches, a.steps))
+        for name, ts in seen.items():
+            n1 = len(ts) // a.steps
+            lines.append('  %s' % name[:110])
+            lines.append('    ' + ' '.join('%.1f' % x for x in ts[:n1]))
     text = '\n'.join(lines)
     print(text)
     if a.out:
