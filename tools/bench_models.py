@@ -30,6 +30,11 @@ CONFIGS = [  # name, dnn, dataset, batch per GPU, lr, compressor, density, clip,
     ("lstm-ptb-topk", "lstm", "ptb", 20, 22.0, "topk", 0.001, 0.25, 35),
     ("lstm-ptb-gaussiank", "lstm", "ptb", 20, 22.0, "gaussiank", 0.001, 0.25, 35),
     ("lstman4-gaussiank", "lstman4", "an4", 4, 0.0002, "gaussiank", 0.001, 400, 35),
+    # merge threshold (elements) as a tenth field: several groups, each launched from the backward hooks on the
+    # communication stream as soon as its gradients exist (run with --only resnet50-)
+    ("resnet50-gaussiank-merged", "resnet50", "imagenet", 32, 0.01, "gaussiank", 0.001, None, 35, 524288000),
+    ("resnet50-gaussiank-groups8M-overlap", "resnet50", "imagenet", 32, 0.01, "gaussiank", 0.001, None, 35, 8388608),
+    ("resnet50-gaussiank-groups2M-overlap", "resnet50", "imagenet", 32, 0.01, "gaussiank", 0.001, None, 35, 2097152),
 ]
 
 
@@ -39,7 +44,8 @@ def run_one(cfg, args):
     from gaussiank_sgd_b200.compression import compressors
     from gaussiank_sgd_b200.dl_trainer import DLTrainer
 
-    name, dnn, dataset, batch, lr, comp, density, clip, num_steps = cfg
+    name, dnn, dataset, batch, lr, comp, density, clip, num_steps = cfg[:9]
+    threshold = cfg[9] if len(cfg) > 9 else 524288000
     rank, world = hvd.rank(), hvd.size()
     device = hvd.comm.device()
     trainer = DLTrainer(rank, world, dist=False, batch_size=batch, is_weak_scaling=True,
@@ -47,7 +53,7 @@ def run_one(cfg, args):
                         num_steps=num_steps, synthetic_samples=batch * world * 64)
     opt = hvd.DistributedOptimizer(trainer.optimizer, named_parameters=trainer.net.named_parameters(),
                                    compression=compressors[comp], is_sparse=density < 1, density=density,
-                                   threshold=524288000, force_compress=density < 1)
+                                   threshold=threshold, force_compress=density < 1)
     hvd.broadcast_parameters(trainer.net.state_dict(), root_rank=0)
     trainer.update_optimizer(opt)
     if density < 1:
@@ -90,6 +96,7 @@ def run_one(cfg, args):
            "parameters": n_params, "loss": round(float(trainer.loss), 4),
            "cuda_graph": bool(getattr(trainer, "_graph", None) is not None and trainer._graph.graph is not None),
            "own_kernels_per_step": trainer.launches_per_step(), "data": "synthetic", "dtype": "fp32",
+           "groups": len(getattr(opt, "_groups", [])), "overlap": bool(getattr(opt, "_overlap", False)),
            "timing": "CUDA events around K x train_and_update() incl. H2D of inputs, max over ranks"}
     trainer.finish()
     if hasattr(opt, "close"):
@@ -241,6 +248,8 @@ def main():
     only = set(args.only.split(",")) if args.only else None
     out = []
     for cfg in CONFIGS:
+        if only is None and len(cfg) > 9:
+            continue                                   # the grouping study only runs when asked for
         if only and cfg[0] not in only and cfg[1] not in only:
             continue
         try:
