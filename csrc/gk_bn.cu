@@ -1153,6 +1153,55 @@ extern "C" int gk_bn_pool_fwd(const float* x, float* yp, unsigned char* pidx, co
   return (int)cudaGetLastError();
 }
 
+// Batch statistics from per-block partial sums that somebody else accumulated (the stem convolution's epilogue,
+// csrc/gk_stem.cu): partials[p][0..C) sums, partials[p][C..2C) sums of squares.  Same finalisation as k_bn_stats.
+__global__ void __launch_bounds__(256) k_bn_finalize_partials(const float* __restrict__ partials, int nparts, int64_t M, int C,
+                                                               float* __restrict__ save_mean, float* __restrict__ save_istd,
+                                                               float* running_mean, float* running_var, int64_t* num_batches,
+                                                               float eps, float momentum) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < C) {
+    double s = 0, ss = 0;
+    for (int p = 0; p < nparts; ++p) {
+      s += (double)__ldg(partials + (size_t)p * 2 * C + c);
+      ss += (double)__ldg(partials + (size_t)p * 2 * C + C + c);
+    }
+    const double mean = s / (double)M;
+    double var = ss / (double)M - mean * mean;
+    if (var < 0) var = 0;
+    save_mean[c] = (float)mean;
+    save_istd[c] = (float)(1.0 / sqrt(var + (double)eps));
+    if (running_mean != nullptr) {
+      const double unbiased = M > 1 ? var * (double)M / (double)(M - 1) : var;
+      running_mean[c] = (float)((1.0 - momentum) * (double)running_mean[c] + momentum * mean);
+      running_var[c] = (float)((1.0 - momentum) * (double)running_var[c] + momentum * unbiased);
+    }
+  }
+  if (c == 0 && num_batches != nullptr) *num_batches += 1;
+}
+
+// gk_bn_pool_fwd without the statistics pass: the sums come from `partials` ([nparts][2C] floats).
+extern "C" int gk_bn_pool_fwd_sums(const float* x, float* yp, unsigned char* pidx, const float* gamma, const float* beta,
+                                   float* running_mean, float* running_var, int64_t* num_batches, float* save_mean,
+                                   float* save_istd, const float* partials, int nparts, int N, int H, int W, int C,
+                                   float eps, float momentum, void* stream) {
+  const int64_t M = (int64_t)N * H * W;
+  const int OH = (H - 1) / 2 + 1, OW = (W - 1) / 2 + 1;
+  if (C % 4 != 0 || C <= 0 || H < 2 || W < 2 || nparts <= 0 || partials == nullptr) return (int)cudaErrorInvalidValue;
+  if (!bn_aligned(x) || !bn_aligned(yp) || !bn_aligned(gamma) || !bn_aligned(beta) || !bn_aligned(save_mean) ||
+      !bn_aligned(save_istd) || (reinterpret_cast<uintptr_t>(pidx) & 3))
+    return (int)cudaErrorMisalignedAddress;
+  cudaStream_t s = (cudaStream_t)stream;
+  k_bn_finalize_partials<<<(C + 255) / 256, 256, 0, s>>>(partials, nparts, M, C, save_mean, save_istd, running_mean,
+                                                        running_var, num_batches, eps, momentum);
+  const int64_t total = (int64_t)N * OH * OW * (C / 4);
+  int64_t blocks = (total + 255) / 256;
+  const int64_t cap = (int64_t)bn_sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  k_bn_pool_apply<<<(unsigned)blocks, 256, 0, s>>>(x, yp, pidx, gamma, beta, save_mean, save_istd, N, H, W, C, OH, OW);
+  return (int)cudaGetLastError();
+}
+
 // Full-resolution gradient of the max pool (dense gather, one thread per input pixel and channel quad): the
 // BN backward then runs on it like on any other gradient.  Cheaper than gathering inside the cooperative
 // kernel, which has one block per SM (16-32 warps) and would evaluate the windows twice.

@@ -28,8 +28,9 @@
 //   warp 1   one lane issues the tcgen05.mma kind::tf32 instructions into one of two TMEM accumulators;
 //            tcgen05.commit publishes the accumulator and releases the chunk buffer.
 //   warp 2   allocates / frees 128 TMEM columns.
-//   warps 4-7  epilogue: tcgen05.ld the 128 x 64 fp32 tile, transpose through padded shared memory, store whole
-//            128-byte lines of the NHWC output (the valid rows of a tile are contiguous in y).
+//   4 epilogue warps, one per TMEM lane quarter: tcgen05.ld the 128 x 64 fp32 tile, transpose through padded shared
+//            memory, store whole 128-byte lines of the NHWC output (the valid rows of a tile are contiguous in y);
+//            optionally accumulate the per-channel sums of y for the BatchNorm that follows.
 // Every mbarrier wait is bounded (2 s on %globaltimer): on expiry the kernel records a code and traps.
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -48,13 +49,15 @@ constexpr int ST_NMMA = ST_TAPS * 3 * 2;           // K = 8 steps per tile
 constexpr int ST_B_MMA = 2 * ST_N * 16;            // weight bytes per step: 2 halves x 64 rows x 16 B
 constexpr int ST_B_BYTES = ST_NMMA * ST_B_MMA;     // 48 KB
 constexpr int ST_EPI_PITCH = 36;                   // floats; 32 + 4 keeps the float4 phases conflict-free
-constexpr int ST_EPI_BYTES = 4 * 32 * ST_EPI_PITCH * 4;
+constexpr int ST_EPI_WARPS = 4;                    // one per TMEM lane quarter (8 warps, one per quarter and channel half: slower)
+constexpr int ST_EPI_BYTES = ST_EPI_WARPS * 32 * ST_EPI_PITCH * 4;
 constexpr int ST_NI = 4;                           // MMA-issuing warps = TMEM accumulators
 constexpr int ST_W_ALLOC = 1 + ST_NI;              // warp 0 producer, 1..ST_NI issuers, then TMEM allocator, then 4 epilogue
 constexpr int ST_W_EPI = 2 + ST_NI;
-constexpr int ST_THREADS = 32 * (ST_W_EPI + 4);
+constexpr int ST_THREADS = 32 * (ST_W_EPI + ST_EPI_WARPS);
+constexpr int WG_THREADS = 32 * (ST_W_EPI + 4);    // the weight-gradient kernel has one light epilogue: 4 warps
 constexpr int ST_TMEM_COLS = 256;
-constexpr int ST_FIXED = ST_B_BYTES + ST_EPI_BYTES + 256;   // + 2 chunk buffers of 3 planes
+constexpr int ST_FIXED = ST_B_BYTES + ST_EPI_BYTES + 1024;  // barriers + statistics; + 2 chunk buffers of 3 planes
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -166,9 +169,10 @@ struct StemGeom {
   int boxP;                                          // positions per TMA box; a chunk buffer plane holds 4 boxes
 };
 
+template <bool STATS>
 __global__ void __launch_bounds__(ST_THREADS, 1)
 k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict__ wpk, float* __restrict__ out,
-              const StemGeom g, unsigned int* __restrict__ err) {
+              float* __restrict__ stats, const StemGeom g, unsigned int* __restrict__ err) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
@@ -176,7 +180,8 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
   const uint32_t sB = base;
   const uint32_t sE = sB + ST_B_BYTES;
   const uint32_t sBar = sE + ST_EPI_BYTES;
-  const uint32_t sX = sBar + 256u;                               // 2 buffers x 3 planes
+  const uint32_t sX = sBar + 1024u;                              // 2 buffers x 3 planes
+  float* const sstat = reinterpret_cast<float*>(smem_raw + (sBar + 256u - raw));   // 64 sums + 64 sums of squares
   auto full = [&](uint32_t s) { return sBar + 8u * s; };
   auto empty = [&](uint32_t s) { return sBar + 16u + 8u * s; };
   const uint32_t bfull = sBar + 32u;
@@ -196,6 +201,7 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
   const int nchunk = (nt + ST_CHUNK - 1) / ST_CHUNK;
 
   if (warp == 0 && lane == 0) tma_prefetch_desc(&mapX);
+  if (threadIdx.x < 2 * ST_N) sstat[threadIdx.x] = 0.f;
   if (warp == 1 && lane == 0) {
     for (uint32_t s = 0; s < 2; ++s) {
       mbar_init(full(s), 1);
@@ -203,7 +209,7 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
     }
     for (uint32_t s = 0; s < ST_NI; ++s) {
       mbar_init(tfull(s), 1);
-      mbar_init(tempty(s), 4);                      // one arrival per epilogue warp
+      mbar_init(tempty(s), ST_EPI_WARPS);           // one arrival per epilogue warp
     }
     mbar_init(bfull, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -272,19 +278,21 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
         mma_commit(empty(buf));                     // this issuer's MMAs on the chunk buffer are done (or it had none)
       }
     }
-  } else if (warp >= ST_W_EPI) {                    // ---- epilogue
-    const int q = warp & 3;                         // TMEM lanes 32q .. 32q+31
+  } else if (warp >= ST_W_EPI) {                    // ---- epilogue: warp = TMEM lane quarter q (lanes 32q .. 32q+31)
+    // These four warps are a serial instruction stream each and the kernel is sensitive to every instruction in
+    // their loop: 32-bit index arithmetic (the host checks the ranges), one shuffle per row.
+    const int q = warp & 3;
     float* const stg = epi + q * 32 * ST_EPI_PITCH;
-    const long long pl = (long long)g.Hp * g.Wp;
+    const uint32_t pl = (uint32_t)(g.Hp * g.Wp), Wp = (uint32_t)g.Wp;
+    float cs[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}}, cq[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
     for (int it = 0; it < nt; ++it) {
       const uint32_t as = (uint32_t)it % ST_NI, aph = ((uint32_t)it / ST_NI) & 1u;
-      // where this lane's row goes: position -> (n, i, j); -1 for the positions that are not output pixels
-      const long long p = (long long)(t0 + it) * ST_M + q * 32 + lane;
-      const int n = (int)(p / pl);
-      const int rem = (int)(p - (long long)n * pl);
-      const int oh = rem / g.Wp, ow = rem - oh * g.Wp;
-      const long long off = (n < g.nimg && oh < g.OH && ow < g.OW)
-                                ? (((long long)n * g.OH + oh) * g.OW + ow) * ST_N : -1ll;
+      // where this lane's row goes: position -> (n, i, j); 0xffffffff for the positions that are not output pixels
+      const uint32_t p = (uint32_t)(t0 + it) * ST_M + (uint32_t)(q * 32 + lane);
+      const uint32_t n = p / pl, rem = p - n * pl;
+      const uint32_t oh = rem / Wp, ow = rem - oh * Wp;
+      const uint32_t off = (n < (uint32_t)g.nimg && oh < (uint32_t)g.OH && ow < (uint32_t)g.OW)
+                               ? ((n * (uint32_t)g.OH + oh) * (uint32_t)g.OW + ow) * ST_N : 0xffffffffu;
       mbar_wait(tfull(as), aph, err, 5);
       tc_fence_after();
       uint32_t v[64];
@@ -306,11 +314,36 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
         for (int r = 0; r < 8; ++r) {               // 4 rows x 128 B per instruction
           const int row = r * 4 + (lane >> 3), ch = lane & 7;
           const uint4 x = *reinterpret_cast<const uint4*>(stg + row * ST_EPI_PITCH + ch * 4);
-          const long long o = __shfl_sync(0xffffffffu, off, row);
-          if (o >= 0) *reinterpret_cast<uint4*>(out + o + half * 32 + ch * 4) = x;
+          const uint32_t o = __shfl_sync(0xffffffffu, off, row);
+          if (o != 0xffffffffu) {
+            *reinterpret_cast<uint4*>(out + o + half * 32 + ch * 4) = x;
+            if (STATS) {  // per-channel sum and sum of squares of the output pixels, for the BatchNorm that follows
+              const float f0 = __uint_as_float(x.x), f1 = __uint_as_float(x.y), f2 = __uint_as_float(x.z), f3 = __uint_as_float(x.w);
+              cs[half][0] += f0; cs[half][1] += f1; cs[half][2] += f2; cs[half][3] += f3;
+              cq[half][0] = fmaf(f0, f0, cq[half][0]); cq[half][1] = fmaf(f1, f1, cq[half][1]);
+              cq[half][2] = fmaf(f2, f2, cq[half][2]); cq[half][3] = fmaf(f3, f3, cq[half][3]);
+            }
+          }
         }
         __syncwarp();
       }
+    }
+    if (STATS) {                                    // lanes l, l+8, l+16, l+24 hold the same four channels
+#pragma unroll
+      for (int half = 0; half < 2; ++half)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float a = cs[half][j], b = cq[half][j];
+          a += __shfl_xor_sync(0xffffffffu, a, 8);  b += __shfl_xor_sync(0xffffffffu, b, 8);
+          a += __shfl_xor_sync(0xffffffffu, a, 16); b += __shfl_xor_sync(0xffffffffu, b, 16);
+          if (lane < 8) {
+            atomicAdd(sstat + half * 32 + lane * 4 + j, a);
+            atomicAdd(sstat + ST_N + half * 32 + lane * 4 + j, b);
+          }
+        }
+      asm volatile("bar.sync 1, %0;" ::"n"(ST_EPI_WARPS * 32) : "memory");      // the epilogue warps only
+      const int et = (int)threadIdx.x - ST_W_EPI * 32;
+      if (et < 2 * ST_N) stats[(size_t)bid * 2 * ST_N + et] = sstat[et];
     }
   }
   tc_fence_before();
@@ -397,7 +430,7 @@ struct WgGeom {
   int dbg;                                           // 1: dump all 128 TMEM lanes (part has 128 rows per CTA)
 };
 
-__global__ void __launch_bounds__(ST_THREADS, 1)
+__global__ void __launch_bounds__(WG_THREADS, 1)
 k_stem_wgrad_tc(const __grid_constant__ CUtensorMap mapG, const __grid_constant__ CUtensorMap mapX,
                 float* __restrict__ part, const WgGeom g, unsigned int* __restrict__ err) {
   extern __shared__ uint8_t smem_raw[];
@@ -619,13 +652,29 @@ int gk_stem_pack_w(const void* w, void* wpk, void* stream) {
 // X: the padded space-to-depth image [nimg, OH+3, OW+3, 12] fp32, wpk: gk_stem_pack_w's output,
 // y: [nimg, OH, OW, 64] fp32 (NHWC).  err (optional, device uint32) receives the code of a wait that timed out.
 // Returns a cudaError_t, or -2 when the shape is not covered, -3 when the driver cannot encode the tensor map.
+int gk_stem_fwd_stats(const void* X, const void* wpk, void* y, void* stats, int nimg, int OH, int OW, void* err,
+                      void* stream);
+
 int gk_stem_fwd(const void* X, const void* wpk, void* y, int nimg, int OH, int OW, void* err, void* stream) {
+  return gk_stem_fwd_stats(X, wpk, y, nullptr, nimg, OH, OW, err, stream);
+}
+
+// Floats of `stats` gk_stem_fwd_stats fills: one row of 64 sums + 64 sums of squares of y per CTA (rows of CTAs
+// that had no tile are zero); gk_stem_stats_rows() rows.
+int gk_stem_stats_rows(void) { return stem_sm_count(); }
+
+// gk_stem_fwd that also leaves the per-channel sum and sum of squares of y over all output pixels in `stats`
+// ([gk_stem_stats_rows()][128] floats, partial per CTA): the batch statistics of the BatchNorm that follows, for
+// free (gk_bn_pool_fwd_sums consumes them).
+int gk_stem_fwd_stats(const void* X, const void* wpk, void* y, void* stats, int nimg, int OH, int OW, void* err,
+                      void* stream) {
   if (nimg <= 0 || OH <= 0 || OW <= 0) return -2;
   const int Hp = OH + 3, Wp = OW + 3;
   const long long P = (long long)nimg * Hp * Wp;
   const long long rows = P - 3LL * Wp - 3;           // one past the last position that is an output pixel
   const int boxP = stem_box(Wp);
   if (rows <= 0 || P > (1LL << 31) - 2048 || boxP > 256) return -2;
+  if ((long long)nimg * OH * OW * ST_N >= (1LL << 32) - 1) return -2;      // 32-bit output offsets in the epilogue
   if ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(wpk) | reinterpret_cast<uintptr_t>(y)) & 15) return -2;
   EncodeTiledFn enc = encode_fn();
   if (!enc) return -3;
@@ -642,7 +691,9 @@ int gk_stem_fwd(const void* X, const void* wpk, void* y, int nimg, int OH, int O
   }
   const int smem = ST_FIXED + 2 * 3 * boxP * 4 * 16 + 1024;
   {
-    cudaError_t e = cudaFuncSetAttribute(k_stem_fwd_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = stats != nullptr
+                        ? cudaFuncSetAttribute(k_stem_fwd_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                        : cudaFuncSetAttribute(k_stem_fwd_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return (int)e;
   }
   StemGeom g;
@@ -650,8 +701,18 @@ int gk_stem_fwd(const void* X, const void* wpk, void* y, int nimg, int OH, int O
   g.ntiles = (int)((rows + ST_M - 1) / ST_M);
   const int sms = stem_sm_count();
   const int grid = g.ntiles < sms ? g.ntiles : sms;
-  k_stem_fwd_tc<<<grid, ST_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(
-      mapX, static_cast<const float*>(wpk), static_cast<float*>(y), g, static_cast<unsigned int*>(err));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (stats != nullptr && grid < sms) {              // rows of the CTAs that do not exist
+    cudaError_t e = cudaMemsetAsync(static_cast<float*>(stats) + (size_t)grid * 2 * ST_N, 0,
+                                    (size_t)(sms - grid) * 2 * ST_N * sizeof(float), s);
+    if (e != cudaSuccess) return (int)e;
+  }
+  if (stats != nullptr)
+    k_stem_fwd_tc<true><<<grid, ST_THREADS, smem, s>>>(mapX, static_cast<const float*>(wpk), static_cast<float*>(y),
+                                                       static_cast<float*>(stats), g, static_cast<unsigned int*>(err));
+  else
+    k_stem_fwd_tc<false><<<grid, ST_THREADS, smem, s>>>(mapX, static_cast<const float*>(wpk), static_cast<float*>(y),
+                                                        nullptr, g, static_cast<unsigned int*>(err));
   return (int)cudaGetLastError();
 }
 
@@ -709,7 +770,7 @@ int gk_stem_wgrad(const void* gy, const void* X, void* gw, void* work, int nimg,
   const int sms = stem_sm_count();
   const int grid = nrows < sms ? (int)nrows : sms;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  k_stem_wgrad_tc<<<grid, ST_THREADS, smem, s>>>(mapG, mapX, static_cast<float*>(work), g, static_cast<unsigned int*>(err));
+  k_stem_wgrad_tc<<<grid, WG_THREADS, smem, s>>>(mapG, mapX, static_cast<float*>(work), g, static_cast<unsigned int*>(err));
   k_stem_wgrad_fold<<<(ST_N * 147 + 255) / 256, 256, 0, s>>>(static_cast<const float*>(work), grid, static_cast<float*>(gw));
   return (int)cudaGetLastError();
 }

@@ -83,7 +83,7 @@ def _stem_conv_s2d(conv, x):
     return F.conv2d(X, w4.contiguous(memory_format=torch.channels_last), None, 1, 0)
 
 
-def _stem_conv(conv, x):
+def _stem_conv(conv, x, want_stats=False):
     """The stem convolution in a shape cuDNN has aligned kernels for: the space-to-depth rewrite when the
     convolution is the 7x7 / stride 2 / padding 3 one on an even-sized image (_stem_conv_s2d), else the 3 input
     channels padded to 4 (zeros in the image and in the weight: same result), else the module as it is.  With
@@ -95,7 +95,8 @@ def _stem_conv(conv, x):
             and tuple(conv.dilation) == (1, 1) and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0
             and x.is_contiguous(memory_format=torch.channels_last)):
         if settings.STEM_TC and conv.out_channels == 64 and stem.supported(x, conv.weight):
-            return stem.stem_conv_tc(x, conv.weight)                # TMA + tcgen05 implicit GEMM (csrc/gk_stem.cu)
+            # TMA + tcgen05 implicit GEMM (csrc/gk_stem.cu); with want_stats it returns (y, sums for the BN)
+            return stem.stem_conv_tc(x, conv.weight, want_stats and settings.STEM_BN_STATS)
         return _stem_conv_s2d(conv, x)
     if not (settings.STEM_PAD4 and x.is_cuda and x.dim() == 4 and x.shape[1] == 3 and conv.in_channels == 3
             and conv.groups == 1 and conv.bias is None and conv.padding_mode == 'zeros'
@@ -110,7 +111,9 @@ def _stem_conv(conv, x):
 
 def _resnet_forward(self, x):
     if _is_stem_pool(self.maxpool):
-        x = bn_relu_maxpool(self.bn1, _stem_conv(self.conv1, x), self.maxpool)
+        y = _stem_conv(self.conv1, x, want_stats=self.bn1.training)
+        y, sums = y if isinstance(y, tuple) else (y, None)          # batch statistics from the convolution's epilogue
+        x = bn_relu_maxpool(self.bn1, y, self.maxpool, presums=sums)
     else:
         x = self.maxpool(bn_act(self.bn1, _stem_conv(self.conv1, x)))
     x = self.layer4(self.layer3(self.layer2(self.layer1(x))))

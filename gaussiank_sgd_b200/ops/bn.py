@@ -192,7 +192,7 @@ class _BnReluPool(torch.autograd.Function):
     written; the backward gathers the pooled gradient through the saved window positions."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, bn):
+    def forward(ctx, x, weight, bias, bn, presums=None):
         N, C, H, W = x.shape
         OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
         yp = torch.empty((N, C, OH, OW), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
@@ -201,6 +201,17 @@ class _BnReluPool(torch.autograd.Function):
         track = bn.track_running_stats and bn.running_mean is not None
         accum, bar = ctx.scratch = _scratch_coop(bn, x.device, C)
         lib = native.cuda_lib()
+        if presums is not None:       # per-CTA sums / sums of squares from the producer of x (ops/stem.py): no statistics pass
+            native.check(lib.gk_bn_pool_fwd_sums(_ptr(x), _ptr(yp), _ptr(pidx), _ptr(weight), _ptr(bias),
+                                                 _ptr(bn.running_mean) if track else None,
+                                                 _ptr(bn.running_var) if track else None,
+                                                 _ptr(bn.num_batches_tracked) if track else None,
+                                                 stats[0].data_ptr(), stats[1].data_ptr(), presums.data_ptr(),
+                                                 presums.shape[0], N, H, W, C, float(bn.eps), float(bn.momentum),
+                                                 _stream()), "gk_bn_pool_fwd_sums")
+            _chain.LAUNCHES["n"] += 2
+            ctx.save_for_backward(x, weight, bias, stats, pidx)
+            return yp
         native.check(lib.gk_bn_pool_fwd(_ptr(x), _ptr(yp), _ptr(pidx), _ptr(weight), _ptr(bias),
                                         _ptr(bn.running_mean) if track else None,
                                         _ptr(bn.running_var) if track else None,
@@ -228,7 +239,7 @@ class _BnReluPool(torch.autograd.Function):
             _ptr(dx), _ptr(dx), dgamma.data_ptr(), dbeta.data_ptr(), accum.data_ptr(), bar.data_ptr(), N, H, W, C,
             2 if settings.BN_STAMPS else 0, _stream()), "gk_bn_pool_bwd")     # dx doubles as the gather buffer
         _chain.LAUNCHES["n"] += 2
-        return dx, dgamma, dbeta, None
+        return dx, dgamma, dbeta, None, None
 
 
 def _ptr_table(ptrs):
@@ -321,13 +332,16 @@ def bn_act(bn, x, residual=None, relu=True, twice=False):
     return (y, y) if twice else y
 
 
-def bn_relu_maxpool(bn, x, pool=None):
-    """``max_pool2d(relu(bn(x)), 3, 2, 1)`` (the ResNet stem) through the fused kernels when possible."""
+def bn_relu_maxpool(bn, x, pool=None, presums=None):
+    """``max_pool2d(relu(bn(x)), 3, 2, 1)`` (the ResNet stem) through the fused kernels when possible.  ``presums``
+    ([parts, 2C] fp32: per-channel sums and sums of squares of x, in partial rows) replaces the statistics pass."""
     N, C, H, W = x.shape if x.dim() == 4 else (0, 0, 0, 0)
     if (settings.FUSED_BN and settings.FUSED_BN_POOL and settings.FUSED_BN_COOP and not _COOP_OFF["off"]
             and eligible(bn, x) and H >= 2 and W >= 2
             and N * H * W < 2 ** 31 and native.cuda_lib().gk_bn_fused_supported(N * H * W, C)):
-        return _BnReluPool.apply(x, bn.weight, bn.bias, bn)
+        if presums is not None and not (bn.training and presums.shape[1] == 2 * C and presums.is_cuda):
+            presums = None
+        return _BnReluPool.apply(x, bn.weight, bn.bias, bn, presums)
     y = bn_act(bn, x, relu=True)
     return pool(y) if pool is not None else F.max_pool2d(y, 3, 2, 1)
 

@@ -45,7 +45,7 @@ def supported(x: torch.Tensor, weight: torch.Tensor) -> bool:
 
 class _StemConvTC(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight):
+    def forward(ctx, x, weight, want_stats=False):
         lib = native.cuda_lib()
         st = torch.cuda.current_stream().cuda_stream
         N, _, H, W = x.shape
@@ -56,17 +56,25 @@ class _StemConvTC(torch.autograd.Function):
         wc = weight.detach().contiguous()                                       # channels_last models stride it
         native.check(lib.gk_stem_pack_w(wc.data_ptr(), wpk.data_ptr(), st), "gk_stem_pack_w")
         y = torch.empty((N, OH, OW, 64), dtype=torch.float32, device=x.device)
-        native.check(lib.gk_stem_fwd(X.data_ptr(), wpk.data_ptr(), y.data_ptr(), N, OH, OW,
-                                     _err_word(x.device).data_ptr(), st), "gk_stem_fwd")
+        sums = (torch.empty((lib.gk_stem_stats_rows(), 128), dtype=torch.float32, device=x.device)
+                if want_stats else None)
+        native.check(lib.gk_stem_fwd_stats(X.data_ptr(), wpk.data_ptr(), y.data_ptr(),
+                                           sums.data_ptr() if want_stats else None, N, OH, OW,
+                                           _err_word(x.device).data_ptr(), st), "gk_stem_fwd")
         calls["fwd"] += 1
         _chain.LAUNCHES["n"] += 3                                                # s2d, weight pack, implicit GEMM
         ctx.save_for_backward(X)
-        return y.permute(0, 3, 1, 2)                                            # NCHW over NHWC memory
+        ctx.want_stats = want_stats
+        y = y.permute(0, 3, 1, 2)                                               # NCHW over NHWC memory
+        if want_stats:
+            ctx.mark_non_differentiable(sums)
+            return y, sums
+        return y
 
     @staticmethod
-    def backward(ctx, gy):
+    def backward(ctx, gy, *unused):
         if not ctx.needs_input_grad[1]:
-            return None, None
+            return None, None, None
         X, = ctx.saved_tensors
         gy = gy.contiguous(memory_format=torch.channels_last)
         N, OH, OW = gy.shape[0], gy.shape[2], gy.shape[3]
@@ -79,17 +87,19 @@ class _StemConvTC(torch.autograd.Function):
                          "gk_stem_wgrad")
             calls["wgrad"] += 1
             _chain.LAUNCHES["n"] += 2                                            # pixel-reduction GEMM, fold
-            return None, gw
+            return None, gw, None
         # weight gradient of the 4x4 form from cuDNN (only the weight's shape matters), folded back to 7x7:
         # gw[o, ch, 2a+dy-1, 2b+dx-1] = gw4[o, (dy*2+dx)*3 + ch, a, b]
         w4 = torch.empty((64, 12, 4, 4), dtype=gy.dtype, device=gy.device).contiguous(memory_format=torch.channels_last)
         _, gw4, _ = torch.ops.aten.convolution_backward(
             gy, X.permute(0, 3, 1, 2), w4, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1, [False, True, False])
         gw = gw4.reshape(64, 2, 2, 3, 4, 4).permute(0, 3, 4, 1, 5, 2).reshape(64, 3, 8, 8)[:, :, 1:, 1:]
-        return None, gw.contiguous()
+        return None, gw.contiguous(), None
 
 
-def stem_conv_tc(x: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+def stem_conv_tc(x: torch.Tensor, weight: torch.Tensor, want_stats: bool = False):
     """``conv2d(x, weight, stride=2, padding=3)`` for a 3-channel channels_last image batch and a [64, 3, 7, 7]
-    weight; returns [N, 64, H/2, W/2] in channels_last memory."""
-    return _StemConvTC.apply(x, weight)
+    weight; returns [N, 64, H/2, W/2] in channels_last memory.  With ``want_stats`` also the per-channel sums and
+    sums of squares of the output ([parts, 128] fp32 partial rows, accumulated in the kernel's epilogue) for
+    ``ops.bn.bn_relu_maxpool(..., presums=...)``."""
+    return _StemConvTC.apply(x, weight, want_stats)

@@ -81,6 +81,7 @@ FUSED_BN_TWICE = _flag("FUSED_BN_TWICE", True)      # block outputs handed out t
 STEM_S2D = _flag("STEM_S2D", True)                  # ResNet stem as a 4x4 convolution on the space-to-depth image
 STEM_TC = _flag("STEM_TC", True)                    # ... and that 4x4 form on tcgen05 tensor cores (csrc/gk_stem.cu)
 STEM_TC_WGRAD = _flag("STEM_TC_WGRAD", True)        # ... and its weight gradient (k_stem_wgrad_tc) instead of cuDNN's
+STEM_BN_STATS = _flag("STEM_BN_STATS", True)        # ... its epilogue accumulates the batch statistics of bn1
 STEM_PAD4 = _flag("STEM_PAD4", True)                # ResNet stem: pad the 3 input channels to 4 (aligned cuDNN kernels)
 BN_STAMPS = _flag("BN_STAMPS", False)                # fused BN kernels record phase time stamps (profiling aid)
 CUDNN_BENCHMARK = _flag("CUDNN_BENCHMARK", True)    # the reference pins benchmark=False, deterministic=True

@@ -320,6 +320,11 @@ int gk_bn_bwd_fused2(const float* dy, const float* dy2, const float* x, const fl
  * yp[N][OH][OW][C] (OH = (H-1)/2+1) and pidx, one byte per pooled element: kh*3+kw of the first maximum of its
  * window; scratch as gk_bn_fwd (accum 2*C doubles + ticket).  The backward takes the pooled gradient and pidx
  * and produces dx, dgamma, dbeta; scratch as gk_bn_bwd_fused; needs gk_bn_fused_supported(N*H*W, C). */
+/* gk_bn_pool_fwd without its statistics pass: the sums come from partials[nparts][2C] (sums, then sums of squares) */
+int gk_bn_pool_fwd_sums(const float* x, float* yp, unsigned char* pidx, const float* gamma, const float* beta,
+                        float* running_mean, float* running_var, int64_t* num_batches, float* save_mean,
+                        float* save_istd, const float* partials, int nparts, int N, int H, int W, int C, float eps,
+                        float momentum, void* stream);
 int gk_bn_pool_fwd(const float* x, float* yp, unsigned char* pidx, const float* gamma, const float* beta,
                    float* running_mean, float* running_var, int64_t* num_batches, float* save_mean, float* save_istd,
                    double* accum, uint32_t* ticket, unsigned long long* bar, int N, int H, int W, int C, float eps,
@@ -389,6 +394,11 @@ int gk_stem_supported(int H, int W);                 /* forward: even sizes, W <
 int gk_stem_s2d(const void* x, void* X, int nimg, int H, int W, void* stream);
 int gk_stem_pack_w(const void* w, void* wpk, void* stream);
 int gk_stem_fwd(const void* X, const void* wpk, void* y, int nimg, int OH, int OW, void* err, void* stream);
+/* ... and leave the per-channel sums / sums of squares of y in stats[gk_stem_stats_rows()][128] (one partial row per
+ * CTA), accumulated in the epilogue: the batch statistics of the BatchNorm that follows (gk_bn_pool_fwd_sums). */
+int gk_stem_stats_rows(void);
+int gk_stem_fwd_stats(const void* X, const void* wpk, void* y, void* stats, int nimg, int OH, int OW, void* err,
+                      void* stream);
 int gk_stem_wgrad_supported(int OH, int OW);         /* OW % 8 == 0, OW <= 128 */
 long long gk_stem_wgrad_workspace(void);             /* floats of scratch for gk_stem_wgrad */
 int gk_stem_wgrad(const void* gy, const void* X, void* gw, void* work, int nimg, int OH, int OW, void* err,

@@ -347,6 +347,41 @@ def test_stem_tensor_core_kernel_matches_fp32_convolution(shape):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(4, 64, 64), (32, 224, 224), (3, 96, 160)])
+def test_stem_epilogue_statistics_feed_the_batch_norm(shape, monkeypatch):
+    """The stem convolution's epilogue accumulates the per-channel sums of its output; bn1 + ReLU + max pool built on
+    them must equal the path that runs its own statistics pass over the same convolution output."""
+    from gaussiank_sgd_b200.models.fuse import _stem_conv
+    from gaussiank_sgd_b200.ops.bn import bn_relu_maxpool
+    N, H, W = shape
+    dev = torch.device("cuda:0")
+    torch.manual_seed(H)
+    conv = nn.Conv2d(3, 64, 7, 2, 3, bias=False).to(dev)
+    bn_a, pool = nn.BatchNorm2d(64).to(dev), nn.MaxPool2d(3, 2, 1)
+    with torch.no_grad():
+        bn_a.weight.uniform_(0.5, 1.5)
+        bn_a.bias.uniform_(-0.5, 0.5)
+    bn_b = copy.deepcopy(bn_a)
+    x = (torch.randn(N, 3, H, W, device=dev) * 2 + 0.3).contiguous(memory_format=torch.channels_last)
+    y, sums = _stem_conv(conv, x, want_stats=True)
+    assert sums is not None and sums.shape[1] == 128
+    M = y.numel() // 64
+    yf = y.detach().permute(0, 2, 3, 1).reshape(M, 64).double()
+    torch.testing.assert_close(sums[:, :64].double().sum(0), yf.sum(0), rtol=1e-5, atol=1e-3 * M ** 0.5)
+    torch.testing.assert_close(sums[:, 64:].double().sum(0), (yf * yf).sum(0), rtol=1e-5, atol=1e-3)
+    out_a = bn_relu_maxpool(bn_a, y, pool, presums=sums)
+    out_b = bn_relu_maxpool(bn_b, y.detach().requires_grad_(True), pool)
+    torch.testing.assert_close(out_a, out_b, rtol=1e-5, atol=2e-5)
+    torch.testing.assert_close(bn_a.running_mean, bn_b.running_mean, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(bn_a.running_var, bn_b.running_var, rtol=1e-5, atol=1e-6)
+    assert int(bn_a.num_batches_tracked) == int(bn_b.num_batches_tracked) == 1
+    d = torch.randn_like(out_a)
+    out_a.backward(d)                                   # through the BN into the convolution's weight gradient
+    assert conv.weight.grad is not None and bool(torch.isfinite(conv.weight.grad).all())
+    assert coop_errors(bn_a) == 0
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("shape", [(32, 256, 28, 28), (8, 2048, 7, 7), (4, 96, 9, 9), (16, 512, 14, 14)])
 @pytest.mark.parametrize("twice", [False, True])
 def test_two_bns_into_one_activation(shape, twice):
