@@ -1084,44 +1084,59 @@ extern "C" int gk_bn_bwd_fused2(const float* dy, const float* dy2, const float* 
 // on the fly (they are still in L2 from the statistics pass), writes the pooled activation and the window
 // position of each maximum (first maximum in scan order, like at::max_pool2d).  The full-resolution
 // activation is never written.  Backward: k_bn_bwd_fused<true> gathers the pooled gradient back.
+// Grid: x = (pooled column, channel quad) in blocks of 256 threads, y = (image, pooled row): no 64-bit divisions
+// on the way to the nine taps (the first version decomposed one flat 64-bit index per thread and was
+// instruction-bound: 48 us for 103 MB).
 __global__ void __launch_bounds__(256) k_bn_pool_apply(const float* __restrict__ x, float* __restrict__ yp,
                                                        unsigned char* __restrict__ pidx,
                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
                                                        const float* __restrict__ save_mean,
                                                        const float* __restrict__ save_istd, int N, int H, int W, int C,
                                                        int OH, int OW) {
-  const int quads = C >> 2;
-  const int64_t total = (int64_t)N * OH * OW * quads;
-  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-    const int q = (int)(t % quads);
-    int64_t p = t / quads;
-    const int ow = (int)(p % OW); p /= OW;
-    const int oh = (int)(p % OH);
-    const int n = (int)(p / OH);
-    float4 mu, is, sc, sh;
-    bn_load_channel_consts(gamma, beta, save_mean, save_istd, q, mu, is, sc, sh);
-    float4 best = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
-    uchar4 bi = make_uchar4(255, 255, 255, 255);
+  const unsigned quads = (unsigned)C >> 2;
+  const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (unsigned)OW * quads) return;
+  const unsigned ow = t / quads, q = t - ow * quads;
+  float4 mu, is, sc, sh;
+  bn_load_channel_consts(gamma, beta, save_mean, save_istd, (int)q, mu, is, sc, sh);
+  for (unsigned row = blockIdx.y; row < (unsigned)(N * OH); row += gridDim.y) {
+  const unsigned n = row / (unsigned)OH, oh = row - n * (unsigned)OH;
+  float4 best = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+  uchar4 bi = make_uchar4(255, 255, 255, 255);
+  const float* xin = x + (size_t)n * H * W * C + 4 * q;
 #pragma unroll
-    for (int kh = 0; kh < 3; ++kh) {
-      const int h = 2 * oh - 1 + kh;
-      if (h < 0 || h >= H) continue;
+  for (int kh = 0; kh < 3; ++kh) {
+    const int h = 2 * (int)oh - 1 + kh;
+    if (h < 0 || h >= H) continue;
 #pragma unroll
-      for (int kw = 0; kw < 3; ++kw) {
-        const int w = 2 * ow - 1 + kw;
-        if (w < 0 || w >= W) continue;
-        const float4 z = f4_fma(bn_ld4(x + (((int64_t)n * H + h) * W + w) * C + 4 * q), sc, sh);
-        const unsigned char code = (unsigned char)(kh * 3 + kw);
-        if (z.x > best.x || bi.x == 255) { best.x = z.x; bi.x = code; }
-        if (z.y > best.y || bi.y == 255) { best.y = z.y; bi.y = code; }
-        if (z.z > best.z || bi.z == 255) { best.z = z.z; bi.z = code; }
-        if (z.w > best.w || bi.w == 255) { best.w = z.w; bi.w = code; }
-      }
+    for (int kw = 0; kw < 3; ++kw) {
+      const int w = 2 * (int)ow - 1 + kw;
+      if (w < 0 || w >= W) continue;
+      const float4 z = f4_fma(bn_ld4(xin + (size_t)(unsigned)(h * W + w) * C), sc, sh);
+      const unsigned char code = (unsigned char)(kh * 3 + kw);
+      if (z.x > best.x || bi.x == 255) { best.x = z.x; bi.x = code; }
+      if (z.y > best.y || bi.y == 255) { best.y = z.y; bi.y = code; }
+      if (z.z > best.z || bi.z == 255) { best.z = z.z; bi.z = code; }
+      if (z.w > best.w || bi.w == 255) { best.w = z.w; bi.w = code; }
     }
-    const int64_t o = (((int64_t)n * OH + oh) * OW + ow) * C + 4 * q;
-    bn_st4(yp + o, make_float4(fmaxf(best.x, 0.f), fmaxf(best.y, 0.f), fmaxf(best.z, 0.f), fmaxf(best.w, 0.f)));
-    *reinterpret_cast<uchar4*>(pidx + o) = bi;
   }
+  const size_t o = ((size_t)row * OW + ow) * C + 4 * q;
+  bn_st4(yp + o, make_float4(fmaxf(best.x, 0.f), fmaxf(best.y, 0.f), fmaxf(best.z, 0.f), fmaxf(best.w, 0.f)));
+  *reinterpret_cast<uchar4*>(pidx + o) = bi;
+  }
+}
+
+static int bn_pool_apply_launch(const float* x, float* yp, unsigned char* pidx, const float* gamma, const float* beta,
+                                const float* save_mean, const float* save_istd, int N, int H, int W, int C, int OH,
+                                int OW, cudaStream_t s) {
+  if ((int64_t)N * OH >= (1LL << 31) || (int64_t)H * W >= (1LL << 31) || (int64_t)OW * (C / 4) >= (1LL << 31))
+    return (int)cudaErrorInvalidValue;
+  const int64_t rows = (int64_t)N * OH;
+  const int64_t per_row = (int64_t)OW * (C / 4);
+  const int T = per_row % 256 == 0 || per_row % 256 > 128 ? 256 : 128;    // 56 x 16 quads: 7 blocks of 128, none half empty
+  dim3 grid((unsigned)((per_row + T - 1) / T), (unsigned)(rows < 65535 ? rows : 65535));
+  k_bn_pool_apply<<<grid, T, 0, s>>>(x, yp, pidx, gamma, beta, save_mean, save_istd, N, H, W, C, OH, OW);
+  return (int)cudaGetLastError();
 }
 
 extern "C" int gk_bn_pool_fwd(const float* x, float* yp, unsigned char* pidx, const float* gamma, const float* beta,
@@ -1145,12 +1160,7 @@ extern "C" int gk_bn_pool_fwd(const float* x, float* yp, unsigned char* pidx, co
     k_bn_stats<<<g.grid, BN_T, 0, s>>>(x, M, C, g.rpb, g.qpb, accum, ticket, save_mean, save_istd, running_mean,
                                        running_var, num_batches, eps, momentum);
   }
-  const int64_t total = (int64_t)N * OH * OW * (C / 4);
-  int64_t blocks = (total + 255) / 256;
-  const int64_t cap = (int64_t)bn_sm_count() * 16;
-  if (blocks > cap) blocks = cap;
-  k_bn_pool_apply<<<(unsigned)blocks, 256, 0, s>>>(x, yp, pidx, gamma, beta, save_mean, save_istd, N, H, W, C, OH, OW);
-  return (int)cudaGetLastError();
+  return bn_pool_apply_launch(x, yp, pidx, gamma, beta, save_mean, save_istd, N, H, W, C, OH, OW, s);
 }
 
 // Batch statistics from per-block partial sums that somebody else accumulated (the stem convolution's epilogue,
@@ -1194,24 +1204,63 @@ extern "C" int gk_bn_pool_fwd_sums(const float* x, float* yp, unsigned char* pid
   cudaStream_t s = (cudaStream_t)stream;
   k_bn_finalize_partials<<<(C + 255) / 256, 256, 0, s>>>(partials, nparts, M, C, save_mean, save_istd, running_mean,
                                                         running_var, num_batches, eps, momentum);
-  const int64_t total = (int64_t)N * OH * OW * (C / 4);
-  int64_t blocks = (total + 255) / 256;
-  const int64_t cap = (int64_t)bn_sm_count() * 16;
-  if (blocks > cap) blocks = cap;
-  k_bn_pool_apply<<<(unsigned)blocks, 256, 0, s>>>(x, yp, pidx, gamma, beta, save_mean, save_istd, N, H, W, C, OH, OW);
-  return (int)cudaGetLastError();
+  return bn_pool_apply_launch(x, yp, pidx, gamma, beta, save_mean, save_istd, N, H, W, C, OH, OW, s);
 }
 
 // Full-resolution gradient of the max pool (dense gather, one thread per input pixel and channel quad): the
 // BN backward then runs on it like on any other gradient.  Cheaper than gathering inside the cooperative
 // kernel, which has one block per SM (16-32 warps) and would evaluate the windows twice.
-__global__ void __launch_bounds__(256) k_pool_gather(BnPool P, float* __restrict__ g, int64_t M, int C) {
-  const int quads = C >> 2;
-  const int64_t total = M * quads;
-  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = t / quads;
-    const int q = (int)(t - r * quads);
-    bn_st4(g + r * C + 4 * q, bn_pool_gather(P, r, C, q));
+// One thread per 2 x 2 block of input pixels and channel quad: the four pixels (2j, 2k), (2j, 2k+1), (2j+1, 2k),
+// (2j+1, 2k+1) lie in the windows (oh, ow) with oh in {j, j+1}, ow in {k, k+1} and in no other, so four loads of
+// (position code, gradient) serve four outputs (separately they take 1 + 2 + 2 + 4).  Grid: x = (column pair,
+// channel quad), y = (image, row pair); 32-bit arithmetic only.  (The flat-index, one-pixel-per-thread version was
+// instruction-bound: 62 us for 26 MB in, 103 MB out.)
+__global__ void __launch_bounds__(256) k_pool_gather(BnPool P, float* __restrict__ g, int N, int C) {
+  const unsigned quads = (unsigned)C >> 2;
+  const unsigned W2 = ((unsigned)P.W + 1u) >> 1, H2 = ((unsigned)P.H + 1u) >> 1;
+  const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= W2 * quads) return;
+  const unsigned k = t / quads, q = t - k * quads;
+  for (unsigned row = blockIdx.y; row < (unsigned)N * H2; row += gridDim.y) {
+    const unsigned n = row / H2, j = row - n * H2;
+    float4 acc[2][2];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int b = 0; b < 2; ++b) acc[a][b] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int dh = 0; dh < 2; ++dh) {
+      const unsigned oh = j + dh;                          // window oh covers input rows 2*oh-1 .. 2*oh+1
+      if (oh >= (unsigned)P.OH) continue;
+#pragma unroll
+      for (int dw = 0; dw < 2; ++dw) {
+        const unsigned ow = k + dw;
+        if (ow >= (unsigned)P.OW) continue;
+        const size_t o = ((size_t)(n * (unsigned)P.OH + oh) * P.OW + ow) * C + 4 * q;
+        const uchar4 id = *reinterpret_cast<const uchar4*>(P.idx + o);
+        const float4 d = bn_ld4(P.dy + o);
+        // pixel (2j + a, 2k + b) sits at window position (2j + a - (2 oh - 1), 2k + b - (2 ow - 1)); with oh = j + dh the
+        // row offset is a + 1 - 2 dh: rows a = 0, 1 for dh = 0 (offsets 1, 2), only a = 1 for dh = 1 (offset 0)
+#pragma unroll
+        for (int a = dh; a < 2; ++a)
+#pragma unroll
+          for (int b = dw; b < 2; ++b) {
+            const unsigned code = (unsigned)((a + 1 - 2 * dh) * 3 + (b + 1 - 2 * dw));
+            acc[a][b].x += id.x == code ? d.x : 0.f; acc[a][b].y += id.y == code ? d.y : 0.f;
+            acc[a][b].z += id.z == code ? d.z : 0.f; acc[a][b].w += id.w == code ? d.w : 0.f;
+          }
+      }
+    }
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+      const unsigned h = 2 * j + a;
+      if (h >= (unsigned)P.H) continue;
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        const unsigned w = 2 * k + b;
+        if (w < (unsigned)P.W) bn_st4(g + ((size_t)(n * (unsigned)P.H + h) * P.W + w) * C + 4 * q, acc[a][b]);
+      }
+    }
   }
 }
 
@@ -1227,11 +1276,13 @@ extern "C" int gk_bn_pool_bwd(const float* dyp, const unsigned char* pidx, const
                                dbeta, accum, bar, M, C, flags | 1, P, true, stream);
   if (!bn_aligned(gfull) || !bn_aligned(dyp) || (reinterpret_cast<uintptr_t>(pidx) & 3) || (C & 3))
     return (int)cudaErrorMisalignedAddress;
-  const int64_t total = M * (C / 4);
-  int64_t blocks = (total + 255) / 256;
-  const int64_t cap = (int64_t)bn_sm_count() * 16;
-  if (blocks > cap) blocks = cap;
-  k_pool_gather<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(P, gfull, M, C);
+  if ((int64_t)N * H >= (1LL << 31) || (int64_t)W * (C / 4) >= (1LL << 31)) return (int)cudaErrorInvalidValue;
+  {
+    const int64_t rows = (int64_t)N * ((H + 1) / 2), per_row = (int64_t)((W + 1) / 2) * (C / 4);
+    const int T = per_row % 256 == 0 || per_row % 256 > 128 ? 256 : 128;
+    dim3 grid((unsigned)((per_row + T - 1) / T), (unsigned)(rows < 65535 ? rows : 65535));
+    k_pool_gather<<<grid, T, 0, (cudaStream_t)stream>>>(P, gfull, N, C);
+  }
   BnPool none = {nullptr, nullptr, 0, 0, 0, 0};
   return bn_bwd_fused_launch(gfull, nullptr, x, nullptr, gamma, beta, save_mean, save_istd, dx, nullptr, dgamma,
                              dbeta, accum, bar, M, C, flags | 1, none, false, stream);
