@@ -363,6 +363,9 @@ __device__ __forceinline__ float to_tf32(float v) {   // round to nearest: the M
 // x [N, H, W, 3] (NHWC) -> X [N, Hp, Wp, 12], X[n, i, j, (dy*2+dx)*3 + c] = x[n, 2(i-2)+dy, 2(j-2)+dx, c], zero in the
 // two leading and one trailing rows / columns.  One thread per (position, dy): six consecutive floats in, six out,
 // both 8-byte aligned.
+// NCHW = true reads the planar [N, 3, H, W] batch as a data loader delivers it (per (c, dy) the two dx values are one
+// aligned float2; no separate NCHW -> NHWC conversion of the input is needed then).
+template <bool NCHW>
 __global__ void __launch_bounds__(256) k_stem_s2d(const float* __restrict__ x, float* __restrict__ X, int nimg, int H, int W,
                                                   long long nhalf) {
   const uint32_t Hp = H / 2 + 3, Wp = W / 2 + 3;   // positions < 2^31 (host check): 32-bit index arithmetic
@@ -375,10 +378,20 @@ __global__ void __launch_bounds__(256) k_stem_s2d(const float* __restrict__ x, f
     const int i = (int)(ni - nn * Hp), n = (int)nn;
     float2 v0 = make_float2(0.f, 0.f), v1 = v0, v2 = v0;
     if (i >= 2 && i < Hp - 1 && j >= 2 && j < Wp - 1) {
-      const float2* r = reinterpret_cast<const float2*>(x + (((long long)n * H + 2 * (i - 2) + dy) * W + 2 * (j - 2)) * 3);
-      v0 = __ldg(r);
-      v1 = __ldg(r + 1);
-      v2 = __ldg(r + 2);
+      if (NCHW) {
+        const size_t plane = (size_t)H * W;
+        const float* r = x + (size_t)n * 3 * plane + (size_t)(2 * (i - 2) + dy) * W + 2 * (j - 2);
+        const float2 c0 = __ldg(reinterpret_cast<const float2*>(r)), c1 = __ldg(reinterpret_cast<const float2*>(r + plane)),
+                     c2 = __ldg(reinterpret_cast<const float2*>(r + 2 * plane));
+        v0 = make_float2(c0.x, c1.x);               // dx = 0: c0 c1 c2, dx = 1: c0 c1 c2
+        v1 = make_float2(c2.x, c0.y);
+        v2 = make_float2(c1.y, c2.y);
+      } else {
+        const float2* r = reinterpret_cast<const float2*>(x + (((long long)n * H + 2 * (i - 2) + dy) * W + 2 * (j - 2)) * 3);
+        v0 = __ldg(r);
+        v1 = __ldg(r + 1);
+        v2 = __ldg(r + 2);
+      }
       v0.x = to_tf32(v0.x); v0.y = to_tf32(v0.y);
       v1.x = to_tf32(v1.x); v1.y = to_tf32(v1.y);
       v2.x = to_tf32(v2.x); v2.y = to_tf32(v2.y);
@@ -628,8 +641,13 @@ int gk_stem_supported(int H, int W) {
   return H >= 2 && W >= 2 && H % 2 == 0 && W % 2 == 0 && stem_box(W / 2 + 3) <= 256;
 }
 
-// x [nimg, H, W, 3] fp32 NHWC  ->  X [nimg, H/2+3, W/2+3, 12] fp32 (values rounded to tf32).
+// x [nimg, H, W, 3] fp32 NHWC (nchw = 0) or [nimg, 3, H, W] (nchw = 1)  ->  X [nimg, H/2+3, W/2+3, 12] fp32 (values
+// rounded to tf32).
+int gk_stem_s2d_layout(const void* x, void* X, int nimg, int H, int W, int nchw, void* stream);
 int gk_stem_s2d(const void* x, void* X, int nimg, int H, int W, void* stream) {
+  return gk_stem_s2d_layout(x, X, nimg, H, W, 0, stream);
+}
+int gk_stem_s2d_layout(const void* x, void* X, int nimg, int H, int W, int nchw, void* stream) {
   if (nimg <= 0 || H % 2 || W % 2) return -2;
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(X)) & 7) return -2;
   const long long nhalf = (long long)nimg * (H / 2 + 3) * (W / 2 + 3) * 2;
@@ -637,8 +655,12 @@ int gk_stem_s2d(const void* x, void* X, int nimg, int H, int W, void* stream) {
   const int threads = 256;
   long long blocks = (nhalf + threads - 1) / threads;
   if (blocks > 148 * 32) blocks = 148 * 32;
-  k_stem_s2d<<<(int)blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const float*>(x), static_cast<float*>(X), nimg, H, W, nhalf);
+  if (nchw)
+    k_stem_s2d<true><<<(int)blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const float*>(x), static_cast<float*>(X), nimg, H, W, nhalf);
+  else
+    k_stem_s2d<false><<<(int)blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const float*>(x), static_cast<float*>(X), nimg, H, W, nhalf);
   return (int)cudaGetLastError();
 }
 

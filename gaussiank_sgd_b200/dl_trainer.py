@@ -709,7 +709,9 @@ class DLTrainer:
             self._next_slot = self._prefetch.put(self._host_batch(self.data_iter())) if self.is_cuda else None
         inputs, labels = self._prefetch.get(slot)
         self._cur_slot = slot
-        if self.channels_last and inputs.dim() == 4:
+        if (self.channels_last and inputs.dim() == 4
+                and not (settings.STEM_TC and getattr(self.net, '_gk_stem_reads_nchw', False))):
+            # (a fused torchvision ResNet reads the NCHW batch in its own space-to-depth kernel: no conversion pass)
             inputs = inputs.contiguous(memory_format=torch.channels_last)
         return inputs, labels
 

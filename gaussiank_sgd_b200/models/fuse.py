@@ -88,15 +88,23 @@ def _stem_conv(conv, x, want_stats=False):
     convolution is the 7x7 / stride 2 / padding 3 one on an even-sized image (_stem_conv_s2d), else the 3 input
     channels padded to 4 (zeros in the image and in the weight: same result), else the module as it is.  With
     C_in = 3 the NHWC rows are 12 bytes and cuDNN falls back to its pre-Hopper indexed kernels.  The parameter
-    keeps its [C_out, 3, k, k] shape in every case."""
+    keeps its [C_out, 3, k, k] shape in every case.  The tensor-core path (ops/stem.py) also reads a plain NCHW batch;
+    the cuDNN paths want channels_last, so an NCHW batch that does not take it is converted here."""
+    s2d_shape = (settings.STEM_S2D and x.is_cuda and x.dim() == 4 and x.shape[1] == 3 and conv.in_channels == 3
+                 and conv.groups == 1 and conv.bias is None and conv.padding_mode == 'zeros'
+                 and tuple(conv.kernel_size) == (7, 7) and tuple(conv.stride) == (2, 2) and tuple(conv.padding) == (3, 3)
+                 and tuple(conv.dilation) == (1, 1) and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0)
+    if s2d_shape and settings.STEM_TC and conv.out_channels == 64 and stem.supported(x, conv.weight):
+        # TMA + tcgen05 implicit GEMM (csrc/gk_stem.cu); with want_stats it returns (y, sums for the BN)
+        return stem.stem_conv_tc(x, conv.weight, want_stats and settings.STEM_BN_STATS)
+    if (settings.CHANNELS_LAST and x.is_cuda and x.dim() == 4
+            and not x.is_contiguous(memory_format=torch.channels_last)):
+        x = x.contiguous(memory_format=torch.channels_last)      # channels_last model, NCHW batch, no tensor-core stem
     if (settings.STEM_S2D and x.is_cuda and x.dim() == 4 and x.shape[1] == 3 and conv.in_channels == 3
             and conv.groups == 1 and conv.bias is None and conv.padding_mode == 'zeros'
             and tuple(conv.kernel_size) == (7, 7) and tuple(conv.stride) == (2, 2) and tuple(conv.padding) == (3, 3)
             and tuple(conv.dilation) == (1, 1) and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0
             and x.is_contiguous(memory_format=torch.channels_last)):
-        if settings.STEM_TC and conv.out_channels == 64 and stem.supported(x, conv.weight):
-            # TMA + tcgen05 implicit GEMM (csrc/gk_stem.cu); with want_stats it returns (y, sums for the BN)
-            return stem.stem_conv_tc(x, conv.weight, want_stats and settings.STEM_BN_STATS)
         return _stem_conv_s2d(conv, x)
     if not (settings.STEM_PAD4 and x.is_cuda and x.dim() == 4 and x.shape[1] == 3 and conv.in_channels == 3
             and conv.groups == 1 and conv.bias is None and conv.padding_mode == 'zeros'
@@ -138,6 +146,7 @@ def fuse_bn_act(model: nn.Module) -> int:
             sites += 2 + (m.downsample is not None)
         elif tv is not None and type(m) is tv.ResNet and type(m.bn1) is nn.BatchNorm2d:
             m.forward = types.MethodType(_resnet_forward, m)
+            m._gk_stem_reads_nchw = True            # the stem takes the loader's NCHW batch (see _stem_conv)
             sites += 1
             # the last block of a stage feeds the next stage's first convolution and its downsample convolution
             stages = [m.layer1, m.layer2, m.layer3, m.layer4]

@@ -181,6 +181,7 @@ def cuda_lib():
             _proto(lib, "gk_stem_stats_rows", [])
             _proto(lib, "gk_bn_pool_fwd_sums", [_P] * 11 + [C.c_int32] * 5 + [C.c_float, C.c_float, _P])
             _proto(lib, "gk_stem_s2d", [_P, _P, C.c_int32, C.c_int32, C.c_int32, _P])
+            _proto(lib, "gk_stem_s2d_layout", [_P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P])
             _proto(lib, "gk_stem_pack_w", [_P, _P, _P])
             _proto(lib, "gk_stem_supported", [C.c_int32, C.c_int32])
             _proto(lib, "gk_stem_wgrad_supported", [C.c_int32, C.c_int32])

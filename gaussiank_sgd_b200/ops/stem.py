@@ -33,10 +33,11 @@ def error_codes():
 
 
 def supported(x: torch.Tensor, weight: torch.Tensor) -> bool:
-    """x: the image batch [N, 3, H, W] in channels_last memory; weight: the stem's [64, 3, 7, 7] parameter."""
+    """x: the image batch [N, 3, H, W], channels_last or plain NCHW memory (the space-to-depth kernel reads either, so
+    a batch straight from the loader needs no layout conversion); weight: the stem's [64, 3, 7, 7] parameter."""
     return (x.is_cuda and x.dtype == torch.float32 and weight.dtype == torch.float32 and x.dim() == 4
             and x.shape[1] == 3 and tuple(weight.shape) == (64, 3, 7, 7)
-            and x.is_contiguous(memory_format=torch.channels_last) and not x.requires_grad
+            and (x.is_contiguous(memory_format=torch.channels_last) or x.is_contiguous()) and not x.requires_grad
             and not torch.is_autocast_enabled()
             and torch.backends.cudnn.allow_tf32        # the kernel is tf32: honour the switch that forbids it
             and x.shape[0] * (x.shape[2] // 2 + 3) * (x.shape[3] // 2 + 3) < 2 ** 31 - 2048
@@ -51,7 +52,8 @@ class _StemConvTC(torch.autograd.Function):
         N, _, H, W = x.shape
         OH, OW = H // 2, W // 2
         X = torch.empty((N, OH + 3, OW + 3, 12), dtype=torch.float32, device=x.device)   # padded space-to-depth image
-        native.check(lib.gk_stem_s2d(x.data_ptr(), X.data_ptr(), N, H, W, st), "gk_stem_s2d")
+        nchw = 0 if x.is_contiguous(memory_format=torch.channels_last) else 1
+        native.check(lib.gk_stem_s2d_layout(x.data_ptr(), X.data_ptr(), N, H, W, nchw, st), "gk_stem_s2d")
         wpk = torch.empty(24 * 512, dtype=torch.float32, device=x.device)
         wc = weight.detach().contiguous()                                       # channels_last models stride it
         native.check(lib.gk_stem_pack_w(wc.data_ptr(), wpk.data_ptr(), st), "gk_stem_pack_w")

@@ -392,6 +392,7 @@ const char* gk_version(void);
  * Return: 0, a cudaError_t, -2 (shape not covered) or -3 (the driver cannot encode the tensor map). */
 int gk_stem_supported(int H, int W);                 /* forward: even sizes, W <= 332 */
 int gk_stem_s2d(const void* x, void* X, int nimg, int H, int W, void* stream);
+int gk_stem_s2d_layout(const void* x, void* X, int nimg, int H, int W, int nchw, void* stream); /* x [N,3,H,W] if nchw */
 int gk_stem_pack_w(const void* w, void* wpk, void* stream);
 int gk_stem_fwd(const void* X, const void* wpk, void* y, int nimg, int OH, int OW, void* err, void* stream);
 /* ... and leave the per-channel sums / sums of squares of y in stats[gk_stem_stats_rows()][128] (one partial row per

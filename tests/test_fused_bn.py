@@ -324,6 +324,9 @@ def test_stem_tensor_core_kernel_matches_fp32_convolution(shape):
     ref = copy.deepcopy(conv).double()
     x = torch.randn(N, 3, H, W, device=dev).contiguous(memory_format=torch.channels_last)
     assert settings.STEM_TC and settings.STEM_S2D
+    if N == 5:
+        x = x.contiguous()                      # a plain NCHW batch, as the loader delivers it: read directly
+        assert not x.is_contiguous(memory_format=torch.channels_last)
     before = dict(stem.calls)
     y = _stem_conv(conv, x)
     assert stem.calls["fwd"] == before["fwd"] + 1, "the tensor-core path was not taken"
