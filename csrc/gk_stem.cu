@@ -584,24 +584,33 @@ k_stem_wgrad_tc(const __grid_constant__ CUtensorMap mapG, const __grid_constant_
 }
 
 // gw[o, ch, u, v] = sum over CTAs of part[cta][o][a*48 + b*12 + c], 2a + dy - 1 = u, 2b + dx - 1 = v,
-// c = (dy*2 + dx)*3 + ch.
-__global__ void k_stem_wgrad_fold(const float* __restrict__ part, int nparts, float* __restrict__ gw) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= ST_N * 3 * 49) return;
-  const int v = i % 7, u = (i / 7) % 7, ch = (i / 49) % 3, o = i / 147;
-  const int dy = (u + 1) & 1, a = (u + 1) >> 1, dx = (v + 1) & 1, b = (v + 1) >> 1;
-  const int c12 = (dy * 2 + dx) * 3 + ch;
-  const float* p = part + (size_t)o * WG_COLS + a * 48 + b * 12 + c12;
+// c = (dy*2 + dx)*3 + ch.  One block per output channel o: thread (column, quarter j) adds every fourth partial
+// (coalesced 768-byte rows, fixed order: deterministic), the quarters meet in shared memory, then 147 threads pick
+// their column.  (One thread per output element walking all partials serially took 15 us.)
+constexpr int WG_FOLD_SPLIT = 4;
+__global__ void __launch_bounds__(WG_COLS * WG_FOLD_SPLIT) k_stem_wgrad_fold(const float* __restrict__ part, int nparts,
+                                                                            float* __restrict__ gw) {
+  __shared__ float red[WG_FOLD_SPLIT][WG_COLS];
+  const int o = blockIdx.x, col = threadIdx.x % WG_COLS, j = threadIdx.x / WG_COLS;
+  const float* p = part + (size_t)o * WG_COLS + col;
   float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-  int k = 0;
-  for (; k + 4 <= nparts; k += 4) {
-    s0 += p[(size_t)(k + 0) * ST_N * WG_COLS];
-    s1 += p[(size_t)(k + 1) * ST_N * WG_COLS];
-    s2 += p[(size_t)(k + 2) * ST_N * WG_COLS];
-    s3 += p[(size_t)(k + 3) * ST_N * WG_COLS];
+  int k = j;
+  for (; k + 3 * WG_FOLD_SPLIT < nparts; k += 4 * WG_FOLD_SPLIT) {
+    s0 += __ldg(p + (size_t)(k) * ST_N * WG_COLS);
+    s1 += __ldg(p + (size_t)(k + WG_FOLD_SPLIT) * ST_N * WG_COLS);
+    s2 += __ldg(p + (size_t)(k + 2 * WG_FOLD_SPLIT) * ST_N * WG_COLS);
+    s3 += __ldg(p + (size_t)(k + 3 * WG_FOLD_SPLIT) * ST_N * WG_COLS);
   }
-  for (; k < nparts; ++k) s0 += p[(size_t)k * ST_N * WG_COLS];
-  gw[i] = (s0 + s1) + (s2 + s3);
+  for (; k < nparts; k += WG_FOLD_SPLIT) s0 += __ldg(p + (size_t)k * ST_N * WG_COLS);
+  red[j][col] = (s0 + s1) + (s2 + s3);
+  __syncthreads();
+  const int i = threadIdx.x;
+  if (i < 147) {
+    const int v = i % 7, u = (i / 7) % 7, ch = i / 49;
+    const int dy = (u + 1) & 1, a = (u + 1) >> 1, dx = (v + 1) & 1, b = (v + 1) >> 1;
+    const int c = a * 48 + b * 12 + (dy * 2 + dx) * 3 + ch;
+    gw[o * 147 + i] = (red[0][c] + red[1][c]) + (red[2][c] + red[3][c]);
+  }
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -793,7 +802,7 @@ int gk_stem_wgrad(const void* gy, const void* X, void* gw, void* work, int nimg,
   const int grid = nrows < sms ? (int)nrows : sms;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   k_stem_wgrad_tc<<<grid, WG_THREADS, smem, s>>>(mapG, mapX, static_cast<float*>(work), g, static_cast<unsigned int*>(err));
-  k_stem_wgrad_fold<<<(ST_N * 147 + 255) / 256, 256, 0, s>>>(static_cast<const float*>(work), grid, static_cast<float*>(gw));
+  k_stem_wgrad_fold<<<ST_N, WG_COLS * WG_FOLD_SPLIT, 0, s>>>(static_cast<const float*>(work), grid, static_cast<float*>(gw));
   return (int)cudaGetLastError();
 }
 
