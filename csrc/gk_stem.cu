@@ -284,6 +284,9 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
     const int q = warp & 3;
     float* const stg = epi + q * 32 * ST_EPI_PITCH;
     const uint32_t pl = (uint32_t)(g.Hp * g.Wp), Wp = (uint32_t)g.Wp;
+    unsigned long long outb_u = reinterpret_cast<unsigned long long>(out) + (unsigned)(lane & 7) * 16u;
+    asm volatile("" : "+l"(outb_u));                // keep it in registers (else re-derived from the parameter bank per store)
+    char* const outb = reinterpret_cast<char*>(outb_u);                    // this lane's 16 bytes of a 128-byte line
     float cs[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}}, cq[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
     for (int it = 0; it < nt; ++it) {
       const uint32_t as = (uint32_t)it % ST_NI, aph = ((uint32_t)it / ST_NI) & 1u;
@@ -291,8 +294,8 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
       const uint32_t p = (uint32_t)(t0 + it) * ST_M + (uint32_t)(q * 32 + lane);
       const uint32_t n = p / pl, rem = p - n * pl;
       const uint32_t oh = rem / Wp, ow = rem - oh * Wp;
-      const uint32_t off = (n < (uint32_t)g.nimg && oh < (uint32_t)g.OH && ow < (uint32_t)g.OW)
-                               ? ((n * (uint32_t)g.OH + oh) * (uint32_t)g.OW + ow) * ST_N : 0xffffffffu;
+      const uint32_t off = (n < (uint32_t)g.nimg && oh < (uint32_t)g.OH && ow < (uint32_t)g.OW)     // byte offset of the row
+                               ? ((n * (uint32_t)g.OH + oh) * (uint32_t)g.OW + ow) * (ST_N * 4u) : 0xffffffffu;
       mbar_wait(tfull(as), aph, err, 5);
       tc_fence_after();
       uint32_t v[64];
@@ -316,7 +319,7 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
           const uint4 x = *reinterpret_cast<const uint4*>(stg + row * ST_EPI_PITCH + ch * 4);
           const uint32_t o = __shfl_sync(0xffffffffu, off, row);
           if (o != 0xffffffffu) {
-            *reinterpret_cast<uint4*>(out + o + half * 32 + ch * 4) = x;
+            *reinterpret_cast<uint4*>(outb + o + half * 128) = x;
             if (STATS) {  // per-channel sum and sum of squares of the output pixels, for the BatchNorm that follows
               const float f0 = __uint_as_float(x.x), f1 = __uint_as_float(x.y), f2 = __uint_as_float(x.z), f3 = __uint_as_float(x.w);
               cs[half][0] += f0; cs[half][1] += f1; cs[half][2] += f2; cs[half][3] += f3;
@@ -705,7 +708,7 @@ int gk_stem_fwd_stats(const void* X, const void* wpk, void* y, void* stats, int 
   const long long rows = P - 3LL * Wp - 3;           // one past the last position that is an output pixel
   const int boxP = stem_box(Wp);
   if (rows <= 0 || P > (1LL << 31) - 2048 || boxP > 256) return -2;
-  if ((long long)nimg * OH * OW * ST_N >= (1LL << 32) - 1) return -2;      // 32-bit output offsets in the epilogue
+  if ((long long)nimg * OH * OW * ST_N * 4 >= (1LL << 32) - 1) return -2;  // 32-bit byte offsets in the epilogue
   if ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(wpk) | reinterpret_cast<uintptr_t>(y)) & 15) return -2;
   EncodeTiledFn enc = encode_fn();
   if (!enc) return -3;

@@ -41,6 +41,7 @@ def supported(x: torch.Tensor, weight: torch.Tensor) -> bool:
             and not torch.is_autocast_enabled()
             and torch.backends.cudnn.allow_tf32        # the kernel is tf32: honour the switch that forbids it
             and x.shape[0] * (x.shape[2] // 2 + 3) * (x.shape[3] // 2 + 3) < 2 ** 31 - 2048
+            and x.shape[0] * (x.shape[2] // 2) * (x.shape[3] // 2) * 256 < 2 ** 32 - 1   # 32-bit byte offsets of y
             and bool(native.cuda_lib().gk_stem_supported(int(x.shape[2]), int(x.shape[3]))))
 
 
