@@ -9,8 +9,9 @@ B200-first differences:
   launch-bound on a B200 when driven op by op from Python;
 * inputs are prefetched to the device on a copy stream from pinned host memory; the loss is read back
   asynchronously one step late instead of a blocking ``loss.item()`` every iteration (:713);
-* NHWC convolutions and ``cudnn.benchmark`` are on (the reference pins benchmark=False /
-  deterministic=True, :20-21); both can be switched off with GK_CHANNELS_LAST=0 / GK_CUDNN_BENCHMARK=0;
+* NHWC convolutions are on, ``cudnn.benchmark`` is on except for the ImageNet-shape models (settings.py: with the
+  autotuner the ranks of a multi-GPU job land on different algorithms and run at the pace of the slowest; the
+  reference pins benchmark=False / deterministic=True, :20-21); GK_CHANNELS_LAST=0/1, GK_CUDNN_BENCHMARK=0/1;
 * datasets fall back to synthetic stand-ins of the same shape when the files are absent (no network).
 """
 from __future__ import annotations
@@ -189,7 +190,8 @@ class DLTrainer:
             self.device = torch.device('cuda', torch.cuda.current_device()) if self.is_cuda else torch.device('cpu')
         self.is_cuda = self.device.type == 'cuda'
         if self.is_cuda:
-            torch.backends.cudnn.benchmark = settings.CUDNN_BENCHMARK
+            torch.backends.cudnn.benchmark = (settings.CUDNN_BENCHMARK if settings.CUDNN_BENCHMARK is not None
+                                              else dataset != 'imagenet')
             if settings.CUDNN_BENCHMARK_LIMIT is not None:      # how many algorithms the autotuner tries (0 = all)
                 torch.backends.cudnn.benchmark_limit = settings.CUDNN_BENCHMARK_LIMIT
         self.trainset = self.testset = self.trainloader = self.testloader = self.train_sampler = None

@@ -84,7 +84,12 @@ STEM_TC_WGRAD = _flag("STEM_TC_WGRAD", True)        # ... and its weight gradien
 STEM_BN_STATS = _flag("STEM_BN_STATS", True)        # ... its epilogue accumulates the batch statistics of bn1
 STEM_PAD4 = _flag("STEM_PAD4", True)                # ResNet stem: pad the 3 input channels to 4 (aligned cuDNN kernels)
 BN_STAMPS = _flag("BN_STAMPS", False)                # fused BN kernels record phase time stamps (profiling aid)
-CUDNN_BENCHMARK = _flag("CUDNN_BENCHMARK", True)    # the reference pins benchmark=False, deterministic=True
+# cuDNN autotuning.  Unset = per workload (DLTrainer): off for the ImageNet-shape models, on for the others.  Measured on
+# ResNet-50: on one GPU the heuristic choice is as fast as the autotuned one (5 115 against 5 071-5 117 images/s), on 8
+# GPUs it is 1.7 % faster (6.48 against 6.59 ms/step) because every rank then runs the same algorithms - the autotuner
+# times each candidate once, ranks land on different kernels, and the step runs at the pace of the slowest rank.
+# (The reference pins benchmark=False, deterministic=True.)
+CUDNN_BENCHMARK = (_flag("CUDNN_BENCHMARK", True) if os.environ.get("GK_CUDNN_BENCHMARK") is not None else None)
 
 CUDNN_BENCHMARK_LIMIT = (int(os.environ["GK_CUDNN_BENCHMARK_LIMIT"])
                          if os.environ.get("GK_CUDNN_BENCHMARK_LIMIT") else None)   # None = torch's default (10)

@@ -100,7 +100,7 @@ def test_cuda_graph_step_equals_eager_step():
         assert abs(l0 - l1) < 1e-3 * max(1.0, abs(l0))
     finally:
         settings.CUDA_GRAPH = True
-        settings.CUDNN_BENCHMARK = True
+        settings.CUDNN_BENCHMARK = None              # back to the per-workload default
         torch.backends.cudnn.deterministic = False
 
 

@@ -67,7 +67,7 @@ def main():
         if want is None:
             want = torch.nn.functional.conv2d(x.double(), conv.weight.double(), None, 2, 3)
         res[name] = {"fwd_us": timed(run(True), args.iters), "fwd_wgrad_us": timed(run(False), args.iters),
-                     "max_abs_err_vs_fp64": float((y.double() - want).abs().max())}
+                     "max_abs_err_vs_fp64": float((y.detach().double() - want.detach()).abs().max())}
     # the implicit-GEMM kernel alone (no space-to-depth kernel, no weight packing)
     settings.STEM_TC = settings.STEM_S2D = settings.STEM_TC_WGRAD = True
     from gaussiank_sgd_b200.ops import native
