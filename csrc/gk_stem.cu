@@ -25,10 +25,11 @@
 // positions of X per chunk, double-buffered).  Warp-specialised:
 //   warp 0   producer: 12 TMA boxes {4 floats, boxP positions} per chunk (tensor map dims {4, P, 3}, strides
 //            {4, 48, 16} B: the plane split happens in the copy engine); one bulk copy of the packed weights.
-//   warp 1   one lane issues the tcgen05.mma kind::tf32 instructions into one of two TMEM accumulators;
-//            tcgen05.commit publishes the accumulator and releases the chunk buffer.
-//   warp 2   allocates / frees 128 TMEM columns.
-//   4 epilogue warps, one per TMEM lane quarter: tcgen05.ld the 128 x 64 fp32 tile, transpose through padded shared
+//   warps 1-4  MMA issuers: one lane each issues the tcgen05.mma kind::tf32 instructions of every fourth tile into
+//            its own TMEM accumulator (one thread can issue an MMA of this size only every ~70-130 cycles, see
+//            tools/experiments/umma_rate.cu); tcgen05.commit publishes the accumulator and releases the chunk buffer.
+//   warp 5   allocates / frees 256 TMEM columns (four 64-column accumulators).
+//   warps 6-9  4 epilogue warps, one per TMEM lane quarter: tcgen05.ld the 128 x 64 fp32 tile, transpose through padded shared
 //            memory, store whole 128-byte lines of the NHWC output (the valid rows of a tile are contiguous in y);
 //            optionally accumulate the per-channel sums of y for the BatchNorm that follows.
 // Every mbarrier wait is bounded (2 s on %globaltimer): on expiry the kernel records a code and traps.
@@ -49,7 +50,7 @@ constexpr int ST_NMMA = ST_TAPS * 3 * 2;           // K = 8 steps per tile
 constexpr int ST_B_MMA = 2 * ST_N * 16;            // weight bytes per step: 2 halves x 64 rows x 16 B
 constexpr int ST_B_BYTES = ST_NMMA * ST_B_MMA;     // 48 KB
 constexpr int ST_EPI_PITCH = 36;                   // floats; 32 + 4 keeps the float4 phases conflict-free
-constexpr int ST_EPI_WARPS = 4;                    // one per TMEM lane quarter (8 warps, one per quarter and channel half: slower)
+constexpr int ST_EPI_WARPS = 4;                    // one per TMEM lane quarter (8, one per quarter and channel half, were slower)
 constexpr int ST_EPI_BYTES = ST_EPI_WARPS * 32 * ST_EPI_PITCH * 4;
 constexpr int ST_NI = 4;                           // MMA-issuing warps = TMEM accumulators
 constexpr int ST_W_ALLOC = 1 + ST_NI;              // warp 0 producer, 1..ST_NI issuers, then TMEM allocator, then 4 epilogue

@@ -106,3 +106,65 @@ def stem_conv_tc(x: torch.Tensor, weight: torch.Tensor, want_stats: bool = False
     sums of squares of the output ([parts, 128] fp32 partial rows, accumulated in the kernel's epilogue) for
     ``ops.bn.bn_relu_maxpool(..., presums=...)``."""
     return _StemConvTC.apply(x, weight, want_stats)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# The same decomposition in plain torch (any device, any float dtype): what the kernels of csrc/gk_stem.cu compute,
+# step by step.  tests/test_components_cpu.py holds it against F.conv2d, so the index conventions of the
+# space-to-depth image, the packed weight and the fold of the weight gradient are pinned on machines without a GPU.
+def space_to_depth_reference(x: torch.Tensor) -> torch.Tensor:
+    """[N, 3, H, W] -> padded space-to-depth image [N, H/2+3, W/2+3, 12] (k_stem_s2d):
+    X[n, i, j, (dy*2+dx)*3 + c] = x[n, c, 2(i-2)+dy, 2(j-2)+dx], zero in the two leading / one trailing rows and columns."""
+    N, C, H, W = x.shape
+    xs = x.permute(0, 2, 3, 1).reshape(N, H // 2, 2, W // 2, 2, C).permute(0, 1, 3, 2, 4, 5).reshape(N, H // 2, W // 2, 4 * C)
+    X = x.new_zeros((N, H // 2 + 3, W // 2 + 3, 4 * C))
+    X[:, 2:-1, 2:-1] = xs
+    return X
+
+
+def pack_weight_reference(w: torch.Tensor) -> torch.Tensor:
+    """[64, 3, 7, 7] -> [24, 2, 64, 4] (k_stem_pack_w; the kernel stores the 64 rows as 8 groups of 8): step
+    m = (a*3 + t)*2 + bp, half kc, row o, float e  <-  W4[o, 4t + e, a, 2bp + kc] with
+    W4[o, (dy*2+dx)*3 + ch, a, b] = w[o, ch, 2a+dy-1, 2b+dx-1] (zero where an index is -1)."""
+    O = w.shape[0]
+    w4 = torch.nn.functional.pad(w, (1, 0, 1, 0)).reshape(O, 3, 4, 2, 4, 2).permute(0, 3, 5, 1, 2, 4).reshape(O, 12, 4, 4)
+    # [o, (t, e), a, (bp, kc)] -> [a, t, bp, kc, o, e]
+    return w4.reshape(O, 3, 4, 4, 2, 2).permute(3, 1, 4, 5, 0, 2).reshape(24, 2, O, 4)
+
+
+def forward_reference(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    """conv2d(x, w, stride 2, padding 3) as the 24 K = 8 steps of k_stem_fwd_tc over the flat padded positions."""
+    N, _, H, W = x.shape
+    OH, OW, Hp, Wp = H // 2, W // 2, H // 2 + 3, W // 2 + 3
+    Xf = space_to_depth_reference(x).reshape(N * Hp * Wp, 12)
+    Xf = torch.cat([Xf, Xf.new_zeros((3 * Wp + 4, 12))])                 # the tensor map's zero fill past the end
+    wpk = pack_weight_reference(w)
+    P = N * Hp * Wp
+    y = x.new_zeros((P, w.shape[0]))
+    for a in range(4):
+        for t in range(3):
+            for bp in range(2):
+                m = (a * 3 + t) * 2 + bp
+                for kc in range(2):
+                    off = a * Wp + 2 * bp + kc
+                    y += Xf[off:off + P, 4 * t:4 * t + 4] @ wpk[m, kc].t()
+    return y.reshape(N, Hp, Wp, -1)[:, :OH, :OW].permute(0, 3, 1, 2)
+
+
+def wgrad_reference(gy: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    """Weight gradient [64, 3, 7, 7] as k_stem_wgrad_tc + k_stem_wgrad_fold compute it: per kernel row a the 64 x 48
+    product of gY (pixels x channels) with the 48-float windows of X, then the fold of the 4x4 form back to 7x7."""
+    N, O, OH, OW = gy.shape
+    X = space_to_depth_reference(x)
+    g = gy.permute(0, 2, 3, 1)                                          # NHWC
+    part = gy.new_zeros((O, 192))
+    for a in range(4):
+        win = torch.cat([X[:, a:a + OH, b:b + OW] for b in range(4)], dim=3)       # [N, OH, OW, 48]: b-major, then c
+        part[:, a * 48:(a + 1) * 48] = torch.einsum("nhwo,nhwk->ok", g, win)
+    gw = gy.new_zeros((O, 3, 7, 7))
+    for u in range(7):
+        for v in range(7):
+            dy, a, dx, b = (u + 1) & 1, (u + 1) >> 1, (v + 1) & 1, (v + 1) >> 1
+            for ch in range(3):
+                gw[:, ch, u, v] = part[:, a * 48 + b * 12 + (dy * 2 + dx) * 3 + ch]
+    return gw

@@ -365,3 +365,24 @@ def test_mixed_precision_bf16_and_fp16_loss_scale(monkeypatch):
     w16, s16, l16 = run(True, "fp16")
     assert s16 == 128.0
     assert torch.isfinite(w16).all() and (w16 - w32).abs().max() < 0.05      # scaled in, divided out
+
+
+def test_stem_tensor_core_decomposition_equals_the_convolution():
+    """ops/stem.py restates what csrc/gk_stem.cu computes (space-to-depth image, 24 packed K = 8 steps, weight
+    gradient per kernel row + fold) in plain torch; it must be the 7x7 / stride 2 / padding 3 convolution exactly."""
+    import torch.nn.functional as F
+    from gaussiank_sgd_b200.ops import stem
+    torch.manual_seed(5)
+    x = torch.randn(2, 3, 12, 20, dtype=torch.float64)
+    w = torch.randn(64, 3, 7, 7, dtype=torch.float64, requires_grad=True)
+    want = F.conv2d(x, w, None, 2, 3)
+    got = stem.forward_reference(x, w.detach())
+    assert got.shape == want.shape
+    torch.testing.assert_close(got, want.detach(), rtol=1e-12, atol=1e-12)
+    gy = torch.randn_like(want)
+    want.backward(gy)
+    torch.testing.assert_close(stem.wgrad_reference(gy, x), w.grad, rtol=1e-12, atol=1e-11)
+    X = stem.space_to_depth_reference(x)
+    assert X.shape == (2, 9, 13, 12) and float(X[:, :2].abs().sum() + X[:, -1:].abs().sum() + X[:, :, :2].abs().sum()
+                                               + X[:, :, -1:].abs().sum()) == 0.0
+    assert float(X[1, 2 + 3, 2 + 4, (1 * 2 + 0) * 3 + 2]) == float(x[1, 2, 2 * 3 + 1, 2 * 4 + 0])

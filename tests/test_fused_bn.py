@@ -351,6 +351,32 @@ def test_stem_tensor_core_kernel_matches_fp32_convolution(shape):
 
 
 @pytest.mark.gpu
+def test_stem_helper_kernels_match_their_torch_restatement():
+    """k_stem_s2d (NHWC and NCHW input) and k_stem_pack_w against ops/stem.py's plain-torch versions, up to the
+    round-to-nearest tf32 conversion both kernels apply."""
+    from gaussiank_sgd_b200.ops import native, stem
+    lib, dev = native.cuda_lib(), torch.device("cuda:0")
+    st = torch.cuda.current_stream().cuda_stream
+    torch.manual_seed(9)
+
+    def tf32(t):        # round to nearest, ties away from zero in magnitude (cvt.rna): add half an ulp of the kept part, truncate
+        b = t.contiguous().view(torch.int32)
+        return ((b + 0x1000) & ~0x1FFF).view(torch.float32)
+
+    x = torch.randn(3, 3, 20, 36, device=dev)
+    want = tf32(stem.space_to_depth_reference(x))
+    for nchw, src in ((1, x), (0, x.contiguous(memory_format=torch.channels_last))):
+        X = torch.full((3, 13, 21, 12), float("nan"), device=dev)
+        native.check(lib.gk_stem_s2d_layout(src.data_ptr(), X.data_ptr(), 3, 20, 36, nchw, st))
+        assert torch.equal(X, want), nchw
+    w = torch.randn(64, 3, 7, 7, device=dev)
+    wpk = torch.empty(24 * 512, device=dev)
+    native.check(lib.gk_stem_pack_w(w.data_ptr(), wpk.data_ptr(), st))
+    ref = tf32(stem.pack_weight_reference(w))                      # [24, 2, 64, 4]; the kernel groups the rows 8 x 8
+    assert torch.equal(wpk.view(24, 2, 64, 4), ref)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("shape", [(4, 64, 64), (32, 224, 224), (3, 96, 160)])
 def test_stem_epilogue_statistics_feed_the_batch_norm(shape, monkeypatch):
     """The stem convolution's epilogue accumulates the per-channel sums of its output; bn1 + ReLU + max pool built on
