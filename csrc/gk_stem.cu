@@ -649,6 +649,35 @@ int stem_box(int Wp) { return ((ST_CHUNK * ST_M + 3 * Wp + 3 + 3) / 4 + 7) & ~7;
 
 extern "C" {
 
+// 1 when this driver can encode the tensor maps the kernels use (cuTensorMapEncodeTiled is exported and accepts the
+// un-swizzled and the 128-byte / 32-byte-atom swizzled forms); nothing is launched, `probe` is any 16-byte aligned
+// device pointer (it is not dereferenced).
+int gk_stem_driver_ok(const void* probe) {
+  EncodeTiledFn enc = encode_fn();
+  if (!enc || probe == nullptr || (reinterpret_cast<uintptr_t>(probe) & 15)) return 0;
+  CUtensorMap m;
+  const cuuint32_t es[3] = {1, 1, 1};
+  {
+    const cuuint64_t dims[3] = {4, 1024, 3};
+    const cuuint64_t strides[2] = {48, 16};
+    const cuuint32_t box[3] = {4, 256, 1};
+    if (enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(probe), dims, strides, box, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return 0;
+  }
+  {
+    const cuuint64_t dims[2] = {48, 1024};
+    const cuuint64_t strides[1] = {48};
+    const cuuint32_t box[2] = {32, 112};
+    if (enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(probe), dims, strides, box, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return 0;
+  }
+  return 1;
+}
+
 // 1 when gk_stem_fwd covers an H x W image (even sizes; the chunk of X must fit four 256-position TMA boxes).
 int gk_stem_supported(int H, int W) {
   return H >= 2 && W >= 2 && H % 2 == 0 && W % 2 == 0 && stem_box(W / 2 + 3) <= 256;

@@ -184,6 +184,7 @@ def cuda_lib():
             _proto(lib, "gk_stem_s2d_layout", [_P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P])
             _proto(lib, "gk_stem_pack_w", [_P, _P, _P])
             _proto(lib, "gk_stem_supported", [C.c_int32, C.c_int32])
+            _proto(lib, "gk_stem_driver_ok", [_P])
             _proto(lib, "gk_stem_wgrad_supported", [C.c_int32, C.c_int32])
             _proto(lib, "gk_stem_wgrad_workspace", [], C.c_longlong)
             _proto(lib, "gk_stem_wgrad", [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P])

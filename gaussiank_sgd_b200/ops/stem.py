@@ -32,6 +32,19 @@ def error_codes():
     return {str(d): int(t.item()) for d, t in _err.items()}
 
 
+_driver = {}
+
+
+def _driver_ok(device) -> bool:
+    """Once per device: can this driver encode the tensor maps of csrc/gk_stem.cu?  (If not, cuDNN keeps the stem.)"""
+    ok = _driver.get(device)
+    if ok is None:
+        ok = _driver[device] = bool(native.cuda_lib().gk_stem_driver_ok(_err_word(device).data_ptr()))
+        if not ok:
+            settings.logger.warning("stem tensor-core kernels disabled: the driver cannot encode their tensor maps")
+    return ok
+
+
 def supported(x: torch.Tensor, weight: torch.Tensor) -> bool:
     """x: the image batch [N, 3, H, W], channels_last or plain NCHW memory (the space-to-depth kernel reads either, so
     a batch straight from the loader needs no layout conversion); weight: the stem's [64, 3, 7, 7] parameter."""
@@ -42,7 +55,8 @@ def supported(x: torch.Tensor, weight: torch.Tensor) -> bool:
             and torch.backends.cudnn.allow_tf32        # the kernel is tf32: honour the switch that forbids it
             and x.shape[0] * (x.shape[2] // 2 + 3) * (x.shape[3] // 2 + 3) < 2 ** 31 - 2048
             and x.shape[0] * (x.shape[2] // 2) * (x.shape[3] // 2) * 256 < 2 ** 32 - 1   # 32-bit byte offsets of y
-            and bool(native.cuda_lib().gk_stem_supported(int(x.shape[2]), int(x.shape[3]))))
+            and bool(native.cuda_lib().gk_stem_supported(int(x.shape[2]), int(x.shape[3])))
+            and _driver_ok(x.device))
 
 
 class _StemConvTC(torch.autograd.Function):

@@ -390,6 +390,7 @@ const char* gk_version(void);
  * wpk 12288 floats (operand order); y / gy [N, H/2, W/2, 64] NHWC; `err` an optional device uint32 that receives
  * the code of a pipeline wait that timed out (the kernels trap instead of hanging).  All pointers 16-byte aligned.
  * Return: 0, a cudaError_t, -2 (shape not covered) or -3 (the driver cannot encode the tensor map). */
+int gk_stem_driver_ok(const void* probe);            /* 1 if the driver encodes the tensor maps used; probe = any device ptr */
 int gk_stem_supported(int H, int W);                 /* forward: even sizes, W <= 332 */
 int gk_stem_s2d(const void* x, void* X, int nimg, int H, int W, void* stream);
 int gk_stem_s2d_layout(const void* x, void* X, int nimg, int H, int W, int nchw, void* stream); /* x [N,3,H,W] if nchw */
