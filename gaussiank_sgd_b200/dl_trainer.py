@@ -16,8 +16,6 @@ B200-first differences:
 """
 from __future__ import annotations
 
-import json
-import math
 import os
 import time
 from typing import Optional

@@ -14,7 +14,7 @@ The planners take the cost models as callables so that they can run either on th
 """
 from __future__ import annotations
 
-from typing import Callable, Dict, List, Sequence, Tuple
+from typing import Callable, Dict, List, Sequence
 
 from ..utils import perf_model as pm
 
