@@ -351,6 +351,30 @@ def test_stem_tensor_core_kernel_matches_fp32_convolution(shape):
 
 
 @pytest.mark.gpu
+def test_fused_resnet_eval_and_nchw_batches_use_the_tensor_core_stem():
+    """Evaluation mode (running statistics, no epilogue sums) and a plain NCHW batch straight from a loader both go
+    through the tcgen05 stem of a rewired torchvision ResNet and agree with the untouched model within TF32."""
+    tv = pytest.importorskip("torchvision")
+    from gaussiank_sgd_b200.ops import stem
+    torch.manual_seed(11)
+    dev = torch.device("cuda:0")
+    net = tv.models.resnet18(num_classes=10).to(dev).to(memory_format=torch.channels_last)
+    ref = copy.deepcopy(net)
+    fuse_bn_act(net)
+    x = torch.randn(4, 3, 64, 64, device=dev)                      # NCHW, as a DataLoader delivers it
+    for mode in ("train", "eval"):
+        getattr(net, mode)(), getattr(ref, mode)()
+        before = stem.calls["fwd"]
+        with torch.no_grad():
+            got, want = net(x), ref(x.contiguous(memory_format=torch.channels_last))
+        assert stem.calls["fwd"] == before + 1, mode
+        torch.testing.assert_close(got, want, rtol=2e-2, atol=2e-2)
+    for (n, b), (_, c) in zip(net.named_buffers(), ref.named_buffers()):          # both stems are tf32, rounded differently
+        torch.testing.assert_close(b.float(), c.float(), rtol=2e-2, atol=2e-3)
+    assert all(v == 0 for v in stem.error_codes().values())
+
+
+@pytest.mark.gpu
 def test_stem_helper_kernels_match_their_torch_restatement():
     """k_stem_s2d (NHWC and NCHW input) and k_stem_pack_w against ops/stem.py's plain-torch versions, up to the
     round-to-nearest tf32 conversion both kernels apply."""
