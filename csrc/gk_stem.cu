@@ -29,7 +29,7 @@
 //            its own TMEM accumulator (one thread can issue an MMA of this size only every ~70-130 cycles, see
 //            tools/experiments/umma_rate.cu); tcgen05.commit publishes the accumulator and releases the chunk buffer.
 //   warp 5   allocates / frees 256 TMEM columns (four 64-column accumulators).
-//   warps 6-9  4 epilogue warps, one per TMEM lane quarter: tcgen05.ld the 128 x 64 fp32 tile, transpose through padded shared
+//   warps 6-13  two groups of 4 epilogue warps (alternate tiles), in a group one warp per TMEM lane quarter: tcgen05.ld the 128 x 64 fp32 tile, transpose through padded shared
 //            memory, store whole 128-byte lines of the NHWC output (the valid rows of a tile are contiguous in y);
 //            optionally accumulate the per-channel sums of y for the BatchNorm that follows.
 // Every mbarrier wait is bounded (2 s on %globaltimer): on expiry the kernel records a code and traps.
@@ -50,7 +50,9 @@ constexpr int ST_NMMA = ST_TAPS * 3 * 2;           // K = 8 steps per tile
 constexpr int ST_B_MMA = 2 * ST_N * 16;            // weight bytes per step: 2 halves x 64 rows x 16 B
 constexpr int ST_B_BYTES = ST_NMMA * ST_B_MMA;     // 48 KB
 constexpr int ST_EPI_PITCH = 36;                   // floats; 32 + 4 keeps the float4 phases conflict-free
-constexpr int ST_EPI_WARPS = 4;                    // one per TMEM lane quarter (8, one per quarter and channel half, were slower)
+constexpr int ST_EPI_GROUPS = 2;                   // epilogue warp groups working on alternate tiles (a tile's epilogue
+                                                   // is ~3000 cycles of latency for a 4-warp group)
+constexpr int ST_EPI_WARPS = 4 * ST_EPI_GROUPS;    // per group one warp per TMEM lane quarter
 constexpr int ST_EPI_BYTES = ST_EPI_WARPS * 32 * ST_EPI_PITCH * 4;
 constexpr int ST_NI = 4;                           // MMA-issuing warps = TMEM accumulators
 constexpr int ST_W_ALLOC = 1 + ST_NI;              // warp 0 producer, 1..ST_NI issuers, then TMEM allocator, then 4 epilogue
@@ -58,6 +60,7 @@ constexpr int ST_W_EPI = 2 + ST_NI;
 constexpr int ST_THREADS = 32 * (ST_W_EPI + ST_EPI_WARPS);
 constexpr int WG_THREADS = 32 * (ST_W_EPI + 4);    // the weight-gradient kernel has one light epilogue: 4 warps
 constexpr int ST_TMEM_COLS = 256;
+static_assert(ST_NI % ST_EPI_GROUPS == 0, "an accumulator must always be drained by the same epilogue group");
 constexpr int ST_FIXED = ST_B_BYTES + ST_EPI_BYTES + 1024;  // barriers + statistics; + 2 chunk buffers of 3 planes
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -210,7 +213,7 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
     }
     for (uint32_t s = 0; s < ST_NI; ++s) {
       mbar_init(tfull(s), 1);
-      mbar_init(tempty(s), ST_EPI_WARPS);           // one arrival per epilogue warp
+      mbar_init(tempty(s), 4);                      // one arrival per warp of the epilogue group that owns the tile
     }
     mbar_init(bfull, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -282,14 +285,15 @@ k_stem_fwd_tc(const __grid_constant__ CUtensorMap mapX, const float* __restrict_
   } else if (warp >= ST_W_EPI) {                    // ---- epilogue: warp = TMEM lane quarter q (lanes 32q .. 32q+31)
     // These four warps are a serial instruction stream each and the kernel is sensitive to every instruction in
     // their loop: 32-bit index arithmetic (the host checks the ranges), one shuffle per row.
-    const int q = warp & 3;
-    float* const stg = epi + q * 32 * ST_EPI_PITCH;
+    const int q = warp & 3;                         // hardware rule: a warp reads TMEM lanes 32 (warp % 4) .. + 31
+    const int grp = (warp - ST_W_EPI) >> 2;         // tiles it = grp, grp + ST_EPI_GROUPS, ...
+    float* const stg = epi + (warp - ST_W_EPI) * 32 * ST_EPI_PITCH;
     const uint32_t pl = (uint32_t)(g.Hp * g.Wp), Wp = (uint32_t)g.Wp;
     unsigned long long outb_u = reinterpret_cast<unsigned long long>(out) + (unsigned)(lane & 7) * 16u;
     asm volatile("" : "+l"(outb_u));                // keep it in registers (else re-derived from the parameter bank per store)
     char* const outb = reinterpret_cast<char*>(outb_u);                    // this lane's 16 bytes of a 128-byte line
     float cs[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}}, cq[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
-    for (int it = 0; it < nt; ++it) {
+    for (int it = grp; it < nt; it += ST_EPI_GROUPS) {
       const uint32_t as = (uint32_t)it % ST_NI, aph = ((uint32_t)it / ST_NI) & 1u;
       // where this lane's row goes: position -> (n, i, j); 0xffffffff for the positions that are not output pixels
       const uint32_t p = (uint32_t)(t0 + it) * ST_M + (uint32_t)(q * 32 + lane);

@@ -8,14 +8,14 @@
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-__global__ void rate(int M, int N, int nacc, int a_major, int mode, int step, int kind, long long* out) {
+__global__ void rate(int M, int N, int nacc, int a_major, int mode, int step, int kind, int nw, long long* out) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ uint64_t bar;
   __shared__ uint32_t tslot;
   const uint32_t base = (smem_u32(smem) + 1023u) & ~1023u;
   for (int w = threadIdx.x; w < 32768; w += blockDim.x) reinterpret_cast<float*>(smem + (base - smem_u32(smem)))[w] = 1.f;
   if (threadIdx.x == 0) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&bar)), "r"(nw));
     asm volatile("fence.mbarrier_init.release.cluster;");
   }
   if (threadIdx.x < 32) {
@@ -27,7 +27,8 @@ __global__ void rate(int M, int N, int nacc, int a_major, int mode, int step, in
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;");
   const uint32_t tmem = tslot;
-  if (mode == 0 ? threadIdx.x == 0 : threadIdx.x < 32) {
+  if ((threadIdx.x & 31) == 0 && (int)(threadIdx.x >> 5) < nw) {
+    const uint32_t wid = threadIdx.x >> 5;
     const uint32_t layout = a_major ? 1u : 0u;
     // kind 0: K-major no swizzle, canonical (LBO 128, SBO 256); kind 1: the stem forward's overlapping form (LBO 16, SBO 128,
     // start 48 B off alignment); kind 2: K-major 128-byte swizzle (SBO 1024)
@@ -46,7 +47,7 @@ __global__ void rate(int M, int N, int nacc, int a_major, int mode, int step, in
     if (mode == 1) asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(elected));
 #pragma unroll 8
     for (int i = 0; i < 512; ++i) {
-      const uint32_t d = tmem + (uint32_t)(i & (nacc - 1)) * (uint32_t)N;
+      const uint32_t d = tmem + (wid * (uint32_t)nacc + (uint32_t)(i & (nacc - 1))) * (uint32_t)N;
       if (elected) asm volatile(
           "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tmov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %6};\n\tsetp.ne.b32 p, %5, 0;\n\t"
           "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, p;\n\t}" ::"r"(d), "r"(a_lo), "r"(hi), "r"(b_lo), "r"(idesc), "r"(1u), "r"(hib));
@@ -70,22 +71,24 @@ int main() {
   long long *d, h[2];
   cudaMalloc(&d, 16);
   cudaFuncSetAttribute(rate, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-  printf("M N nacc major : issue cyc/MMA, complete cyc/MMA\n");
+  printf("512 MMAs (kind::tf32, K = 8) per issuing warp, each warp into its own TMEM accumulator; clock64 of warp 0 from its first issue to the arrival of every warp's commit\n");
   const int Ns[] = {8, 16, 48, 64, 128, 256};
   const int mode = 0;
-  for (int cfg = 0; cfg < 5; ++cfg)
+  for (int cfg = 0; cfg < 5; cfg += 1)
     for (int M = 64; M <= 128; M += 64)
-      for (int ni = 2; ni < 6; ++ni)
-        for (int nacc = 1; nacc <= 2; nacc *= 2) {
+      for (int ni = 0; ni < 6; ++ni)
+        for (int nw = 1; nw <= 4; nw *= 2) {
+          const int nacc = 1;
+          if (Ns[ni] * nw > 512) continue;
           const int major = cfg == 4, kind = cfg < 3 ? cfg : (cfg == 3 ? 1 : 0), step = cfg == 0 ? 0 : (cfg == 3 ? 3 : 64);
           const int N = Ns[ni];
-          if (N * nacc > 512) continue;
+
           for (int rep = 0; rep < 2; ++rep) {
-            rate<<<1, 128, 200 * 1024>>>(M, N, nacc, major, mode, step, kind, d);
+            rate<<<1, 128, 200 * 1024>>>(M, N, nacc, major, mode, step, kind, nw, d);
             if (cudaDeviceSynchronize() != cudaSuccess) { printf("error\n"); return 1; }
           }
           cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost);
-          printf("cfg %d (major %s kind %d step %d) M %3d N %3d nacc %d : %6.1f %6.1f\n", cfg, major ? "MN" : "K", kind, step * 16, M, N, nacc, h[0] / 512.0, h[1] / 512.0);
+          printf("cfg %d (major %s kind %d step %d) M %3d N %3d issuing warps %d : %6.1f cycles per MMA per warp, %6.1f per MMA overall\n", cfg, major ? "MN" : "K", kind, step * 16, M, N, nw, h[1] / 512.0, h[1] / 512.0 / nw);
         }
   return 0;
 }
