@@ -127,9 +127,9 @@ __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::
 // D fp32 (1 << 4), A and B tf32 (2 << 7, 2 << 10), both K-major, N >> 3 at bit 17, M >> 4 at bit 24.
 constexpr uint32_t ST_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(ST_N >> 3) << 17) | ((uint32_t)(ST_M >> 4) << 24);
 
-// The same instruction with the descriptors given as (lo, hi) words: lo = start address >> 4 | LBO >> 4 << 16,
-// hi = SBO >> 4 | version | layout type.  Stepping an operand is then one 32-bit add on lo (a single thread issues
-// every MMA of the CTA, so the instructions between two MMAs are on the critical path).
+// tcgen05.mma kind::tf32 with the shared-memory descriptors given as (lo, hi) words: lo = start address >> 4 |
+// LBO >> 4 << 16, hi = SBO >> 4 | version 1 | layout type << 29.  Stepping an operand is then one 32-bit add on lo
+// (an issuing thread's instruction stream is one dependent chain: what stands between two MMAs costs cycles).
 __device__ __forceinline__ void mma_tf32_w(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
                                            uint32_t idesc, uint32_t accumulate) {
   asm volatile(
