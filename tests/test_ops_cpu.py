@@ -275,3 +275,103 @@ def test_zabs_matches_reference(reference_modules):
     for rho in [0.001, 0.004, 0.015625, 0.05, 0.25]:
         left, right = utils.gen_threshold_from_normal_distribution(1 - rho, 0.0, 1.0)
         assert right == ch.gaussian_zabs(rho)
+
+
+# ---------------------------------------------------------------------------------------------- properties
+from hypothesis import HealthCheck, given, settings as hsettings, strategies as st  # noqa: E402
+
+
+@hsettings(max_examples=30, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+@given(comp=st.sampled_from(COMPS + ["dgcsampling"]),
+       n=st.integers(min_value=1, max_value=40000),
+       density=st.sampled_from([0.001, 0.004, 0.015625, 0.05]),
+       kind=st.sampled_from(["normal", "laplace", "shifted", "ties"]),
+       chunk=st.sampled_from([128, 1024, 8192]),
+       seed=st.integers(min_value=0, max_value=2 ** 16))
+def test_compress_invariants_hold_for_any_input(comp, n, density, kind, chunk, seed):
+    """Whatever the selector, size, density, data and block table: what was sent plus what stayed equals gradient plus
+    old residual bit for bit, indices come out unique and ascending, the count respects the slot capacity and the
+    header, the gradient arena is consumed, and exact top-k sends exactly k."""
+    g, r = _data(n, seed, kind), _data(n, seed + 1, kind) * 0.5
+    c, G, R, idx, val, seq = _run_cpu_chain(comp, g, r, density, chunk=chunk)
+    ctrl = c.read_ctrl()
+    acc = g + r
+    assert seq == 1 and ctrl["sent"] == idx.numel() <= c.cap and ctrl["total"] >= ctrl["sent"]
+    if idx.numel():
+        assert int(idx.min()) >= 0 and int(idx.max()) < n
+        assert torch.all(idx[1:] > idx[:-1])
+        assert torch.equal(val, acc[idx])                      # values travel unchanged
+    rebuilt = R.clone()
+    rebuilt[idx] += val
+    assert torch.equal(rebuilt, acc)                           # nothing lost, nothing invented
+    assert torch.count_nonzero(R[idx]) == 0                    # sent coordinates leave the residual
+    assert torch.count_nonzero(G) == 0
+    if comp == "topk" and ctrl["total"] <= c.cap:
+        k = ch.compute_k(n, density)
+        assert idx.numel() == min(k, n)
+        if 0 < idx.numel() < n:
+            rest = torch.ones(n, dtype=torch.bool)
+            rest[idx] = False
+            assert acc.abs()[idx].min() >= acc.abs()[rest].max()
+
+
+def _fill_cpu_arena(arena, lists, seq):
+    from gaussiank_sgd_b200.ops import native as N
+    P = len(lists)
+    for r, (sel, v) in enumerate(lists):
+        words = sel.numpy().astype(np.uint64) | (v.numpy().view(np.uint32).astype(np.uint64) << np.uint64(32))
+        base = ((seq & 1) * P + r) * arena.slot_stride
+        arena.t[base] = int(sel.numel()) | (seq << 32)
+        arena.t[base + N.GK_SLOT_HDR: base + N.GK_SLOT_HDR + sel.numel()] = torch.from_numpy(words.view(np.int64))
+
+
+@hsettings(max_examples=25, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+@given(P=st.integers(min_value=1, max_value=8), k=st.integers(min_value=0, max_value=400),
+       momentum=st.sampled_from([0.0, 0.9]), nesterov=st.booleans(), wd=st.sampled_from([0.0, 1e-3]),
+       first=st.booleans(), seed=st.integers(min_value=0, max_value=2 ** 16))
+def test_folded_update_equals_scatter_then_sgd_for_any_lists(P, k, momentum, nesterov, wd, first, seed):
+    """gkcpu_sgd_recv (receive folded into the update, no dense gradient) against gkcpu_scatter + gkcpu_sgd for random
+    rank counts, list lengths (empty lists and coordinates held by several ranks included) and hyper-parameters:
+    coordinates nobody sent are bit-identical, the others agree to rounding, the mask arena comes back zero."""
+    if nesterov and momentum == 0.0:
+        nesterov = False
+    g = torch.Generator().manual_seed(seed)
+    sizes = [130, 4097, 17, 2500]
+    offs, total = [], 0
+    for s in sizes:
+        offs.append(total)
+        total += (s + 63) // 64 * 64
+    tables = ch.FlatTables(list(zip(offs, sizes)), [0, 1, 0, 1], "cpu")
+    hyp = [{"lr": 0.05, "momentum": momentum, "weight_decay": 0.0, "nesterov": nesterov},
+           {"lr": 0.1, "momentum": momentum, "weight_decay": wd, "nesterov": nesterov}]
+    valid = torch.cat([torch.arange(o, o + s) for o, s in zip(offs, sizes)])
+    shared = valid[torch.randperm(valid.numel(), generator=g)[:min(k, 50)]]
+    lists = []
+    for r in range(P):
+        sel = valid[torch.randperm(valid.numel(), generator=g)[:k]]
+        if r % 2:
+            sel = torch.cat([sel, shared])
+        sel = sel.unique()
+        lists.append((sel, torch.randn(sel.numel(), generator=g)))
+    cap = max([l[0].numel() for l in lists] + [1]) + 8
+    arena = ch.SlotBuffer(P, cap, "cpu", parities=2)
+    ctrl = torch.zeros(ch.CTRL_DTYPE.itemsize, dtype=torch.uint8)
+    seq = 5
+    ctrl.view(torch.int32)[10] = seq
+    _fill_cpu_arena(arena, lists, seq)
+    hy = ch.make_hyper(hyp, "cpu", first)
+    P0, M0 = torch.randn(total, generator=g), torch.randn(total, generator=g) * 0.1
+    mom = (lambda M: M) if momentum else (lambda M: None)
+    P1, M1, G = P0.clone(), M0.clone(), torch.zeros(total)
+    ch.scatter(arena.src(wait=True, timeout_s=2.0), ctrl, G, 1.0 / P)
+    ch.sgd_step(P1, G, mom(M1), tables, hy)
+    P2, M2, mask = P0.clone(), M0.clone(), torch.zeros(total)
+    ch.sgd_recv_step(P2, mask.view(torch.int32), mom(M2), tables, hy, arena.src(wait=True, timeout_s=2.0), ctrl, 1.0 / P)
+    assert torch.count_nonzero(mask) == 0 and int(ctrl.view(torch.int32)[11]) == 0
+    touched = torch.zeros(total, dtype=torch.bool)
+    for sel, _ in lists:
+        touched[sel] = True
+    assert torch.equal(P1[~touched], P2[~touched]) and torch.equal(M1[~touched], M2[~touched])
+    eps = 4 * torch.finfo(torch.float32).eps
+    assert (P1 - P2).abs().max() <= eps * max(1.0, float(P1.abs().max()))
+    assert (M1 - M2).abs().max() <= eps * max(1.0, float(M1.abs().max()))
