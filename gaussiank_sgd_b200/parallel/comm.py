@@ -39,6 +39,8 @@ def init(backend: Optional[str] = None, device: Optional[torch.device] = None, t
             device = torch.device("cpu")
     if device.type == "cuda":
         torch.cuda.set_device(device)
+    else:
+        _set_cpu_threads()
     _state["device"] = device
     if world > 1 and not dist.is_initialized():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -50,6 +52,29 @@ def init(backend: Optional[str] = None, device: Optional[torch.device] = None, t
         dist.init_process_group(backend=backend, timeout=datetime.timedelta(seconds=timeout_s), **kwargs)
         _state["owns_pg"] = True
     _state["initialized"] = True
+
+
+def _set_cpu_threads() -> None:
+    """CPU workers: split the cores among the workers of this host.  torchrun exports OMP_NUM_THREADS=1 when the user
+    set nothing, which leaves all but one core per worker idle (ResNet-20, 2 gloo workers on 8 cores: 52.9 ms/step
+    with 1 thread each, 25.3 with 4); mpirun-style launches default to every core in every process, which
+    oversubscribes.  ``GK_CPU_THREADS=n`` pins the count; an OMP_NUM_THREADS other than 1 is taken as the user's
+    choice and left alone."""
+    want = os.environ.get("GK_CPU_THREADS")
+    if want:
+        n = max(1, int(want))
+    else:
+        if os.environ.get("OMP_NUM_THREADS", "1") != "1":
+            return
+        try:
+            cores = len(os.sched_getaffinity(0))
+        except (AttributeError, OSError):
+            cores = os.cpu_count() or 1
+        n = max(1, cores // max(_env_int("LOCAL_WORLD_SIZE", _env_int("WORLD_SIZE", 1)), 1))
+    try:
+        torch.set_num_threads(n)
+    except RuntimeError:
+        pass
 
 
 _shutdown_hooks = []
