@@ -91,7 +91,9 @@ assert C.sizeof(GkCtrl) == 328 and C.sizeof(GkHyper) == 32
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC"]
-GXX_FLAGS = ["-O2", "-ffp-contract=off", "-std=c++17", "-shared", "-fPIC"]
+# AVX2 + FMA (any x86-64 host of a B200 has them): the dense loops vectorise and std::fmaf is one instruction;
+# -ffp-contract=off keeps every other multiply-add unfused, as in the CUDA twins
+GXX_FLAGS = ["-O3", "-mavx2", "-mfma", "-ffp-contract=off", "-std=c++17", "-shared", "-fPIC"]
 
 
 def _stale(so: str, srcs) -> bool:
