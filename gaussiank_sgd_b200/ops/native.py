@@ -131,16 +131,33 @@ def build_cuda(force: bool = False, verbose: bool = False) -> str:
     return CUDA_SO
 
 
+def _host_has_avx2_fma() -> bool:
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("flags"):
+                    flags = set(line.split(":", 1)[1].split())
+                    return "avx2" in flags and "fma" in flags
+    except OSError:
+        pass
+    return True          # no /proc/cpuinfo (not Linux / x86): leave the decision to the compiler flags below
+
+
 def build_cpu(force: bool = False) -> str:
+    """libgk_cpu.so (AVX2 + FMA).  A host without those extensions - the in-tree library travels between machines -
+    gets its own plain build next to it."""
     src = os.path.join(CSRC, "gk_cpu.cpp")
     hdr = os.path.join(INCLUDE, "gk_b200.h")
-    if force or _stale(CPU_SO, [src, hdr]):
-        cmd = ["g++"] + GXX_FLAGS + ["-o", CPU_SO + ".tmp", src]
+    so, flags = CPU_SO, GXX_FLAGS
+    if not _host_has_avx2_fma():
+        so, flags = CPU_SO.replace(".so", "_generic.so"), [f for f in GXX_FLAGS if f not in ("-mavx2", "-mfma")]
+    if force or _stale(so, [src, hdr]):
+        cmd = ["g++"] + flags + ["-o", so + ".tmp", src]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("g++ failed:\n" + r.stdout + r.stderr)
-        os.replace(CPU_SO + ".tmp", CPU_SO)
-    return CPU_SO
+        os.replace(so + ".tmp", so)
+    return so
 
 
 _lock = threading.Lock()
@@ -226,8 +243,7 @@ def cuda_lib():
 def cpu_lib():
     with _lock:
         if "cpu" not in _libs:
-            build_cpu()
-            lib = C.CDLL(CPU_SO)
+            lib = C.CDLL(build_cpu())
             ch, ds, sr = C.POINTER(GkChain), C.POINTER(GkDst), C.POINTER(GkSrc)
             _proto(lib, "gkcpu_version", [], C.c_char_p)
             _proto(lib, "gkcpu_compress", [ch, ds])
