@@ -59,24 +59,36 @@ void publish(const GkChain* c, const GkDst* d, uint64_t poff, uint32_t seqn, uin
 
 // acc = grad (+ resid) -> resid, optional zeroing of grad; returns moments of the segment
 void accumulate_segment(const GkChain* c, const GkSeg& sg, double& sum, double& sq, double& sa, float& mx) {
-  sum = sq = sa = 0;
-  mx = 0.f;
+  // four interleaved fp64 accumulators per moment (element i of a block goes to accumulator i % 4), added up in a
+  // fixed order at the end: deterministic, and the adds no longer form one dependency chain
+  double s4[4] = {0, 0, 0, 0}, q4[4] = {0, 0, 0, 0}, a4[4] = {0, 0, 0, 0};
+  float m4[4] = {0.f, 0.f, 0.f, 0.f};
   for (int b = sg.blk_begin; b < sg.blk_end; ++b) {
     const GkBlk& B = c->blk[b];
-    const float* src = c->gsrc ? c->gsrc[b] : c->grad + B.start;
-    for (int i = 0; i < B.len; ++i) {
-      const int j = B.start + i;
+    const float* __restrict src = c->gsrc ? c->gsrc[b] : c->grad + B.start;
+    float* __restrict res = c->resid + B.start;
+    const bool use_r = c->use_residual != 0;
+    auto one = [&](int i, int lane) {
       float x = src[i];
-      if (c->use_residual) x += c->resid[j];
-      c->resid[j] = x;
-      if (c->zero_grad && !c->gsrc) c->grad[j] = 0.f;
+      if (use_r) x += res[i];
+      res[i] = x;
       const double xd = (double)x;
-      sum += xd;
-      sq += xd * xd;
-      sa += std::fabs(xd);
-      mx = std::max(mx, std::fabs(x));
+      s4[lane] += xd;
+      q4[lane] += xd * xd;
+      a4[lane] += std::fabs(xd);
+      m4[lane] = std::max(m4[lane], std::fabs(x));
+    };
+    int i = 0;
+    for (; i + 4 <= B.len; i += 4) {
+      one(i, 0); one(i + 1, 1); one(i + 2, 2); one(i + 3, 3);
     }
+    for (int l = 0; i < B.len; ++i, ++l) one(i, l);
+    if (c->zero_grad && !c->gsrc) std::memset(c->grad + B.start, 0, sizeof(float) * (size_t)B.len);
   }
+  sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+  sq = (q4[0] + q4[1]) + (q4[2] + q4[3]);
+  sa = (a4[0] + a4[1]) + (a4[2] + a4[3]);
+  mx = std::max(std::max(m4[0], m4[1]), std::max(m4[2], m4[3]));
 }
 
 uint32_t count_gt(const GkChain* c, const GkSeg& sg, float thr) {
